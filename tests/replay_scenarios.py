@@ -1,0 +1,81 @@
+"""Deterministic replay call sequences, driven through the PUBLIC replay API only
+(add / sample / size / batch_of_ids_transitions_and_logits / update_priorities),
+so the same scenario runs against the unmodified reference classes (to make the
+golden fixtures), the oracle restatement and the CUDA-backed product classes."""
+import collections
+import zlib
+
+import numpy as np
+
+from dqn_mgsc_zoo_b200 import synthetic
+
+Pair = collections.namedtuple("Pair", "a b")
+
+
+def _crc(arr):
+    return zlib.crc32(np.ascontiguousarray(arr).tobytes())
+
+
+def pairs_uniform(make, seed, capacity, n_add, sample_every, batch):
+    """FIFO / reservoir with a RandomState: record every sampled `a` column."""
+    rs = np.random.RandomState(seed)
+    rep = make(capacity, Pair(None, None), rs)
+    drawn, sizes = [], []
+    for i in range(n_add):
+        rep.add(Pair(i, 2 * i + 1))
+        if i % sample_every == sample_every - 1:
+            s = rep.sample(batch)
+            assert np.array_equal(s.b, 2 * s.a + 1)
+            drawn.append(np.asarray(s.a, dtype=np.int64))
+            sizes.append(rep.size)
+    # the caller shares the RandomState with the replay: its next draw is part of the contract
+    return {"drawn": np.stack(drawn), "sizes": np.array(sizes), "next_draw": rs.randint(1 << 30)}
+
+
+def pairs_mgsc(make, seed, capacity, n_add, every, batch, meta):
+    """MGSC replays with a Generator: weighted samples, meta batches, priority writes."""
+    rng = np.random.default_rng(seed)
+    rep = make(capacity, Pair(None, None), rng)
+    drawn, meta_idx, meta_logits = [], [], []
+    for i in range(n_add):
+        rep.add(Pair(i, 2 * i + 1))
+        if i % every == every - 1 and rep.size >= max(batch, meta):
+            idx, tr, lg = rep.batch_of_ids_transitions_and_logits(meta)
+            meta_idx.append(np.asarray(idx, dtype=np.int64))
+            meta_logits.append(np.asarray(lg, dtype=np.float32))
+            new = np.asarray(lg, dtype=np.float32) + np.float32(0.25) * np.cos(np.asarray(tr.a)).astype(np.float32)
+            rep.update_priorities(idx, new)
+            drawn.append(np.asarray(rep.sample(batch).a, dtype=np.int64))
+    return {"drawn": np.stack(drawn), "meta_idx": np.stack(meta_idx),
+            "meta_logits": np.stack(meta_logits), "next_draw": rng.integers(1 << 30)}
+
+
+def frames_uniform(make, accumulator, structure, seed, capacity, n_add, sample_every, batch, num_actions=6,
+                   hw=(84, 84), short_every=5, max_len=23):
+    """Atari-shaped transitions (short episodes => many early-episode stacks)."""
+    rs = np.random.RandomState(seed)
+    rep = make(capacity, structure, rs)
+    stream = synthetic.transition_stream(np.random.default_rng(seed + 1), num_actions, accumulator,
+                                         hw=hw, short_every=short_every, max_len=max_len)
+    crcs, acts, rews, discs = [], [], [], []
+    for i in range(n_add):
+        rep.add(next(stream))
+        if i % sample_every == sample_every - 1:
+            s = rep.sample(batch)
+            crcs.append([_crc(s.s_tm1), _crc(s.s_t)])
+            acts.append(np.asarray(s.a_tm1, dtype=np.int64))
+            rews.append(np.asarray(s.r_t, dtype=np.float64))
+            discs.append(np.asarray(s.discount_t, dtype=np.float64))
+    return {"crc": np.array(crcs, dtype=np.int64), "a": np.stack(acts), "r": np.stack(rews),
+            "d": np.stack(discs), "shape": np.array(s.s_tm1.shape), "dtype": str(s.s_tm1.dtype)}
+
+
+SCENARIOS = {
+    "fifo_pairs": dict(kind="fifo", fn="pairs_uniform", args=dict(seed=7, capacity=37, n_add=180, sample_every=3, batch=8)),
+    "fifo_pairs_tiny": dict(kind="fifo", fn="pairs_uniform", args=dict(seed=1, capacity=4, n_add=40, sample_every=1, batch=5)),
+    "reservoir_pairs": dict(kind="reservoir", fn="pairs_uniform", args=dict(seed=11, capacity=50, n_add=600, sample_every=4, batch=8)),
+    "mgsc_fifo_pairs": dict(kind="mgsc_fifo", fn="pairs_mgsc", args=dict(seed=3, capacity=24, n_add=90, every=2, batch=6, meta=5)),
+    "mgsc_reservoir_pairs": dict(kind="mgsc_reservoir", fn="pairs_mgsc", args=dict(seed=5, capacity=24, n_add=140, every=2, batch=6, meta=5)),
+    "fifo_frames": dict(kind="fifo", fn="frames_uniform", args=dict(seed=13, capacity=64, n_add=260, sample_every=10, batch=16)),
+    "reservoir_frames": dict(kind="reservoir", fn="frames_uniform", args=dict(seed=17, capacity=48, n_add=300, sample_every=10, batch=16)),
+}
