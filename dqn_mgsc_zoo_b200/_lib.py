@@ -1,0 +1,72 @@
+"""ctypes binding of libdqnb200.so (the C ABI declared in include/dqnb200.h).
+
+There is no CPU fallback: if the shared library is missing or a call fails, an
+exception is raised.  Build the library with `python -m dqn_mgsc_zoo_b200.build`
+(or `__graft_entry__.build()`).
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdqnb200.so")
+
+c_i64, c_i32, c_int, c_f32 = ctypes.c_int64, ctypes.c_int32, ctypes.c_int, ctypes.c_float
+c_vp, c_up, c_sz = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t
+STREAM = ctypes.c_size_t   # uintptr_t
+
+# name -> argtypes; every function returns int status except dqnb_version/dqnb_last_error.
+SIGNATURES = {
+    "dqnb_device_count": [ctypes.POINTER(c_int)],
+    "dqnb_dev_alloc": [c_int, c_sz, ctypes.POINTER(c_vp)],
+    "dqnb_dev_free": [c_int, c_vp],
+    "dqnb_copy_h2d": [c_vp, c_vp, c_sz, STREAM],
+    "dqnb_copy_d2h": [c_vp, c_vp, c_sz, STREAM],
+    "dqnb_stream_sync": [STREAM],
+    "dqnb_replay_create": [c_i64, c_int, c_int, c_int, c_i64, c_int, ctypes.POINTER(c_vp)],
+    "dqnb_replay_destroy": [c_vp],
+    "dqnb_replay_put": [c_vp, c_i64, c_vp, c_vp, c_i32, c_f32, c_f32, STREAM],
+    "dqnb_replay_flush": [c_vp, STREAM],
+    "dqnb_replay_gather": [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
+    "dqnb_replay_gather_dev": [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
+    "dqnb_replay_gather_host": [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
+    "dqnb_replay_set_gather_splits": [c_vp, c_int],
+    "dqnb_replay_stats": [c_vp, ctypes.POINTER(c_i64)],
+}
+
+
+class DqnbError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Loads libdqnb200.so (once) and declares every signature.  Raises if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise DqnbError(
+            "libdqnb200.so not found at %s - build it with `python -m dqn_mgsc_zoo_b200.build`; "
+            "there is no CPU fallback for the learner hot path" % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.dqnb_version.restype = c_int
+    lib.dqnb_version.argtypes = []
+    lib.dqnb_last_error.restype = ctypes.c_char_p
+    lib.dqnb_last_error.argtypes = []
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)       # AttributeError if the symbol is missing
+        fn.restype = c_int
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(status):
+    if status != 0:
+        raise DqnbError("libdqnb200 error %d: %s" % (status, load().dqnb_last_error().decode()))
+
+
+def call(name, *args):
+    check(getattr(load(), name)(*args))

@@ -1,0 +1,447 @@
+// Replay frame store: host bookkeeping (plane pool, dedup, staging) + kernel launches.
+// Replaces the item storage of the reference replays (replay.py:163-333,
+// replay_circular.py:90-146,568-664,1217-1312); see include/dqnb200.h.
+#include <algorithm>
+#include <vector>
+
+#include "replay_kernels.cuh"
+
+using namespace dqnb;
+
+namespace {
+constexpr int kStageRecords = 64;            // puts per staging batch
+constexpr int kStagePlanes = 256;            // uploaded planes per staging batch
+constexpr int kIdxRing = 8;
+constexpr int kGatherThreads = 256;
+
+struct Stage {
+  uint8_t* host = nullptr;   // pinned: [records][dst ids][planes...]
+  uint8_t* dev = nullptr;
+  cudaEvent_t copied = nullptr;
+  bool in_flight = false;
+  int n_planes = 0, n_records = 0;
+};
+}  // namespace
+
+struct dqnb_replay {
+  int device = 0;
+  int64_t capacity = 0;
+  int H = 0, W = 0, S = 0, plane_bytes = 0;
+  int64_t plane_stride = 0;
+  // device state
+  uint8_t* d_planes = nullptr;
+  int64_t pool_planes = 0;
+  int32_t* d_slot_ids = nullptr;
+  int32_t* d_actions = nullptr;
+  float* d_rewards = nullptr;
+  float* d_discounts = nullptr;
+  // staging
+  Stage stage[2];
+  int cur = 0;
+  size_t hdr_records = 0, hdr_dst = 0, hdr_bytes = 0;
+  // host bookkeeping
+  std::vector<int32_t> refcount, free_list, pending_free, slot_ids;
+  std::vector<uint8_t> slot_staged;      // slot already has a record in the open batch
+  std::vector<uint8_t> last_st;
+  int32_t last_ids[8];
+  bool have_last = false;
+  // gather index ring + host-return buffers
+  int32_t* h_idx = nullptr;
+  int32_t* d_idx = nullptr;
+  int64_t idx_cap = 0;
+  cudaEvent_t idx_ev[kIdxRing] = {};
+  bool idx_busy[kIdxRing] = {};
+  int idx_cur = 0;
+  uint8_t* d_out = nullptr;
+  int64_t out_cap = 0;
+  int gather_splits = 0;
+  int64_t n_puts = 0, n_uploaded = 0, n_chained = 0, n_growths = 0;
+
+  SlotRecord* rec_of(Stage& s) { return reinterpret_cast<SlotRecord*>(s.host); }
+  int32_t* dst_of(Stage& s) { return reinterpret_cast<int32_t*>(s.host + hdr_records); }
+  uint8_t* planes_of(Stage& s) { return s.host + hdr_bytes; }
+};
+
+namespace {
+
+int grow_pool(dqnb_replay* h, int64_t want) {
+  // Rare: reallocate the pool and copy (device-wide sync).  Plane ids stay valid.
+  int64_t new_planes = std::max<int64_t>(want, h->pool_planes + h->pool_planes / 2 + 64);
+  uint8_t* np = nullptr;
+  cudaError_t e = cudaMalloc(&np, (size_t)new_planes * h->plane_stride);
+  if (e != cudaSuccess) {
+    set_error("plane pool growth to %lld planes failed: %s", (long long)new_planes, cudaGetErrorString(e));
+    return DQNB_ENOMEM;
+  }
+  DQNB_CUDA(cudaDeviceSynchronize());
+  if (h->d_planes) {
+    DQNB_CUDA(cudaMemcpy(np, h->d_planes, (size_t)h->pool_planes * h->plane_stride, cudaMemcpyDeviceToDevice));
+    DQNB_CUDA(cudaFree(h->d_planes));
+  }
+  h->d_planes = np;
+  h->refcount.resize(new_planes, 0);
+  for (int64_t p = new_planes - 1; p >= h->pool_planes; --p) h->free_list.push_back((int32_t)p);
+  h->pool_planes = new_planes;
+  h->n_growths++;
+  return DQNB_OK;
+}
+
+int flush(dqnb_replay* h, cudaStream_t st) {
+  Stage& s = h->stage[h->cur];
+  if (s.n_records == 0 && s.n_planes == 0) return DQNB_OK;
+  size_t bytes = h->hdr_bytes + (size_t)s.n_planes * h->plane_stride;
+  DQNB_CUDA(cudaMemcpyAsync(s.dev, s.host, bytes, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaEventRecord(s.copied, st));
+  s.in_flight = true;
+  int grid = s.n_planes + (s.n_records + 127) / 128;
+  commit_kernel<<<grid, 128, 0, st>>>(
+      h->d_planes, h->plane_stride, h->plane_bytes, s.dev + h->hdr_bytes,
+      reinterpret_cast<const int32_t*>(s.dev + h->hdr_records), s.n_planes,
+      reinterpret_cast<const SlotRecord*>(s.dev), s.n_records, h->d_slot_ids, h->d_actions,
+      h->d_rewards, h->d_discounts);
+  DQNB_CUDA(cudaGetLastError());
+  for (int i = 0; i < s.n_records; ++i) h->slot_staged[h->rec_of(s)[i].slot] = 0;
+  // planes released during this batch may be handed out again only now (stream order
+  // puts their next write after every earlier reader).
+  h->free_list.insert(h->free_list.end(), h->pending_free.begin(), h->pending_free.end());
+  h->pending_free.clear();
+  s.n_planes = s.n_records = 0;
+  h->cur ^= 1;
+  Stage& nx = h->stage[h->cur];
+  if (nx.in_flight) {
+    DQNB_CUDA(cudaEventSynchronize(nx.copied));
+    nx.in_flight = false;
+  }
+  return DQNB_OK;
+}
+
+inline void release_plane(dqnb_replay* h, int32_t p) {
+  if (p >= 0 && --h->refcount[p] == 0) h->pending_free.push_back(p);
+}
+
+// Copies channel c of an HWC stack into a staged plane; returns the new plane id.
+int stage_plane(dqnb_replay* h, const uint8_t* stack, int c, cudaStream_t st, int32_t* out_id) {
+  if (h->stage[h->cur].n_planes == kStagePlanes) DQNB_TRY(flush(h, st));
+  if (h->free_list.empty()) {
+    DQNB_TRY(flush(h, st));   // recycles pending_free
+    if (h->free_list.empty()) DQNB_TRY(grow_pool(h, 0));
+  }
+  int32_t p = h->free_list.back();
+  h->free_list.pop_back();
+  h->refcount[p] = 1;
+  Stage& s = h->stage[h->cur];
+  uint8_t* dst = h->planes_of(s) + (size_t)s.n_planes * h->plane_stride;
+  const int n = h->plane_bytes, S = h->S;
+  if (S == 4) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(stack);
+    const int sh = 8 * c;
+    for (int i = 0; i < n; ++i) dst[i] = (uint8_t)(src[i] >> sh);
+  } else {
+    for (int i = 0; i < n; ++i) dst[i] = stack[(size_t)i * S + c];
+  }
+  h->dst_of(s)[s.n_planes] = p;
+  s.n_planes++;
+  h->n_uploaded++;
+  *out_id = p;
+  return DQNB_OK;
+}
+
+// For each channel of `cur`: -1 if all zero, d>=0 if equal to channel d of `prev`, -2 if new.
+void match_channels(const uint8_t* cur, const uint8_t* prev, int npx, int S, int* match) {
+  if (S == 4) {
+    const uint32_t* a = reinterpret_cast<const uint32_t*>(cur);
+    const uint32_t* b = prev ? reinterpret_cast<const uint32_t*>(prev) : nullptr;
+    uint32_t any = 0, dshift = 0, dsame = 0;
+    if (b) {
+      for (int i = 0; i < npx; ++i) {
+        uint32_t x = a[i], y = b[i];
+        any |= x;
+        dshift |= (x & 0x00FFFFFFu) ^ (y >> 8);
+        dsame |= x ^ y;
+      }
+    } else {
+      for (int i = 0; i < npx; ++i) any |= a[i];
+      dshift = dsame = 0xFFFFFFFFu;
+    }
+    for (int c = 0; c < 4; ++c) {
+      if (((any >> (8 * c)) & 0xFF) == 0) match[c] = -1;
+      else if (c < 3 && ((dshift >> (8 * c)) & 0xFF) == 0) match[c] = c + 1;
+      else if (((dsame >> (8 * c)) & 0xFF) == 0) match[c] = c;
+      else match[c] = -2;
+    }
+    return;
+  }
+  for (int c = 0; c < S; ++c) {
+    bool zero = true;
+    for (int i = 0; i < npx && zero; ++i) zero = cur[(size_t)i * S + c] == 0;
+    match[c] = zero ? -1 : -2;
+    if (zero || !prev) continue;
+    for (int d = 0; d < S && match[c] == -2; ++d) {
+      bool eq = true;
+      for (int i = 0; i < npx && eq; ++i) eq = cur[(size_t)i * S + c] == prev[(size_t)i * S + d];
+      if (eq) match[c] = d;
+    }
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------- C ABI
+extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int stack,
+                                  int64_t initial_planes, int device, dqnb_replay** out) {
+  DQNB_REQUIRE(out != nullptr, "out is null");
+  DQNB_REQUIRE(capacity > 0 && capacity < (1LL << 31), "capacity %lld out of range", (long long)capacity);
+  DQNB_REQUIRE(height > 0 && width > 0, "bad frame shape %dx%d", height, width);
+  DQNB_REQUIRE(stack >= 1 && stack <= 4, "stack depth %d not in 1..4", stack);
+  DeviceGuard guard(device);
+  dqnb_replay* h = new dqnb_replay();
+  h->device = device;
+  h->capacity = capacity;
+  h->H = height; h->W = width; h->S = stack;
+  h->plane_bytes = height * width;
+  h->plane_stride = (h->plane_bytes + 15) / 16 * 16;
+  h->hdr_records = sizeof(SlotRecord) * kStageRecords;
+  h->hdr_dst = sizeof(int32_t) * kStagePlanes;
+  h->hdr_bytes = h->hdr_records + h->hdr_dst;
+  h->slot_ids.assign((size_t)capacity * 8, -1);
+  h->slot_staged.assign((size_t)capacity, 0);
+  h->last_st.resize((size_t)h->plane_bytes * stack);
+  DQNB_CUDA(cudaMalloc(&h->d_slot_ids, sizeof(int32_t) * 8 * capacity));
+  DQNB_CUDA(cudaMemset(h->d_slot_ids, 0xFF, sizeof(int32_t) * 8 * capacity));
+  DQNB_CUDA(cudaMalloc(&h->d_actions, sizeof(int32_t) * capacity));
+  DQNB_CUDA(cudaMalloc(&h->d_rewards, sizeof(float) * capacity));
+  DQNB_CUDA(cudaMalloc(&h->d_discounts, sizeof(float) * capacity));
+  DQNB_CUDA(cudaMemset(h->d_actions, 0, sizeof(int32_t) * capacity));
+  DQNB_CUDA(cudaMemset(h->d_rewards, 0, sizeof(float) * capacity));
+  DQNB_CUDA(cudaMemset(h->d_discounts, 0, sizeof(float) * capacity));
+  size_t stage_bytes = h->hdr_bytes + (size_t)kStagePlanes * h->plane_stride;
+  for (Stage& s : h->stage) {
+    DQNB_CUDA(cudaMallocHost(&s.host, stage_bytes));
+    DQNB_CUDA(cudaMalloc(&s.dev, stage_bytes));
+    DQNB_CUDA(cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
+  }
+  for (int i = 0; i < kIdxRing; ++i) DQNB_CUDA(cudaEventCreateWithFlags(&h->idx_ev[i], cudaEventDisableTiming));
+  if (initial_planes <= 0) initial_planes = capacity + capacity / 8 + 64;
+  DQNB_TRY(grow_pool(h, initial_planes));
+  h->n_growths = 0;
+  DQNB_CUDA(cudaFuncSetAttribute(gather_stack4<kGatherThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 8 * 16 * 1024));
+  *out = h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_destroy(dqnb_replay* h) {
+  if (!h) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaDeviceSynchronize();
+  cudaFree(h->d_planes); cudaFree(h->d_slot_ids); cudaFree(h->d_actions);
+  cudaFree(h->d_rewards); cudaFree(h->d_discounts); cudaFree(h->d_idx); cudaFree(h->d_out);
+  if (h->h_idx) cudaFreeHost(h->h_idx);
+  for (Stage& s : h->stage) {
+    if (s.host) cudaFreeHost(s.host);
+    cudaFree(s.dev);
+    if (s.copied) cudaEventDestroy(s.copied);
+  }
+  for (int i = 0; i < kIdxRing; ++i) if (h->idx_ev[i]) cudaEventDestroy(h->idx_ev[i]);
+  delete h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_put(dqnb_replay* h, int64_t slot, const uint8_t* s_tm1, const uint8_t* s_t,
+                               int32_t action, float reward, float discount, uintptr_t stream) {
+  DQNB_REQUIRE(h && s_tm1 && s_t, "null argument");
+  DQNB_REQUIRE(slot >= 0 && slot < h->capacity, "slot %lld outside [0,%lld)", (long long)slot, (long long)h->capacity);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const int S = h->S;
+  const size_t stack_bytes = (size_t)h->plane_bytes * S;
+  if (h->slot_staged[slot] || h->stage[h->cur].n_records == kStageRecords) DQNB_TRY(flush(h, st));
+
+  int32_t ids[8];
+  for (int k = 0; k < 8; ++k) ids[k] = -1;
+  // s_tm1: chained to the previous put's s_t (TransitionAccumulator hands over the very
+  // same observation, replay.py:1184-1190) -> share its planes; otherwise upload it.
+  const bool chained = h->have_last && memcmp(s_tm1, h->last_st.data(), stack_bytes) == 0;
+  if (chained) {
+    for (int c = 0; c < S; ++c) {
+      ids[c] = h->last_ids[c];
+      if (ids[c] >= 0) h->refcount[ids[c]]++;
+    }
+    h->n_chained++;
+  } else {
+    int m[4];
+    match_channels(s_tm1, nullptr, h->plane_bytes, S, m);
+    for (int c = 0; c < S; ++c)
+      if (m[c] != -1) DQNB_TRY(stage_plane(h, s_tm1, c, st, &ids[c]));
+  }
+  int m[4];
+  match_channels(s_t, s_tm1, h->plane_bytes, S, m);
+  for (int c = 0; c < S; ++c) {
+    if (m[c] == -1) continue;
+    if (m[c] >= 0 && ids[m[c]] >= 0) {
+      ids[S + c] = ids[m[c]];
+      h->refcount[ids[S + c]]++;
+    } else {
+      DQNB_TRY(stage_plane(h, s_t, c, st, &ids[S + c]));
+    }
+  }
+  // release what the slot held, then what `last` held; take refs for the new `last`.
+  int32_t* old = &h->slot_ids[(size_t)slot * 8];
+  for (int k = 0; k < 8; ++k) release_plane(h, old[k]);
+  for (int k = 0; k < 8; ++k) old[k] = ids[k];
+  if (h->have_last)
+    for (int c = 0; c < S; ++c) release_plane(h, h->last_ids[c]);
+  for (int c = 0; c < S; ++c) {
+    h->last_ids[c] = ids[S + c];
+    if (ids[S + c] >= 0) h->refcount[ids[S + c]]++;
+  }
+  memcpy(h->last_st.data(), s_t, stack_bytes);
+  h->have_last = true;
+
+  Stage& s = h->stage[h->cur];
+  SlotRecord& r = h->rec_of(s)[s.n_records++];
+  r.slot = (int32_t)slot; r.action = action; r.reward = reward; r.discount = discount;
+  for (int k = 0; k < 8; ++k) r.plane_ids[k] = ids[k];
+  h->slot_staged[slot] = 1;
+  h->n_puts++;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_flush(dqnb_replay* h, uintptr_t stream) {
+  DQNB_REQUIRE(h, "null handle");
+  DeviceGuard guard(h->device);
+  return flush(h, as_stream(stream));
+}
+
+namespace {
+
+ReplayDeviceView view_of(const dqnb_replay* h) {
+  ReplayDeviceView v;
+  v.planes = h->d_planes; v.slot_ids = h->d_slot_ids; v.actions = h->d_actions;
+  v.rewards = h->d_rewards; v.discounts = h->d_discounts;
+  v.plane_stride = h->plane_stride; v.plane_bytes = h->plane_bytes; v.stack = h->S;
+  return v;
+}
+
+int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* s_tm1, uint8_t* s_t,
+                  int32_t* a, float* r, float* d, cudaStream_t st) {
+  if (n == 0) return DQNB_OK;
+  ReplayDeviceView v = view_of(h);
+  if (h->S == 4 && h->plane_bytes % 16 == 0) {
+    // enough CTAs to cover the 148 SMs twice for small batches; whole planes for big ones
+    int splits = h->gather_splits;
+    if (splits <= 0) splits = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * kNumSMs + n - 1) / n), 16);
+    int chunk = ((h->plane_bytes + splits - 1) / splits + 15) / 16 * 16;
+    chunk = std::min(chunk, 16 * 1024);
+    splits = (h->plane_bytes + chunk - 1) / chunk;
+    dim3 grid(splits, (unsigned)n);
+    gather_stack4<kGatherThreads><<<grid, kGatherThreads, 8 * (size_t)chunk, st>>>(
+        v, slots_dev, (int)n, chunk, s_tm1, s_t, a, r, d);
+  } else {
+    gather_generic<<<(unsigned)n, 128, 0, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
+  }
+  DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+
+// int64 host slots -> int32 device slots through a small pinned ring.
+int upload_slots(dqnb_replay* h, const int64_t* slots, int64_t n, cudaStream_t st, const int32_t** out) {
+  if (n > h->idx_cap) {
+    DQNB_CUDA(cudaDeviceSynchronize());
+    if (h->h_idx) cudaFreeHost(h->h_idx);
+    cudaFree(h->d_idx);
+    h->idx_cap = std::max<int64_t>(n, 1024);
+    DQNB_CUDA(cudaMallocHost(&h->h_idx, sizeof(int32_t) * h->idx_cap * kIdxRing));
+    DQNB_CUDA(cudaMalloc(&h->d_idx, sizeof(int32_t) * h->idx_cap * kIdxRing));
+    for (bool& b : h->idx_busy) b = false;
+  }
+  int k = h->idx_cur;
+  h->idx_cur = (k + 1) % kIdxRing;
+  if (h->idx_busy[k]) DQNB_CUDA(cudaEventSynchronize(h->idx_ev[k]));
+  int32_t* hp = h->h_idx + (size_t)k * h->idx_cap;
+  int32_t* dp = h->d_idx + (size_t)k * h->idx_cap;
+  for (int64_t i = 0; i < n; ++i) {
+    if (slots[i] < 0 || slots[i] >= h->capacity) {
+      set_error("slot %lld outside [0,%lld)", (long long)slots[i], (long long)h->capacity);
+      return DQNB_EINVAL;
+    }
+    hp[i] = (int32_t)slots[i];
+  }
+  DQNB_CUDA(cudaMemcpyAsync(dp, hp, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaEventRecord(h->idx_ev[k], st));
+  h->idx_busy[k] = true;
+  *out = dp;
+  return DQNB_OK;
+}
+
+}  // namespace
+
+extern "C" int dqnb_replay_gather_dev(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* s_tm1_dev,
+                                      uint8_t* s_t_dev, int32_t* a_dev, float* r_dev, float* disc_dev,
+                                      uintptr_t stream) {
+  DQNB_REQUIRE(h && slots_dev && s_tm1_dev && s_t_dev && a_dev && r_dev && disc_dev, "null argument");
+  DQNB_REQUIRE(n >= 0 && n < 65536 * 16, "n=%lld out of range", (long long)n);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(flush(h, st));
+  return launch_gather(h, slots_dev, n, s_tm1_dev, s_t_dev, a_dev, r_dev, disc_dev, st);
+}
+
+extern "C" int dqnb_replay_gather(dqnb_replay* h, const int64_t* slots_host, int64_t n, uint8_t* s_tm1_dev,
+                                  uint8_t* s_t_dev, int32_t* a_dev, float* r_dev, float* disc_dev,
+                                  uintptr_t stream) {
+  DQNB_REQUIRE(h && (slots_host || n == 0), "null argument");
+  DQNB_REQUIRE(n >= 0 && n < 65536 * 16, "n=%lld out of range", (long long)n);
+  if (n == 0) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  const int32_t* dslots = nullptr;
+  DQNB_TRY(upload_slots(h, slots_host, n, as_stream(stream), &dslots));
+  return dqnb_replay_gather_dev(h, dslots, n, s_tm1_dev, s_t_dev, a_dev, r_dev, disc_dev, stream);
+}
+
+extern "C" int dqnb_replay_gather_host(dqnb_replay* h, const int64_t* slots_host, int64_t n,
+                                       uint8_t* s_tm1_host, uint8_t* s_t_host, int32_t* a_host,
+                                       float* r_host, float* disc_host, uintptr_t stream) {
+  DQNB_REQUIRE(h && (n == 0 || (slots_host && s_tm1_host && s_t_host && a_host && r_host && disc_host)),
+               "null argument");
+  if (n == 0) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const size_t stack_bytes = (size_t)h->plane_bytes * h->S;
+  const size_t row = 2 * stack_bytes + 16;
+  if ((int64_t)(row * n) > h->out_cap) {
+    DQNB_CUDA(cudaDeviceSynchronize());
+    cudaFree(h->d_out);
+    h->out_cap = (int64_t)(row * n);
+    DQNB_CUDA(cudaMalloc(&h->d_out, (size_t)h->out_cap));
+  }
+  uint8_t* d1 = h->d_out;
+  uint8_t* d2 = d1 + stack_bytes * n;
+  int32_t* da = reinterpret_cast<int32_t*>(d2 + stack_bytes * n);
+  float* dr = reinterpret_cast<float*>(da + n);
+  float* dd = dr + n;
+  DQNB_TRY(dqnb_replay_gather(h, slots_host, n, d1, d2, da, dr, dd, stream));
+  DQNB_CUDA(cudaMemcpyAsync(s_tm1_host, d1, stack_bytes * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaMemcpyAsync(s_t_host, d2, stack_bytes * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaMemcpyAsync(a_host, da, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaMemcpyAsync(r_host, dr, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaMemcpyAsync(disc_host, dd, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_set_gather_splits(dqnb_replay* h, int splits) {
+  DQNB_REQUIRE(h && splits >= 0, "bad argument");
+  h->gather_splits = splits;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]) {
+  DQNB_REQUIRE(h && out, "null argument");
+  int64_t used = h->pool_planes - (int64_t)h->free_list.size() - (int64_t)h->pending_free.size();
+  out[0] = used; out[1] = h->pool_planes; out[2] = h->n_puts; out[3] = h->n_uploaded;
+  out[4] = h->n_chained; out[5] = h->n_growths;
+  out[6] = h->pool_planes * h->plane_stride + h->capacity * (8 * 4 + 12);
+  out[7] = 0;
+  return DQNB_OK;
+}

@@ -1,0 +1,77 @@
+"""Thin Python handle over the C-ABI replay frame store (dqnb_replay_*)."""
+import ctypes
+
+import numpy as np
+
+from dqn_mgsc_zoo_b200 import _lib
+
+
+def _ptr(arr):
+    return arr.ctypes.data
+
+
+class FrameStore:
+    """uint8 frame planes + per-slot (action, reward, discount) resident in HBM."""
+
+    def __init__(self, capacity, height, width, stack, device=0, stream=0, initial_planes=0):
+        self.capacity, self.shape, self.device, self.stream = int(capacity), (height, width, stack), device, stream
+        h = ctypes.c_void_p()
+        _lib.call("dqnb_replay_create", self.capacity, height, width, stack, int(initial_planes), device,
+                  ctypes.byref(h))
+        self._h = h
+        self._put = _lib.load().dqnb_replay_put
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if self._h is not None:
+            _lib.call("dqnb_replay_destroy", self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def put(self, slot, s_tm1, s_t, action, reward, discount):
+        s_tm1 = np.ascontiguousarray(s_tm1, dtype=np.uint8)
+        s_t = np.ascontiguousarray(s_t, dtype=np.uint8)
+        if s_tm1.shape != self.shape or s_t.shape != self.shape:
+            raise ValueError("stack shape %s/%s does not match store %s" % (s_tm1.shape, s_t.shape, self.shape))
+        _lib.check(self._put(self._h, int(slot), _ptr(s_tm1), _ptr(s_t), int(action), float(reward),
+                             float(discount), self.stream))
+
+    def flush(self):
+        _lib.call("dqnb_replay_flush", self._h, self.stream)
+
+    def gather_host(self, slots):
+        """Returns (s_tm1, a_i32, r_f32, disc_f32, s_t) NumPy arrays for host int64 slots."""
+        slots = np.ascontiguousarray(slots, dtype=np.int64)
+        n = slots.size
+        s1 = np.empty((n,) + self.shape, dtype=np.uint8)
+        s2 = np.empty((n,) + self.shape, dtype=np.uint8)
+        a = np.empty(n, dtype=np.int32)
+        r = np.empty(n, dtype=np.float32)
+        d = np.empty(n, dtype=np.float32)
+        _lib.call("dqnb_replay_gather_host", self._h, _ptr(slots), n, _ptr(s1), _ptr(s2), _ptr(a), _ptr(r),
+                  _ptr(d), self.stream)
+        return s1, a, r, d, s2
+
+    def gather(self, slots, s_tm1_ptr, s_t_ptr, a_ptr, r_ptr, d_ptr, stream=None):
+        """Gather into caller-provided device pointers (ints), asynchronously."""
+        slots = np.ascontiguousarray(slots, dtype=np.int64)
+        _lib.call("dqnb_replay_gather", self._h, _ptr(slots), slots.size, s_tm1_ptr, s_t_ptr, a_ptr, r_ptr,
+                  d_ptr, self.stream if stream is None else stream)
+
+    def set_gather_splits(self, splits):
+        _lib.call("dqnb_replay_set_gather_splits", self._h, int(splits))
+
+    def stats(self):
+        out = (ctypes.c_int64 * 8)()
+        _lib.call("dqnb_replay_stats", self._h, out)
+        keys = ("planes_in_use", "pool_planes", "puts", "planes_uploaded", "chained_puts", "pool_growths",
+                "hbm_bytes")
+        return dict(zip(keys, list(out)))

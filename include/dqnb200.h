@@ -1,0 +1,88 @@
+/* dqnb200.h — C ABI of libdqnb200.so: the B200 (sm_100a) DQN learner hot path.
+ *
+ * The reference (Stalfoes/dqn_mgsc_zoo) is pure Python with no FFI; its seams for
+ * this path are duck-typed Python objects.  Each entry point below names the
+ * reference interface (file:line under /root/reference/dqn_zoo) it stands in for.
+ * INTEGRATION.md shows the ctypes binding a maintainer would add.
+ *
+ * Conventions: every function returns 0 on success or a negative DQNB_E* code;
+ * dqnb_last_error() returns a thread-local message for the last failure.  No C++
+ * types or exceptions cross the boundary.  Handles are opaque and not
+ * thread-safe per handle.  `stream` is a cudaStream_t passed as uintptr_t
+ * (0 = the legacy default stream).  "host" pointers are caller-owned CPU memory,
+ * "dev" pointers are CUDA device memory on the handle's device.
+ */
+#ifndef DQNB200_H_
+#define DQNB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DQNB_OK 0
+#define DQNB_EINVAL (-1)   /* bad argument */
+#define DQNB_ECUDA (-2)    /* CUDA runtime error (message has the cudaError string) */
+#define DQNB_ENOMEM (-3)   /* host or device allocation failed */
+#define DQNB_ESTATE (-4)   /* call not valid in the handle's current state */
+
+typedef struct dqnb_replay dqnb_replay;
+typedef struct dqnb_logits dqnb_logits;
+typedef struct dqnb_learner dqnb_learner;
+
+int dqnb_version(void);
+const char* dqnb_last_error(void);
+int dqnb_device_count(int* count);
+/* Raw device buffers for callers without their own allocator (tests, non-Python hosts). */
+int dqnb_dev_alloc(int device, size_t bytes, void** dev_ptr);
+int dqnb_dev_free(int device, void* dev_ptr);
+int dqnb_copy_h2d(void* dev_dst, const void* host_src, size_t bytes, uintptr_t stream);
+int dqnb_copy_d2h(void* host_dst, const void* dev_src, size_t bytes, uintptr_t stream);
+int dqnb_stream_sync(uintptr_t stream);
+
+/* ------------------------------------------------------------------ replay frame store
+ * Stands in for the item storage of TransitionReplay / ReservoirTransitionReplay
+ * (replay.py:163-333) and CircularBuffer / MGSC*TransitionReplay storage
+ * (replay_circular.py:90-146,568-664,1217-1312) for items shaped like
+ * replay.Transition (replay.py:39-44): two HxWxS uint8 stacks + action, reward, discount.
+ *
+ * The store keeps single HxW frames ("planes") in an HBM pool, deduplicated across the
+ * overlapping stacks of consecutive transitions, plus a per-slot table of the 2*S plane
+ * ids (-1 = the all-zero plane the processor pads with, processors.py:57-69).  Which slot
+ * an item goes to (FIFO ring position or reservoir index j) is decided by the host-side
+ * mirror of the reference class, which also owns the NumPy random stream. */
+int dqnb_replay_create(int64_t capacity, int height, int width, int stack, int64_t initial_planes,
+                       int device, dqnb_replay** out);
+int dqnb_replay_destroy(dqnb_replay* h);
+/* replaces `add` storage (replay.py:184-193, :267-283): put one transition into `slot`,
+ * releasing whatever the slot held.  s_tm1/s_t are host HxWxS uint8 (C order). */
+int dqnb_replay_put(dqnb_replay* h, int64_t slot, const uint8_t* s_tm1, const uint8_t* s_t,
+                    int32_t action, float reward, float discount, uintptr_t stream);
+/* push staged puts to the device (also done implicitly by gather). */
+int dqnb_replay_flush(dqnb_replay* h, uintptr_t stream);
+/* replaces get()+np.stack of sample() (replay.py:195-206): gather+stack n slots into
+ * device arrays s_tm1/s_t [n,H,W,S] u8, a [n] i32, r [n] f32, discount [n] f32. */
+int dqnb_replay_gather(dqnb_replay* h, const int64_t* slots_host, int64_t n, uint8_t* s_tm1_dev,
+                       uint8_t* s_t_dev, int32_t* a_dev, float* r_dev, float* disc_dev,
+                       uintptr_t stream);
+/* same, slot indices already on the device (int32), for use inside a captured CUDA graph. */
+int dqnb_replay_gather_dev(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* s_tm1_dev,
+                           uint8_t* s_t_dev, int32_t* a_dev, float* r_dev, float* disc_dev,
+                           uintptr_t stream);
+/* gather + device->host copy into caller (host) arrays; blocks until the data is there.
+ * This is what the drop-in `sample()` returns as NumPy arrays. */
+int dqnb_replay_gather_host(dqnb_replay* h, const int64_t* slots_host, int64_t n, uint8_t* s_tm1_host,
+                            uint8_t* s_t_host, int32_t* a_host, float* r_host, float* disc_host,
+                            uintptr_t stream);
+/* tuning knob for the gather grid: CTAs per sampled transition (0 = automatic). */
+int dqnb_replay_set_gather_splits(dqnb_replay* h, int splits);
+/* counters: [0] planes in use, [1] pool capacity (planes), [2] puts, [3] planes uploaded,
+ * [4] chained puts (s_tm1 matched the previous s_t), [5] pool growths, [6] bytes of HBM held */
+int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DQNB200_H_ */
