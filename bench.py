@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""Headline benchmark: learner updates/s (double-Q Nature-DQN, batch 32, 1M-transition HBM
+replay, synthetic 84x84x4 uint8 frames) + replay gather GB/s.  See DESIGN.md "Measurement".
+
+  python bench.py --gpus N --steps K --warmup W            # this repo (CUDA path)
+  python bench.py --impl reference --gpus N --steps K ...  # CPU port of the reference path
+
+One JSON line on stdout (rank 0).  N>1: launched by torchrun, one process per GPU, each rank
+an independent agent replica (own replay, params, RNG) - the way the reference scales (SLURM
+arrays); no data-path collective; value = total updates of all ranks / max-over-ranks time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NUM_ACTIONS = 6
+BATCH = 32
+ADDS_PER_LEARN = 4                 # learn_period 16 frames / action repeat 4 (dqn/agent.py:152)
+TARGET_SYNC_UPDATES = 7500         # 1.2e5 frames / 16 (double_q/run_atari.py:86)
+PLANE = 84 * 84
+GATHER_BYTES_PER_TRANSITION = 13 * PLANE + 12     # 5 planes read + 8 written + scalars
+UPDATE_BYTES = 49.05e6             # params/opt-state touched once + batch
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--capacity", type=int, default=1_000_000)
+    ap.add_argument("--gather-n", type=int, default=4096)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="fp32")
+    return ap.parse_args()
+
+
+class EpisodeSource:
+    """Fast synthetic transitions with the reference stack layout (A000, AB00, ... ) and
+    chained observations (s_tm1 of a transition *is* the previous s_t object)."""
+
+    def __init__(self, seed, block=2048):
+        self.rng = np.random.default_rng(seed)
+        self.block = block
+        self.frames = None
+        self.pos = block
+        self.left = 0
+        self.prev = None
+        self.window = None
+
+    def _frame(self):
+        if self.pos == self.block:
+            self.frames = self.rng.integers(0, 256, size=(self.block, 84, 84), dtype=np.uint8)
+            self.pos = 0
+        f = self.frames[self.pos]
+        self.pos += 1
+        return f
+
+    def _obs(self, frame):
+        self.window = (self.window + [frame])[-4:]
+        obs = np.zeros((84, 84, 4), dtype=np.uint8)
+        for c, f in enumerate(self.window):
+            obs[:, :, c] = f
+        return obs
+
+    def next(self):
+        """-> (s_tm1, a, r, discount, s_t)"""
+        if self.left == 0:
+            self.left = int(self.rng.integers(50, 2000))
+            self.window = []
+            self.prev = self._obs(self._frame())
+        self.left -= 1
+        s_t = self._obs(self._frame())
+        u = self.rng.random(2)
+        r = -1.0 if u[0] < 0.05 else (1.0 if u[0] > 0.95 else 0.0)
+        d = 0.0 if (self.left == 0 or u[1] < 0.01) else 0.99
+        tr = (self.prev, int(self.rng.integers(0, NUM_ACTIONS)), r, d, s_t)
+        self.prev = s_t
+        return tr
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.12)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_arm(seconds, steps=None, warmup=3, capacity=4096):
+    """The reference path on host cores: replay.sample(32) (oracle restatement of replay.py)
+    + `update` (torch-CPU fp32 port, all threads).  Bounded sample of the same workload."""
+    from oracle import replay_oracle as ro
+    from oracle import torch_port
+    port = torch_port.make(NUM_ACTIONS, shared_bias=True, double_q=True, threads=os.cpu_count())
+    rep = ro.FifoReplay(capacity, ro.Transition(None, None, None, None, None), np.random.RandomState(0))
+    src = EpisodeSource(1, block=256)
+    for _ in range(capacity):
+        rep.add(ro.Transition(*src.next()))
+
+    def one_step():
+        for _ in range(ADDS_PER_LEARN):
+            rep.add(ro.Transition(*src.next()))
+        s0, a, r, d, s1 = rep.sample(BATCH)
+        return port.update(s0, a, r, d, s1)
+
+    for _ in range(warmup):
+        one_step()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        one_step()
+        n += 1
+        el = time.perf_counter() - t0
+        if (steps is not None and n >= steps) or (steps is None and el >= seconds) or el > 240:
+            break
+    return {"value": n / el, "unit": "updates/s", "cores": port.threads, "kind": "port",
+            "sample": "%d updates of batch %d (4 adds + sample(32) from a %d-transition host FIFO replay + "
+                      "torch-CPU fp32 double-Q update), %.1f s" % (n, BATCH, capacity, el),
+            "steps": n, "seconds": el}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    res = cpu_reference_arm(args.cpu_seconds, steps=args.steps, warmup=max(3, min(args.warmup, 10)))
+    line = {
+        "impl": "reference", "metric": "learner_updates_per_s", "value": res["value"], "unit": "updates/s",
+        "n_gpus": args.gpus, "steps": res["steps"], "warmup": max(3, min(args.warmup, 10)),
+        "ms_per_step": 1e3 / res["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, res_capacity=4096),
+        "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": res["value"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, res_capacity=None):
+    return {"workload": "double_q learner, Nature CNN, batch 32, %d-transition FIFO replay, synthetic 84x84x4 "
+                        "uint8 frames, %d actions" % (res_capacity or args.capacity, NUM_ACTIONS),
+            "batch": BATCH, "replay_capacity": res_capacity or args.capacity, "adds_per_learn": ADDS_PER_LEARN,
+            "target_sync_every_updates": TARGET_SYNC_UPDATES, "parallelism": "replicas x%d" % args.gpus,
+            "l2": "replay pool (7 GB) >> L2, random slots every step; params/opt state L2-resident as in training"}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from dqn_mgsc_zoo_b200 import learner as lrn
+    from dqn_mgsc_zoo_b200 import replay as rp
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- build the workload: full replay + learner with 100 warm updates worth of state
+    t_fill = time.perf_counter()
+    replay = rp.TransitionReplay(args.capacity, rp.Transition(None, None, None, None, None),
+                                 np.random.RandomState(rank), device=local_rank)
+    src = EpisodeSource(1000 + rank)
+    for _ in range(args.capacity):
+        replay.add(rp.Transition(*src.next()))
+    store = replay.frame_store
+    store.flush()
+    t_fill = time.perf_counter() - t_fill
+    L = lrn.Learner(NUM_ACTIONS, BATCH, shared_bias=True, double_q=True, precision=args.precision,
+                    device=local_rank)
+    from dqn_mgsc_zoo_b200 import networks
+    init = networks.init_params(np.random.default_rng(rank), NUM_ACTIONS, shared_bias=True)
+    L.set_params(init, lrn.ONLINE)
+    L.set_params(init, lrn.TARGET)
+
+    state = {"updates": 0}
+
+    def device_step():
+        slots = replay.sample_slots(BATCH)
+        L.update_from_replay(store, slots)
+        state["updates"] += 1
+        if state["updates"] % TARGET_SYNC_UPDATES == 0:
+            L.sync_target()
+
+    def e2e_step():
+        for _ in range(ADDS_PER_LEARN):
+            replay.add(rp.Transition(*pending.pop()))
+        device_step()
+        return L.loss()          # D2H read of the step's result
+
+    def timed(fn, steps):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(3, args.warmup)):
+        device_step()
+    with ClockSampler(local_rank) as clocks:
+        ms = timed(device_step, args.steps)
+    value = world * args.steps / (ms * 1e-3)
+
+    # ---- e2e: new transitions arrive from host memory every step, loss is read back
+    e2e_steps = min(args.steps, 1000)
+    pending = [src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + 5))]
+    up0 = store.stats()["planes_uploaded"]
+    for _ in range(5):
+        e2e_step()
+    up0 = store.stats()["planes_uploaded"]
+    ms_e2e = timed(e2e_step, e2e_steps)
+    planes = store.stats()["planes_uploaded"] - up0
+    h2d = planes * PLANE / e2e_steps + ADDS_PER_LEARN * 64 + BATCH * 4
+    e2e = {"value": world * e2e_steps / (ms_e2e * 1e-3), "unit": "updates/s",
+           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "steps": e2e_steps,
+           "what": "4 replay.add(host transition) + sample_slots + update_from_replay + loss readback"}
+
+    # ---- literal seam: update(host NumPy batch), 3.6 MB H2D per step like the reference's jit dispatch
+    hb = store.gather_host(replay.sample_slots(BATCH))
+    for _ in range(3):
+        L.update_host(*hb)
+    hsteps = min(args.steps, 300)
+    ms_host = timed(lambda: (L.update_host(*hb), L.loss()), hsteps)
+    e2e["host_batch_updates_per_s"] = world * hsteps / (ms_host * 1e-3)
+    e2e["host_batch_h2d_bytes_per_step"] = 2 * BATCH * 28224 + 12 * BATCH
+
+    # ---- replay gather throughput at n transitions per launch (HBM roofline kernel)
+    n = args.gather_n
+    bufs = [torch.empty((n, 84, 84, 4), dtype=torch.uint8, device="cuda") for _ in range(2)]
+    ai = torch.empty(n, dtype=torch.int32, device="cuda")
+    rf, df = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+    rs = np.random.RandomState(99 + rank)
+    slot_sets = [rs.randint(args.capacity, size=n).astype(np.int64) for _ in range(24)]
+
+    def gather_step(i=[0]):
+        store.gather(slot_sets[i[0] % len(slot_sets)], bufs[0].data_ptr(), bufs[1].data_ptr(), ai.data_ptr(),
+                     rf.data_ptr(), df.data_ptr())
+        i[0] += 1
+    for _ in range(4):
+        gather_step()
+    greps = 20
+    ms_g = timed(gather_step, greps) / greps
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    achieved = n * GATHER_BYTES_PER_TRANSITION / (ms_g * 1e-3) / 1e9
+    roofline = {"kernel": "gather_stack4", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "transitions_per_launch": n, "us_per_launch": ms_g * 1e3,
+                "note": "timed with CUDA events around %d launches incl. the 16 KB slot-index upload each" % greps}
+    ms_upd = ms / args.steps
+    roofline_update = {"bound": "hbm", "achieved": UPDATE_BYTES / (ms_upd * 1e-3) / 1e9, "peak": peak,
+                       "unit": "GB/s", "frac": UPDATE_BYTES / (ms_upd * 1e-3) / 1e9 / peak,
+                       "note": "whole update graph vs 49.05 MB touched-once bytes; batch 32 is latency bound"}
+
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        res = cpu_reference_arm(args.cpu_seconds)
+        cpu = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    launches = L.launches_per_update() + 1
+    line = {
+        "metric": "learner_updates_per_s", "value": value, "unit": "updates/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
+        "config": workload_config(args), "clocks": clocks.summary(), "e2e": e2e,
+        "gpu_launches": int(launches * args.steps), "launches_per_update": int(launches),
+        "roofline": roofline, "roofline_update": roofline_update, "cpu_baseline": cpu,
+        "replay_gather_gbs": achieved, "replay_fill_seconds": t_fill, "replay_stats": store.stats(),
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -31,6 +31,17 @@ SIGNATURES = {
     "dqnb_replay_gather_host": [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
     "dqnb_replay_set_gather_splits": [c_vp, c_int],
     "dqnb_replay_stats": [c_vp, ctypes.POINTER(c_i64)],
+    "dqnb_learner_create": [c_vp, c_int, ctypes.POINTER(c_vp)],
+    "dqnb_learner_destroy": [c_vp],
+    "dqnb_learner_num_params": [c_vp, ctypes.POINTER(c_i64)],
+    "dqnb_learner_write": [c_vp, c_int, c_vp, c_i64, STREAM],
+    "dqnb_learner_read": [c_vp, c_int, c_vp, c_i64, STREAM],
+    "dqnb_learner_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
+    "dqnb_learner_update_host": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
+    "dqnb_learner_update_from_replay": [c_vp, c_vp, c_vp, STREAM],
+    "dqnb_learner_sync_target": [c_vp, STREAM],
+    "dqnb_learner_q_values": [c_vp, c_int, c_vp, c_i32, c_vp, STREAM],
+    "dqnb_learner_launches_per_update": [c_vp, ctypes.POINTER(c_i64)],
 }
 
 

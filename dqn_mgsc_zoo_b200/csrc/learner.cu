@@ -1,0 +1,456 @@
+// DQN / double-DQN learner step on the device: Nature-CNN forward for 2-3 nets, TD/loss,
+// backward, centered RMSProp, target sync; captured once as a CUDA graph with parallel
+// branches.  Replaces the jitted `update` of dqn/agent.py:109-119 / double_q/agent.py:85-121
+// and the target sync of dqn/agent.py:155-156.  See include/dqnb200.h.
+#include <algorithm>
+#include <vector>
+
+#include "head_kernels.cuh"
+#include "learner_internal.cuh"
+
+using namespace dqnb;
+
+namespace {
+
+struct ArenaLayout {
+  int64_t w1, b1, w2, b2, w3, b3, fw1, fb1, fw2, fb2, total;
+};
+
+ArenaLayout make_layout(int A, int shared_bias) {
+  ArenaLayout L;
+  int64_t o = 0;
+  L.w1 = o; o += (int64_t)Conv1::KCOL * Conv1::COUT;
+  L.b1 = o; o += Conv1::COUT;
+  L.w2 = o; o += (int64_t)Conv2::KCOL * Conv2::COUT;
+  L.b2 = o; o += Conv2::COUT;
+  L.w3 = o; o += (int64_t)Conv3::KCOL * Conv3::COUT;
+  L.b3 = o; o += Conv3::COUT;
+  L.fw1 = o; o += (int64_t)kFc1In * kFc1Out;
+  L.fb1 = o; o += kFc1Out;
+  L.fw2 = o; o += (int64_t)kFc1Out * A;
+  L.fb2 = o; o += shared_bias ? 1 : A;
+  L.total = o;
+  return L;
+}
+
+int pick_splits(size_t ctas, int K, int want_ctas = 2 * kNumSMs) {
+  int kchunks = (K + kBK - 1) / kBK;
+  int s = (int)((want_ctas + ctas - 1) / ctas);
+  s = std::min(s, std::max(1, kchunks / 4));
+  return std::max(1, s);
+}
+
+}  // namespace
+
+struct dqnb_learner {
+  dqnb_learner_config cfg;
+  int device = 0;
+  int B = 0, A = 0, nets = 2;
+  ArenaLayout L;
+  // parameter / optimiser arenas (flat fp32, oracle leaf order)
+  float *online = nullptr, *target = nullptr, *mu = nullptr, *nu = nullptr, *grad = nullptr;
+  // batch
+  uint8_t *s_tm1 = nullptr, *s_t = nullptr;
+  int32_t* act = nullptr;
+  float *rew = nullptr, *disc = nullptr, *row_weight = nullptr;
+  // activations per net, gradients
+  float *a1[kMaxNets] = {}, *a2[kMaxNets] = {}, *a3[kMaxNets] = {}, *h1[kMaxNets] = {}, *q[kMaxNets] = {};
+  float *dh1 = nullptr, *dy3 = nullptr, *dy2 = nullptr, *dy1 = nullptr;
+  float *td = nullptr, *row_loss = nullptr, *dq_taken = nullptr, *loss = nullptr;
+  // split-K scratch (one region per op so graph branches can overlap)
+  float* ws = nullptr;
+  unsigned* counters = nullptr;
+  size_t ws_off = 0, cnt_off = 0, ws_cap = 0, cnt_cap = 0;
+  bool sizing = false;
+  // graph
+  cudaGraphExec_t graph = nullptr;
+  cudaStream_t side[3] = {};
+  cudaEvent_t ev[8] = {};
+  int64_t updates = 0;
+  int64_t launches_per_update = 0;
+  // pinned staging for host-batch updates and slot uploads
+  uint8_t* pinned = nullptr;
+  size_t pinned_bytes = 0;
+  int32_t* d_slots = nullptr;
+  cudaEvent_t pinned_free = nullptr;
+  bool pinned_busy = false;
+  float* pinned_loss = nullptr;
+
+  SplitK take_scratch(size_t ws_floats, size_t tiles) {
+    SplitK sk{ws ? ws + ws_off : nullptr, counters ? counters + cnt_off : nullptr};
+    ws_off += ws_floats;
+    cnt_off += tiles;
+    return sk;
+  }
+};
+
+namespace {
+
+template <class P>
+int run_gemm(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
+  SplitK sk = h->take_scratch(gemm_ws_floats(p, Z, splits), gemm_tiles(p, Z));
+  h->launches_per_update++;
+  if (h->sizing) return DQNB_OK;
+  DQNB_CUDA(launch_gemm(p, Z, splits, sk, st));
+  return DQNB_OK;
+}
+
+template <class L, class TIn, int BM>
+int conv_fwd(dqnb_learner* h, int nets, int rows, const TIn* const* x, const float* const* params,
+             int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st) {
+  ConvFwd<L, TIn, BM> p;
+  p.M = rows * L::HOUT * L::WOUT; p.N = L::COUT; p.K = L::KCOL;
+  for (int z = 0; z < nets; ++z) {
+    p.x[z] = x[z]; p.w[z] = params[z] + w_off; p.bias[z] = params[z] + b_off; p.y[z] = y[z];
+  }
+  return run_gemm(h, p, nets, pick_splits(gemm_tiles(p, nets), p.K), st);
+}
+
+// Forward of `nets` networks over `rows` images each: x[z] uint8 NHWC -> h1[z], (q via head).
+int forward_torso(dqnb_learner* h, int nets, int rows, const uint8_t* const* x, const float* const* params,
+                  cudaStream_t st) {
+  const float* in2[kMaxNets]; const float* in3[kMaxNets]; const float* in4[kMaxNets];
+  for (int z = 0; z < nets; ++z) { in2[z] = h->a1[z]; in3[z] = h->a2[z]; in4[z] = h->a3[z]; }
+  DQNB_TRY((conv_fwd<Conv1, uint8_t, 64>(h, nets, rows, x, params, h->L.w1, h->L.b1, h->a1, st)));
+  DQNB_TRY((conv_fwd<Conv2, float, 32>(h, nets, rows, in2, params, h->L.w2, h->L.b2, h->a2, st)));
+  DQNB_TRY((conv_fwd<Conv3, float, 32>(h, nets, rows, in3, params, h->L.w3, h->L.b3, h->a3, st)));
+  DenseFwd p;
+  p.M = rows; p.N = kFc1Out; p.K = kFc1In;
+  for (int z = 0; z < nets; ++z) {
+    p.x[z] = in4[z]; p.w[z] = params[z] + h->L.fw1; p.bias[z] = params[z] + h->L.fb1; p.y[z] = h->h1[z];
+  }
+  return run_gemm(h, p, nets, pick_splits(gemm_tiles(p, nets), p.K), st);
+}
+
+HeadArgs head_args(dqnb_learner* h, int rows, const float* const* params, int nets) {
+  HeadArgs g;
+  g.batch = rows; g.num_actions = h->A; g.shared_bias = h->cfg.shared_bias; g.double_q = nets == 3;
+  g.grad_bound = h->cfg.grad_error_bound;
+  g.inv_mean = 1.0f / (float)(h->cfg.loss_mean_over > 0 ? h->cfg.loss_mean_over : rows);
+  for (int z = 0; z < kMaxNets; ++z) {
+    int zz = std::min(z, nets - 1);
+    g.h1[z] = h->h1[zz]; g.w2[z] = params[zz] + h->L.fw2; g.b2[z] = params[zz] + h->L.fb2; g.q[z] = h->q[zz];
+  }
+  g.action = h->act; g.reward = h->rew; g.discount = h->disc; g.row_weight = nullptr;
+  g.td = h->td; g.row_loss = h->row_loss; g.dq_taken = h->dq_taken; g.dh1 = h->dh1;
+  return g;
+}
+
+}  // namespace
+
+namespace {
+
+template <class L, class TIn>
+int conv_wgrad(dqnb_learner* h, int rows, const TIn* x, const float* dy, int64_t w_off, cudaStream_t st) {
+  ConvWgrad<L, TIn> p;
+  p.M = L::KCOL + 1; p.N = L::COUT; p.K = rows * L::HOUT * L::WOUT;
+  p.x = x; p.dy = dy; p.grad = h->grad + w_off;
+  return run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st);
+}
+
+template <class L>
+int conv_dgrad(dqnb_learner* h, int rows, const float* dy, const float* w, const float* act_in, float* dx,
+               cudaStream_t st) {
+  ConvDgrad<L> p;
+  p.M = rows * ConvDgrad<L>::NY * ConvDgrad<L>::NX; p.N = L::CIN;
+  p.K = ConvDgrad<L>::T * ConvDgrad<L>::T * L::COUT;
+  p.dy = dy; p.w = w; p.act_in = act_in; p.dx = dx;
+  const int Z = L::STRIDE * L::STRIDE;
+  return run_gemm(h, p, Z, pick_splits(gemm_tiles(p, Z), p.K), st);
+}
+
+// fork: `to` waits for everything recorded on `from` so far (works inside stream capture).
+int fork(cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
+  DQNB_CUDA(cudaEventRecord(ev, from));
+  DQNB_CUDA(cudaStreamWaitEvent(to, ev, 0));
+  return DQNB_OK;
+}
+
+// Enqueues one full update on `st` (+ side streams for independent branches).  In sizing mode
+// nothing is launched; scratch offsets and the launch count are tallied instead.
+int enqueue_update(dqnb_learner* h, cudaStream_t st) {
+  h->ws_off = h->cnt_off = 0;
+  h->launches_per_update = 0;
+  const int B = h->B, nets = h->nets;
+  const bool live = !h->sizing;
+  cudaStream_t s1 = h->side[0], s2 = h->side[1], s3 = h->side[2];
+  const uint8_t* xin[kMaxNets] = {h->s_tm1, h->s_t, h->s_t};
+  const float* params[kMaxNets] = {h->online, h->target, h->online};
+
+  DQNB_TRY(forward_torso(h, nets, B, xin, params, st));
+  HeadArgs g = head_args(h, B, params, nets);
+  h->launches_per_update++;
+  if (live) {
+    head_td_kernel<<<(B + 3) / 4, 128, 0, st>>>(g);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  // branch s1: fc2 parameter grads + loss.   branch s2: fc1 weight grad.
+  if (live) { DQNB_TRY(fork(h->ev[0], st, s1)); DQNB_TRY(fork(h->ev[0], st, s2)); }
+  h->launches_per_update++;
+  if (live) {
+    int n = kFc1Out * h->A;
+    fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
+                                                     h->dq_taken, h->row_loss, h->grad + h->L.fw2,
+                                                     h->grad + h->L.fb2, h->loss);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  {
+    DenseWgrad p;
+    p.M = kFc1In + 1; p.N = kFc1Out; p.K = B;
+    p.x = h->a3[0]; p.dy = h->dh1; p.grad = h->grad + h->L.fw1;
+    DQNB_TRY(run_gemm(h, p, 1, 1, s2));
+  }
+  {  // main: fc1 dgrad -> dy3 (masked by conv3's relu)
+    DenseDgrad p;
+    p.M = B; p.N = kFc1In; p.K = kFc1Out;
+    p.dy = h->dh1; p.w = h->online + h->L.fw1; p.act = h->a3[0]; p.dx = h->dy3;
+    DQNB_TRY(run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st));
+  }
+  if (live) DQNB_TRY(fork(h->ev[1], st, s3));
+  DQNB_TRY((conv_wgrad<Conv3, float>(h, B, h->a2[0], h->dy3, h->L.w3, s3)));
+  DQNB_TRY((conv_dgrad<Conv3>(h, B, h->dy3, h->online + h->L.w3, h->a2[0], h->dy2, st)));
+  if (live) DQNB_TRY(fork(h->ev[2], st, s3));
+  DQNB_TRY((conv_wgrad<Conv2, float>(h, B, h->a1[0], h->dy2, h->L.w2, s3)));
+  DQNB_TRY((conv_dgrad<Conv2>(h, B, h->dy2, h->online + h->L.w2, h->a1[0], h->dy1, st)));
+  DQNB_TRY((conv_wgrad<Conv1, uint8_t>(h, B, h->s_tm1, h->dy1, h->L.w1, st)));
+  // join, then the optimiser over the whole arena
+  if (live) {
+    DQNB_TRY(fork(h->ev[3], s1, st));
+    DQNB_TRY(fork(h->ev[4], s2, st));
+    DQNB_TRY(fork(h->ev[5], s3, st));
+  }
+  h->launches_per_update++;
+  if (live) {
+    int64_t n4 = (h->L.total >> 2) + 1;
+    rmsprop_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(h->online, h->mu, h->nu, h->grad, h->L.total,
+                                                               h->cfg.learning_rate, h->cfg.decay, h->cfg.eps);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  return DQNB_OK;
+}
+
+int build_graph(dqnb_learner* h) {
+  cudaStream_t cap;
+  DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+  DQNB_CUDA(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+  int rc = enqueue_update(h, cap);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(cap, &graph);
+  if (rc != DQNB_OK) { if (graph) cudaGraphDestroy(graph); cudaStreamDestroy(cap); return rc; }
+  DQNB_CUDA(e);
+  DQNB_CUDA(cudaGraphInstantiate(&h->graph, graph, 0));
+  DQNB_CUDA(cudaGraphDestroy(graph));
+  DQNB_CUDA(cudaStreamDestroy(cap));
+  return DQNB_OK;
+}
+
+template <class T>
+int dmalloc(T** p, size_t count) {
+  DQNB_CUDA(cudaMalloc(p, sizeof(T) * std::max<size_t>(count, 4)));
+  DQNB_CUDA(cudaMemset(*p, 0, sizeof(T) * std::max<size_t>(count, 4)));
+  return DQNB_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------- C ABI
+extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, dqnb_learner** out) {
+  DQNB_REQUIRE(cfg && out, "null argument");
+  DQNB_REQUIRE(cfg->num_actions >= 1 && cfg->num_actions <= kMaxActions, "num_actions %d not in 1..%d",
+               cfg->num_actions, kMaxActions);
+  DQNB_REQUIRE(cfg->batch_size >= 1 && cfg->batch_size <= 65536, "batch_size %d out of range", cfg->batch_size);
+  DQNB_REQUIRE(cfg->precision == DQNB_FP32, "precision %d not available in this build", cfg->precision);
+  DeviceGuard guard(device);
+  dqnb_learner* h = new dqnb_learner();
+  h->cfg = *cfg;
+  h->device = device;
+  h->B = cfg->batch_size; h->A = cfg->num_actions; h->nets = cfg->double_q ? 3 : 2;
+  h->L = make_layout(h->A, cfg->shared_bias);
+  const size_t B = h->B, P = h->L.total;
+  DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
+  DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
+  DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));
+  DQNB_TRY(dmalloc(&h->act, B)); DQNB_TRY(dmalloc(&h->rew, B)); DQNB_TRY(dmalloc(&h->disc, B));
+  DQNB_TRY(dmalloc(&h->d_slots, B));
+  for (int z = 0; z < h->nets; ++z) {
+    DQNB_TRY(dmalloc(&h->a1[z], B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->a2[z], B * Conv2::OUT_PER_IMG));
+    DQNB_TRY(dmalloc(&h->a3[z], B * Conv3::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->h1[z], B * kFc1Out));
+    DQNB_TRY(dmalloc(&h->q[z], B * h->A));
+  }
+  DQNB_TRY(dmalloc(&h->dh1, B * kFc1Out)); DQNB_TRY(dmalloc(&h->dy3, B * Conv3::OUT_PER_IMG));
+  DQNB_TRY(dmalloc(&h->dy2, B * Conv2::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->dy1, B * Conv1::OUT_PER_IMG));
+  DQNB_TRY(dmalloc(&h->td, B)); DQNB_TRY(dmalloc(&h->row_loss, B)); DQNB_TRY(dmalloc(&h->dq_taken, B));
+  DQNB_TRY(dmalloc(&h->loss, 1));
+  for (auto& s : h->side) DQNB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  for (auto& e : h->ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  DQNB_CUDA(cudaEventCreateWithFlags(&h->pinned_free, cudaEventDisableTiming));
+  h->pinned_bytes = 2 * B * Conv1::IN_PER_IMG + 16 * B;
+  DQNB_CUDA(cudaMallocHost(&h->pinned, h->pinned_bytes));
+  DQNB_CUDA(cudaMallocHost(&h->pinned_loss, 64));
+  // size the split-K scratch with a dry pass, then record the graph
+  h->sizing = true;
+  DQNB_TRY(enqueue_update(h, nullptr));
+  h->sizing = false;
+  h->ws_cap = h->ws_off; h->cnt_cap = h->cnt_off;
+  DQNB_TRY(dmalloc(&h->ws, h->ws_cap)); DQNB_TRY(dmalloc(&h->counters, h->cnt_cap));
+  DQNB_TRY(build_graph(h));
+  *out = h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
+  if (!h) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaDeviceSynchronize();
+  if (h->graph) cudaGraphExecDestroy(h->graph);
+  float* fl[] = {h->online, h->target, h->mu, h->nu, h->grad, h->rew, h->disc, h->dh1, h->dy3, h->dy2, h->dy1,
+                 h->td, h->row_loss, h->dq_taken, h->loss, h->ws};
+  for (float* p : fl) cudaFree(p);
+  for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
+  cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
+  for (auto& s : h->side) if (s) cudaStreamDestroy(s);
+  for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+  if (h->pinned_free) cudaEventDestroy(h->pinned_free);
+  if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->pinned_loss) cudaFreeHost(h->pinned_loss);
+  delete h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_num_params(dqnb_learner* h, int64_t* n) {
+  DQNB_REQUIRE(h && n, "null argument");
+  *n = h->L.total;
+  return DQNB_OK;
+}
+
+namespace {
+int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
+  const int64_t P = h->L.total, BA = (int64_t)h->B * h->A;
+  switch (which) {
+    case DQNB_ONLINE: *p = h->online; *n = P; break;
+    case DQNB_TARGET: *p = h->target; *n = P; break;
+    case DQNB_MU: *p = h->mu; *n = P; break;
+    case DQNB_NU: *p = h->nu; *n = P; break;
+    case DQNB_GRAD: *p = h->grad; *n = P; break;
+    case DQNB_Q_TM1: *p = h->q[0]; *n = BA; break;
+    case DQNB_Q_TARGET_T: *p = h->q[1]; *n = BA; break;
+    case DQNB_Q_T: DQNB_REQUIRE(h->nets == 3, "Q_T only exists for double-Q learners"); *p = h->q[2]; *n = BA; break;
+    case DQNB_TD: *p = h->td; *n = h->B; break;
+    case DQNB_LOSS: *p = h->loss; *n = 1; break;
+    default: set_error("unknown state array %d", which); return DQNB_EINVAL;
+  }
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host, int64_t n, uintptr_t stream) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DQNB_REQUIRE(which >= DQNB_ONLINE && which <= DQNB_NU, "state array %d is read-only", which);
+  DeviceGuard guard(h->device);
+  float* p; int64_t len;
+  DQNB_TRY(locate(h, which, &p, &len));
+  DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
+  DQNB_CUDA(cudaMemcpyAsync(p, host, sizeof(float) * n, cudaMemcpyHostToDevice, as_stream(stream)));
+  DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_read(dqnb_learner* h, int which, float* host, int64_t n, uintptr_t stream) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DeviceGuard guard(h->device);
+  float* p; int64_t len;
+  DQNB_TRY(locate(h, which, &p, &len));
+  DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
+  DQNB_CUDA(cudaMemcpyAsync(host, p, sizeof(float) * n, cudaMemcpyDeviceToHost, as_stream(stream)));
+  DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, const int32_t* a_dev,
+                                   const float* r_dev, const float* disc_dev, const uint8_t* s_t_dev,
+                                   uintptr_t stream) {
+  DQNB_REQUIRE(h && s_tm1_dev && a_dev && r_dev && disc_dev && s_t_dev, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const size_t B = h->B, img = (size_t)Conv1::IN_PER_IMG * B;
+  if (s_tm1_dev != h->s_tm1) {   // external batch: bring it into the graph's fixed buffers
+    DQNB_CUDA(cudaMemcpyAsync(h->s_tm1, s_tm1_dev, img, cudaMemcpyDeviceToDevice, st));
+    DQNB_CUDA(cudaMemcpyAsync(h->s_t, s_t_dev, img, cudaMemcpyDeviceToDevice, st));
+    DQNB_CUDA(cudaMemcpyAsync(h->act, a_dev, 4 * B, cudaMemcpyDeviceToDevice, st));
+    DQNB_CUDA(cudaMemcpyAsync(h->rew, r_dev, 4 * B, cudaMemcpyDeviceToDevice, st));
+    DQNB_CUDA(cudaMemcpyAsync(h->disc, disc_dev, 4 * B, cudaMemcpyDeviceToDevice, st));
+  }
+  DQNB_CUDA(cudaGraphLaunch(h->graph, st));
+  h->updates++;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_update_host(dqnb_learner* h, const uint8_t* s_tm1_host, const int32_t* a_host,
+                                        const float* r_host, const float* disc_host, const uint8_t* s_t_host,
+                                        uintptr_t stream) {
+  DQNB_REQUIRE(h && s_tm1_host && a_host && r_host && disc_host && s_t_host, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const size_t B = h->B, img = (size_t)Conv1::IN_PER_IMG * B;
+  if (h->pinned_busy) DQNB_CUDA(cudaEventSynchronize(h->pinned_free));
+  uint8_t* p = h->pinned;
+  memcpy(p, s_tm1_host, img); memcpy(p + img, s_t_host, img);
+  memcpy(p + 2 * img, a_host, 4 * B); memcpy(p + 2 * img + 4 * B, r_host, 4 * B);
+  memcpy(p + 2 * img + 8 * B, disc_host, 4 * B);
+  DQNB_CUDA(cudaMemcpyAsync(h->s_tm1, p, img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->s_t, p + img, img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->act, p + 2 * img, 4 * B, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->rew, p + 2 * img + 4 * B, 4 * B, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->disc, p + 2 * img + 8 * B, 4 * B, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaEventRecord(h->pinned_free, st));
+  h->pinned_busy = true;
+  return dqnb_learner_update(h, h->s_tm1, h->act, h->rew, h->disc, h->s_t, stream);
+}
+
+extern "C" int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* replay, const int64_t* slots_host,
+                                               uintptr_t stream) {
+  DQNB_REQUIRE(h && replay && slots_host, "null argument");
+  int H, W, S;
+  replay_frame_shape(replay, &H, &W, &S);
+  DQNB_REQUIRE(H == Conv1::HIN && W == Conv1::WIN && S == Conv1::CIN, "replay frames %dx%dx%d are not 84x84x4", H, W, S);
+  DeviceGuard guard(h->device);
+  DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->s_tm1, h->s_t, h->act, h->rew, h->disc, as_stream(stream)));
+  return dqnb_learner_update(h, h->s_tm1, h->act, h->rew, h->disc, h->s_t, stream);
+}
+
+extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
+  DQNB_REQUIRE(h, "null argument");
+  DeviceGuard guard(h->device);
+  DQNB_CUDA(cudaMemcpyAsync(h->target, h->online, sizeof(float) * h->L.total, cudaMemcpyDeviceToDevice, as_stream(stream)));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_host, int32_t n,
+                                     float* q_host, uintptr_t stream) {
+  DQNB_REQUIRE(h && s_host && q_host, "null argument");
+  DQNB_REQUIRE(n >= 1 && n <= h->B, "n=%d not in 1..batch_size", n);
+  DQNB_REQUIRE(which_params == 0 || which_params == 1, "which_params must be 0 (online) or 1 (target)");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  // acting runs between updates on the same stream, so net-0 buffers can be borrowed
+  DQNB_CUDA(cudaMemcpyAsync(h->s_tm1, s_host, (size_t)n * Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, st));
+  const uint8_t* xin[kMaxNets] = {h->s_tm1, h->s_tm1, h->s_tm1};
+  const float* prm = which_params ? h->target : h->online;
+  const float* params[kMaxNets] = {prm, prm, prm};
+  h->ws_off = h->cnt_off = 0;
+  DQNB_TRY(forward_torso(h, 1, n, xin, params, st));
+  HeadArgs g = head_args(h, n, params, 2);
+  g.h1[1] = g.h1[0]; g.q[1] = h->q[1];   // head also evaluates a dummy target row; harmless
+  g.td = h->td; g.dh1 = h->dh1;
+  head_td_kernel<<<(n + 3) / 4, 128, 0, st>>>(g);
+  DQNB_CUDA(cudaGetLastError());
+  DQNB_CUDA(cudaMemcpyAsync(q_host, h->q[0], sizeof(float) * n * h->A, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n) {
+  DQNB_REQUIRE(h && n, "null argument");
+  *n = h->launches_per_update;
+  return DQNB_OK;
+}

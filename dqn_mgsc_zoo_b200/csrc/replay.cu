@@ -445,3 +445,15 @@ extern "C" int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]) {
   out[7] = 0;
   return DQNB_OK;
 }
+
+// ---- internal hooks (learner_internal.cuh)
+namespace dqnb {
+int replay_gather_into(dqnb_replay* h, const int64_t* slots_host, int64_t n, uint8_t* s_tm1, uint8_t* s_t,
+                       int32_t* a, float* r, float* d, cudaStream_t st) {
+  return dqnb_replay_gather(h, slots_host, n, s_tm1, s_t, a, r, d, reinterpret_cast<uintptr_t>(st));
+}
+int replay_frame_shape(const dqnb_replay* h, int* height, int* width, int* stack) {
+  *height = h->H; *width = h->W; *stack = h->S;
+  return DQNB_OK;
+}
+}  // namespace dqnb

@@ -1,0 +1,142 @@
+"""Python handle over the C-ABI learner (dqnb_learner_*): the device-side `update`."""
+import collections
+import ctypes
+
+import numpy as np
+
+from dqn_mgsc_zoo_b200 import _lib
+
+ONLINE, TARGET, MU, NU, GRAD, Q_TM1, Q_TARGET_T, Q_T, TD, LOSS = range(10)
+PRECISIONS = {"fp32": 0, "bf16": 1}
+
+
+class LearnerConfig(ctypes.Structure):
+    _fields_ = [("num_actions", ctypes.c_int32), ("shared_bias", ctypes.c_int32),
+                ("double_q", ctypes.c_int32), ("batch_size", ctypes.c_int32),
+                ("loss_mean_over", ctypes.c_int32), ("precision", ctypes.c_int32),
+                ("learning_rate", ctypes.c_float), ("decay", ctypes.c_float),
+                ("eps", ctypes.c_float), ("grad_error_bound", ctypes.c_float)]
+
+
+def param_shapes(num_actions, shared_bias=False):
+    """Leaf shapes in arena order (haiku names in networks.NATURE_HAIKU_NAMES)."""
+    s = collections.OrderedDict()
+    s["conv1.w"], s["conv1.b"] = (8, 8, 4, 32), (32,)
+    s["conv2.w"], s["conv2.b"] = (4, 4, 32, 64), (64,)
+    s["conv3.w"], s["conv3.b"] = (3, 3, 64, 64), (64,)
+    s["fc1.w"], s["fc1.b"] = (3136, 512), (512,)
+    s["fc2.w"], s["fc2.b"] = (512, num_actions), ((1,) if shared_bias else (num_actions,))
+    return s
+
+
+def flatten_params(params):
+    return np.concatenate([np.asarray(v, dtype=np.float32).ravel() for v in params.values()])
+
+
+def unflatten_params(flat, num_actions, shared_bias=False):
+    out, o = collections.OrderedDict(), 0
+    for k, shape in param_shapes(num_actions, shared_bias).items():
+        n = int(np.prod(shape))
+        out[k] = np.asarray(flat[o:o + n]).reshape(shape)
+        o += n
+    return out
+
+
+class Learner:
+    def __init__(self, num_actions, batch_size, shared_bias=False, double_q=False, learning_rate=0.00025,
+                 decay=0.95, eps=0.01 / 32 ** 2, grad_error_bound=1.0 / 32, precision="fp32", device=0,
+                 stream=0, loss_mean_over=0):
+        self.num_actions, self.batch_size = int(num_actions), int(batch_size)
+        self.shared_bias, self.double_q = bool(shared_bias), bool(double_q)
+        self.device, self.stream = device, stream
+        cfg = LearnerConfig(self.num_actions, int(self.shared_bias), int(self.double_q), self.batch_size,
+                            int(loss_mean_over), PRECISIONS[precision], learning_rate, decay, eps,
+                            grad_error_bound)
+        h = ctypes.c_void_p()
+        _lib.call("dqnb_learner_create", ctypes.byref(cfg), device, ctypes.byref(h))
+        self._h = h
+        n = ctypes.c_int64()
+        _lib.call("dqnb_learner_num_params", self._h, ctypes.byref(n))
+        self.num_params = n.value
+        self._update_from_replay = _lib.load().dqnb_learner_update_from_replay
+
+    def close(self):
+        if self._h is not None:
+            _lib.call("dqnb_learner_destroy", self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _len(self, which):
+        if which <= GRAD:
+            return self.num_params
+        if which in (Q_TM1, Q_TARGET_T, Q_T):
+            return self.batch_size * self.num_actions
+        return self.batch_size if which == TD else 1
+
+    def write(self, which, array):
+        a = np.ascontiguousarray(array, dtype=np.float32).ravel()
+        _lib.call("dqnb_learner_write", self._h, which, a.ctypes.data, a.size, self.stream)
+
+    def read(self, which):
+        out = np.empty(self._len(which), dtype=np.float32)
+        _lib.call("dqnb_learner_read", self._h, which, out.ctypes.data, out.size, self.stream)
+        if which in (Q_TM1, Q_TARGET_T, Q_T):
+            return out.reshape(self.batch_size, self.num_actions)
+        return out
+
+    def set_params(self, params, which=ONLINE):
+        self.write(which, flatten_params(params))
+
+    def get_params(self, which=ONLINE):
+        return unflatten_params(self.read(which), self.num_actions, self.shared_bias)
+
+    def loss(self):
+        return float(self.read(LOSS)[0])
+
+    def update_host(self, s_tm1, a_tm1, r_t, discount_t, s_t):
+        """`update(transitions)` with NumPy inputs, like the reference's jit dispatch."""
+        s0 = np.ascontiguousarray(s_tm1, dtype=np.uint8)
+        s1 = np.ascontiguousarray(s_t, dtype=np.uint8)
+        a = np.ascontiguousarray(a_tm1, dtype=np.int32)
+        r = np.ascontiguousarray(r_t, dtype=np.float32)
+        d = np.ascontiguousarray(discount_t, dtype=np.float32)
+        want = (self.batch_size, 84, 84, 4)
+        if s0.shape != want or s1.shape != want or a.shape != (self.batch_size,):
+            raise ValueError("batch shapes %s %s %s do not match batch_size=%d"
+                             % (s0.shape, s1.shape, a.shape, self.batch_size))
+        _lib.call("dqnb_learner_update_host", self._h, s0.ctypes.data, a.ctypes.data, r.ctypes.data,
+                  d.ctypes.data, s1.ctypes.data, self.stream)
+
+    def update_device(self, s_tm1_ptr, a_ptr, r_ptr, d_ptr, s_t_ptr):
+        _lib.call("dqnb_learner_update", self._h, s_tm1_ptr, a_ptr, r_ptr, d_ptr, s_t_ptr, self.stream)
+
+    def update_from_replay(self, frame_store, slots):
+        slots = np.ascontiguousarray(slots, dtype=np.int64)
+        if slots.size != self.batch_size:
+            raise ValueError("need %d slots, got %d" % (self.batch_size, slots.size))
+        _lib.check(self._update_from_replay(self._h, frame_store.handle, slots.ctypes.data, self.stream))
+
+    def sync_target(self):
+        _lib.call("dqnb_learner_sync_target", self._h, self.stream)
+
+    def q_values(self, observations, which=ONLINE):
+        s = np.ascontiguousarray(observations, dtype=np.uint8)
+        if s.ndim == 3:
+            s = s[None]
+        q = np.empty((s.shape[0], self.num_actions), dtype=np.float32)
+        _lib.call("dqnb_learner_q_values", self._h, which, s.ctypes.data, s.shape[0], q.ctypes.data,
+                  self.stream)
+        return q
+
+    def launches_per_update(self):
+        n = ctypes.c_int64()
+        _lib.call("dqnb_learner_launches_per_update", self._h, ctypes.byref(n))
+        return n.value
+
+    def synchronize(self):
+        _lib.call("dqnb_stream_sync", self.stream)

@@ -82,6 +82,72 @@ int dqnb_replay_set_gather_splits(dqnb_replay* h, int splits);
  * [4] chained puts (s_tm1 matched the previous s_t), [5] pool growths, [6] bytes of HBM held */
 int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]);
 
+/* ------------------------------------------------------------------ learner
+ * Stands in for the jitted `update` closure of Dqn / DoubleDqn (dqn/agent.py:85-119,
+ * double_q/agent.py:85-121): Nature-CNN forward (networks.py:181-221,338-363) of the online
+ * net on s_tm1 and the target net on s_t (+ the online net on s_t for double-Q), the rlax
+ * q_learning / double_q_learning TD error with clip_gradient and l2_loss, reverse mode
+ * through the online net, optax.rmsprop(centered=True) + apply_updates
+ * (dqn/run_atari.py:208-213), and the target sync of dqn/agent.py:155-156.
+ * Parameters live in one flat fp32 arena in haiku leaf order:
+ * conv2_d{w[8,8,4,32],b} conv2_d_1{w[4,4,32,64],b} conv2_d_2{w[3,3,64,64],b}
+ * linear{w[3136,512],b} linear_1{w[512,A], b[A] or b[1] when shared_bias}. */
+#define DQNB_FP32 0   /* SIMT fp32 kernels; parity tolerance rel 1e-5 */
+#define DQNB_BF16 1   /* tcgen05 bf16 operands, fp32 accumulate; parity tolerance rel 1e-3 class */
+
+typedef struct dqnb_learner_config {
+  int32_t num_actions;
+  int32_t shared_bias;      /* 1: single shared output bias (networks.py:120-134) */
+  int32_t double_q;         /* 1: rlax.double_q_learning (double_q/agent.py:97-104) */
+  int32_t batch_size;
+  int32_t loss_mean_over;   /* rows the loss mean runs over; 0 = batch_size (DP ranks pass the global batch) */
+  int32_t precision;        /* DQNB_FP32 or DQNB_BF16 */
+  float learning_rate;      /* optax.rmsprop learning_rate */
+  float decay;              /* optax.rmsprop decay */
+  float eps;                /* optax.rmsprop eps (inside the rsqrt) */
+  float grad_error_bound;   /* rlax.clip_gradient bound */
+} dqnb_learner_config;
+
+/* state arrays addressable by read/write */
+#define DQNB_ONLINE 0
+#define DQNB_TARGET 1
+#define DQNB_MU 2
+#define DQNB_NU 3
+#define DQNB_GRAD 4       /* flat gradient of the last update */
+#define DQNB_Q_TM1 5      /* [batch, A] online q(s_tm1) of the last update */
+#define DQNB_Q_TARGET_T 6 /* [batch, A] target q(s_t) */
+#define DQNB_Q_T 7        /* [batch, A] online q(s_t) (double-Q only) */
+#define DQNB_TD 8         /* [batch] td errors */
+#define DQNB_LOSS 9       /* [1] mean loss */
+
+int dqnb_learner_create(const dqnb_learner_config* cfg, int device, dqnb_learner** out);
+int dqnb_learner_destroy(dqnb_learner* h);
+int dqnb_learner_num_params(dqnb_learner* h, int64_t* n);
+/* host <-> device copies of a state array (synchronous); n must equal the array length. */
+int dqnb_learner_write(dqnb_learner* h, int which, const float* host, int64_t n, uintptr_t stream);
+int dqnb_learner_read(dqnb_learner* h, int which, float* host, int64_t n, uintptr_t stream);
+/* one `update` on a batch that is already in device memory (asynchronous). */
+int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, const int32_t* a_dev,
+                        const float* r_dev, const float* disc_dev, const uint8_t* s_t_dev,
+                        uintptr_t stream);
+/* one `update` on host arrays, the way the reference calls its jitted update with NumPy
+ * transitions (dqn/agent.py:179-189): H2D copy through pinned staging, then the step. */
+int dqnb_learner_update_host(dqnb_learner* h, const uint8_t* s_tm1_host, const int32_t* a_host,
+                             const float* r_host, const float* disc_host, const uint8_t* s_t_host,
+                             uintptr_t stream);
+/* `_learn` (dqn/agent.py:179-189) with the sampled batch never leaving HBM: gather+stack the
+ * given replay slots straight into the learner's batch buffers, then the step. */
+int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* replay, const int64_t* slots_host,
+                                    uintptr_t stream);
+/* target_params = online_params (dqn/agent.py:155-156). */
+int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream);
+/* Q-values of n <= batch_size host observations under the online (0) or target (1) params;
+ * the forward half of select_action (dqn/agent.py:121-129).  Synchronous. */
+int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_host, int32_t n,
+                          float* q_host, uintptr_t stream);
+/* number of kernel launches (graph nodes) one update issues. */
+int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
+
 #ifdef __cplusplus
 }
 #endif

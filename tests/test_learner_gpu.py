@@ -1,0 +1,123 @@
+"""GPU parity of the learner step (through the C ABI) against the float64 NumPy oracle.
+fp32 mode tolerance: rel 1e-5 (north_star), measured as max|x - ref| / max|ref| per tensor."""
+import numpy as np
+import pytest
+
+from dqn_mgsc_zoo_b200 import learner as lrn
+from dqn_mgsc_zoo_b200 import replay as rp
+from dqn_mgsc_zoo_b200 import synthetic
+from oracle import learner_oracle as net
+from oracle import update_oracle as upd
+
+pytestmark = pytest.mark.gpu
+TOL = {"fp32": 1e-5}
+
+
+def rel(x, ref):
+    x, ref = np.asarray(x, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    return np.abs(x - ref).max() / (np.abs(ref).max() + 1e-30)
+
+
+def setup(seed, B, A, shared, double_q, precision="fp32"):
+    rng = np.random.default_rng(seed)
+    online = net.init_params(rng, A, shared)
+    target = net.init_params(rng, A, shared)
+    L = lrn.Learner(A, B, shared_bias=shared, double_q=double_q, precision=precision)
+    L.set_params(online, lrn.ONLINE)
+    L.set_params(target, lrn.TARGET)
+    return rng, online, target, L
+
+
+@pytest.mark.parametrize("B,A,shared,double_q", [(32, 6, False, False), (32, 18, True, True), (5, 4, False, True),
+                                                 (96, 6, False, False)])
+def test_single_update_matches_oracle(B, A, shared, double_q):
+    rng, online, target, L = setup(1, B, A, shared, double_q)
+    assert L.num_params == net.flatten(online).size
+    P = L.num_params
+    mu = (rng.normal(size=P) * 1e-3).astype(np.float32)
+    nu = (mu.astype(np.float64) ** 2 + rng.random(P) * 1e-4).astype(np.float32)
+    L.write(lrn.MU, mu)
+    L.write(lrn.NU, nu)
+    batch = synthetic.random_batch(rng, B, A)
+    batch[2][:3] = [30.0, -30.0, 0.5]          # force cotangent clipping on some rows
+    want = upd.update(online, target, mu.astype(np.float64), nu.astype(np.float64), batch, double_q)
+    L.update_host(*batch)
+    tol = TOL["fp32"]
+    assert rel(L.read(lrn.Q_TM1), want["q_tm1"]) < tol
+    assert rel(L.read(lrn.Q_TARGET_T), want["q_target_t"]) < tol
+    if double_q:
+        assert rel(L.read(lrn.Q_T), want["q_sel_t"]) < tol
+    assert rel(L.read(lrn.TD), want["td"]) < tol
+    assert abs(L.loss() - want["loss"]) < tol * max(1.0, abs(want["loss"]))
+    got_g = lrn.unflatten_params(L.read(lrn.GRAD), A, shared)
+    for k, g in want["grads"].items():
+        assert rel(got_g[k], g) < tol, k
+    got_p = L.get_params()
+    for k, p in want["params"].items():
+        assert rel(got_p[k], p) < tol, k
+        # the step itself (p_new - p_old), which is what 1e-5 on params would otherwise hide
+        # (allow for the fp32 rounding of p itself: one ulp of |p| relative to the step size)
+        step = p - online[k]
+        ulp = 2.0 ** -23 * np.abs(p).max() / (np.abs(step).max() + 1e-30)
+        assert rel(got_p[k].astype(np.float64) - online[k], step) < 20 * tol + 2 * ulp, k
+    assert rel(L.read(lrn.MU), want["mu"]) < tol
+    assert rel(L.read(lrn.NU), want["nu"]) < tol
+
+
+def test_chained_updates_track_oracle():
+    """60 chained updates with target syncs.  fp32 rounding is amplified by the optimiser
+    (rsqrt near eps) and by relu/argmax flips, so the yardstick is self-calibrating: the CUDA
+    path may drift from the float64 oracle no further than 3x what the *same oracle run in
+    float32* drifts (+1e-4), and must stay within 1e-4 over the first 10 steps."""
+    B, A, steps = 32, 6, 60
+    rng, online, target, L = setup(2, B, A, False, False)
+    P = L.num_params
+    o64 = dict(p=online, t=target, mu=np.zeros(P), nu=np.zeros(P))
+    o32 = dict(p={k: v.astype(np.float32) for k, v in online.items()},
+               t={k: v.astype(np.float32) for k, v in target.items()},
+               mu=np.zeros(P, np.float32), nu=np.zeros(P, np.float32))
+    h32 = upd.RmsProp(np.float32(upd.DQN_RMSPROP.lr), np.float32(upd.DQN_RMSPROP.decay),
+                      np.float32(upd.DQN_RMSPROP.eps))
+    for step in range(steps):
+        batch = synthetic.random_batch(rng, B, A)
+        for o, h in ((o64, upd.DQN_RMSPROP), (o32, h32)):
+            out = upd.update(o["p"], o["t"], o["mu"], o["nu"], batch, h=h)
+            o["p"], o["mu"], o["nu"] = out["params"], out["mu"], out["nu"]
+        L.update_host(*batch)
+        if step % 25 == 24:
+            for o in (o64, o32):
+                o["t"] = {k: v.copy() for k, v in o["p"].items()}
+            L.sync_target()
+        if step == 9:
+            got = L.get_params()
+            for k in online:
+                assert rel(got[k], o64["p"][k]) < 1e-4, (k, "10 steps")
+    got = L.get_params()
+    for k in online:
+        drift32 = rel(o32["p"][k], o64["p"][k])
+        assert rel(got[k], o64["p"][k]) < 3 * drift32 + 1e-4, (k, drift32)
+    assert rel(L.read(lrn.TARGET), net.flatten(o64["t"])) < 3 * rel(net.flatten(o32["t"]), net.flatten(o64["t"])) + 1e-4
+
+
+def test_update_from_replay_equals_update_host():
+    B, A = 32, 6
+    rng, online, target, L = setup(3, B, A, False, True)
+    _, _, _, L2 = setup(3, B, A, False, True)
+    rep = rp.TransitionReplay(500, rp.Transition(None, None, None, None, None), np.random.RandomState(0))
+    stream = synthetic.transition_stream(rng, A, rp.TransitionAccumulator(), max_len=60)
+    for _ in range(500):
+        rep.add(next(stream))
+    for _ in range(3):
+        slots = rep.sample_slots(B)
+        L.update_from_replay(rep.frame_store, slots)
+        s0, a, r, d, s1 = rep.frame_store.gather_host(slots)
+        L2.update_host(s0, a, r, d, s1)
+    assert np.array_equal(L.read(lrn.ONLINE), L2.read(lrn.ONLINE))   # deterministic kernels
+    assert np.isfinite(L.loss())
+
+
+def test_q_values_match_oracle():
+    rng, online, target, L = setup(4, 32, 6, False, False)
+    obs = rng.integers(0, 256, (7, 84, 84, 4), dtype=np.uint8)
+    assert rel(L.q_values(obs), net.forward(online, obs)) < 1e-5
+    assert rel(L.q_values(obs[0], lrn.TARGET), net.forward(target, obs[:1])) < 1e-5
