@@ -337,6 +337,14 @@ int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
     case DQNB_Q_T: DQNB_REQUIRE(h->nets == 3, "Q_T only exists for double-Q learners"); *p = h->q[2]; *n = BA; break;
     case DQNB_TD: *p = h->td; *n = h->B; break;
     case DQNB_LOSS: *p = h->loss; *n = 1; break;
+    // undocumented debug taps (activation gradients / activations of the online net)
+    case 100: *p = h->dh1; *n = (int64_t)h->B * kFc1Out; break;
+    case 101: *p = h->dy3; *n = (int64_t)h->B * Conv3::OUT_PER_IMG; break;
+    case 102: *p = h->dy2; *n = (int64_t)h->B * Conv2::OUT_PER_IMG; break;
+    case 103: *p = h->dy1; *n = (int64_t)h->B * Conv1::OUT_PER_IMG; break;
+    case 111: *p = h->a3[0]; *n = (int64_t)h->B * Conv3::OUT_PER_IMG; break;
+    case 112: *p = h->a2[0]; *n = (int64_t)h->B * Conv2::OUT_PER_IMG; break;
+    case 113: *p = h->a1[0]; *n = (int64_t)h->B * Conv1::OUT_PER_IMG; break;
     default: set_error("unknown state array %d", which); return DQNB_EINVAL;
   }
   return DQNB_OK;

@@ -148,6 +148,11 @@ int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_ho
 /* number of kernel launches (graph nodes) one update issues. */
 int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
 
+/* Test hook (not part of the drop-in surface): C[M,N] = A*B^T through the tcgen05 tile GEMM on
+ * fp32 device matrices (operands rounded to bf16); *_mn_major selects [K,M]/[K,N] storage. */
+int dqnb_selftest_tc_gemm(const float* a_dev, const float* b_dev, float* c_dev, int M, int N, int K,
+                          int a_mn_major, int b_mn_major, int bn, int splits, uintptr_t stream);
+
 #ifdef __cplusplus
 }
 #endif

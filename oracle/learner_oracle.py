@@ -141,6 +141,7 @@ def backward(params, cache, dq):
     g["fc2.w"] = h1.T @ dq
     g["fc2.b"] = dq.sum().reshape(1) if params["fc2.b"].shape == (1,) else dq.sum(0)
     dh1 = (dq @ params["fc2.w"].T) * (h1 > 0)
+    cache["dy.fc1"] = dh1
     g["fc1.w"] = h0.T @ dh1
     g["fc1.b"] = dh1.sum(0)
     dx = (dh1 @ params["fc1.w"].T).reshape(cache["conv3.out"].shape)
@@ -148,6 +149,7 @@ def backward(params, cache, dq):
                  "conv3": cache["conv2.out"].shape}
     for name, _, s, _, _ in reversed(LAYERS):
         dy = dx * (cache[name + ".out"] > 0)
+        cache["dy." + name] = dy          # kept for debugging / intermediate parity checks
         dw, db, dx = conv_bwd(dy, cache[name + ".cols"], shapes_in[name],
                               params[name + ".w"], s, need_dx=(name != "conv1"))
         g[name + ".w"], g[name + ".b"] = dw, db

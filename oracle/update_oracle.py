@@ -69,7 +69,7 @@ def loss_and_grads(online, target, batch, double_q=False, grad_bound=1.0 / 32, m
     td, loss, dq = td_and_dq(q_tm1, np.asarray(a), r, disc, q_tgt, q_sel, grad_bound, mean_over)
     grads = net.backward(online, cache, dq)
     return {"q_tm1": q_tm1, "q_target_t": q_tgt, "q_sel_t": q_sel, "td": td, "loss": loss,
-            "dq": dq, "grads": grads}
+            "dq": dq, "grads": grads, "cache": cache}
 
 
 def update(online, target, mu, nu, batch, double_q=False, grad_bound=1.0 / 32, h=DQN_RMSPROP):
