@@ -1,0 +1,177 @@
+"""Drop-in DQN / Double-DQN agents whose `_learn` runs on the B200 learner.
+
+Mirrors dqn/agent.py:40-229 (`Dqn`) and double_q/agent.py:40-233 (`DoubleDqn`): same
+constructor keywords, `step` / `reset` / `get_state` / `set_state`, `statistics`,
+`online_params`, `exploration_epsilon`, same learn / target-sync schedule (dqn/agent.py:149-156),
+same error on a repeat before any action.  What changes is below the seam:
+
+  * `network` is a `networks.NatureCnnSpec` and `optimizer` a `networks.RmsPropSpec` (the
+    haiku / optax objects of the reference cannot exist without those packages);
+  * `_learn` (dqn/agent.py:179-189) hands the sampled replay *slots* to
+    `dqnb_learner_update_from_replay`: gather+stack, forward x2/x3, TD, backward, RMSProp run
+    as device work with the batch never leaving HBM.  A replay that is not backed by the HBM
+    frame store still works: its host `sample()` batch goes through `dqnb_learner_update_host`;
+  * the target sync (`:155-156`) is a device copy;
+  * acting (`:121-131,169-177`) runs the batch-1 forward on the device and draws the
+    eps-greedy action from a NumPy Generator seeded from `rng_key` (same distribution as
+    distrax.EpsilonGreedy; not the same threefry stream).
+"""
+import collections
+from typing import Any, Callable, Mapping
+
+import numpy as np
+
+from dqn_mgsc_zoo_b200 import learner as lrn
+from dqn_mgsc_zoo_b200 import networks
+from dqn_mgsc_zoo_b200 import parts
+
+# optax.rmsprop(centered=True) state is (ScaleByRStdDevState(mu, nu), ScaleByScheduleState/EmptyState);
+# get_state() keeps that shape with haiku-shaped trees of NumPy arrays inside.
+ScaleByRStdDevState = collections.namedtuple("ScaleByRStdDevState", "mu nu")
+EmptyState = collections.namedtuple("EmptyState", "")
+
+
+class Dqn(parts.Agent):
+    """Deep Q-Network agent (dqn/agent.py:40)."""
+
+    _DOUBLE_Q = False
+
+    def __init__(
+        self,
+        preprocessor,
+        sample_network_input,
+        network: networks.NatureCnnSpec,
+        optimizer: networks.RmsPropSpec,
+        transition_accumulator: Any,
+        replay,
+        batch_size: int,
+        exploration_epsilon: Callable[[int], float],
+        min_replay_capacity_fraction: float,
+        learn_period: int,
+        target_network_update_period: int,
+        grad_error_bound: float,
+        rng_key,
+        device: int = 0,
+        precision: str = "fp32",
+    ):
+        if not optimizer.centered:
+            raise ValueError("the CUDA learner implements optax.rmsprop(centered=True) only "
+                             "(dqn/run_atari.py:208-213)")
+        if tuple(np.shape(sample_network_input)) != (84, 84, 4):
+            raise ValueError("the CUDA learner is built for 84x84x4 observations, got %s"
+                             % (np.shape(sample_network_input),))
+        self._preprocessor = preprocessor
+        self._replay = replay
+        self._transition_accumulator = transition_accumulator
+        self._batch_size = batch_size
+        self._exploration_epsilon = exploration_epsilon
+        self._min_replay_capacity = min_replay_capacity_fraction * replay.capacity
+        self._learn_period = learn_period
+        self._target_network_update_period = target_network_update_period
+        self._network = network
+
+        # jax.random.split(rng_key) -> (agent key, network init key) in the reference.
+        seeds = np.random.SeedSequence(networks.key_to_seed(rng_key)).spawn(2)
+        self._rng = np.random.default_rng(seeds[0])
+        self._learner = lrn.Learner(
+            network.num_actions, batch_size, shared_bias=network.shared_bias, double_q=self._DOUBLE_Q,
+            learning_rate=optimizer.learning_rate, decay=optimizer.decay, eps=optimizer.eps,
+            grad_error_bound=grad_error_bound, precision=precision, device=device)
+        init = networks.init_params(np.random.default_rng(seeds[1]), network.num_actions, network.shared_bias)
+        self._learner.set_params(init, lrn.ONLINE)
+        self._learner.sync_target()           # self._target_params = self._online_params
+
+        self._action = None
+        self._frame_t = -1
+        self._statistics = {'state_value': np.nan}
+
+    # ------------------------------------------------------------------ parts.Agent
+    def step(self, timestep) -> parts.Action:
+        """Selects action given timestep and potentially learns (dqn/agent.py:133-158)."""
+        self._frame_t += 1
+
+        timestep = self._preprocessor(timestep)
+
+        if timestep is None:  # Repeat action.
+            if self._action is None:
+                raise RuntimeError('Cannot repeat if action has never been selected.')
+            action = self._action
+        else:
+            action = self._action = self._act(timestep)
+            for transition in self._transition_accumulator.step(timestep, action):
+                self._replay.add(transition)
+
+        if self._replay.size < self._min_replay_capacity:
+            return action
+
+        if self._frame_t % self._learn_period == 0:
+            self._learn()
+
+        if self._frame_t % self._target_network_update_period == 0:
+            self._learner.sync_target()
+
+        return action
+
+    def reset(self) -> None:
+        self._transition_accumulator.reset()
+        parts.reset_processor(self._preprocessor)
+        self._action = None
+
+    def _act(self, timestep) -> parts.Action:
+        q_t = self._learner.q_values(timestep.observation)[0]
+        self._statistics['state_value'] = float(q_t.max())
+        return parts.Action(parts.epsilon_greedy(self._rng, q_t, self.exploration_epsilon))
+
+    def _learn(self) -> None:
+        store = getattr(self._replay, "frame_store", None)
+        if store is not None and hasattr(self._replay, "sample_slots"):
+            self._learner.update_from_replay(store, self._replay.sample_slots(self._batch_size))
+        else:
+            t = self._replay.sample(self._batch_size)
+            self._learner.update_host(t.s_tm1, t.a_tm1, t.r_t, t.discount_t, t.s_t)
+
+    @property
+    def online_params(self):
+        """Current Q-network parameters as a haiku-shaped tree of NumPy arrays (D2H copy)."""
+        return networks.to_haiku_tree(self._learner.get_params(lrn.ONLINE))
+
+    @property
+    def statistics(self) -> Mapping[str, float]:
+        return self._statistics
+
+    @property
+    def exploration_epsilon(self) -> float:
+        return self._exploration_epsilon(self._frame_t)
+
+    @property
+    def learner(self) -> lrn.Learner:
+        return self._learner
+
+    def get_state(self) -> Mapping[str, Any]:
+        """Same keys as dqn/agent.py:210-220; device arrays come back as NumPy."""
+        tree = lambda which: networks.to_haiku_tree(self._learner.get_params(which))
+        return {
+            'rng_key': self._rng.bit_generator.state,
+            'frame_t': self._frame_t,
+            'opt_state': (ScaleByRStdDevState(mu=tree(lrn.MU), nu=tree(lrn.NU)), EmptyState()),
+            'online_params': tree(lrn.ONLINE),
+            'target_params': tree(lrn.TARGET),
+            'replay': self._replay.get_state(),
+        }
+
+    def set_state(self, state: Mapping[str, Any]) -> None:
+        self._rng.bit_generator.state = state['rng_key']
+        self._frame_t = state['frame_t']
+        rms = state['opt_state'][0]
+        self._learner.set_params(networks.from_haiku_tree(rms.mu), lrn.MU)
+        self._learner.set_params(networks.from_haiku_tree(rms.nu), lrn.NU)
+        self._learner.set_params(networks.from_haiku_tree(state['online_params']), lrn.ONLINE)
+        self._learner.set_params(networks.from_haiku_tree(state['target_params']), lrn.TARGET)
+        self._replay.set_state(state['replay'])
+
+
+class DoubleDqn(Dqn):
+    """Double DQN (tuned) agent (double_q/agent.py:40): the online net on s_t picks the action,
+    the target net values it (rlax.double_q_learning, double_q/agent.py:85-111)."""
+
+    _DOUBLE_Q = True

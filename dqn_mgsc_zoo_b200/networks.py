@@ -25,6 +25,40 @@ class NatureCnnSpec(typing.NamedTuple):
     shared_bias: bool = False
 
 
+class RmsPropSpec(typing.NamedTuple):
+    """Stands in for optax.rmsprop(learning_rate, decay, eps, centered=True)
+    (dqn/run_atari.py:208-213); the update itself is the fused CUDA kernel."""
+    learning_rate: float = 0.00025
+    decay: float = 0.95
+    eps: float = 0.01 / 32 ** 2
+    centered: bool = True
+
+
+class AdamSpec(typing.NamedTuple):
+    """Stands in for optax.adam(learning_rate) (dqn_mgsc_batched/run_atari.py:241-243)."""
+    learning_rate: float = 0.00025
+    b1: float = 0.9
+    b2: float = 0.999
+    eps: float = 1e-8
+
+
+def rmsprop(learning_rate, decay=0.9, eps=1e-8, centered=False) -> RmsPropSpec:
+    """optax.rmsprop signature."""
+    return RmsPropSpec(learning_rate, decay, eps, centered)
+
+
+def adam(learning_rate, b1=0.9, b2=0.999, eps=1e-8) -> AdamSpec:
+    """optax.adam signature."""
+    return AdamSpec(learning_rate, b1, b2, eps)
+
+
+def key_to_seed(rng_key):
+    """A jax PRNGKey is a (2,) uint32 array; accept that, an int, or a SeedSequence-able list."""
+    if isinstance(rng_key, (int, np.integer)):
+        return int(rng_key)
+    return [int(x) for x in np.asarray(rng_key).ravel()]
+
+
 def dqn_atari_network(num_actions: int) -> NatureCnnSpec:
     """networks.py:352-363."""
     return NatureCnnSpec(num_actions, False)

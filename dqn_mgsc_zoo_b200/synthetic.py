@@ -83,3 +83,60 @@ def random_batch(rng, batch, num_actions, hw=FRAME_HW):
     r = rng.choice([-1.0, 0.0, 1.0], size=batch, p=[0.05, 0.90, 0.05]).astype(np.float32)
     d = np.where(rng.random(batch) < 0.02, 0.0, 0.99).astype(np.float32)
     return s_tm1, a, r, d, s_t
+
+
+class SyntheticEnvironment:
+    """dm_env-style environment emitting random 84x84 uint8 frames (stands in for
+    gym_atari.GymAtari, which stays on the host and outside the path): `reset()` -> FIRST
+    timestep, `step(action)` -> MID ... LAST after `episode_length(rng)` steps."""
+
+    def __init__(self, rng, num_actions=6, hw=FRAME_HW, min_len=5, max_len=60):
+        self._rng, self._num_actions, self._hw = rng, num_actions, hw
+        self._min_len, self._max_len = min_len, max_len
+        self._left = 0
+
+    def _frame(self):
+        return self._rng.integers(0, 256, size=self._hw, dtype=np.uint8)
+
+    def reset(self):
+        self._left = int(self._rng.integers(self._min_len, self._max_len + 1))
+        return TimeStep(0, None, None, self._frame())
+
+    def step(self, action):
+        if not 0 <= int(action) < self._num_actions:
+            raise ValueError("action %r out of range" % (action,))
+        self._left -= 1
+        last = self._left <= 0
+        reward = float(self._rng.choice([-1.0, 0.0, 1.0], p=[0.05, 0.90, 0.05]))
+        return TimeStep(2 if last else 1, reward, 0.0 if last else 1.0, self._frame())
+
+
+class StackingPreprocessor:
+    """Minimal stand-in for `processors.atari` (processors.py:421-508) on frames that are
+    already 84x84 grayscale: action repeat (returns None on skipped frames, summing rewards),
+    4-frame stack with TRAILING zero padding, discount x0.99.  Has `reset()` like the
+    reference processor so `processors.reset` / `parts.reset_processor` clears it."""
+
+    def __init__(self, num_action_repeats=1, additional_discount=0.99):
+        self._repeats, self._gamma = num_action_repeats, additional_discount
+        self.reset()
+
+    def reset(self):
+        self._window = collections.deque(maxlen=STACK)
+        self._count, self._reward, self._discount = 0, 0.0, 1.0
+
+    def __call__(self, timestep):
+        if timestep.first():
+            self.reset()
+            self._window.append(timestep.observation)
+            return TimeStep(0, None, None, stack_frames(self._window))
+        self._count += 1
+        self._reward += timestep.reward
+        self._discount *= timestep.discount
+        if self._count < self._repeats and not timestep.last():
+            return None
+        self._window.append(timestep.observation)
+        out = TimeStep(timestep.step_type, self._reward, self._discount * self._gamma,
+                       stack_frames(self._window))
+        self._count, self._reward, self._discount = 0, 0.0, 1.0
+        return out

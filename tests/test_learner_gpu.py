@@ -64,14 +64,38 @@ def test_single_update_matches_oracle(B, A, shared, double_q):
     assert rel(L.read(lrn.NU), want["nu"]) < tol
 
 
-def test_chained_updates_track_oracle():
-    """40 chained updates with a target sync.  Not a tight parity test: in fp32 a relu
-    pre-activation within ~1e-6 of zero can land on the other side of zero than in float64
-    (measured: about one unit in 550k every third step), which flips one mask bit, changes a
-    few gradient entries by O(1e-3) of the tensor max, and RMSProp's normalisation then
-    amplifies the difference step after step (scripts/debug_chain.py, scripts/debug_dy.py).
-    Single-step parity is pinned at 1e-5 above; here: tight over the first 5 steps, then the
-    loss trajectory and the parameters must stay close."""
+def test_chained_updates_teacher_forced():
+    """40 chained updates with a target sync, checked step by step: before every step the
+    oracle takes the device's own state (params, mu, nu), so each step is a one-step parity
+    check at the fp32 tolerance on the state the learner is really in."""
+    B, A, steps = 32, 6, 40
+    rng, online, target, L = setup(2, B, A, False, False)
+    for step in range(steps):
+        online = {k: v.astype(np.float64) for k, v in L.get_params().items()}
+        mu, nu = L.read(lrn.MU).astype(np.float64), L.read(lrn.NU).astype(np.float64)
+        batch = synthetic.random_batch(rng, B, A)
+        want = upd.update(online, target, mu, nu, batch)
+        L.update_host(*batch)
+        assert abs(L.loss() - want["loss"]) < 1e-5 * max(1.0, abs(want["loss"])), step
+        assert rel(L.read(lrn.GRAD), want["flat_grad"]) < 1e-5, step
+        assert rel(L.read(lrn.MU), want["mu"]) < 1e-5, step
+        assert rel(L.read(lrn.NU), want["nu"]) < 1e-5, step
+        # the parameter *step*: rsqrt(nu - mu^2 + eps) amplifies gradient error where nu ~ mu^2
+        d_got = L.read(lrn.ONLINE).astype(np.float64) - net.flatten(online)
+        d_want = net.flatten(want["params"]) - net.flatten(online)
+        assert rel(d_got, d_want) < 2e-3, step
+        if step == 24:
+            target = {k: v.copy() for k, v in want["params"].items()}
+            L.sync_target()
+            assert np.array_equal(L.read(lrn.TARGET), L.read(lrn.ONLINE))
+
+
+def test_chained_updates_free_running():
+    """The same 40 updates free-running against the float64 oracle.  Not a tight test: a relu
+    pre-activation within ~1e-6 of zero can land on the other side of zero in fp32 (about one
+    unit in 550k every third step, scripts/debug_chain.py), which flips a mask bit, and
+    RMSProp's normalisation amplifies that step after step.  Tight over the first 5 steps;
+    afterwards the loss trajectory and the parameters must stay close."""
     B, A, steps = 32, 6, 40
     rng, online, target, L = setup(2, B, A, False, False)
     P = L.num_params
@@ -91,8 +115,7 @@ def test_chained_updates_track_oracle():
                 assert rel(got[k], online[k]) < 1e-5, (k, "5 steps")
     got = L.get_params()
     for k in online:
-        assert rel(got[k], online[k]) < 1e-2, k
-    assert rel(L.read(lrn.TARGET), net.flatten(target)) < 1e-2
+        assert rel(got[k], online[k]) < 5e-2, k
 
 
 def test_update_from_replay_equals_update_host():
