@@ -342,6 +342,7 @@ int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
     case 101: *p = h->dy3; *n = (int64_t)h->B * Conv3::OUT_PER_IMG; break;
     case 102: *p = h->dy2; *n = (int64_t)h->B * Conv2::OUT_PER_IMG; break;
     case 103: *p = h->dy1; *n = (int64_t)h->B * Conv1::OUT_PER_IMG; break;
+    case 110: *p = h->h1[0]; *n = (int64_t)h->B * kFc1Out; break;
     case 111: *p = h->a3[0]; *n = (int64_t)h->B * Conv3::OUT_PER_IMG; break;
     case 112: *p = h->a2[0]; *n = (int64_t)h->B * Conv2::OUT_PER_IMG; break;
     case 113: *p = h->a1[0]; *n = (int64_t)h->B * Conv1::OUT_PER_IMG; break;

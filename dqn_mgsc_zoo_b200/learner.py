@@ -76,7 +76,7 @@ class Learner:
             return self.num_params
         if which in (Q_TM1, Q_TARGET_T, Q_T):
             return self.batch_size * self.num_actions
-        dbg = {100: 512, 101: 3136, 102: 5184, 103: 12800, 111: 3136, 112: 5184, 113: 12800}
+        dbg = {100: 512, 101: 3136, 102: 5184, 103: 12800, 110: 512, 111: 3136, 112: 5184, 113: 12800}
         if which in dbg:
             return self.batch_size * dbg[which]
         return self.batch_size if which == TD else 1

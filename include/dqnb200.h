@@ -153,6 +153,10 @@ int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
 int dqnb_selftest_tc_gemm(const float* a_dev, const float* b_dev, float* c_dev, int M, int N, int K,
                           int a_mn_major, int b_mn_major, int bn, int splits, uintptr_t stream);
 
+/* Same for the TF32 slab kernel (fp32 operands, tcgen05.mma.kind::tf32); M, N, K multiples of 4. */
+int dqnb_selftest_tf32_gemm(const float* a_dev, const float* b_dev, float* c_dev, int M, int N, int K,
+                            int a_mn_major, int b_mn_major, int bn, int splits, uintptr_t stream);
+
 #ifdef __cplusplus
 }
 #endif
