@@ -109,9 +109,43 @@ template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
+// Timeline stamps (diagnostics): every CTA folds its begin / end %globaltimer (ns) into the
+// launch's slot: tl[0] = min begin, tl[1] = max end, tl[2] = max begin (launch ramp),
+// tl[3] = longest single-CTA duration.  tl == nullptr: off.
+constexpr int kTlSlot = 4;
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned long long tl_begin(unsigned long long* tl) {
+  if (tl == nullptr || threadIdx.x != 0) return 0;
+  const unsigned long long now = global_ns();
+  atomicMin(tl, now);
+  atomicMax(tl + 2, now);
+  return now;
+}
+__device__ __forceinline__ void tl_end(unsigned long long* tl, unsigned long long began = 0) {
+  if (tl == nullptr || threadIdx.x != 0) return;
+  const unsigned long long now = global_ns();
+  atomicMax(tl + 1, now);
+  if (began) atomicMax(tl + 3, now - began);
+}
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 #endif
+
+// Round-to-nearest fp32 -> tf32 (10 explicit mantissa bits, low 13 bits cleared).  tcgen05's
+// kind::tf32 simply ignores the low bits (truncation, a bias toward zero that adds up layer by
+// layer), so every tensor that feeds a TF32 GEMM is rounded here by the kernel that produces it.
+__device__ __forceinline__ float tf32_rn(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 tf32_rn4(float4 v) {
+  return make_float4(tf32_rn(v.x), tf32_rn(v.y), tf32_rn(v.z), tf32_rn(v.w));
+}
 
 }  // namespace dqnb

@@ -24,6 +24,8 @@ constexpr int kBK = 16;
 struct SplitK {
   float* ws;          // [Z * tiles * splits][BM*BN]
   unsigned* counters; // [Z * tiles], zero before first use
+  long long* dbg = nullptr;   // optional: CTA (0,0,0) writes clock64() at its phase boundaries (gemm_tf32)
+  unsigned long long* tl = nullptr;   // optional timeline slot (common.cuh tl_begin / tl_end)
 };
 
 template <class P>
@@ -33,6 +35,7 @@ __global__ void __launch_bounds__(kGemmThreads) gemm_simt(P p, SplitK sk) {
   __shared__ __align__(16) float As[kBK][BM + 4];
   __shared__ __align__(16) float Bs[kBK][BN + 4];
   __shared__ bool is_last;
+  tl_begin(sk.tl);
 
   const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
   const int tiles_n = (p.N + BN - 1) / BN;
@@ -111,6 +114,7 @@ __global__ void __launch_bounds__(kGemmThreads) gemm_simt(P p, SplitK sk) {
         int m = m0 + ty * TM + i, n = n0 + tx * TN + j;
         if (m < p.M && n < p.N) p.store(z, m, n, acc[i][j]);
       }
+    tl_end(sk.tl);
     return;
   }
   // ---- deterministic split-K: partial -> workspace; last arriver reduces in split order
@@ -129,7 +133,10 @@ __global__ void __launch_bounds__(kGemmThreads) gemm_simt(P p, SplitK sk) {
     if (is_last) *c = 0;
   }
   __syncthreads();
-  if (!is_last) return;
+  if (!is_last) {
+    tl_end(sk.tl);
+    return;
+  }
   __threadfence();
   const float* base = sk.ws + (size_t)(z * tiles + tile) * splits * (BM * BN);
 #pragma unroll
@@ -142,6 +149,7 @@ __global__ void __launch_bounds__(kGemmThreads) gemm_simt(P p, SplitK sk) {
       int m = m0 + ty * TM + i, n = n0 + tx * TN + j;
       if (m < p.M && n < p.N) p.store(z, m, n, s);
     }
+  tl_end(sk.tl);
 }
 
 template <class P>

@@ -3,31 +3,35 @@
 // C[M,N] (+)= A[M,K] * B[N,K]^T with fp32 data fed to the 5th-gen tensor cores as TF32
 // (tcgen05.mma.kind::tf32, fp32 accumulators in TMEM).  One CTA computes one 128 x BN tile
 // over its split-K range of at most KB_MAX 32-float k-blocks.  Because that range is short,
-// there is no smem ring: warps 0-3 issue *all* operand copies of the CTA up front (16-byte
-// cp.async straight into the 128-byte-swizzled canonical UMMA layouts; uint8 sources are
-// converted in registers), one commit group per k-block; each thread then retires its groups in
-// order, proxy-fences and arrives on that k-block's mbarrier.  Warp 4's elected lane waits
+// there is no smem ring: warps 0-7 issue *all* operand copies of the CTA up front (16-byte
+// cp.async straight into the 128-byte-swizzled canonical UMMA layouts; uint8 sources go
+// through registers), one commit group per k-block; each thread then retires its groups in
+// order, proxy-fences and arrives on that k-block's mbarrier.  Warp 8's elected lane waits
 // per k-block and issues the MMAs, so tensor work overlaps the tail of the loads; a final
-// tcgen05.commit releases the epilogue, where thread t owns accumulator row t (TMEM lane t).
+// tcgen05.commit releases the epilogue, where thread t < 128 owns accumulator row t (TMEM lane t).
 // Every barrier is used exactly once (parity 0): no phase bookkeeping.
 //
 // A problem type P provides
-//   static constexpr int BN, KB_MAX;
+//   static constexpr int BN, KB_MAX;                BN in {32, 64, 128}
 //   static constexpr bool A_MN_MAJOR, B_MN_MAJOR;   operand source contiguous along M/N instead of K
 //   static constexpr bool DEFER_REDUCE;             split-K partials are left for a later kernel
 //   int M, N, K;
-//   void a_chunk(int z, int i, int j, uint32_t dst) const;   K-major: A[m=i, k=j..j+3] -> 16 B at dst
-//                                                            MN-major: A[m=i..i+3, k=j]     (zero-fill OOB)
-//   void b_chunk(int z, int i, int j, uint32_t dst) const;   same for B[n, k]
-//   void store_row(int z, int m, int n0, const float (&v)[16], int valid_n) const;
-//   void store_partial(int z, int split, int m, int n0, const float (&v)[16], int valid_n) const;  (DEFER_REDUCE)
-// grid = (tiles_m * tiles_n, splits, Z), block = 160 threads.
+//   ARow a_row(int z, int i) const;   decoded context of row i (K-major) / rows i..i+3 (MN-major)
+//   ACol a_col(int z, int j) const;   decoded context of k = j..j+3 (K-major) / k = j (MN-major)
+//   void a_put(const ARow&, const ACol&, uint32_t dst) const;   the 16-byte chunk -> smem (zero-fill OOB)
+//   BRow b_row / BCol b_col / b_put: same for B[n, k]
+//   void store4(int z, int split, int m, int n, float4 v) const;   C[m, n..n+3]: the finished sum, or this
+//                                                                   split's partial when DEFER_REDUCE
+// grid = (tiles_m * tiles_n, splits, Z), block = 288 threads.
 #pragma once
+#include <type_traits>
+
 #include "gemm_simt.cuh"
 
 namespace dqnb {
 
-constexpr int kT32Threads = 160;   // 4 producer/epilogue warps + 1 MMA-issue warp
+constexpr int kT32Producers = 256; // warps 0-7 stage operands; warps 0-3 also run the epilogue
+constexpr int kT32Threads = 288;   // + warp 8, whose elected lane issues the MMAs
 constexpr int kT32BM = 128;
 constexpr int kT32BK = 32;         // fp32 per k-block = one 128-byte swizzle row
 
@@ -100,6 +104,32 @@ __device__ __forceinline__ void t32_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// ---- thread-block cluster primitives (split-K partials are reduced through distributed smem)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_map(uint32_t local_smem_addr, uint32_t cta_rank) {
+  uint32_t remote;
+  asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_smem_addr), "r"(cta_rank));
+  return remote;
+}
+// volatile (ordered after the barrier asm) but no memory clobber: the data is stable between the
+// two cluster barriers, so the compiler may still batch the epilogue's global loads around it.
+__device__ __forceinline__ float4 ld_cluster_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+// this CTA's own shared::cta address as a shared::cluster address
+__device__ __forceinline__ uint32_t local_as_cluster(uint32_t local_smem_addr) {
+  uint32_t rank;
+  asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  uint32_t remote;
+  asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_smem_addr), "r"(rank));
+  return remote;
+}
+constexpr int kT32MaxCluster = 8;   // portable cluster size limit = most split-K CTAs per tile
+
 __host__ __device__ constexpr int t32_tmem_cols(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : 256; }
 __host__ __device__ constexpr int t32_tile_bytes(int rows, bool mn_major) {
   // K-major: [rows][128 B].  MN-major: [ceil(rows/32) mn-blocks][8 k-groups][4 k][128 B]
@@ -110,28 +140,42 @@ __host__ __device__ constexpr int t32_smem_bytes() {
   return P::KB_MAX * (t32_tile_bytes(kT32BM, P::A_MN_MAJOR) + t32_tile_bytes(P::BN, P::B_MN_MAJOR)) + 1024;
 }
 
-// Stage one [ROWS x 32] operand k-block.  K-major: chunk id -> (row = id/8, c = id%8);
-// MN-major: (k = id / CH, mn-chunk = id % CH).  Consecutive threads take consecutive chunks
-// of the contiguous source dimension.
-template <int ROWS, bool MN_MAJOR, class F>
-__device__ __forceinline__ void t32_stage(uint32_t tile, int r0, int k0, F&& chunk) {
-  if (!MN_MAJOR) {
-#pragma unroll 4
-    for (int id = threadIdx.x; id < ROWS * 8; id += 128) {
-      int row = id >> 3, c = id & 7;
-      chunk(r0 + row, k0 + c * 4, tile + (row >> 3) * 1024 + (row & 7) * 128 + ((c ^ (row & 7)) << 4));
-    }
-  } else {
-    constexpr int CH = ((ROWS + 31) / 32) * 8;   // 16-byte mn-chunks per k row
-#pragma unroll 4
-    for (int id = threadIdx.x; id < kT32BK * CH; id += 128) {
-      int k = id / CH, cc = id - k * CH;
+// Which 16-byte chunks of a [ROWS x 32] operand k-block producer thread t stages.
+//   K-major : the 16-byte column c = t%8 of rows t/8 + 32u           (u < ROWS/32)
+//   MN-major: the mn-chunk cc = t % CH of k rows t/CH + (256/CH) u   (CH = ROWS/4, u < CH/8)
+// so a thread meets only NROW distinct rows and NCOL distinct k positions per k-block: the
+// problem's index decoding (a_row / a_col) is done once per context, not once per chunk, and
+// consecutive threads read consecutive chunks of the contiguous source dimension.
+template <int ROWS, bool MN_MAJOR>
+struct T32Map {
+  static_assert(ROWS % 32 == 0 && ROWS <= 128, "operand tile rows must be 32, 64, 96 or 128");
+  static constexpr int CH = ROWS / 4;
+  static constexpr int NROW = MN_MAJOR ? 1 : ROWS / 32;
+  static constexpr int NCOL = MN_MAJOR ? CH / 8 : 1;
+  static_assert(!MN_MAJOR || (kT32Producers % CH == 0 && CH % 8 == 0), "MN-major tile rows must be 32, 64 or 128");
+  __device__ static __forceinline__ int row_index(int t, int u) { return MN_MAJOR ? 4 * (t % CH) : (t >> 3) + 32 * u; }
+  __device__ static __forceinline__ int col_index(int t, int u) {
+    return MN_MAJOR ? t / CH + (kT32Producers / CH) * u : 4 * (t & 7);
+  }
+  __device__ static __forceinline__ uint32_t offset(int t, int ur, int uc) {
+    if (!MN_MAJOR) {
+      int row = (t >> 3) + 32 * ur, c = t & 7;
+      return (row >> 3) * 1024 + (row & 7) * 128 + ((c ^ (row & 7)) << 4);
+    } else {
       // SWIZZLE_128B_BASE32B atom = 4 k-rows x 128 B, 32-byte units XOR-ed with the k-row
-      int j = cc >> 3, c32 = (cc >> 1) & 3, h = cc & 1, g = k >> 2, kr = k & 3;
-      chunk(r0 + cc * 4, k0 + k, tile + j * 4096 + g * 512 + kr * 128 + ((c32 ^ kr) << 5) + (h << 4));
+      int cc = t % CH, kk = t / CH + (kT32Producers / CH) * uc;
+      int j = cc >> 3, c32 = (cc >> 1) & 3, h = cc & 1, g = kk >> 2, kr = kk & 3;
+      return j * 4096 + g * 512 + kr * 128 + ((c32 ^ kr) << 5) + (h << 4);
     }
   }
-}
+};
+
+// Optional members of a problem type, detected here:
+//   static constexpr bool A_REG = true;  uint32_t a_get(row, col) const;  void a_store(dst, word) const;
+// A operand chunks come through registers (4 packed uint8 -> 4 floats).  All loads of the CTA's
+// K range are issued before the first use so they share one memory round trip.
+template <class P, class = void> struct t32_a_reg : std::false_type {};
+template <class P> struct t32_a_reg<P, std::enable_if_t<P::A_REG>> : std::true_type {};
 
 // Retire this thread's commit groups oldest-first: when group I has landed, make it visible to
 // the tensor core (async proxy) and arrive on k-block I's barrier.
@@ -155,9 +199,11 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   __shared__ uint64_t full_bar[KB];
   __shared__ uint64_t done_bar;
   __shared__ uint32_t tmem_slot;
-  __shared__ bool is_last;
 
   const int t = threadIdx.x, warp = t >> 5;
+  const unsigned long long tl_t0 = tl_begin(sk.tl);
+  const bool dbg = sk.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  if (dbg && t == 0) sk.dbg[0] = clock64();
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int tiles_n = (p.N + BN - 1) / BN;
   const int tile = blockIdx.x, tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
@@ -169,31 +215,84 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   const int nkb = max(kb_end - kb_beg, 0);
 
   if (t == 0) {
-    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], 128);
+    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], kT32Producers);
     mbar_init(&done_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 4) t32_alloc<COLS>(&tmem_slot);
+  if (warp == 8) t32_alloc<COLS>(&tmem_slot);
   t32_fence_before();
   __syncthreads();
   t32_fence_after();
   const uint32_t tmem = tmem_slot;
+  if (dbg && t == 0) sk.dbg[1] = clock64();     // setup done
 
-  if (warp < 4) {
+  if (warp < 8) {
     // ---- producers: everything in flight at once, one commit group per k-block
-#pragma unroll 1
-    for (int i = 0; i < nkb; ++i) {
+    using MA = T32Map<kT32BM, P::A_MN_MAJOR>;
+    using MB = T32Map<BN, P::B_MN_MAJOR>;
+    typename P::ARow arow[MA::NROW];
+    typename P::BRow brow[MB::NROW];
+#pragma unroll
+    for (int u = 0; u < MA::NROW; ++u) arow[u] = p.a_row(z, m0 + MA::row_index(t, u));
+#pragma unroll
+    for (int u = 0; u < MB::NROW; ++u) brow[u] = p.b_row(z, n0 + MB::row_index(t, u));
+    auto stage_b = [&](int i) {
       const int k0 = (kb_beg + i) * kT32BK;
-      t32_stage<kT32BM, P::A_MN_MAJOR>(smem + i * A_TILE, m0, k0,
-                                       [&](int r, int k, uint32_t dst) { p.a_chunk(z, r, k, dst); });
-      t32_stage<BN, P::B_MN_MAJOR>(smem + KB * A_TILE + i * B_TILE, n0, k0,
-                                   [&](int r, int k, uint32_t dst) { p.b_chunk(z, r, k, dst); });
-      cp_commit();
+      const uint32_t tile = smem + KB * A_TILE + i * B_TILE;
+#pragma unroll
+      for (int uc = 0; uc < MB::NCOL; ++uc) {
+        typename P::BCol col = p.b_col(z, k0 + MB::col_index(t, uc));
+#pragma unroll
+        for (int ur = 0; ur < MB::NROW; ++ur) p.b_put(brow[ur], col, tile + MB::offset(t, ur, uc));
+      }
+    };
+    if constexpr (t32_a_reg<P>::value) {
+      constexpr int NW = MA::NROW * MA::NCOL;
+      uint32_t word[KB * NW];
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+#pragma unroll
+        for (int uc = 0; uc < MA::NCOL; ++uc) {
+          typename P::ACol col = p.a_col(z, (kb_beg + i) * kT32BK + MA::col_index(t, uc));
+#pragma unroll
+          for (int ur = 0; ur < MA::NROW; ++ur)
+            word[(i * MA::NCOL + uc) * MA::NROW + ur] = i < nkb ? p.a_get(arow[ur], col) : 0u;
+        }
+      }
+#pragma unroll 1
+      for (int i = 0; i < nkb; ++i) {
+        stage_b(i);
+        cp_commit();
+      }
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+#pragma unroll
+        for (int uc = 0; uc < MA::NCOL; ++uc)
+#pragma unroll
+          for (int ur = 0; ur < MA::NROW; ++ur)
+            if (i < nkb) p.a_store(smem + i * A_TILE + MA::offset(t, ur, uc), word[(i * MA::NCOL + uc) * MA::NROW + ur]);
+      }
+    } else {
+#pragma unroll 1
+      for (int i = 0; i < nkb; ++i) {
+        const int k0 = (kb_beg + i) * kT32BK;
+        const uint32_t tile = smem + i * A_TILE;
+#pragma unroll
+        for (int uc = 0; uc < MA::NCOL; ++uc) {
+          typename P::ACol col = p.a_col(z, k0 + MA::col_index(t, uc));
+#pragma unroll
+          for (int ur = 0; ur < MA::NROW; ++ur) p.a_put(arow[ur], col, tile + MA::offset(t, ur, uc));
+        }
+        stage_b(i);
+        cp_commit();
+      }
     }
 #pragma unroll 1
     for (int i = nkb; i < KB; ++i) cp_commit();     // empty groups keep the wait counts static
+    if (dbg && t == 0) sk.dbg[2] = clock64();     // all copies issued
     t32_retire_groups<KB>(nkb, full_bar);
-  } else if (t == 128) {
+    if (dbg && t == 0) sk.dbg[3] = clock64();     // this thread's copies landed
+  } else if (t == kT32Producers) {
     // ---- MMA issuer
     const uint32_t idesc = t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     for (int i = 0; i < nkb; ++i) {
@@ -210,16 +309,14 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
     t32_commit(&done_bar);
   }
 
+  // ---- epilogue, part 1: accumulators TMEM -> registers -> this CTA's smem tile [128][BN+4]
+  // (the operand slab is dead once the MMAs are done).  Thread t < 128 owns row t (TMEM lane t).
+  constexpr int PSTRIDE = BN + 4;   // floats; +4 keeps the float4 row writes off one bank
   if (warp < 4) {
-    // ---- epilogue: thread = one output row (TMEM lane); 16 columns at a time
     if (nkb > 0) mbar_wait(&done_bar, 0);
     t32_fence_after();
-    const int m = m0 + t;
+    if (dbg && t == 0) sk.dbg[4] = clock64();     // MMAs complete
     const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-    const bool direct = splits == 1;
-    float* mine = nullptr;
-    if (!direct && !P::DEFER_REDUCE)
-      mine = sk.ws + ((size_t)(z * gridDim.x + tile) * splits + split) * (kT32BM * BN);
 #pragma unroll 1
     for (int c = 0; c < BN; c += 16) {
       float v[16];
@@ -228,58 +325,64 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = 0.f;
       }
-      const int valid = min(16, p.N - (n0 + c));
-      if (P::DEFER_REDUCE) {
-        if (m < p.M && valid > 0) p.store_partial(z, split, m, n0 + c, v, valid);
-      } else if (direct) {
-        if (m < p.M && valid > 0) p.store_row(z, m, n0 + c, v, valid);
-      } else {
-        // column-major partial tile: consecutive threads (rows) -> consecutive addresses
 #pragma unroll
-        for (int i = 0; i < 16; ++i) mine[(size_t)(c + i) * kT32BM + t] = v[i];
-      }
+      for (int i = 0; i < 16; i += 4) st16(smem + (t * PSTRIDE + c + i) * 4, v[i], v[i + 1], v[i + 2], v[i + 3]);
     }
   }
-  if (!P::DEFER_REDUCE && splits > 1) {
-    // ---- deterministic split-K fix-up: last CTA of the tile adds the partials in split order
-    __threadfence();
-    __syncthreads();
-    if (t == 0) {
-      unsigned* cnt = sk.counters + z * gridDim.x + tile;
-      unsigned old = atomicAdd(cnt, 1u);
-      is_last = (old == (unsigned)splits - 1);
-      if (is_last) *cnt = 0;
-    }
-    __syncthreads();
-    if (is_last && warp < 4) {
-      __threadfence();
-      const int m = m0 + t;
-      const float* base = sk.ws + (size_t)(z * gridDim.x + tile) * splits * (kT32BM * BN);
-#pragma unroll 1
-      for (int c = 0; c < BN; c += 16) {
-        float v[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = 0.f;
-        for (int q = 0; q < splits; ++q)
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] += __ldcg(base + (size_t)q * (kT32BM * BN) + (size_t)(c + i) * kT32BM + t);
-        const int valid = min(16, p.N - (n0 + c));
-        if (m < p.M && valid > 0) p.store_row(z, m, n0 + c, v, valid);
+  if (dbg && t == 0) sk.dbg[5] = clock64();       // tile parked in smem
+  // ---- part 2: split-K CTAs of a tile form a cluster along grid.y (unless the problem defers the
+  // reduction): CTA `split` sums rows [split*R, (split+1)*R) of all partial tiles, in split order,
+  // through distributed shared memory.  Either way the tile leaves as coalesced float4 items
+  // handed to p.store4 (bias / relu / mask / partial-buffer placement live there).
+  const bool clustered = !P::DEFER_REDUCE && splits > 1;
+  if (clustered) cluster_sync_all(); else __syncthreads();
+  if (dbg && t == 0) sk.dbg[7] = clock64();
+  if (warp < 8) {
+    constexpr int G4 = BN / 4;
+    const int nsum = clustered ? splits : 1;
+    const int R = clustered ? (kT32BM + splits - 1) / splits : kT32BM;
+    const int row_beg = clustered ? split * R : 0;
+    const int row_end = min(min(kT32BM, row_beg + R), p.M - m0);
+#pragma unroll 2
+    for (int item = t; item < (row_end - row_beg) * G4; item += kT32Producers) {
+      const int r = row_beg + item / G4, c4 = item % G4;
+      const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < nsum; ++q) {
+        const float4 x = ld_cluster_f4(clustered ? cluster_map(local, (uint32_t)q) : local_as_cluster(local));
+        v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
       }
+      if (n0 + c4 * 4 < p.N) p.store4(z, split, m0 + r, n0 + c4 * 4, v);
     }
   }
+  if (dbg && t == 0) sk.dbg[6] = clock64();       // my rows reduced and stored
+  if (clustered) cluster_sync_all();   // nobody leaves (and frees its smem) while a peer may still read it
+
   t32_fence_before();
   __syncthreads();
-  if (warp == 4) t32_dealloc<COLS>(tmem);
+  if (warp == 8) t32_dealloc<COLS>(tmem);
+  tl_end(sk.tl, tl_t0);
 }
 
+// Split-K factor: at least what makes the K range fit the slab; more (down to 4 k-blocks per
+// CTA) when the tile count alone would leave most of the 148 SMs idle.
 template <class P>
-inline int t32_splits_for(const P& p) {   // fewest splits that fit the slab
+inline int t32_splits_for(const P& p, int Z, int want_ctas = 120) {
   int kblocks = (p.K + kT32BK - 1) / kT32BK;
-  return (kblocks + P::KB_MAX - 1) / P::KB_MAX;
+  int min_s = (kblocks + P::KB_MAX - 1) / P::KB_MAX;
+  int tiles = ((p.M + kT32BM - 1) / kT32BM) * ((p.N + P::BN - 1) / P::BN) * Z;
+  int s = want_ctas / (tiles > 0 ? tiles : 1);
+  int cap = kblocks / 4 > min_s ? kblocks / 4 : min_s;
+  s = s < min_s ? min_s : (s > cap ? cap : s);
+  if (!P::DEFER_REDUCE && s > kT32MaxCluster) s = kT32MaxCluster;   // min_s > 8 is rejected at launch
+  if (tiles * s > kNumSMs && kNumSMs / tiles >= min_s) s = kNumSMs / tiles;   // one CTA per SM: stay in one wave
+  int per = (kblocks + s - 1) / s;
+  return (kblocks + per - 1) / per;
 }
 template <class P>
-inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cudaStream_t st) {
+// `priority`: CUDA launch priority (lower = scheduled first); kernels of the dependent chain get
+// the device's greatest priority so that side-branch kernels do not take their SMs.
+inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cudaStream_t st, int priority = 0) {
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tf32<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, t32_smem_bytes<P>());
@@ -290,21 +393,36 @@ inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cu
     configured = true;
   }
   static_assert(t32_smem_bytes<P>() <= 227 * 1024, "slab does not fit in shared memory: lower KB_MAX or BN");
+  static_assert(kT32BM * (P::BN + 4) * 4 <= t32_smem_bytes<P>() - 1024,
+                "the accumulator tile must fit in the (dead) operand slab");
   int kblocks = (p.K + kT32BK - 1) / kT32BK;
   if ((kblocks + splits - 1) / splits > P::KB_MAX) return cudaErrorInvalidValue;
+  const bool clustered = !P::DEFER_REDUCE && splits > 1;
+  if (clustered && splits > kT32MaxCluster) return cudaErrorInvalidValue;
   int tiles = ((p.M + kT32BM - 1) / kT32BM) * ((p.N + P::BN - 1) / P::BN);
-  dim3 grid(tiles, splits, Z);
-  gemm_tf32<P><<<grid, kT32Threads, t32_smem_bytes<P>(), st>>>(p, sk);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(tiles, splits, Z);
+  cfg.blockDim = dim3(kT32Threads);
+  cfg.dynamicSmemBytes = t32_smem_bytes<P>();
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  unsigned na = 0;
+  attr[na].id = cudaLaunchAttributePriority;
+  attr[na++].val.priority = priority;
+  if (clustered) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 1; attr[na].val.clusterDim.y = splits; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, gemm_tf32<P>, p, sk);
 }
 template <class P>
 inline size_t gemm_tf32_tiles(const P& p, int Z) {
   return (size_t)((p.M + kT32BM - 1) / kT32BM) * ((p.N + P::BN - 1) / P::BN) * Z;
 }
 template <class P>
-inline size_t gemm_tf32_ws_floats(const P& p, int Z, int splits) {
-  if (splits <= 1 || P::DEFER_REDUCE) return 0;
-  return gemm_tf32_tiles(p, Z) * splits * kT32BM * P::BN;
-}
+inline size_t gemm_tf32_ws_floats(const P&, int, int) { return 0; }   // partials never touch global memory
 
 }  // namespace dqnb

@@ -11,6 +11,12 @@ struct HeadArgs {
   float grad_bound;        // rlax.clip_gradient bound (dqn/agent.py:101-103)
   float inv_mean;          // 1 / (number of rows the loss mean runs over)
   const float* h1[kMaxNets];   // [batch,512] relu(fc1): online(s_tm1), target(s_t), online(s_t)
+  // TF32 mode: fc1 leaves split-K partials [net][split][batch][512]; the head sums them in split
+  // order, adds the bias, applies the relu and writes h1 (fc1_part == nullptr: h1 is read as is)
+  const float* fc1_part;
+  int fc1_splits;
+  const float* b1[kMaxNets];   // fc1 bias
+  float* h1_out[kMaxNets];
   const float* w2[kMaxNets];   // [512,A]
   const float* b2[kMaxNets];   // [A] or [1]
   const int32_t* action;
@@ -22,6 +28,8 @@ struct HeadArgs {
   float* row_loss;          // [batch] 0.5*td^2
   float* dq_taken;          // [batch] d loss / d q_tm1[b, a_b]
   float* dh1;               // [batch,512] gradient wrt fc1 pre-activation (relu-masked)
+  unsigned long long* tl;   // optional timeline slot
+  int round_tf32;           // dh1 feeds TF32 GEMMs: round it to nearest here
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -42,43 +50,109 @@ __device__ __forceinline__ void warp_argmax(float v, int lane, float& best, int&
   }
 }
 
-// One warp per batch row: fc2 forward for every net, q_learning / double_q_learning target
-// (rlax), td, clipped cotangent, per-row loss, and the fc2 input gradient dh1.
-__global__ void __launch_bounds__(128) head_td_kernel(HeadArgs g) {
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= g.batch) return;
+// One CTA (4 warps) per batch row.  (1) h1 of every net into smem (finishing fc1 when it was
+// left as split-K partials), (2) fc2: the (net, action) dot products are dealt round-robin to
+// the warps, (3) warp 0 forms the q_learning / double_q_learning target (rlax), the td error,
+// the clipped cotangent and the per-row loss, (4) all threads write the fc2 input gradient dh1.
+constexpr int kHeadThreads = 128;
+__global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
+  __shared__ __align__(16) float h_s[1][kFc1Out];
+  __shared__ float q_s[kMaxNets][kMaxActions];
+  __shared__ float dq_s;
+  __shared__ int act_s;
+  const unsigned long long tl_t0 = tl_begin(g.tl);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int row = blockIdx.x;
   const int A = g.num_actions, nets = g.double_q ? 3 : 2;
-  float qv[kMaxNets];   // lane a keeps q_z[row, a]
-  for (int z = 0; z < nets; ++z) {
-    const float* h = g.h1[z] + (size_t)row * kFc1Out;
-    float mine = -INFINITY;
-    for (int a = 0; a < A; ++a) {
-      float s = 0.f;
-      for (int k = lane; k < kFc1Out; k += 32) s = fmaf(h[k], g.w2[z][(size_t)k * A + a], s);
-      s = warp_sum(s) + g.b2[z][g.shared_bias ? 0 : a];
-      if (lane == a) mine = s;
+  static_assert(kFc1Out == 4 * kHeadThreads, "one float4 of h1 per thread");
+  __shared__ float red_s[kHeadThreads / 32][kMaxNets][kMaxActions];
+  // (1) h1: thread t owns columns 4t..4t+3 of every net
+  float4 hv[kMaxNets];
+  if (g.fc1_part != nullptr) {
+    float4 acc[kMaxNets];
+#pragma unroll
+    for (int z = 0; z < kMaxNets; ++z) acc[z] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const size_t split_stride = (size_t)g.batch * (kFc1Out / 4);
+    const float4* src = reinterpret_cast<const float4*>(g.fc1_part + (size_t)row * kFc1Out) + t;
+#pragma unroll 4
+    for (int q = 0; q < g.fc1_splits; ++q) {
+#pragma unroll
+      for (int z = 0; z < kMaxNets; ++z) {
+        if (z < nets) {
+          const float4 x = __ldcg(src + ((size_t)z * g.fc1_splits + q) * split_stride);
+          acc[z].x += x.x; acc[z].y += x.y; acc[z].z += x.z; acc[z].w += x.w;
+        }
+      }
     }
-    qv[z] = mine;
-    if (lane < A) g.q[z][(size_t)row * A + lane] = mine;
+#pragma unroll
+    for (int z = 0; z < kMaxNets; ++z) {
+      if (z < nets) {
+        const float4 bias = __ldg(reinterpret_cast<const float4*>(g.b1[z]) + t);
+        hv[z] = make_float4(fmaxf(acc[z].x + bias.x, 0.f), fmaxf(acc[z].y + bias.y, 0.f),
+                            fmaxf(acc[z].z + bias.z, 0.f), fmaxf(acc[z].w + bias.w, 0.f));
+        reinterpret_cast<float4*>(g.h1_out[z] + (size_t)row * kFc1Out)[t] = hv[z];
+      }
+    }
+  } else {
+#pragma unroll
+    for (int z = 0; z < kMaxNets; ++z)
+      if (z < nets) hv[z] = reinterpret_cast<const float4*>(g.h1[z] + (size_t)row * kFc1Out)[t];
   }
-  float best; int sel;
-  warp_argmax(qv[g.double_q ? 2 : 1], lane, best, sel);          // selector net
-  const float q_next = __shfl_sync(0xffffffffu, qv[1], sel);      // value from the target net
-  const int act = g.action[row];
-  const float q_taken = __shfl_sync(0xffffffffu, qv[0], act);
-  const float td = g.reward[row] + g.discount[row] * q_next - q_taken;
-  float cot = fminf(fmaxf(td * g.inv_mean, -g.grad_bound), g.grad_bound);
-  if (g.row_weight) cot *= g.row_weight[row];
-  const float dq = -cot;
-  if (lane == 0) {
-    g.td[row] = td;
-    g.row_loss[row] = 0.5f * td * td;
-    g.dq_taken[row] = dq;
+  if (t < kMaxNets * kMaxActions) (&q_s[0][0])[t] = -INFINITY;
+  // (2) fc2: q[z][a] = sum_k h1[z][k] w2[z][k][a].  Thread t covers k = 4t..4t+3, whose weights
+  // are 4A consecutive floats (coalesced across the CTA); warp shuffle, then 4 warp partials.
+#pragma unroll 2
+  for (int a = 0; a < A; ++a) {
+#pragma unroll
+    for (int z = 0; z < kMaxNets; ++z) {
+      if (z < nets) {
+        const float* w2 = g.w2[z] + (size_t)(4 * t) * A + a;
+        float s = hv[z].x * __ldg(w2);
+        s = fmaf(hv[z].y, __ldg(w2 + A), s);
+        s = fmaf(hv[z].z, __ldg(w2 + 2 * A), s);
+        s = fmaf(hv[z].w, __ldg(w2 + 3 * A), s);
+        s = warp_sum(s);
+        if (lane == 0) red_s[warp][z][a] = s;
+      }
+    }
   }
-  const float* h = g.h1[0] + (size_t)row * kFc1Out;
-  for (int k = lane; k < kFc1Out; k += 32)
-    g.dh1[(size_t)row * kFc1Out + k] = h[k] > 0.f ? dq * g.w2[0][(size_t)k * A + act] : 0.f;
+  if (t < kFc1Out / 4) reinterpret_cast<float4*>(h_s[0])[t] = hv[0];   // relu mask for dh1 below
+  __syncthreads();
+  if (t < nets * A) {
+    const int z = t / A, a = t - z * A;
+    float s = g.b2[z][g.shared_bias ? 0 : a];
+#pragma unroll
+    for (int w = 0; w < kHeadThreads / 32; ++w) s += red_s[w][z][a];
+    q_s[z][a] = s;
+    g.q[z][(size_t)row * A + a] = s;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float best; int sel;
+    warp_argmax(q_s[g.double_q ? 2 : 1][lane], lane, best, sel);   // selector net (lanes >= A hold -inf)
+    const float q_next = q_s[1][sel];                                // value from the target net
+    const int act = g.action[row];
+    const float q_taken = q_s[0][act];
+    const float td = g.reward[row] + g.discount[row] * q_next - q_taken;
+    float cot = fminf(fmaxf(td * g.inv_mean, -g.grad_bound), g.grad_bound);
+    if (g.row_weight) cot *= g.row_weight[row];
+    const float dq = -cot;
+    if (lane == 0) {
+      g.td[row] = td;
+      g.row_loss[row] = 0.5f * td * td;
+      g.dq_taken[row] = dq;
+      dq_s = dq;
+      act_s = act;
+    }
+  }
+  __syncthreads();
+  const float dq = dq_s;
+  const int act = act_s;
+  for (int k = t; k < kFc1Out; k += kHeadThreads) {
+    const float d = h_s[0][k] > 0.f ? dq * g.w2[0][(size_t)k * A + act] : 0.f;
+    g.dh1[(size_t)row * kFc1Out + k] = g.round_tf32 ? tf32_rn(d) : d;
+  }
+  tl_end(g.tl, tl_t0);
 }
 
 // fc2 parameter gradients + scalar loss.  thread (k,a): gW2[k,a] = sum_b h1[b,k] * dq[b,a];
@@ -86,7 +160,8 @@ __global__ void __launch_bounds__(128) head_td_kernel(HeadArgs g) {
 __global__ void fc2_wgrad_kernel(int batch, int A, int shared_bias, float inv_mean, const float* __restrict__ h1,
                                  const int32_t* __restrict__ action, const float* __restrict__ dq_taken,
                                  const float* __restrict__ row_loss, float* __restrict__ gw2,
-                                 float* __restrict__ gb2, float* __restrict__ loss) {
+                                 float* __restrict__ gb2, float* __restrict__ loss, unsigned long long* tl) {
+  tl_begin(tl);
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e < kFc1Out * A) {
     int k = e / A, a = e - k * A;
@@ -113,12 +188,15 @@ __global__ void fc2_wgrad_kernel(int batch, int A, int shared_bias, float inv_me
     l = warp_sum(l);
     if (lane == 0) *loss = l * inv_mean;
   }
+  tl_end(tl);
 }
 
 // K5: optax.rmsprop(centered=True) + apply_updates, one pass over the flat arena
 // (op order of Digraph.gv:711-752; eps inside the rsqrt).
 __global__ void rmsprop_kernel(float* __restrict__ p, float* __restrict__ mu, float* __restrict__ nu,
-                               const float* __restrict__ g, int64_t n, float lr, float decay, float eps) {
+                               const float* __restrict__ g, int64_t n, float lr, float decay, float eps,
+                               unsigned long long* tl) {
+  tl_begin(tl);
   const float om = 1.0f - decay;
   int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t n4 = n >> 2;
@@ -146,6 +224,117 @@ __global__ void rmsprop_kernel(float* __restrict__ p, float* __restrict__ mu, fl
       p[i] = p[i] + (-lr) * (gv * rsqrtf(v - m * m + eps));
     }
   }
+  tl_end(tl);
+}
+
+// K5 with the split-K reduction of the weight gradients folded in.  A region of the arena whose
+// gradient still sits in `splits` partial buffers (each `count` floats, arena layout) is summed
+// here in split order (bit-reproducible) and written to g; other elements read g as is.
+// APPLY=false only materialises g (the data-parallel learner all-reduces it before the update).
+struct GradRegion {
+  int64_t off, count;      // floats; both multiples of 4
+  const float* part;
+  int splits;
+};
+constexpr int kMaxGradRegions = 4;
+struct GradRegions {
+  GradRegion r[kMaxGradRegions];
+  int n;
+};
+
+__device__ __forceinline__ void rmsprop4(float4& pv, float4& mv, float4& nv, const float4& gv, float lr, float decay,
+                                         float eps) {
+  const float om = 1.0f - decay;
+#define DQNB_RMS(c)                                              \
+  mv.c = om * gv.c + decay * mv.c;                               \
+  nv.c = om * (gv.c * gv.c) + decay * nv.c;                      \
+  pv.c = pv.c + (-lr) * (gv.c * rsqrtf(nv.c - mv.c * mv.c + eps));
+  DQNB_RMS(x) DQNB_RMS(y) DQNB_RMS(z) DQNB_RMS(w)
+#undef DQNB_RMS
+}
+
+// Elements [0, split_end) get 8 lanes per float4: lane s sums partials s, s+8, ... and an xor
+// butterfly adds the 8 lane sums (every lane performs the same commutative additions, so the
+// result is reproducible).  Elements [skip_lo, skip_hi) are updated elsewhere (fc1's fused
+// weight-gradient epilogue) and are not visited.  The rest: one thread per float4, g read as is.
+template <bool APPLY>
+__global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, float* __restrict__ mu,
+                                      float* __restrict__ nu, float* __restrict__ g, int64_t n, GradRegions regs, int64_t split_end,
+                                      int64_t skip_lo, int64_t skip_hi, float lr, float decay, float eps,
+                                      unsigned long long* tl) {
+  tl_begin(tl);
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nA = (split_end >> 2) * 8;
+  if (gid < nA) {
+    const int64_t i4 = gid >> 3, i = i4 << 2;
+    const int sub = (int)(gid & 7);
+    float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool summed = false;
+#pragma unroll
+    for (int r = 0; r < kMaxGradRegions; ++r) {
+      if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
+        const float* src = regs.r[r].part + (i - regs.r[r].off);
+        for (int q = sub; q < regs.r[r].splits; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].count));
+          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
+        }
+        summed = true;
+      }
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      gv.x += __shfl_xor_sync(0xffffffffu, gv.x, o);
+      gv.y += __shfl_xor_sync(0xffffffffu, gv.y, o);
+      gv.z += __shfl_xor_sync(0xffffffffu, gv.z, o);
+      gv.w += __shfl_xor_sync(0xffffffffu, gv.w, o);
+    }
+    if (sub == 0) {
+      if (summed) reinterpret_cast<float4*>(g)[i4] = gv;
+      else gv = reinterpret_cast<const float4*>(g)[i4];
+      if (APPLY) {
+        float4 mv = reinterpret_cast<float4*>(mu)[i4], nv = reinterpret_cast<float4*>(nu)[i4];
+        float4 pv = reinterpret_cast<float4*>(p)[i4];
+        rmsprop4(pv, mv, nv, gv, lr, decay, eps);
+        reinterpret_cast<float4*>(mu)[i4] = mv;
+        reinterpret_cast<float4*>(nu)[i4] = nv;
+        reinterpret_cast<float4*>(p)[i4] = pv;
+        if (p_r != nullptr) reinterpret_cast<float4*>(p_r)[i4] = tf32_rn4(pv);
+      }
+    }
+  } else if (APPLY) {
+    int64_t i = split_end + ((gid - nA) << 2);
+    if (i >= skip_lo) i += skip_hi - skip_lo;
+    const int64_t n4 = n >> 2, i4 = i >> 2;
+    if (i4 < n4) {
+      const float4 gv = reinterpret_cast<const float4*>(g)[i4];
+      float4 mv = reinterpret_cast<float4*>(mu)[i4], nv = reinterpret_cast<float4*>(nu)[i4];
+      float4 pv = reinterpret_cast<float4*>(p)[i4];
+      rmsprop4(pv, mv, nv, gv, lr, decay, eps);
+      reinterpret_cast<float4*>(mu)[i4] = mv;
+      reinterpret_cast<float4*>(nu)[i4] = nv;
+      reinterpret_cast<float4*>(p)[i4] = pv;
+      if (p_r != nullptr) reinterpret_cast<float4*>(p_r)[i4] = tf32_rn4(pv);
+    } else if (i4 == n4) {   // scalar tail
+      const float om = 1.0f - decay;
+      for (int64_t k = n4 << 2; k < n; ++k) {
+        float gk = g[k];
+        float m = om * gk + decay * mu[k];
+        float v = om * (gk * gk) + decay * nu[k];
+        mu[k] = m; nu[k] = v;
+        p[k] = p[k] + (-lr) * (gk * rsqrtf(v - m * m + eps));
+        if (p_r != nullptr) p_r[k] = tf32_rn(p[k]);
+      }
+    }
+  }
+  tl_end(tl);
+}
+__global__ void round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = tf32_rn(src[i]);
+}
+inline unsigned rmsprop_reduce_blocks(int64_t n, int64_t split_end, int64_t skip_lo, int64_t skip_hi) {
+  int64_t threads = (split_end >> 2) * 8 + ((n - split_end - (skip_hi - skip_lo)) >> 2) + 1;
+  return (unsigned)((threads + 255) / 256);
 }
 
 }  // namespace dqnb

@@ -2,11 +2,14 @@
 // backward, centered RMSProp, target sync; captured once as a CUDA graph with parallel
 // branches.  Replaces the jitted `update` of dqn/agent.py:109-119 / double_q/agent.py:85-121
 // and the target sync of dqn/agent.py:155-156.  See include/dqnb200.h.
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
 #include "head_kernels.cuh"
 #include "learner_internal.cuh"
+#include "nature_tf32.cuh"
 
 using namespace dqnb;
 
@@ -49,6 +52,7 @@ struct dqnb_learner {
   ArenaLayout L;
   // parameter / optimiser arenas (flat fp32, oracle leaf order)
   float *online = nullptr, *target = nullptr, *mu = nullptr, *nu = nullptr, *grad = nullptr;
+  float *online_r = nullptr, *target_r = nullptr;   // TF32 mode: weights rounded to tf32 (GEMM operands)
   // batch
   uint8_t *s_tm1 = nullptr, *s_t = nullptr;
   int32_t* act = nullptr;
@@ -62,9 +66,35 @@ struct dqnb_learner {
   unsigned* counters = nullptr;
   size_t ws_off = 0, cnt_off = 0, ws_cap = 0, cnt_cap = 0;
   bool sizing = false;
+  // TF32 mode: split-K partials of the weight gradients, reduced inside the RMSProp kernel
+  bool tf32 = false;
+  // profiling (dqnb_learner_profile): one event after every launch, all work on one stream
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_ev;
+  std::vector<const char*> prof_name;
+  size_t prof_n = 0;
+  long long* dbg_clocks = nullptr;   // [64][8] phase clocks of CTA 0 of each tensor-core launch
+  // timeline (dqnb_learner_timeline): every launch of the update owns a slot {min begin, max end} in ns
+  unsigned long long* d_tl = nullptr;
+  std::vector<const char*> tl_name;
+  int tl_n = 0, tl_graph_n = 0;
+  unsigned long long* next_tl(const char* name) {
+    if (sizing) return nullptr;
+    if ((int)tl_name.size() <= tl_n) tl_name.push_back(name);
+    tl_name[tl_n] = name;
+    return d_tl ? d_tl + kTlSlot * tl_n++ : nullptr;
+  }
+  float* gpart = nullptr;
+  size_t part_off = 0, part_cap = 0;
+  float* fc1_part = nullptr;     // fc1 forward split-K partials [nets][splits][rows][512], summed by the head
+  size_t fc1_part_cap = 0;
+  int fc1_splits = 0, fc1_rows = 0;
+  GradRegions regions;
   // graph
   cudaGraphExec_t graph = nullptr;
   cudaStream_t side[3] = {};
+  cudaStream_t chain = nullptr;   // stream of the dependent kernel chain in the enqueue in progress
+  int prio_hi = 0;                // greatest launch priority of the device
   cudaEvent_t ev[8] = {};
   int64_t updates = 0;
   int64_t launches_per_update = 0;
@@ -82,17 +112,40 @@ struct dqnb_learner {
     cnt_off += tiles;
     return sk;
   }
+  // partial-gradient buffer for one wgrad op; registers the arena region it reduces into
+  float* take_part(int64_t arena_off, int64_t count, int splits) {
+    float* ptr = gpart ? gpart + part_off : nullptr;
+    part_off += (size_t)count * splits;
+    GradRegion& r = regions.r[regions.n++];
+    r.off = arena_off; r.count = count; r.part = ptr; r.splits = splits;
+    return ptr;
+  }
 };
 
 namespace {
+
+// profiling hook: timestamp after the launch that was just enqueued on `st`
+int mark(dqnb_learner* h, cudaStream_t st, const char* name) {
+  if (!h->profiling) return DQNB_OK;
+  if (h->prof_n == h->prof_ev.size()) {
+    cudaEvent_t e;
+    DQNB_CUDA(cudaEventCreate(&e));
+    h->prof_ev.push_back(e);
+    h->prof_name.push_back(name);
+  }
+  h->prof_name[h->prof_n] = name;
+  DQNB_CUDA(cudaEventRecord(h->prof_ev[h->prof_n++], st));
+  return DQNB_OK;
+}
 
 template <class P>
 int run_gemm(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
   SplitK sk = h->take_scratch(gemm_ws_floats(p, Z, splits), gemm_tiles(p, Z));
   h->launches_per_update++;
   if (h->sizing) return DQNB_OK;
+  sk.tl = h->next_tl(P::NAME);
   DQNB_CUDA(launch_gemm(p, Z, splits, sk, st));
-  return DQNB_OK;
+  return mark(h, st, P::NAME);
 }
 
 template <class L, class TIn, int BM>
@@ -130,6 +183,11 @@ HeadArgs head_args(dqnb_learner* h, int rows, const float* const* params, int ne
   for (int z = 0; z < kMaxNets; ++z) {
     int zz = std::min(z, nets - 1);
     g.h1[z] = h->h1[zz]; g.w2[z] = params[zz] + h->L.fw2; g.b2[z] = params[zz] + h->L.fb2; g.q[z] = h->q[zz];
+  }
+  g.fc1_part = nullptr; g.fc1_splits = 0; g.tl = nullptr; g.round_tf32 = 0;
+  for (int z = 0; z < kMaxNets; ++z) {
+    int zz = std::min(z, nets - 1);
+    g.b1[z] = params[zz] + h->L.fb1; g.h1_out[z] = h->h1[zz];
   }
   g.action = h->act; g.reward = h->rew; g.discount = h->disc; g.row_weight = nullptr;
   g.td = h->td; g.row_loss = h->row_loss; g.dq_taken = h->dq_taken; g.dh1 = h->dh1;
@@ -170,10 +228,11 @@ int fork(cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
 // nothing is launched; scratch offsets and the launch count are tallied instead.
 int enqueue_update(dqnb_learner* h, cudaStream_t st) {
   h->ws_off = h->cnt_off = 0;
+  h->tl_n = 0;
   h->launches_per_update = 0;
   const int B = h->B, nets = h->nets;
   const bool live = !h->sizing;
-  cudaStream_t s1 = h->side[0], s2 = h->side[1], s3 = h->side[2];
+  cudaStream_t s1 = h->profiling ? st : h->side[0], s2 = h->profiling ? st : h->side[1], s3 = h->profiling ? st : h->side[2];
   const uint8_t* xin[kMaxNets] = {h->s_tm1, h->s_t, h->s_t};
   const float* params[kMaxNets] = {h->online, h->target, h->online};
 
@@ -181,8 +240,10 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
   HeadArgs g = head_args(h, B, params, nets);
   h->launches_per_update++;
   if (live) {
-    head_td_kernel<<<(B + 3) / 4, 128, 0, st>>>(g);
+    g.tl = h->next_tl("head_td");
+    head_td_kernel<<<B, kHeadThreads, 0, st>>>(g);
     DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, st, "head_td"));
   }
   // branch s1: fc2 parameter grads + loss.   branch s2: fc1 weight grad.
   if (live) { DQNB_TRY(fork(h->ev[0], st, s1)); DQNB_TRY(fork(h->ev[0], st, s2)); }
@@ -191,8 +252,9 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
     int n = kFc1Out * h->A;
     fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
                                                      h->dq_taken, h->row_loss, h->grad + h->L.fw2,
-                                                     h->grad + h->L.fb2, h->loss);
+                                                     h->grad + h->L.fb2, h->loss, h->next_tl("fc2_wgrad"));
     DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, s1, "fc2_wgrad"));
   }
   {
     DenseWgrad p;
@@ -223,22 +285,210 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
   if (live) {
     int64_t n4 = (h->L.total >> 2) + 1;
     rmsprop_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(h->online, h->mu, h->nu, h->grad, h->L.total,
-                                                               h->cfg.learning_rate, h->cfg.decay, h->cfg.eps);
+                                                               h->cfg.learning_rate, h->cfg.decay, h->cfg.eps,
+                                                               h->next_tl("rmsprop"));
     DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, st, "rmsprop"));
   }
   return DQNB_OK;
+}
+
+// ------------------------------------------------------------------ TF32 tensor-core path
+template <class P>
+int run_t32(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
+  SplitK sk = h->take_scratch(gemm_tf32_ws_floats(p, Z, splits), gemm_tf32_tiles(p, Z));
+  h->launches_per_update++;
+  if (h->sizing) return DQNB_OK;
+  sk.tl = h->next_tl(P::NAME);
+  if (h->profiling && getenv("DQNB_PROFILE_TWICE")) {   // warm the instruction cache with an untimed twin launch
+    DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st));
+    DQNB_TRY(mark(h, st, "(twin)"));
+  }
+  if (h->profiling && h->dbg_clocks) sk.dbg = h->dbg_clocks + 8 * h->prof_n;
+  DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, st == h->chain ? h->prio_hi : 0));
+  return mark(h, st, P::NAME);
+}
+
+template <class L, class TIn>
+int t32_conv_fwd(dqnb_learner* h, int nets, int rows, const TIn* const* x, const float* const* params,
+                 const float* const* wts, int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st) {
+  T32ConvFwd<L, TIn> p;
+  p.M = rows * L::HOUT * L::WOUT; p.N = L::COUT; p.K = L::KCOL;
+  for (int z = 0; z < kMaxNets; ++z) {
+    int zz = std::min(z, nets - 1);
+    p.x[z] = x[zz]; p.w[z] = wts[zz] + w_off; p.bias[z] = params[zz] + b_off; p.y[z] = y[zz];
+  }
+  return run_t32(h, p, nets, t32_splits_for(p, nets), st);
+}
+
+// `params`: fp32 arenas (biases); `wts`: their tf32-rounded shadows (GEMM weight operands).
+int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const* x, const float* const* params,
+                       const float* const* wts, cudaStream_t st) {
+  const float* in2[kMaxNets]; const float* in3[kMaxNets]; const float* in4[kMaxNets];
+  for (int z = 0; z < nets; ++z) { in2[z] = h->a1[z]; in3[z] = h->a2[z]; in4[z] = h->a3[z]; }
+  DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
+  DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
+  DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
+  T32DenseFwd p;
+  p.merged = nets == 3;
+  p.batch = rows;
+  p.M = p.merged ? 2 * rows : rows; p.N = kFc1Out; p.K = kFc1In;
+  const int Z = p.merged ? 2 : nets;
+  for (int z = 0; z < kMaxNets; ++z) {
+    int zz = std::min(z, nets - 1);
+    p.x[z] = in4[zz]; p.w[z] = wts[zz] + h->L.fw1;
+  }
+  p.splits = t32_splits_for(p, Z, kNumSMs);
+  h->fc1_splits = p.splits;
+  h->fc1_rows = rows;
+  const size_t need = (size_t)nets * p.splits * rows * kFc1Out;
+  if (h->sizing) h->fc1_part_cap = std::max(h->fc1_part_cap, need);
+  p.part = h->fc1_part;
+  return run_t32(h, p, Z, p.splits, st);
+}
+
+// `bias_st`: stream for the separate bias column-sum kernel (BIAS_ROW = false); it must already
+// be ordered after the producer of dy.
+template <class L, class TIn, int KB, bool BIAS_ROW>
+int t32_conv_wgrad(dqnb_learner* h, int rows, const TIn* x, const float* dy, int64_t w_off, cudaStream_t st,
+                   cudaStream_t bias_st = nullptr) {
+  using P = T32ConvWgrad<L, TIn, KB, BIAS_ROW>;
+  P p;
+  p.M = P::ROWS; p.N = L::COUT; p.K = rows * L::HOUT * L::WOUT;
+  p.x = x; p.dy = dy;
+  const int splits = t32_splits_for(p, 1);
+  p.gpart = h->take_part(w_off, (int64_t)P::PART, splits);
+  if (!BIAS_ROW) {
+    h->launches_per_update++;
+    if (!h->sizing) {
+      bias_colsum_kernel<L::COUT><<<splits, 256, 0, bias_st>>>(dy, p.K, p.gpart, P::PART, (size_t)L::KCOL * L::COUT,
+                                                               h->next_tl("bias_colsum"));
+      DQNB_CUDA(cudaGetLastError());
+      DQNB_TRY(mark(h, bias_st, "bias_colsum"));
+    }
+  }
+  return run_t32(h, p, 1, splits, st);
+}
+
+template <class L, int KB>
+int t32_conv_dgrad(dqnb_learner* h, int rows, const float* dy, const float* w, const float* act_in, float* dx,
+                   cudaStream_t st) {
+  T32ConvDgrad<L, KB> p;
+  p.M = rows * T32ConvDgrad<L, KB>::NY * T32ConvDgrad<L, KB>::NX; p.N = L::CIN;
+  p.K = T32ConvDgrad<L, KB>::T * T32ConvDgrad<L, KB>::T * L::COUT;
+  p.dy = dy; p.w = w; p.act_in = act_in; p.dx = dx;
+  const int Z = L::STRIDE * L::STRIDE;
+  return run_t32(h, p, Z, t32_splits_for(p, Z), st);
+}
+
+template <int KB, int BN>
+int t32_dense_wgrad(dqnb_learner* h, int rows, bool fuse, cudaStream_t st) {
+  T32DenseWgrad<KB, BN> p;
+  p.M = kFc1In + 1; p.N = kFc1Out; p.K = rows;
+  p.x = h->a3[0]; p.dy = h->dh1;
+  const int splits = t32_splits_for(p, 1);
+  p.fuse = FusedRmsProp{nullptr, nullptr, nullptr, nullptr, nullptr, 0.f, 0.f, 0.f};
+  p.gpart = nullptr;
+  if (fuse && splits == 1) {
+    const int64_t o = h->L.fw1;
+    p.fuse = FusedRmsProp{h->online + o, h->online_r + o, h->mu + o, h->nu + o, h->grad + o,
+                          h->cfg.learning_rate, h->cfg.decay, h->cfg.eps};
+  } else {
+    p.gpart = h->take_part(h->L.fw1, (int64_t)p.M * p.N, splits);
+  }
+  return run_t32(h, p, 1, splits, st);
+}
+
+// One full update with every GEMM on tcgen05 (TF32).  Same dependency structure as the fp32
+// graph; the weight-gradient partials are summed by the optimiser kernel.
+int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
+  h->ws_off = h->cnt_off = h->part_off = 0;
+  h->regions.n = 0;
+  h->tl_n = 0;
+  h->launches_per_update = 0;
+  h->chain = st;
+  const int B = h->B, nets = h->nets;
+  const bool live = !h->sizing;
+  cudaStream_t s1 = h->profiling ? st : h->side[0], s2 = h->profiling ? st : h->side[1], s3 = h->profiling ? st : h->side[2];
+  const uint8_t* xin[kMaxNets] = {h->s_tm1, h->s_t, h->s_t};
+  const float* params[kMaxNets] = {h->online, h->target, h->online};
+
+  const float* wts[kMaxNets] = {h->online_r, h->target_r, h->online_r};
+  DQNB_TRY(forward_torso_tf32(h, nets, B, xin, params, wts, st));
+  HeadArgs g = head_args(h, B, params, nets);
+  g.round_tf32 = 1;
+  g.fc1_part = h->fc1_part; g.fc1_splits = h->fc1_splits;
+  h->launches_per_update++;
+  if (live) {
+    g.tl = h->next_tl("head_td");
+    head_td_kernel<<<B, kHeadThreads, 0, st>>>(g);
+    DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, st, "head_td"));
+  }
+  if (live) DQNB_TRY(fork(h->ev[0], st, s1));
+  h->launches_per_update++;
+  if (live) {
+    int n = kFc1Out * h->A;
+    fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
+                                                     h->dq_taken, h->row_loss, h->grad + h->L.fw2,
+                                                     h->grad + h->L.fb2, h->loss, h->next_tl("fc2_wgrad"));
+    DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, s1, "fc2_wgrad"));
+  }
+  {
+    T32DenseDgrad p;
+    p.M = B; p.N = kFc1In; p.K = kFc1Out;
+    p.dy = h->dh1; p.w = h->online_r + h->L.fw1; p.act = h->a3[0]; p.dx = h->dy3;
+    DQNB_TRY(run_t32(h, p, 1, t32_splits_for(p, 1), st));
+  }
+  if (live) DQNB_TRY(fork(h->ev[1], st, s3));
+  DQNB_TRY((t32_conv_wgrad<Conv3, float, 8, true>(h, B, h->a2[0], h->dy3, h->L.w3, s3)));
+  DQNB_TRY((t32_conv_dgrad<Conv3, 6>(h, B, h->dy3, h->online_r + h->L.w3, h->a2[0], h->dy2, st)));
+  if (live) { DQNB_TRY(fork(h->ev[2], st, s3)); DQNB_TRY(fork(h->ev[2], st, s2)); DQNB_TRY(fork(h->ev[2], st, s1)); }
+  // fc1's weight gradient is ordered after fc1's dgrad (which reads the old weights) so that, when
+  // the batch is one K block (no split-K), its epilogue can apply RMSProp to fc1 on the spot.  It
+  // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
+  // kernels (conv2 dgrad, conv1 wgrad) leave room for its small CTAs beside their own on every SM.
+  bool fused = false;
+  if (B <= kT32BK) { fused = true; DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2))); }
+  else DQNB_TRY((t32_dense_wgrad<4, 128>(h, B, false, s2)));
+  DQNB_TRY((t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1)));
+  DQNB_TRY((t32_conv_dgrad<Conv2, 8>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
+  if (live) DQNB_TRY(fork(h->ev[6], st, s1));
+  DQNB_TRY((t32_conv_wgrad<Conv1, uint8_t, 8, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1)));
+  if (live) {
+    DQNB_TRY(fork(h->ev[3], s1, st));
+    DQNB_TRY(fork(h->ev[4], s2, st));
+    DQNB_TRY(fork(h->ev[5], s3, st));
+  }
+  h->launches_per_update++;
+  if (live) {
+    const int64_t split_end = fused ? h->L.fw1 : h->L.fw2;
+    const int64_t skip_lo = fused ? h->L.fw1 : 0, skip_hi = fused ? h->L.fw2 : 0;
+    rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
+        h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+        h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce"));
+    DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, st, "rmsprop_reduce"));
+  }
+  return DQNB_OK;
+}
+
+int enqueue_any(dqnb_learner* h, cudaStream_t st) {
+  return h->tf32 ? enqueue_update_tf32(h, st) : enqueue_update(h, st);
 }
 
 int build_graph(dqnb_learner* h) {
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
   DQNB_CUDA(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
-  int rc = enqueue_update(h, cap);
+  int rc = enqueue_any(h, cap);
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(cap, &graph);
   if (rc != DQNB_OK) { if (graph) cudaGraphDestroy(graph); cudaStreamDestroy(cap); return rc; }
   DQNB_CUDA(e);
-  DQNB_CUDA(cudaGraphInstantiate(&h->graph, graph, 0));
+  // Per-node priorities: the kernels of the dependent chain outrank the side-branch kernels.
+  DQNB_CUDA(cudaGraphInstantiateWithFlags(&h->graph, graph, cudaGraphInstantiateFlagUseNodePriority));
   DQNB_CUDA(cudaGraphDestroy(graph));
   DQNB_CUDA(cudaStreamDestroy(cap));
   return DQNB_OK;
@@ -259,15 +509,18 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   DQNB_REQUIRE(cfg->num_actions >= 1 && cfg->num_actions <= kMaxActions, "num_actions %d not in 1..%d",
                cfg->num_actions, kMaxActions);
   DQNB_REQUIRE(cfg->batch_size >= 1 && cfg->batch_size <= 65536, "batch_size %d out of range", cfg->batch_size);
-  DQNB_REQUIRE(cfg->precision == DQNB_FP32, "precision %d not available in this build", cfg->precision);
+  DQNB_REQUIRE(cfg->precision == DQNB_FP32 || cfg->precision == DQNB_TF32,
+               "precision %d not available in this build (DQNB_FP32 or DQNB_TF32)", cfg->precision);
   DeviceGuard guard(device);
   dqnb_learner* h = new dqnb_learner();
   h->cfg = *cfg;
   h->device = device;
   h->B = cfg->batch_size; h->A = cfg->num_actions; h->nets = cfg->double_q ? 3 : 2;
+  h->tf32 = cfg->precision == DQNB_TF32;
   h->L = make_layout(h->A, cfg->shared_bias);
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
+  if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
   DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));
   DQNB_TRY(dmalloc(&h->act, B)); DQNB_TRY(dmalloc(&h->rew, B)); DQNB_TRY(dmalloc(&h->disc, B));
@@ -282,6 +535,11 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   DQNB_TRY(dmalloc(&h->td, B)); DQNB_TRY(dmalloc(&h->row_loss, B)); DQNB_TRY(dmalloc(&h->dq_taken, B));
   DQNB_TRY(dmalloc(&h->loss, 1));
   for (auto& s : h->side) DQNB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  {
+    int least = 0, greatest = 0;
+    DQNB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    h->prio_hi = greatest;
+  }
   for (auto& e : h->ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   DQNB_CUDA(cudaEventCreateWithFlags(&h->pinned_free, cudaEventDisableTiming));
   h->pinned_bytes = 2 * B * Conv1::IN_PER_IMG + 16 * B;
@@ -289,11 +547,15 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   DQNB_CUDA(cudaMallocHost(&h->pinned_loss, 64));
   // size the split-K scratch with a dry pass, then record the graph
   h->sizing = true;
-  DQNB_TRY(enqueue_update(h, nullptr));
+  DQNB_TRY(enqueue_any(h, nullptr));
   h->sizing = false;
-  h->ws_cap = h->ws_off; h->cnt_cap = h->cnt_off;
+  h->ws_cap = h->ws_off; h->cnt_cap = h->cnt_off; h->part_cap = h->part_off;
   DQNB_TRY(dmalloc(&h->ws, h->ws_cap)); DQNB_TRY(dmalloc(&h->counters, h->cnt_cap));
+  if (h->part_cap) DQNB_TRY(dmalloc(&h->gpart, h->part_cap));
+  if (h->fc1_part_cap) DQNB_TRY(dmalloc(&h->fc1_part, h->fc1_part_cap));
+  DQNB_CUDA(cudaMalloc(&h->d_tl, sizeof(unsigned long long) * kTlSlot * 64));
   DQNB_TRY(build_graph(h));
+  h->tl_graph_n = h->tl_n;
   *out = h;
   return DQNB_OK;
 }
@@ -304,7 +566,7 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   cudaDeviceSynchronize();
   if (h->graph) cudaGraphExecDestroy(h->graph);
   float* fl[] = {h->online, h->target, h->mu, h->nu, h->grad, h->rew, h->disc, h->dh1, h->dy3, h->dy2, h->dy1,
-                 h->td, h->row_loss, h->dq_taken, h->loss, h->ws};
+                 h->td, h->row_loss, h->dq_taken, h->loss, h->ws, h->gpart, h->fc1_part, h->online_r, h->target_r};
   for (float* p : fl) cudaFree(p);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
   cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
@@ -360,6 +622,11 @@ extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host,
   DQNB_TRY(locate(h, which, &p, &len));
   DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
   DQNB_CUDA(cudaMemcpyAsync(p, host, sizeof(float) * n, cudaMemcpyHostToDevice, as_stream(stream)));
+  if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
+    float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
+    round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
+    DQNB_CUDA(cudaGetLastError());
+  }
   DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
   return DQNB_OK;
 }
@@ -431,6 +698,9 @@ extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
   DQNB_REQUIRE(h, "null argument");
   DeviceGuard guard(h->device);
   DQNB_CUDA(cudaMemcpyAsync(h->target, h->online, sizeof(float) * h->L.total, cudaMemcpyDeviceToDevice, as_stream(stream)));
+  if (h->tf32)
+    DQNB_CUDA(cudaMemcpyAsync(h->target_r, h->online_r, sizeof(float) * h->L.total, cudaMemcpyDeviceToDevice,
+                              as_stream(stream)));
   return DQNB_OK;
 }
 
@@ -447,11 +717,17 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
   const float* prm = which_params ? h->target : h->online;
   const float* params[kMaxNets] = {prm, prm, prm};
   h->ws_off = h->cnt_off = 0;
-  DQNB_TRY(forward_torso(h, 1, n, xin, params, st));
+  const float* prm_r = which_params ? h->target_r : h->online_r;
+  const float* wts[kMaxNets] = {prm_r, prm_r, prm_r};
+  if (h->tf32) DQNB_TRY(forward_torso_tf32(h, 1, n, xin, params, wts, st));
+  else DQNB_TRY(forward_torso(h, 1, n, xin, params, st));
   HeadArgs g = head_args(h, n, params, 2);
   g.h1[1] = g.h1[0]; g.q[1] = h->q[1];   // head also evaluates a dummy target row; harmless
+  if (h->tf32) {   // one net's partials; the dummy second net re-reads them
+    g.fc1_part = h->fc1_part; g.fc1_splits = h->fc1_splits;
+  }
   g.td = h->td; g.dh1 = h->dh1;
-  head_td_kernel<<<(n + 3) / 4, 128, 0, st>>>(g);
+  head_td_kernel<<<n, kHeadThreads, 0, st>>>(g);
   DQNB_CUDA(cudaGetLastError());
   DQNB_CUDA(cudaMemcpyAsync(q_host, h->q[0], sizeof(float) * n * h->A, cudaMemcpyDeviceToHost, st));
   DQNB_CUDA(cudaStreamSynchronize(st));
@@ -461,5 +737,84 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
 extern "C" int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n) {
   DQNB_REQUIRE(h && n, "null argument");
   *n = h->launches_per_update;
+  return DQNB_OK;
+}
+
+// Per-kernel timing of one update: the same launches as the graph, but eagerly on one stream
+// with a CUDA event after each, averaged over `iters` runs (the first is a warm-up).  State is
+// advanced like by `iters` updates on the batch currently in the learner's buffers.
+extern "C" int dqnb_learner_profile(dqnb_learner* h, int iters, char* report, size_t report_len, uintptr_t stream) {
+  DQNB_REQUIRE(h && report && report_len > 0 && iters >= 1, "bad argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  cudaEvent_t begin;
+  DQNB_CUDA(cudaEventCreate(&begin));
+  std::vector<double> total;
+  if (!h->dbg_clocks) DQNB_CUDA(cudaMalloc(&h->dbg_clocks, sizeof(long long) * 8 * 64));
+  DQNB_CUDA(cudaMemset(h->dbg_clocks, 0, sizeof(long long) * 8 * 64));
+  h->profiling = true;
+  int rc = DQNB_OK;
+  for (int it = 0; it <= iters && rc == DQNB_OK; ++it) {
+    h->prof_n = 0;
+    cudaEventRecord(begin, st);
+    rc = enqueue_any(h, st);
+    if (rc != DQNB_OK) break;
+    if (cudaStreamSynchronize(st) != cudaSuccess) { set_error("profile: stream sync failed"); rc = DQNB_ECUDA; break; }
+    if (it == 0) { total.assign(h->prof_n, 0.0); continue; }
+    for (size_t i = 0; i < h->prof_n; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, i == 0 ? begin : h->prof_ev[i - 1], h->prof_ev[i]);
+      total[i] += ms * 1e3;
+    }
+  }
+  h->profiling = false;
+  cudaEventDestroy(begin);
+  DQNB_TRY(rc);
+  size_t off = 0;
+  double sum = 0;
+  std::vector<long long> clk(8 * 64, 0);
+  cudaMemcpy(clk.data(), h->dbg_clocks, sizeof(long long) * 8 * 64, cudaMemcpyDeviceToHost);
+  for (size_t i = 0; i < h->prof_n && off + 200 < report_len; ++i) {
+    off += snprintf(report + off, report_len - off, "%-16s %8.2f us", h->prof_name[i], total[i] / iters);
+    const long long* c = &clk[8 * i];
+    if (i < 64 && c[0] != 0)   // CTA 0 phase durations in SM cycles (last iteration)
+      off += snprintf(report + off, report_len - off,
+                      "   cta0 cycles: setup %lld issue %lld land %lld mma %lld epi %lld fixup %lld (sync1 %lld)",
+                      c[1] - c[0], c[2] - c[1], c[3] - c[2], c[4] - c[3], c[5] - c[4], c[6] - c[5],
+                      c[7] ? c[7] - c[5] : 0LL);
+    off += snprintf(report + off, report_len - off, "\n");
+    sum += total[i] / iters;
+  }
+  if (off + 64 < report_len) snprintf(report + off, report_len - off, "%-16s %8.2f us\n", "sum", sum);
+  return DQNB_OK;
+}
+
+// Timeline of one *graph* update as it really runs (parallel branches, launch gaps): begin / end
+// of every kernel in microseconds relative to the first kernel's begin, from %globaltimer stamps.
+extern "C" int dqnb_learner_timeline(dqnb_learner* h, char* report, size_t report_len, uintptr_t stream) {
+  DQNB_REQUIRE(h && report && report_len > 0, "bad argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const int n = h->tl_graph_n;
+  std::vector<unsigned long long> init(kTlSlot * 64, 0ull), got(kTlSlot * 64);
+  for (int i = 0; i < 64; ++i) init[kTlSlot * i] = ~0ull;
+  const size_t bytes = sizeof(unsigned long long) * kTlSlot * 64;
+  for (int rep = 0; rep < 3; ++rep) {   // the last repetition is reported
+    DQNB_CUDA(cudaMemcpyAsync(h->d_tl, init.data(), bytes, cudaMemcpyHostToDevice, st));
+    DQNB_CUDA(cudaStreamSynchronize(st));
+    DQNB_CUDA(cudaGraphLaunch(h->graph, st));
+    DQNB_CUDA(cudaStreamSynchronize(st));
+  }
+  DQNB_CUDA(cudaMemcpy(got.data(), h->d_tl, bytes, cudaMemcpyDeviceToHost));
+  unsigned long long t0 = ~0ull, t1 = 0;
+  for (int i = 0; i < n; ++i) { t0 = std::min(t0, got[kTlSlot * i]); t1 = std::max(t1, got[kTlSlot * i + 1]); }
+  size_t off = 0;
+  for (int i = 0; i < n && off + 128 < report_len; ++i) {
+    const unsigned long long* g = &got[kTlSlot * i];
+    off += snprintf(report + off, report_len - off,
+                    "%-16s begin %8.2f  end %8.2f  (%6.2f us)  last CTA starts +%5.2f, longest CTA %5.2f\n", h->tl_name[i],
+                    (g[0] - t0) * 1e-3, (g[1] - t0) * 1e-3, (g[1] - g[0]) * 1e-3, (g[2] - g[0]) * 1e-3, g[3] * 1e-3);
+  }
+  if (off + 64 < report_len) snprintf(report + off, report_len - off, "span %.2f us\n", (t1 - t0) * 1e-3);
   return DQNB_OK;
 }

@@ -31,6 +31,7 @@ __device__ __forceinline__ float to_unit(float v) { return v; }
 // C[m=(b,i,j), n=cout] = relu(sum_k x[b, i*s+kh, j*s+kw, c] * W[k, n] + bias[n])
 template <class L, class TIn, int BM_>
 struct ConvFwd {
+  static constexpr const char* NAME = "conv_fwd";
   static constexpr int BM = BM_, BN = (L::COUT < 64 ? L::COUT : 64);
   static constexpr bool A_K_CONTIG = true, B_N_CONTIG = true;
   int M, N, K;
@@ -63,6 +64,7 @@ struct ConvFwd {
 // yields the bias gradient, which sits right behind the weights in the arena.
 template <class L, class TIn>
 struct ConvWgrad {
+  static constexpr const char* NAME = "conv_wgrad";
   static constexpr int BM = 64, BN = (L::COUT < 64 ? L::COUT : 64);
   static constexpr bool A_K_CONTIG = false, B_N_CONTIG = true;
   int M, N, K;              // M = KCOL + 1, N = COUT, K = B*HOUT*WOUT
@@ -95,6 +97,7 @@ struct ConvWgrad {
 // dx[b,y,x,c] = relu'(act_in) * sum_{th,tw,o} dy[b, yy-th, xx-tw, o] * W[kh,kw,c,o]
 template <class L>
 struct ConvDgrad {
+  static constexpr const char* NAME = "conv_dgrad";
   static constexpr int BM = 64, BN = (L::CIN < 64 ? L::CIN : 64);
   static constexpr bool A_K_CONTIG = true, B_N_CONTIG = false;
   static constexpr int S = L::STRIDE, T = L::KS / L::STRIDE;
@@ -142,6 +145,7 @@ struct ConvDgrad {
 // ---------------------------------------------------------------- dense layers (fc1)
 // y[m,n] = relu(sum_k x[m,k] W[k,n] + bias[n])
 struct DenseFwd {
+  static constexpr const char* NAME = "fc1_fwd";
   static constexpr int BM = 32, BN = 64;
   static constexpr bool A_K_CONTIG = true, B_N_CONTIG = true;
   int M, N, K;
@@ -162,6 +166,7 @@ struct DenseFwd {
 
 // dW[m'=k_in, n] = sum_b x[b,m'] * dy[b,n];  row m' == IN is ones -> bias gradient.
 struct DenseWgrad {
+  static constexpr const char* NAME = "fc1_wgrad";
   static constexpr int BM = 64, BN = 64;
   static constexpr bool A_K_CONTIG = false, B_N_CONTIG = true;
   int M, N, K;              // M = IN + 1, N = OUT, K = batch
@@ -182,6 +187,7 @@ struct DenseWgrad {
 
 // dx[m,n=k_in] = relu'(act[m,n]) * sum_k dy[m,k] * W[n,k]
 struct DenseDgrad {
+  static constexpr const char* NAME = "fc1_dgrad";
   static constexpr int BM = 32, BN = 64;
   static constexpr bool A_K_CONTIG = true, B_N_CONTIG = false;
   int M, N, K;              // M = batch, N = IN, K = OUT

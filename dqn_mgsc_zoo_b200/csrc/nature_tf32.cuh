@@ -1,0 +1,166 @@
+// Operand providers that put every layer op of the Nature CNN (networks.py:181-221) on the
+// TF32 tensor-core slab kernel gemm_tf32<P>.  Same GEMM formulations as nature_problems.cuh
+// (implicit im2col forward, dgrad by stride-parity class, wgrad with a ones row for the bias),
+// but operands move as 16-byte chunks (4 fp32) straight from the NHWC activations / HWIO
+// weights into swizzled shared memory with cp.async; uint8 frames go through registers
+// (0..255 is exact in TF32) and the 1/255 of networks.py:193 is applied to the accumulator.
+// Index decoding is split into a per-row and a per-k context (see T32Map in gemm_tf32.cuh) so
+// the divisions happen a handful of times per thread, not once per chunk.
+// Weight gradients leave their split-K partials in gpart[split][...] (arena layout, bias row
+// right behind the weights); rmsprop_reduce_kernel sums them in split order.
+#pragma once
+#include "gemm_tf32.cuh"
+#include "head_kernels.cuh"
+#include "nature_problems.cuh"
+
+namespace dqnb {
+
+__device__ __forceinline__ void t32_widen4(uint32_t dst, uint32_t w) {
+  st16(dst, (float)(w & 0xFF), (float)((w >> 8) & 0xFF), (float)((w >> 16) & 0xFF), (float)(w >> 24));
+}
+template <class T> struct InScale { static constexpr float value = 1.0f; };
+template <> struct InScale<uint8_t> { static constexpr float value = 1.0f / 255.0f; };
+
+// Contexts shared by most operands: a base pointer (null = out of range) on one side and an
+// element offset (-1 = out of range) on the other.
+template <class T>
+__device__ __forceinline__ void t32_put_ptr_off(uint32_t dst, const T* base, int off, const T* fallback) {
+  const bool ok = base != nullptr && off >= 0;
+  cp16(dst, ok ? base + off : fallback, ok);
+}
+constexpr int kT32Ones = -2;   // offset code of the all-ones wgrad row (bias gradient)
+
+// B operand = a row-major [K][N] fp32 matrix (haiku weights, or dy for the weight gradients),
+// i.e. N-contiguous: MN-major chunks of 4 consecutive n for one k.
+struct T32MatKN {
+  using Row = int;            // n (first of 4) or -1
+  using Col = const float*;   // mat + k*N or null
+  __device__ static Row row(int n, int N) { return n < N ? n : -1; }
+  __device__ static Col col(const float* mat, int k, int K, int N) { return k < K ? mat + (size_t)k * N : nullptr; }
+};
+
+// ---------------------------------------------------------------- conv forward
+// C[m=(b,i,j), n=cout] = relu(scale * sum_k x[b, i*s+kh, j*s+kw, c] * W[k, n] + bias[n])
+template <class L, class TIn>
+struct T32ConvFwd {
+  static constexpr const char* NAME = "conv_fwd";
+  // conv1 (uint8 frames, 300 tiles for double-Q): half slabs so that two CTAs share an SM.
+  static constexpr int BN = L::COUT, KB_MAX = sizeof(TIn) == 1 ? 4 : 8;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
+  static constexpr bool A_REG = sizeof(TIn) == 1;   // uint8 frames (conv1): 4 packed bytes per chunk
+  int M, N, K;
+  const TIn* x[kMaxNets];
+  const float* w[kMaxNets];
+  const float* bias[kMaxNets];
+  float* y[kMaxNets];
+  using ARow = const TIn*;    // &x[b, i*s, j*s, 0] or null
+  using ACol = int;           // offset of (kh, kw, c) inside the patch or -1
+  using BRow = T32MatKN::Row;
+  using BCol = T32MatKN::Col;
+  __device__ ARow a_row(int z, int m) const {
+    if (m >= M) return nullptr;
+    int b = m / (L::HOUT * L::WOUT), r = m - b * (L::HOUT * L::WOUT);
+    int i = r / L::WOUT, j = r - i * L::WOUT;
+    return x[z] + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
+  }
+  __device__ ACol a_col(int, int k) const {
+    if (k >= K) return -1;
+    int kh = k / L::ROWLEN;
+    return kh * (L::WIN * L::CIN) + (k - kh * L::ROWLEN);
+  }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, x[0]); }
+  __device__ uint32_t a_get(ARow r, ACol c) const {
+    return (r != nullptr && c >= 0) ? __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(r) + c)) : 0u;
+  }
+  __device__ void a_store(uint32_t dst, uint32_t wd) const { t32_widen4(dst, wd); }
+  __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
+  __device__ BCol b_col(int z, int k) const { return T32MatKN::col(w[z], k, K, N); }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, w[0]); }
+  __device__ void store4(int z, int, int m, int n, float4 v) const {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
+    constexpr float s = InScale<TIn>::value;
+    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) =
+        tf32_rn4(make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                             fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f)));
+  }
+};
+
+// ---------------------------------------------------------------- conv weight gradient
+// dW[m'=(kh,kw,c), n] = scale * sum_{k'=(b,i,j)} x[...] * dy[k', n]; row m' == KCOL is all ones
+// and yields the bias gradient, which sits right behind the weights in the arena.  Where KCOL is
+// a multiple of 128 that one row would cost a whole extra M tile (conv1: 3 tiles instead of 2),
+// so BIAS_ROW = false leaves it to bias_colsum_kernel, which fills the same gpart row.
+template <class L, class TIn, int KB_, bool BIAS_ROW = true>
+struct T32ConvWgrad {
+  static constexpr const char* NAME = "conv_wgrad";
+  static constexpr int BN = L::COUT, KB_MAX = KB_;
+  static constexpr bool A_MN_MAJOR = true, B_MN_MAJOR = true, DEFER_REDUCE = true;
+  static constexpr bool A_REG = sizeof(TIn) == 1;
+  static constexpr int ROWS = L::KCOL + (BIAS_ROW ? 1 : 0);
+  static constexpr size_t PART = (size_t)(L::KCOL + 1) * L::COUT;   // floats per split in gpart
+  int M, N, K;              // M = ROWS, N = COUT, K = B*HOUT*WOUT
+  const TIn* x;
+  const float* dy;
+  float* gpart;             // [splits][(KCOL + 1) * COUT]
+  using ARow = int;           // offset of (kh, kw, c..c+3) inside the patch, kT32Ones, or -1
+  using ACol = const TIn*;    // &x[b, i*s, j*s, 0] of output position k, or null
+  using BRow = T32MatKN::Row;
+  using BCol = T32MatKN::Col;
+  __device__ ARow a_row(int, int m) const {
+    if (m >= ROWS) return -1;
+    if (m == L::KCOL) return kT32Ones;
+    int kh = m / L::ROWLEN;
+    return kh * (L::WIN * L::CIN) + (m - kh * L::ROWLEN);
+  }
+  __device__ ACol a_col(int, int k) const {
+    if (k >= K) return nullptr;
+    int b = k / (L::HOUT * L::WOUT), q = k - b * (L::HOUT * L::WOUT);
+    int i = q / L::WOUT, j = q - i * L::WOUT;
+    return x + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
+  }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const {
+    if (r == kT32Ones) st16(dst, c != nullptr ? 1.f : 0.f, 0.f, 0.f, 0.f);
+    else t32_put_ptr_off(dst, c, r, x);
+  }
+  __device__ uint32_t a_get(ARow r, ACol c) const {
+    if (c == nullptr || r == -1) return 0u;
+    if (r == kT32Ones) return 1u;       // widens to (1, 0, 0, 0)
+    return __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(c) + r));
+  }
+  __device__ void a_store(uint32_t dst, uint32_t wd) const { t32_widen4(dst, wd); }
+  __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
+  __device__ BCol b_col(int, int k) const { return T32MatKN::col(dy, k, K, N); }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, dy); }
+  __device__ void store4(int, int split, int m, int n, float4 v) const {
+    const float s = m < L::KCOL ? InScale<TIn>::value : 1.0f;
+    *reinterpret_cast<float4*>(gpart + (size_t)split * PART + (size_t)m * N + n) =
+        make_float4(v.x * s, v.y * s, v.z * s, v.w * s);
+  }
+};
+
+// Bias gradient of a conv layer = column sums of dy[rows][C]: block q adds its share of the rows
+// (fixed order) into gpart[q][KCOL*C + c], next to split q's weight-gradient partial.
+template <int C>
+__global__ void __launch_bounds__(256) bias_colsum_kernel(const float* __restrict__ dy, int rows, float* __restrict__ gpart,
+                                                          size_t part_stride, size_t row_off, unsigned long long* tl) {
+  const unsigned long long tl_t0 = tl_begin(tl);
+  constexpr int LANES = 256 / C;
+  __shared__ float acc_s[LANES][C];
+  const int q = blockIdx.x, nq = gridDim.x, t = threadIdx.x, c = t % C, lane = t / C;
+  const int beg = (int)((int64_t)rows * q / nq), end = (int)((int64_t)rows * (q + 1) / nq);
+  float acc = 0.f;
+  for (int r = beg + lane; r < end; r += LANES) acc += __ldg(dy + (size_t)r * C + c);
+  acc_s[lane][c] = acc;
+  __syncthreads();
+  if (t < C) {
+    float v = 0.f;
+#pragma unroll
+    for (int l = 0; l < LANES; ++l) v += acc_s[l][t];
+    gpart[(size_t)q * part_stride + row_off + t] = v;
+  }
+  tl_end(tl, tl_t0);
+}
+
+#include "nature_tf32_more.inl"
+
+}  // namespace dqnb

@@ -1,0 +1,179 @@
+// Included by nature_tf32.cuh inside namespace dqnb: conv input gradient and the dense (fc1) ops.
+
+// ---------------------------------------------------------------- conv input gradient
+// One GEMM per stride-parity class z = py*S + px (see ConvDgrad in nature_problems.cuh).
+// dx[b,y,x,c] = relu'(act_in) * sum_{th,tw,o} dy[b, yy-th, xx-tw, o] * W[kh,kw,c,o]
+template <class L, int KB_>
+struct T32ConvDgrad {
+  static constexpr const char* NAME = "conv_dgrad";
+  static constexpr int BN = L::CIN, KB_MAX = KB_;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
+  static constexpr int S = L::STRIDE, T = L::KS / L::STRIDE;
+  static constexpr int NY = (L::HIN + S - 1) / S, NX = (L::WIN + S - 1) / S;
+  static_assert(L::KS % L::STRIDE == 0, "taps per parity class must be uniform");
+  int M, N, K;              // M = B*NY*NX, N = CIN, K = T*T*COUT
+  const float* dy;          // [B,HOUT,WOUT,COUT], already relu-masked
+  const float* w;           // HWIO
+  const float* act_in;      // layer input (post-relu output of the previous layer)
+  float* dx;
+  struct ARow { int base, yy, xx; };   // base = offset of dy[b, yy, xx, 0]; -1 = out of range
+  struct ACol { int off, th, tw; };    // off = o - (th*WOUT + tw)*COUT;    th = -1 = out of range
+  using BRow = int;                    // c*COUT or -1
+  using BCol = int;                    // offset of W[kh, kw, 0, o] or -1
+  __device__ ARow a_row(int, int m) const {
+    if (m >= M) return {-1, 0, 0};
+    int b = m / (NY * NX), r = m - b * (NY * NX);
+    int yy = r / NX, xx = r - yy * NX;
+    return {((b * L::HOUT + yy) * L::WOUT + xx) * L::COUT, yy, xx};
+  }
+  __device__ ACol a_col(int, int k) const {
+    if (k >= K) return {0, -1, 0};
+    int tap = k / L::COUT, o = k - tap * L::COUT;
+    int th = tap / T, tw = tap - th * T;
+    return {o - (th * L::WOUT + tw) * L::COUT, th, tw};
+  }
+  __device__ void a_put(const ARow& r, const ACol& c, uint32_t dst) const {
+    const int i = r.yy - c.th, j = r.xx - c.tw;
+    const bool ok = r.base >= 0 && c.th >= 0 && i >= 0 && i < L::HOUT && j >= 0 && j < L::WOUT;
+    cp16(dst, ok ? dy + r.base + c.off : dy, ok);
+  }
+  __device__ BRow b_row(int, int n) const { return n < N ? n * L::COUT : -1; }
+  __device__ BCol b_col(int z, int k) const {
+    if (k >= K) return -1;
+    int tap = k / L::COUT, o = k - tap * L::COUT;
+    int th = tap / T, tw = tap - th * T;
+    int kh = (z / S) + S * th, kw = (z % S) + S * tw;
+    return (kh * L::KS + kw) * (L::CIN * L::COUT) + o;
+  }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const {
+    const bool ok = r >= 0 && c >= 0;
+    cp16(dst, ok ? w + r + c : w, ok);
+  }
+  __device__ void store4(int z, int, int m, int n, float4 v) const {
+    int b = m / (NY * NX), r = m - b * (NY * NX);
+    int yy = r / NX, xx = r - yy * NX;
+    int y = (z / S) + S * yy, x = (z % S) + S * xx;
+    if (y >= L::HIN || x >= L::WIN) return;
+    const size_t idx = ((size_t)(b * L::HIN + y) * L::WIN + x) * L::CIN + n;
+    const float4 a = __ldg(reinterpret_cast<const float4*>(act_in + idx));
+    *reinterpret_cast<float4*>(dx + idx) =
+        tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
+  }
+};
+
+// ---------------------------------------------------------------- dense layers (fc1)
+// y[m,n] = relu(sum_k x[m,k] W[k,n] + bias[n]).  K = 3136 needs more split-K CTAs than a cluster
+// holds, so the partials go to part[net][split][row][n] and the head kernel (the only consumer)
+// finishes the sum, bias and relu.  Double-Q evaluates the online weights on two inputs (s_tm1 and
+// s_t): with `merged` those two batches are stacked into one A tile (rows [0,B) and [B,2B)) so the
+// 6.4 MB weight matrix is staged once for both; z = 1 is then the target net on s_t.
+struct T32DenseFwd {
+  static constexpr const char* NAME = "fc1_fwd";
+  static constexpr int BN = 128, KB_MAX = 6;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = true;
+  int M, N, K;              // M = rows per GEMM (2 * batch when merged)
+  const float* x[kMaxNets];
+  const float* w[kMaxNets];
+  float* part;              // [nets][splits][batch][N]
+  int splits, batch, merged;
+  using ARow = const float*;   // x + m*K or null
+  using ACol = int;            // k or -1
+  using BRow = T32MatKN::Row;
+  using BCol = T32MatKN::Col;
+  __device__ ARow a_row(int z, int m) const {
+    if (!merged) return m < batch ? x[z] + (size_t)m * K : nullptr;
+    if (z == 1) return m < batch ? x[1] + (size_t)m * K : nullptr;
+    if (m < batch) return x[0] + (size_t)m * K;
+    return m < 2 * batch ? x[2] + (size_t)(m - batch) * K : nullptr;
+  }
+  __device__ ACol a_col(int, int k) const { return k < K ? k : -1; }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, x[0]); }
+  __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
+  __device__ BCol b_col(int z, int k) const { return T32MatKN::col(w[z], k, K, N); }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, w[0]); }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const {
+    int net = z, row = m;
+    if (merged) {
+      if (z == 0 && m >= batch) { net = 2; row = m - batch; }
+      if (row >= batch) return;
+    }
+    *reinterpret_cast<float4*>(part + (((size_t)net * splits + split) * batch + row) * N + n) = v;
+  }
+};
+
+// dW[m'=k_in, n] = sum_b x[b,m'] * dy[b,n];  row m' == IN is ones -> bias gradient.
+// When the whole batch fits one CTA's K range (splits == 1, the batch-32 case) the epilogue can
+// apply centered RMSProp to fc1 (95 % of all parameters) on the spot: `fuse` points at the arena
+// slices of fc1 {p, mu, nu, g}; the launch is then ordered after fc1's dgrad, which needs the
+// old weights.
+struct FusedRmsProp {
+  float *p, *p_r, *mu, *nu, *g;   // null p: not fused; p_r: tf32-rounded shadow of p
+  float lr, decay, eps;
+};
+template <int KB_, int BN_>
+struct T32DenseWgrad {
+  static constexpr const char* NAME = "fc1_wgrad";
+  static constexpr int BN = BN_, KB_MAX = KB_;
+  static constexpr bool A_MN_MAJOR = true, B_MN_MAJOR = true, DEFER_REDUCE = true;
+  int M, N, K;              // M = IN + 1, N = OUT, K = batch
+  const float* x;           // [batch, IN]
+  const float* dy;          // [batch, OUT]
+  float* gpart;             // [splits][(IN + 1) * OUT]
+  FusedRmsProp fuse;
+  using ARow = int;            // m (first of 4), kT32Ones, or -1
+  using ACol = const float*;   // x + k*IN or null
+  using BRow = T32MatKN::Row;
+  using BCol = T32MatKN::Col;
+  __device__ ARow a_row(int, int m) const { return m < M - 1 ? m : (m == M - 1 ? kT32Ones : -1); }
+  __device__ ACol a_col(int, int k) const { return k < K ? x + (size_t)k * (M - 1) : nullptr; }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const {
+    if (r == kT32Ones) st16(dst, c != nullptr ? 1.f : 0.f, 0.f, 0.f, 0.f);
+    else t32_put_ptr_off(dst, c, r, x);
+  }
+  __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
+  __device__ BCol b_col(int, int k) const { return T32MatKN::col(dy, k, K, N); }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, dy); }
+  __device__ void store4(int, int split, int m, int n, float4 v) const {
+    const size_t idx = (size_t)m * N + n;
+    if (fuse.p == nullptr) {
+      *reinterpret_cast<float4*>(gpart + (size_t)split * ((size_t)M * N) + idx) = v;
+      return;
+    }
+    float4 mv = *reinterpret_cast<const float4*>(fuse.mu + idx), nv = *reinterpret_cast<const float4*>(fuse.nu + idx);
+    float4 pv = *reinterpret_cast<const float4*>(fuse.p + idx);
+    rmsprop4(pv, mv, nv, v, fuse.lr, fuse.decay, fuse.eps);
+    *reinterpret_cast<float4*>(fuse.g + idx) = v;
+    *reinterpret_cast<float4*>(fuse.mu + idx) = mv;
+    *reinterpret_cast<float4*>(fuse.nu + idx) = nv;
+    *reinterpret_cast<float4*>(fuse.p + idx) = pv;
+    *reinterpret_cast<float4*>(fuse.p_r + idx) = tf32_rn4(pv);
+  }
+};
+
+// dx[m,n=k_in] = relu'(act[m,n]) * sum_k dy[m,k] * W[n,k]
+struct T32DenseDgrad {
+  static constexpr const char* NAME = "fc1_dgrad";
+  static constexpr int BN = 64, KB_MAX = 8;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
+  int M, N, K;              // M = batch, N = IN, K = OUT
+  const float* dy;          // [batch, OUT]
+  const float* w;           // [IN, OUT]
+  const float* act;         // [batch, IN] forward activation feeding this layer
+  float* dx;
+  using ARow = const float*;
+  using ACol = int;
+  using BRow = const float*;
+  using BCol = int;
+  __device__ ARow a_row(int, int m) const { return m < M ? dy + (size_t)m * K : nullptr; }
+  __device__ ACol a_col(int, int k) const { return k < K ? k : -1; }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, dy); }
+  __device__ BRow b_row(int, int n) const { return n < N ? w + (size_t)n * K : nullptr; }
+  __device__ BCol b_col(int, int k) const { return k < K ? k : -1; }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, w); }
+  __device__ void store4(int, int, int m, int n, float4 v) const {
+    const size_t idx = (size_t)m * N + n;
+    const float4 a = __ldg(reinterpret_cast<const float4*>(act + idx));
+    *reinterpret_cast<float4*>(dx + idx) =
+        tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
+  }
+};

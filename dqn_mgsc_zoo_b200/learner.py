@@ -7,7 +7,7 @@ import numpy as np
 from dqn_mgsc_zoo_b200 import _lib
 
 ONLINE, TARGET, MU, NU, GRAD, Q_TM1, Q_TARGET_T, Q_T, TD, LOSS = range(10)
-PRECISIONS = {"fp32": 0, "bf16": 1}
+PRECISIONS = {"fp32": 0, "tf32": 2}
 
 
 class LearnerConfig(ctypes.Structure):
@@ -135,6 +135,18 @@ class Learner:
         _lib.call("dqnb_learner_q_values", self._h, which, s.ctypes.data, s.shape[0], q.ctypes.data,
                   self.stream)
         return q
+
+    def profile(self, iters=20):
+        """Per-kernel device times (us) of one update; advances the state by `iters` updates."""
+        buf = ctypes.create_string_buffer(8192)
+        _lib.call("dqnb_learner_profile", self._h, int(iters), buf, len(buf), self.stream)
+        return buf.value.decode()
+
+    def timeline(self):
+        """Begin/end (us) of every kernel of one graph update; advances the state by 3 updates."""
+        buf = ctypes.create_string_buffer(8192)
+        _lib.call("dqnb_learner_timeline", self._h, buf, len(buf), self.stream)
+        return buf.value.decode()
 
     def launches_per_update(self):
         n = ctypes.c_int64()

@@ -93,7 +93,8 @@ int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]);
  * conv2_d{w[8,8,4,32],b} conv2_d_1{w[4,4,32,64],b} conv2_d_2{w[3,3,64,64],b}
  * linear{w[3136,512],b} linear_1{w[512,A], b[A] or b[1] when shared_bias}. */
 #define DQNB_FP32 0   /* SIMT fp32 kernels; parity tolerance rel 1e-5 */
-#define DQNB_BF16 1   /* tcgen05 bf16 operands, fp32 accumulate; parity tolerance rel 1e-3 class */
+#define DQNB_BF16 1   /* reserved (bf16 operands); not built: TF32 keeps fp32 storage and is 8x more precise */
+#define DQNB_TF32 2   /* tcgen05.mma.kind::tf32 on the fp32 arrays, fp32 accumulate in TMEM; parity tolerance rel 1e-3 */
 
 typedef struct dqnb_learner_config {
   int32_t num_actions;
@@ -101,7 +102,7 @@ typedef struct dqnb_learner_config {
   int32_t double_q;         /* 1: rlax.double_q_learning (double_q/agent.py:97-104) */
   int32_t batch_size;
   int32_t loss_mean_over;   /* rows the loss mean runs over; 0 = batch_size (DP ranks pass the global batch) */
-  int32_t precision;        /* DQNB_FP32 or DQNB_BF16 */
+  int32_t precision;        /* DQNB_FP32 or DQNB_TF32 */
   float learning_rate;      /* optax.rmsprop learning_rate */
   float decay;              /* optax.rmsprop decay */
   float eps;                /* optax.rmsprop eps (inside the rsqrt) */
@@ -145,6 +146,13 @@ int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream);
  * the forward half of select_action (dqn/agent.py:121-129).  Synchronous. */
 int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_host, int32_t n,
                           float* q_host, uintptr_t stream);
+/* Diagnostics: per-kernel device times of one update (the graph's launches run eagerly on one
+ * stream with a CUDA event after each), averaged over `iters` updates of the batch currently in
+ * the learner's buffers; writes a text table "name  us" into `report`. */
+int dqnb_learner_profile(dqnb_learner* h, int iters, char* report, size_t report_len, uintptr_t stream);
+/* Diagnostics: begin/end (us, from %globaltimer) of every kernel of one update as the CUDA graph
+ * really runs it; text table into `report`.  Advances the state by 3 updates. */
+int dqnb_learner_timeline(dqnb_learner* h, char* report, size_t report_len, uintptr_t stream);
 /* number of kernel launches (graph nodes) one update issues. */
 int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
 
