@@ -41,7 +41,8 @@ def parse_args():
     ap.add_argument("--gather-n", type=int, default=4096)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--precision", default="fp32")
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "fp32"],
+                    help="arithmetic of the conv/dense GEMMs: tf32 = tcgen05 tensor cores, fp32 = SIMT")
     return ap.parse_args()
 
 
@@ -237,7 +238,13 @@ def run_ours(args, rank, world, local_rank):
         for _ in range(ADDS_PER_LEARN):
             replay.add(rp.Transition(*pending.pop()))
         device_step()
-        return L.loss()          # D2H read of the step's result
+        return L.loss_lagged()   # queue this step's loss D2H, return the previous step's (already landed)
+
+    def e2e_step_sync():
+        for _ in range(ADDS_PER_LEARN):
+            replay.add(rp.Transition(*pending.pop()))
+        device_step()
+        return L.loss()          # blocking D2H read of this step's loss
 
     def timed(fn, steps):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -262,17 +269,25 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- e2e: new transitions arrive from host memory every step, loss is read back
     e2e_steps = min(args.steps, 1000)
-    pending = [src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + 5))]
-    up0 = store.stats()["planes_uploaded"]
+    sync_steps = min(args.steps, 300)
+    pending = [src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + sync_steps + 10))]
     for _ in range(5):
         e2e_step()
     up0 = store.stats()["planes_uploaded"]
-    ms_e2e = timed(e2e_step, e2e_steps)
+    ms_e2e = timed(e2e_step, e2e_steps)      # the closing barrier waits for the last step's update
+    last_loss = L.loss_take()                 # drain: the final step's loss
     planes = store.stats()["planes_uploaded"] - up0
-    h2d = planes * PLANE / e2e_steps + ADDS_PER_LEARN * 64 + BATCH * 4
+    h2d = planes * PLANE / e2e_steps + ADDS_PER_LEARN * 64 + BATCH * 8
+    for _ in range(3):
+        e2e_step_sync()
+    ms_sync = timed(e2e_step_sync, sync_steps)
     e2e = {"value": world * e2e_steps / (ms_e2e * 1e-3), "unit": "updates/s",
            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "steps": e2e_steps,
-           "what": "4 replay.add(host transition) + sample_slots + update_from_replay + loss readback"}
+           "what": "per step: 4 replay.add(host transition) [H2D of the new frames via pinned staging] + "
+                   "sample_slots + update_from_replay + D2H of the step's loss; the loss copy is queued "
+                   "behind the update and consumed one step later, so host work overlaps the device",
+           "blocking_loss_updates_per_s": world * sync_steps / (ms_sync * 1e-3),
+           "last_loss": last_loss}
 
     # ---- literal seam: update(host NumPy batch), 3.6 MB H2D per step like the reference's jit dispatch
     hb = store.gather_host(replay.sample_slots(BATCH))
@@ -315,6 +330,20 @@ def run_ours(args, rank, world, local_rank):
                        "unit": "GB/s", "frac": UPDATE_BYTES / (ms_upd * 1e-3) / 1e9 / peak,
                        "note": "whole update graph vs 49.05 MB touched-once bytes; batch 32 is latency bound"}
 
+    # ---- the same step with the GEMMs in plain fp32 (SIMT path), for the record
+    other = {}
+    if args.precision == "tf32":
+        L32 = lrn.Learner(NUM_ACTIONS, BATCH, shared_bias=True, double_q=True, precision="fp32", device=local_rank)
+        L32.set_params(init, lrn.ONLINE)
+        L32.set_params(init, lrn.TARGET)
+
+        def fp32_step():
+            L32.update_from_replay(store, replay.sample_slots(BATCH))
+        for _ in range(10):
+            fp32_step()
+        n32 = min(args.steps, 300)
+        other["fp32_simt_updates_per_s"] = world * n32 / (timed(fp32_step, n32) * 1e-3)
+
     if rank != 0:
         return
     cpu = None
@@ -330,7 +359,7 @@ def run_ours(args, rank, world, local_rank):
         "config": workload_config(args), "clocks": clocks.summary(), "e2e": e2e,
         "gpu_launches": int(launches * args.steps), "launches_per_update": int(launches),
         "roofline": roofline, "roofline_update": roofline_update, "cpu_baseline": cpu,
-        "replay_gather_gbs": achieved, "replay_fill_seconds": t_fill, "replay_stats": store.stats(),
+        "other_precisions": other, "replay_gather_gbs": achieved, "replay_fill_seconds": t_fill, "replay_stats": store.stats(),
     }
     print(json.dumps(line), flush=True)
     if dist is not None:

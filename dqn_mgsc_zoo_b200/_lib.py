@@ -41,6 +41,8 @@ SIGNATURES = {
     "dqnb_learner_update_from_replay": [c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_sync_target": [c_vp, STREAM],
     "dqnb_learner_q_values": [c_vp, c_int, c_vp, c_i32, c_vp, STREAM],
+    "dqnb_learner_loss_post": [c_vp, STREAM],
+    "dqnb_learner_loss_take": [c_vp, ctypes.POINTER(ctypes.c_float)],
     "dqnb_learner_launches_per_update": [c_vp, ctypes.POINTER(c_i64)],
     "dqnb_learner_profile": [c_vp, c_int, ctypes.c_char_p, c_sz, STREAM],
     "dqnb_learner_timeline": [c_vp, ctypes.c_char_p, c_sz, STREAM],

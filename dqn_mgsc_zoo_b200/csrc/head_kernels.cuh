@@ -157,10 +157,20 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
 
 // fc2 parameter gradients + scalar loss.  thread (k,a): gW2[k,a] = sum_b h1[b,k] * dq[b,a];
 // block 0 also writes the bias gradient and loss (fixed summation order => reproducible).
+// Host-visible loss ring: every update writes (update sequence number, mean loss) into slot
+// seq % 8 of a pinned, device-mapped array, so the host can pick a step's loss up by polling plain
+// memory - no copy-engine operation and no stream synchronisation on the training stream.
+constexpr int kLossRing = 8;
+struct LossRing {
+  unsigned long long* ring;   // pinned host memory (device-accessible); null = off
+  unsigned* seq;              // device counter of updates executed
+};
+
 __global__ void fc2_wgrad_kernel(int batch, int A, int shared_bias, float inv_mean, const float* __restrict__ h1,
                                  const int32_t* __restrict__ action, const float* __restrict__ dq_taken,
                                  const float* __restrict__ row_loss, float* __restrict__ gw2,
-                                 float* __restrict__ gb2, float* __restrict__ loss, unsigned long long* tl) {
+                                 float* __restrict__ gb2, float* __restrict__ loss, LossRing ring,
+                                 unsigned long long* tl) {
   tl_begin(tl);
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e < kFc1Out * A) {
@@ -186,7 +196,16 @@ __global__ void fc2_wgrad_kernel(int batch, int A, int shared_bias, float inv_me
     float l = 0.f;
     for (int b = lane; b < batch; b += 32) l += row_loss[b];
     l = warp_sum(l);
-    if (lane == 0) *loss = l * inv_mean;
+    if (lane == 0) {
+      const float mean = l * inv_mean;
+      *loss = mean;
+      if (ring.ring != nullptr) {   // (seq, loss) as one 8-byte store into pinned host memory
+        const unsigned seq = *ring.seq + 1;
+        *ring.seq = seq;
+        ring.ring[seq & (kLossRing - 1)] = ((unsigned long long)seq << 32) | __float_as_uint(mean);
+        __threadfence_system();
+      }
+    }
   }
   tl_end(tl);
 }

@@ -5,6 +5,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <chrono>
 #include <vector>
 
 #include "head_kernels.cuh"
@@ -78,8 +79,9 @@ struct dqnb_learner {
   unsigned long long* d_tl = nullptr;
   std::vector<const char*> tl_name;
   int tl_n = 0, tl_graph_n = 0;
+  bool tl_on = false;   // only launches of an update own timeline slots (q_values reuses the kernels)
   unsigned long long* next_tl(const char* name) {
-    if (sizing) return nullptr;
+    if (sizing || !tl_on || tl_n >= 64) return nullptr;
     if ((int)tl_name.size() <= tl_n) tl_name.push_back(name);
     tl_name[tl_n] = name;
     return d_tl ? d_tl + kTlSlot * tl_n++ : nullptr;
@@ -105,6 +107,12 @@ struct dqnb_learner {
   cudaEvent_t pinned_free = nullptr;
   bool pinned_busy = false;
   float* pinned_loss = nullptr;
+  // loss read-back without copies: the update writes (seq, loss) into a pinned ring (LossRing)
+  unsigned long long* loss_ring = nullptr;   // pinned, device-mapped, kLossRing entries
+  unsigned* d_seq = nullptr;                 // device: updates executed so far
+  uint32_t seq_host = 0;                     // host: updates launched so far
+  uint32_t loss_want[kLossRing] = {};        // sequence numbers of the outstanding posts
+  uint64_t loss_posted = 0, loss_taken = 0;
 
   SplitK take_scratch(size_t ws_floats, size_t tiles) {
     SplitK sk{ws ? ws + ws_off : nullptr, counters ? counters + cnt_off : nullptr};
@@ -252,7 +260,8 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
     int n = kFc1Out * h->A;
     fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
                                                      h->dq_taken, h->row_loss, h->grad + h->L.fw2,
-                                                     h->grad + h->L.fb2, h->loss, h->next_tl("fc2_wgrad"));
+                                                     h->grad + h->L.fb2, h->loss, LossRing{h->loss_ring, h->d_seq},
+                                                     h->next_tl("fc2_wgrad"));
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, s1, "fc2_wgrad"));
   }
@@ -326,7 +335,18 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
                        const float* const* wts, cudaStream_t st) {
   const float* in2[kMaxNets]; const float* in3[kMaxNets]; const float* in4[kMaxNets];
   for (int z = 0; z < nets; ++z) { in2[z] = h->a1[z]; in3[z] = h->a2[z]; in4[z] = h->a3[z]; }
-  DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
+  if (nets == 3 && x[1] == x[2] && wts[0] == wts[2]) {   // double-Q update: one merged conv1 GEMM
+    T32ConvFwdDoubleQ<Conv1, uint8_t> p;
+    p.Mh = rows * Conv1::HOUT * Conv1::WOUT;
+    p.M = 2 * p.Mh; p.N = 2 * Conv1::COUT; p.K = Conv1::KCOL;
+    p.x[0] = x[0]; p.x[1] = x[1];
+    p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
+    p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
+    for (int z = 0; z < kMaxNets; ++z) p.y[z] = h->a1[z];
+    DQNB_TRY(run_t32(h, p, 1, t32_splits_for(p, 1), st));
+  } else {
+    DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
+  }
   DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
   DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
   T32DenseFwd p;
@@ -431,7 +451,8 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     int n = kFc1Out * h->A;
     fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
                                                      h->dq_taken, h->row_loss, h->grad + h->L.fw2,
-                                                     h->grad + h->L.fb2, h->loss, h->next_tl("fc2_wgrad"));
+                                                     h->grad + h->L.fb2, h->loss, LossRing{h->loss_ring, h->d_seq},
+                                                     h->next_tl("fc2_wgrad"));
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, s1, "fc2_wgrad"));
   }
@@ -450,7 +471,11 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
   // kernels (conv2 dgrad, conv1 wgrad) leave room for its small CTAs beside their own on every SM.
   bool fused = false;
-  if (B <= kT32BK) { fused = true; DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2))); }
+  if (B <= kT32BK) {
+    fused = true;
+    if (live && !h->profiling) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
+    DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2)));
+  }
   else DQNB_TRY((t32_dense_wgrad<4, 128>(h, B, false, s2)));
   DQNB_TRY((t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1)));
   DQNB_TRY((t32_conv_dgrad<Conv2, 8>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
@@ -475,7 +500,10 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
 }
 
 int enqueue_any(dqnb_learner* h, cudaStream_t st) {
-  return h->tf32 ? enqueue_update_tf32(h, st) : enqueue_update(h, st);
+  h->tl_on = true;
+  const int rc = h->tf32 ? enqueue_update_tf32(h, st) : enqueue_update(h, st);
+  h->tl_on = false;
+  return rc;
 }
 
 int build_graph(dqnb_learner* h) {
@@ -545,6 +573,9 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   h->pinned_bytes = 2 * B * Conv1::IN_PER_IMG + 16 * B;
   DQNB_CUDA(cudaMallocHost(&h->pinned, h->pinned_bytes));
   DQNB_CUDA(cudaMallocHost(&h->pinned_loss, 64));
+  DQNB_CUDA(cudaHostAlloc(&h->loss_ring, sizeof(unsigned long long) * kLossRing, cudaHostAllocMapped));
+  memset(h->loss_ring, 0, sizeof(unsigned long long) * kLossRing);
+  DQNB_TRY(dmalloc(&h->d_seq, 1));
   // size the split-K scratch with a dry pass, then record the graph
   h->sizing = true;
   DQNB_TRY(enqueue_any(h, nullptr));
@@ -575,6 +606,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   if (h->pinned_free) cudaEventDestroy(h->pinned_free);
   if (h->pinned) cudaFreeHost(h->pinned);
   if (h->pinned_loss) cudaFreeHost(h->pinned_loss);
+  if (h->loss_ring) cudaFreeHost(h->loss_ring);
+  cudaFree(h->d_seq);
   delete h;
   return DQNB_OK;
 }
@@ -658,6 +691,7 @@ extern "C" int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, co
   }
   DQNB_CUDA(cudaGraphLaunch(h->graph, st));
   h->updates++;
+  h->seq_host++;
   return DQNB_OK;
 }
 
@@ -692,6 +726,41 @@ extern "C" int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* rep
   DeviceGuard guard(h->device);
   DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->s_tm1, h->s_t, h->act, h->rew, h->disc, as_stream(stream)));
   return dqnb_learner_update(h, h->s_tm1, h->act, h->rew, h->disc, h->s_t, stream);
+}
+
+extern "C" int dqnb_learner_loss_post(dqnb_learner* h, uintptr_t) {
+  DQNB_REQUIRE(h, "null argument");
+  DQNB_REQUIRE(h->seq_host > 0, "no update launched yet");
+  DQNB_REQUIRE(h->loss_posted - h->loss_taken < kLossRing, "%d loss read-backs already outstanding: take one first",
+               kLossRing);
+  h->loss_want[h->loss_posted & (kLossRing - 1)] = h->seq_host;
+  h->loss_posted++;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_loss_take(dqnb_learner* h, float* loss) {
+  DQNB_REQUIRE(h && loss, "null argument");
+  DQNB_REQUIRE(h->loss_posted > h->loss_taken, "no loss read-back outstanding");
+  const uint32_t want = h->loss_want[h->loss_taken & (kLossRing - 1)];
+  h->loss_taken++;
+  volatile unsigned long long* slot = h->loss_ring + (want & (kLossRing - 1));
+  const auto t0 = std::chrono::steady_clock::now();
+  for (uint64_t spins = 0;; ++spins) {
+    const unsigned long long v = *slot;
+    const uint32_t seq = (uint32_t)(v >> 32);
+    if (seq == want) {
+      const uint32_t bits = (uint32_t)v;
+      memcpy(loss, &bits, sizeof(float));
+      return DQNB_OK;
+    }
+    DQNB_REQUIRE((int32_t)(seq - want) < 0, "loss read-back overrun: %d more updates were launched before the take",
+                 kLossRing);
+    if ((spins & 1023) == 1023) {
+      DeviceGuard guard(h->device);
+      DQNB_CUDA(cudaGetLastError());   // surface a faulted device instead of spinning forever
+      DQNB_REQUIRE(std::chrono::steady_clock::now() - t0 < std::chrono::seconds(30), "loss read-back timed out");
+    }
+  }
 }
 
 extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
@@ -759,6 +828,7 @@ extern "C" int dqnb_learner_profile(dqnb_learner* h, int iters, char* report, si
     cudaEventRecord(begin, st);
     rc = enqueue_any(h, st);
     if (rc != DQNB_OK) break;
+    h->seq_host++;
     if (cudaStreamSynchronize(st) != cudaSuccess) { set_error("profile: stream sync failed"); rc = DQNB_ECUDA; break; }
     if (it == 0) { total.assign(h->prof_n, 0.0); continue; }
     for (size_t i = 0; i < h->prof_n; ++i) {
@@ -803,6 +873,7 @@ extern "C" int dqnb_learner_timeline(dqnb_learner* h, char* report, size_t repor
     DQNB_CUDA(cudaMemcpyAsync(h->d_tl, init.data(), bytes, cudaMemcpyHostToDevice, st));
     DQNB_CUDA(cudaStreamSynchronize(st));
     DQNB_CUDA(cudaGraphLaunch(h->graph, st));
+    h->seq_host++;
     DQNB_CUDA(cudaStreamSynchronize(st));
   }
   DQNB_CUDA(cudaMemcpy(got.data(), h->d_tl, bytes, cudaMemcpyDeviceToHost));

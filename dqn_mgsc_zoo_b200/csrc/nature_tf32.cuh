@@ -85,6 +85,65 @@ struct T32ConvFwd {
   }
 };
 
+// Double-Q conv1: three nets but only two distinct inputs and two distinct weight sets.  Staging
+// the im2col A tile is what a conv1 CTA spends its time on, so one GEMM covers all three: rows
+// [0, Mh) are s_tm1, rows [Mh, 2Mh) are s_t, columns [0, COUT) the online filters and
+// [COUT, 2 COUT) the target filters.  The (s_tm1, target) quadrant is computed and dropped (MMA time
+// is not the limit); 200 tiles instead of 300.
+template <class L, class TIn>
+struct T32ConvFwdDoubleQ {
+  static constexpr const char* NAME = "conv_fwd_dq";
+  static constexpr int BN = 2 * L::COUT, KB_MAX = 8;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
+  static constexpr bool A_REG = sizeof(TIn) == 1;
+  int M, N, K, Mh;          // M = 2 * Mh, N = 2 * COUT
+  const TIn* x[2];          // s_tm1, s_t
+  const float* w[2];        // online, target
+  const float* bias[2];
+  float* y[kMaxNets];       // online(s_tm1), target(s_t), online(s_t)
+  using ARow = const TIn*;
+  using ACol = int;
+  struct BRow { int n, which; };   // n (first of 4) inside the net's COUT columns; n = -1: out of range
+  using BCol = int;                // k or -1
+  __device__ ARow a_row(int, int m) const {
+    if (m >= M) return nullptr;
+    const int half = m >= Mh, mm = m - half * Mh;
+    int b = mm / (L::HOUT * L::WOUT), r = mm - b * (L::HOUT * L::WOUT);
+    int i = r / L::WOUT, j = r - i * L::WOUT;
+    return x[half] + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
+  }
+  __device__ ACol a_col(int, int k) const {
+    if (k >= K) return -1;
+    int kh = k / L::ROWLEN;
+    return kh * (L::WIN * L::CIN) + (k - kh * L::ROWLEN);
+  }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, x[0]); }
+  __device__ uint32_t a_get(ARow r, ACol c) const {
+    return (r != nullptr && c >= 0) ? __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(r) + c)) : 0u;
+  }
+  __device__ void a_store(uint32_t dst, uint32_t wd) const { t32_widen4(dst, wd); }
+  __device__ BRow b_row(int, int n) const {
+    if (n >= N) return {-1, 0};
+    return {n % L::COUT, n / L::COUT};
+  }
+  __device__ BCol b_col(int, int k) const { return k < K ? k : -1; }
+  __device__ void b_put(const BRow& r, BCol c, uint32_t dst) const {
+    const bool ok = r.n >= 0 && c >= 0;
+    cp16(dst, ok ? w[r.which] + (size_t)c * L::COUT + r.n : w[0], ok);
+  }
+  __device__ void store4(int, int, int m, int n, float4 v) const {
+    const int half = m >= Mh, which = n >= L::COUT;
+    if (!half && which) return;
+    const int nn = n - which * L::COUT;
+    float* dst = half ? (which ? y[1] : y[2]) : y[0];
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[which] + nn));
+    constexpr float s = InScale<TIn>::value;
+    *reinterpret_cast<float4*>(dst + (size_t)(m - half * Mh) * L::COUT + nn) =
+        tf32_rn4(make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                             fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f)));
+  }
+};
+
 // ---------------------------------------------------------------- conv weight gradient
 // dW[m'=(kh,kw,c), n] = scale * sum_{k'=(b,i,j)} x[...] * dy[k', n]; row m' == KCOL is all ones
 // and yields the bias gradient, which sits right behind the weights in the arena.  Where KCOL is
@@ -149,6 +208,7 @@ __global__ void __launch_bounds__(256) bias_colsum_kernel(const float* __restric
   const int q = blockIdx.x, nq = gridDim.x, t = threadIdx.x, c = t % C, lane = t / C;
   const int beg = (int)((int64_t)rows * q / nq), end = (int)((int64_t)rows * (q + 1) / nq);
   float acc = 0.f;
+#pragma unroll 8
   for (int r = beg + lane; r < end; r += LANES) acc += __ldg(dy + (size_t)r * C + c);
   acc_s[lane][c] = acc;
   __syncthreads();
@@ -160,6 +220,11 @@ __global__ void __launch_bounds__(256) bias_colsum_kernel(const float* __restric
   }
   tl_end(tl, tl_t0);
 }
+
+// An empty node: delays the side-branch kernel queued behind it by one launch latency, so that the
+// chain kernel released by the same event gets its CTAs placed first (launch priorities order
+// pending CTAs but cannot evict ones that are already resident).
+__global__ void stagger_kernel() {}
 
 #include "nature_tf32_more.inl"
 

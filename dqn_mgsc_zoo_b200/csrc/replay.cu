@@ -13,6 +13,8 @@ constexpr int kStageRecords = 64;            // puts per staging batch
 constexpr int kStagePlanes = 256;            // uploaded planes per staging batch
 constexpr int kIdxRing = 8;
 constexpr int kGatherThreads = 256;
+constexpr size_t kZeroCopyBytes = 128 * 1024;   // staged batches up to this size are read in place by the GPU
+constexpr int64_t kZeroCopySlots = 0;           // gather index lists: in-place reads by the gather CTAs measured slower (+7 us at n=32) than the copy
 
 struct Stage {
   uint8_t* host = nullptr;   // pinned: [records][dst ids][planes...]
@@ -52,6 +54,7 @@ struct dqnb_replay {
   cudaEvent_t idx_ev[kIdxRing] = {};
   bool idx_busy[kIdxRing] = {};
   int idx_cur = 0;
+  int idx_pending = -1;                  // ring entry handed to the next gather without a copy
   uint8_t* d_out = nullptr;
   int64_t out_cap = 0;
   int gather_splits = 0;
@@ -90,16 +93,24 @@ int flush(dqnb_replay* h, cudaStream_t st) {
   Stage& s = h->stage[h->cur];
   if (s.n_records == 0 && s.n_planes == 0) return DQNB_OK;
   size_t bytes = h->hdr_bytes + (size_t)s.n_planes * h->plane_stride;
-  DQNB_CUDA(cudaMemcpyAsync(s.dev, s.host, bytes, cudaMemcpyHostToDevice, st));
-  DQNB_CUDA(cudaEventRecord(s.copied, st));
-  s.in_flight = true;
-  int grid = s.n_planes + (s.n_records + 127) / 128;
-  commit_kernel<<<grid, 128, 0, st>>>(
-      h->d_planes, h->plane_stride, h->plane_bytes, s.dev + h->hdr_bytes,
-      reinterpret_cast<const int32_t*>(s.dev + h->hdr_records), s.n_planes,
-      reinterpret_cast<const SlotRecord*>(s.dev), s.n_records, h->d_slot_ids, h->d_actions,
+  // A handful of planes (the steady state: ~1 new frame per put) is read by the commit kernel
+  // straight from the pinned staging buffer over PCIe; a copy-engine hop between two kernels of
+  // the training stream costs more than the transfer.  Big batches (initial fill) are copied.
+  const bool zero_copy = bytes <= kZeroCopyBytes;
+  const uint8_t* src = zero_copy ? s.host : s.dev;
+  if (!zero_copy) {
+    DQNB_CUDA(cudaMemcpyAsync(s.dev, s.host, bytes, cudaMemcpyHostToDevice, st));
+    DQNB_CUDA(cudaEventRecord(s.copied, st));
+  }
+  int grid = s.n_planes + (s.n_records + kCommitThreads - 1) / kCommitThreads;
+  commit_kernel<<<grid, kCommitThreads, 0, st>>>(
+      h->d_planes, h->plane_stride, h->plane_bytes, src + h->hdr_bytes,
+      reinterpret_cast<const int32_t*>(src + h->hdr_records), s.n_planes,
+      reinterpret_cast<const SlotRecord*>(src), s.n_records, h->d_slot_ids, h->d_actions,
       h->d_rewards, h->d_discounts);
   DQNB_CUDA(cudaGetLastError());
+  if (zero_copy) DQNB_CUDA(cudaEventRecord(s.copied, st));   // staging is free once the kernel has read it
+  s.in_flight = true;
   for (int i = 0; i < s.n_records; ++i) h->slot_staged[h->rec_of(s)[i].slot] = 0;
   // planes released during this batch may be handed out again only now (stream order
   // puts their next write after every earlier reader).
@@ -341,6 +352,11 @@ int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* 
     gather_generic<<<(unsigned)n, 128, 0, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
   }
   DQNB_CUDA(cudaGetLastError());
+  if (h->idx_pending >= 0) {
+    DQNB_CUDA(cudaEventRecord(h->idx_ev[h->idx_pending], st));
+    h->idx_busy[h->idx_pending] = true;
+    h->idx_pending = -1;
+  }
   return DQNB_OK;
 }
 
@@ -366,6 +382,11 @@ int upload_slots(dqnb_replay* h, const int64_t* slots, int64_t n, cudaStream_t s
       return DQNB_EINVAL;
     }
     hp[i] = (int32_t)slots[i];
+  }
+  if (n <= kZeroCopySlots) {   // the gather kernel reads the pinned list in place
+    h->idx_pending = k;        // launch_gather records idx_ev[k] behind the kernel
+    *out = hp;
+    return DQNB_OK;
   }
   DQNB_CUDA(cudaMemcpyAsync(dp, hp, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
   DQNB_CUDA(cudaEventRecord(h->idx_ev[k], st));

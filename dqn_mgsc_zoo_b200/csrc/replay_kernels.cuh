@@ -28,8 +28,11 @@ struct ReplayDeviceView {
   int stack;                 // S
 };
 
-// Staged uploads -> pool.  grid.x = n_planes + ceil(n_records/128).
-__global__ void commit_kernel(uint8_t* __restrict__ planes, int64_t plane_stride, int plane_bytes,
+// Staged uploads -> pool.  grid.x = n_planes + ceil(n_records/kCommitThreads).  The staged data
+// may sit in pinned host memory (read over PCIe), so a thread issues all its loads before the
+// first store.
+constexpr int kCommitThreads = 256;
+__global__ void __launch_bounds__(kCommitThreads) commit_kernel(uint8_t* __restrict__ planes, int64_t plane_stride, int plane_bytes,
                               const uint8_t* __restrict__ staged_planes, const int32_t* __restrict__ staged_dst,
                               int n_planes, const SlotRecord* __restrict__ records, int n_records,
                               int32_t* __restrict__ slot_ids, int32_t* __restrict__ actions,
@@ -39,7 +42,15 @@ __global__ void commit_kernel(uint8_t* __restrict__ planes, int64_t plane_stride
     const uint4* src = reinterpret_cast<const uint4*>(staged_planes + (int64_t)b * plane_stride);
     uint4* dst = reinterpret_cast<uint4*>(planes + (int64_t)staged_dst[b] * plane_stride);
     int n16 = (int)(plane_stride >> 4);
-    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = src[i];
+    for (int i0 = threadIdx.x; i0 < n16; i0 += 4 * kCommitThreads) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * kCommitThreads < n16) v[u] = src[i0 + u * kCommitThreads];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * kCommitThreads < n16) dst[i0 + u * kCommitThreads] = v[u];
+    }
     return;
   }
   int r = (b - n_planes) * blockDim.x + threadIdx.x;

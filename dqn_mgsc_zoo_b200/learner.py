@@ -55,6 +55,7 @@ class Learner:
         h = ctypes.c_void_p()
         _lib.call("dqnb_learner_create", ctypes.byref(cfg), device, ctypes.byref(h))
         self._h = h
+        self._loss_outstanding = 0
         n = ctypes.c_int64()
         _lib.call("dqnb_learner_num_params", self._h, ctypes.byref(n))
         self.num_params = n.value
@@ -100,6 +101,24 @@ class Learner:
 
     def loss(self):
         return float(self.read(LOSS)[0])
+
+    def loss_post(self):
+        """Queues a read-back of the latest update's loss behind it (does not wait)."""
+        _lib.call("dqnb_learner_loss_post", self._h, self.stream)
+        self._loss_outstanding += 1
+
+    def loss_take(self):
+        """Waits for the oldest queued loss read-back and returns it."""
+        out = ctypes.c_float()
+        _lib.call("dqnb_learner_loss_take", self._h, ctypes.byref(out))
+        self._loss_outstanding -= 1
+        return float(out.value)
+
+    def loss_lagged(self):
+        """loss_post() for this update, then the previous update's loss (None the first time):
+        per-step statistics without ever idling the device."""
+        self.loss_post()
+        return self.loss_take() if self._loss_outstanding > 1 else None
 
     def update_host(self, s_tm1, a_tm1, r_t, discount_t, s_t):
         """`update(transitions)` with NumPy inputs, like the reference's jit dispatch."""

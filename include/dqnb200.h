@@ -153,6 +153,14 @@ int dqnb_learner_profile(dqnb_learner* h, int iters, char* report, size_t report
 /* Diagnostics: begin/end (us, from %globaltimer) of every kernel of one update as the CUDA graph
  * really runs it; text table into `report`.  Advances the state by 3 updates. */
 int dqnb_learner_timeline(dqnb_learner* h, char* report, size_t report_len, uintptr_t stream);
+/* Loss read-back that neither drains the stream nor uses a copy engine: every update writes
+ * (sequence number, mean loss) into a pinned host ring of 8 entries.  `post` notes the sequence
+ * number of the update launched last; `take` polls host memory until the OLDEST posted entry has
+ * landed and returns it (per-step statistics, consumed one step behind, learner never idle).
+ * At most 8 posts may be outstanding, and a post must be taken before 8 further updates are
+ * launched (overrun is reported as an error); `take` with none outstanding is an error. */
+int dqnb_learner_loss_post(dqnb_learner* h, uintptr_t stream);
+int dqnb_learner_loss_take(dqnb_learner* h, float* loss);
 /* number of kernel launches (graph nodes) one update issues. */
 int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
 
