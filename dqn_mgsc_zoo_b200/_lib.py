@@ -41,6 +41,28 @@ SIGNATURES = {
     "dqnb_learner_update_from_replay": [c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_sync_target": [c_vp, STREAM],
     "dqnb_learner_q_values": [c_vp, c_int, c_vp, c_i32, c_vp, STREAM],
+    "dqnb_learner_device_ptr": [c_vp, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_i64)],
+    "dqnb_learner_write_dev": [c_vp, c_int, c_vp, c_i64, STREAM],
+    "dqnb_learner_apply_grads": [c_vp, STREAM],
+    "dqnb_learner_get_config": [c_vp, c_vp, ctypes.POINTER(c_int)],
+    "dqnb_mgsc_create": [c_vp, c_vp, ctypes.POINTER(c_vp)],
+    "dqnb_mgsc_destroy": [c_vp],
+    "dqnb_mgsc_meta_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_f32, c_f32, c_vp, c_vp,
+                              ctypes.POINTER(c_f32), STREAM],
+    "dqnb_mgsc_meta_update_host": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_f32, c_f32, c_vp,
+                                   c_vp, ctypes.POINTER(c_f32), STREAM],
+    "dqnb_mgsc_read": [c_vp, c_int, c_vp, c_i64],
+    "dqnb_mgsc_write": [c_vp, c_int, c_vp, c_i64],
+    "dqnb_mgsc_adam_count": [c_vp, ctypes.POINTER(c_i32), ctypes.POINTER(c_i32)],
+    "dqnb_logits_create": [c_i64, c_int, ctypes.POINTER(c_vp)],
+    "dqnb_logits_destroy": [c_vp],
+    "dqnb_logits_fill": [c_vp, c_i64, c_i64, STREAM],
+    "dqnb_logits_set": [c_vp, c_vp, c_vp, c_i64, STREAM],
+    "dqnb_logits_get": [c_vp, c_vp, c_vp, c_i64, STREAM],
+    "dqnb_logits_sample": [c_vp, c_vp, c_i64, c_vp, STREAM],
+    "dqnb_logits_lse": [c_vp, ctypes.POINTER(c_f32), STREAM],
+    "dqnb_logits_read": [c_vp, c_vp, c_i64],
+    "dqnb_logits_write": [c_vp, c_vp, c_i64],
     "dqnb_learner_loss_post": [c_vp, STREAM],
     "dqnb_learner_loss_take": [c_vp, ctypes.POINTER(ctypes.c_float)],
     "dqnb_learner_launches_per_update": [c_vp, ctypes.POINTER(c_i64)],

@@ -175,3 +175,93 @@ class DoubleDqn(Dqn):
     the target net values it (rlax.double_q_learning, double_q/agent.py:85-111)."""
 
     _DOUBLE_Q = True
+
+
+ScaleByAdamState = collections.namedtuple("ScaleByAdamState", "count mu nu")
+
+
+class MGSCDqn(Dqn):
+    """MGSC agent (dqn_mgsc_batched/agent.py:40-398): DQN whose replay sampling logits are
+    meta-learned.  Extra constructor keywords `meta_optimizer` (networks.AdamSpec, the reference
+    passes optax.adam, dqn_mgsc_batched/run_atari.py:241-243) and `meta_batch_size`.
+
+    Per step (agent.py:252-278): meta-learn on the newest transition *before* it is added to the
+    replay, then add, learn from a logit-weighted sample, sync.  `meta_update` (agent.py:160-220)
+    runs on the device (dqnb_mgsc_meta_update: per-sample gradients, two virtual RMSProp steps,
+    softmax backward, Adam on the logits); neither params nor RMSProp state advance in it.
+    """
+
+    def __init__(self, *args, meta_optimizer: networks.AdamSpec, meta_batch_size: int, **kwargs):
+        super().__init__(*args, **kwargs)
+        self._meta_batch_size = meta_batch_size
+        self._meta = lrn.MetaLearner(self._learner, meta_batch_size, learning_rate=meta_optimizer.learning_rate,
+                                     b1=meta_optimizer.b1, b2=meta_optimizer.b2, eps=meta_optimizer.eps)
+        self._last_transitions = []
+        self._statistics['meta_loss'] = np.nan
+
+    def step(self, timestep) -> parts.Action:
+        self._frame_t += 1
+
+        timestep = self._preprocessor(timestep)
+
+        transitions = []
+        if timestep is None:  # Repeat action.
+            if self._action is None:
+                raise RuntimeError('Cannot repeat if action has never been selected.')
+            action = self._action
+        else:
+            action = self._action = self._act(timestep)
+            transitions = [t for t in self._transition_accumulator.step(timestep, action)]
+            self._last_transitions = self._last_transitions + transitions
+
+        # Meta-prioritization learn step (agent.py:252-262)
+        if (self._frame_t % self._learn_period == 0) and (
+                self._replay.size >= max(self._meta_batch_size, self._min_replay_capacity)):
+            if len(self._last_transitions) != 0:
+                self._meta_prioritization_learn(self._last_transitions[-1])
+                self._last_transitions.clear()
+        if timestep is not None:
+            for transition in transitions:
+                self._replay.add(transition)
+
+        if self._replay.size < self._min_replay_capacity:
+            return action
+
+        if self._frame_t % self._learn_period == 0:
+            self._learn()
+
+        if self._frame_t % self._target_network_update_period == 0:
+            self._learner.sync_target()
+
+        return action
+
+    def reset(self) -> None:
+        super().reset()
+        self._last_transitions = []
+
+    def _meta_prioritization_learn(self, online_transition) -> None:
+        """agent.py:307-345: draw a uniform meta batch, meta_update, write the logits back."""
+        store = getattr(self._replay, "frame_store", None)
+        if store is not None and hasattr(self._replay, "batch_of_ids_slots_and_logits"):
+            indices, slots, logits = self._replay.batch_of_ids_slots_and_logits(self._meta_batch_size)
+            new_logits, loss = self._meta.meta_update_from_replay(store, slots, logits, online_transition)
+        else:
+            indices, transitions, logits = self._replay.batch_of_ids_transitions_and_logits(self._meta_batch_size)
+            new_logits, loss = self._meta.meta_update(transitions, logits, online_transition)
+        self._statistics['meta_loss'] = loss
+        self._replay.update_priorities(indices, new_logits)
+
+    @property
+    def meta_learner(self) -> lrn.MetaLearner:
+        return self._meta
+
+    def get_state(self) -> Mapping[str, Any]:
+        state = dict(super().get_state())
+        m = self._meta.get_state()
+        state['meta_opt_state'] = (ScaleByAdamState(count=m['count'], mu=m['mu'], nu=m['nu']), EmptyState())
+        return state
+
+    def set_state(self, state: Mapping[str, Any]) -> None:
+        super().set_state(state)
+        adam = state['meta_opt_state'][0]
+        self._meta.set_state({'count': adam.count, 'mu': adam.mu, 'nu': adam.nu})

@@ -290,6 +290,7 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
     DQNB_TRY(fork(h->ev[4], s2, st));
     DQNB_TRY(fork(h->ev[5], s3, st));
   }
+  if (h->cfg.defer_apply) return DQNB_OK;
   h->launches_per_update++;
   if (live) {
     int64_t n4 = (h->L.total >> 2) + 1;
@@ -471,7 +472,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
   // kernels (conv2 dgrad, conv1 wgrad) leave room for its small CTAs beside their own on every SM.
   bool fused = false;
-  if (B <= kT32BK) {
+  if (B <= kT32BK && !h->cfg.defer_apply) {
     fused = true;
     if (live && !h->profiling) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
     DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2)));
@@ -490,9 +491,14 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   if (live) {
     const int64_t split_end = fused ? h->L.fw1 : h->L.fw2;
     const int64_t skip_lo = fused ? h->L.fw1 : 0, skip_hi = fused ? h->L.fw2 : 0;
-    rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
-        h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
-        h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce"));
+    if (h->cfg.defer_apply)   // sum the split-K partials into DQNB_GRAD, nothing else
+      rmsprop_reduce_kernel<false><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
+          h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+          h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("grad_reduce"));
+    else
+      rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
+          h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+          h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce"));
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, st, "rmsprop_reduce"));
   }
@@ -612,6 +618,13 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   return DQNB_OK;
 }
 
+extern "C" int dqnb_learner_get_config(dqnb_learner* h, dqnb_learner_config* cfg, int* device) {
+  DQNB_REQUIRE(h && cfg && device, "null argument");
+  *cfg = h->cfg;
+  *device = h->device;
+  return DQNB_OK;
+}
+
 extern "C" int dqnb_learner_num_params(dqnb_learner* h, int64_t* n) {
   DQNB_REQUIRE(h && n, "null argument");
   *n = h->L.total;
@@ -661,6 +674,48 @@ extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host,
     DQNB_CUDA(cudaGetLastError());
   }
   DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_device_ptr(dqnb_learner* h, int which, void** ptr, int64_t* n) {
+  DQNB_REQUIRE(h && ptr && n, "null argument");
+  float* p; int64_t len;
+  DQNB_TRY(locate(h, which, &p, &len));
+  *ptr = p; *n = len;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* dev_src, int64_t n, uintptr_t stream) {
+  DQNB_REQUIRE(h && dev_src, "null argument");
+  DQNB_REQUIRE(which >= DQNB_ONLINE && which <= DQNB_GRAD, "state array %d is read-only", which);
+  DeviceGuard guard(h->device);
+  float* p; int64_t len;
+  DQNB_TRY(locate(h, which, &p, &len));
+  DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
+  if (p != dev_src) DQNB_CUDA(cudaMemcpyAsync(p, dev_src, sizeof(float) * n, cudaMemcpyDeviceToDevice, as_stream(stream)));
+  if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
+    float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
+    round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream) {
+  DQNB_REQUIRE(h, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  if (h->tf32) {
+    GradRegions none{};
+    rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, 0, 0, 0), 256, 0, st>>>(
+        h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, none, 0, 0, 0, h->cfg.learning_rate,
+        h->cfg.decay, h->cfg.eps, nullptr);
+  } else {
+    int64_t n4 = (h->L.total >> 2) + 1;
+    rmsprop_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(h->online, h->mu, h->nu, h->grad, h->L.total,
+                                                               h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, nullptr);
+  }
+  DQNB_CUDA(cudaGetLastError());
   return DQNB_OK;
 }
 

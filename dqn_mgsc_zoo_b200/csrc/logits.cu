@@ -1,0 +1,336 @@
+// K8a: the MGSC logit ring in HBM (replay_circular.py:148-248 CircularLogitBuffer and the logits
+// half of MGSCReservoirDistribution :500-560).  The reference keeps a float32 NumPy array of
+// `capacity` logits (-inf = empty slot) on the host and walks all of it on every add
+// (logsumexp, :166-179) and every sample (softmax + float64 cumsum + searchsorted inside
+// Generator.choice, :205-217): 1.94 ms per add and 57 ms per sample at capacity 1e6.
+// Here the array lives on the device (4 MB at 1e6: L2-resident), head/tail/size bookkeeping and
+// the random draws stay on the host (same Generator stream as the reference):
+//   fill   : logits[i] = logsumexp(all) - log(size)          two small kernels, no host round trip
+//   sample : p = exp(l - lse) in float32, CDF in float64 (blocked prefix sums + in-order scan inside
+//            the hit block), cdf/cdf[-1] <= u  counted like searchsorted(side='right')
+// HBM/L2-bound streaming reductions; no tensor cores.
+#include <math.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace dqnb;
+
+namespace {
+constexpr int kBlk = 1024;        // logits per CDF block
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ float block_max(float v, float* red) {
+  const int t = threadIdx.x;
+  red[t] = v;
+  __syncthreads();
+  for (int s = kThreads / 2; s > 0; s >>= 1) { if (t < s) red[t] = fmaxf(red[t], red[t + s]); __syncthreads(); }
+  const float r = red[0];
+  __syncthreads();
+  return r;
+}
+template <class T>
+__device__ __forceinline__ T block_sum(T v, T* red) {
+  const int t = threadIdx.x;
+  red[t] = v;
+  __syncthreads();
+  for (int s = kThreads / 2; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  const T r = red[0];
+  __syncthreads();
+  return r;
+}
+
+// pass 1: per-block max
+__global__ void max_kernel(const float* __restrict__ l, int64_t n, float* __restrict__ part) {
+  __shared__ float red[kThreads];
+  float m = -INFINITY;
+  for (int64_t i = (int64_t)blockIdx.x * kBlk + threadIdx.x; i < min((int64_t)(blockIdx.x + 1) * kBlk, n); i += kThreads)
+    m = fmaxf(m, l[i]);
+  m = block_max(m, red);
+  if (threadIdx.x == 0) part[blockIdx.x] = m;
+}
+// pass 2 (one block): global max c -> stat[0]
+__global__ void max_final_kernel(const float* __restrict__ part, int nb, float* __restrict__ stat) {
+  __shared__ float red[kThreads];
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < nb; i += kThreads) m = fmaxf(m, part[i]);
+  m = block_max(m, red);
+  if (threadIdx.x == 0) stat[0] = m;
+}
+// pass 3: per-block sum of exp(l - c) in float32 (the reference sums float32, np.sum pairwise)
+__global__ void sumexp_kernel(const float* __restrict__ l, int64_t n, const float* __restrict__ stat,
+                              float* __restrict__ part) {
+  __shared__ float red[kThreads];
+  const float c = stat[0];
+  float s = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * kBlk + threadIdx.x; i < min((int64_t)(blockIdx.x + 1) * kBlk, n); i += kThreads)
+    s += expf(l[i] - c);
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+// pass 4 (one block): lse = c + log(sum) -> stat[1]; optionally logits[fill_at] = lse - log(size)
+__global__ void lse_final_kernel(const float* __restrict__ part, int nb, float* __restrict__ stat,
+                                 float* __restrict__ l, int64_t fill_at, double log_size) {
+  __shared__ float red[kThreads];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < nb; i += kThreads) s += part[i];
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) {
+    const float lse = stat[0] + logf(s);
+    stat[1] = lse;
+    // np.float32 lse minus np.log(int) (float64), rounded when stored into the float32 array
+    if (fill_at >= 0) l[fill_at] = (float)((double)lse - log_size);
+  }
+}
+// CDF pass: block sums of p = exp(l - lse) accumulated in float64, in index order inside a thread's
+// contiguous run so the blocked sum stays close to the sequential cumsum of the reference.
+__global__ void psum_kernel(const float* __restrict__ l, int64_t n, const float* __restrict__ stat,
+                            double* __restrict__ part) {
+  __shared__ double red[kThreads];
+  const float lse = stat[1];
+  constexpr int RUN = kBlk / kThreads;
+  const int64_t beg = (int64_t)blockIdx.x * kBlk + threadIdx.x * RUN;
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < RUN; ++k)
+    if (beg + k < n) s += (double)expf(l[beg + k] - lse);
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+// (one warp) inclusive prefix of the block sums: lane-contiguous chunks summed in order, a warp
+// scan of the chunk totals, then the chunk re-walked with its offset.
+__global__ void pscan_kernel(double* __restrict__ part, int nb, double* __restrict__ total) {
+  const int lane = threadIdx.x;
+  const int chunk = (nb + 31) / 32, beg = lane * chunk, end = min(beg + chunk, nb);
+  double s = 0.0;
+  for (int i = beg; i < end; ++i) s += part[i];
+  double incl = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  double acc = incl - s;
+  for (int i = beg; i < end; ++i) { acc += part[i]; part[i] = acc; }
+  if (lane == 31) *total = incl;
+}
+// One thread per uniform: binary search over block prefixes, then an in-order scan of the block.
+__global__ void search_kernel(const float* __restrict__ l, int64_t n, const float* __restrict__ stat,
+                              const double* __restrict__ prefix, int nb, const double* __restrict__ total,
+                              const double* __restrict__ u, int count, int64_t* __restrict__ out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= count) return;
+  const double tot = *total, x = u[k];
+  const float lse = stat[1];
+  // first block whose inclusive prefix / total > x
+  int lo = 0, hi = nb - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (prefix[mid] / tot > x) hi = mid; else lo = mid + 1;
+  }
+  double acc = lo > 0 ? prefix[lo - 1] : 0.0;
+  const int64_t beg = (int64_t)lo * kBlk, end = min(beg + kBlk, n);
+  int64_t idx = end;   // searchsorted(side='right'): number of cdf entries <= x
+  for (int64_t i = beg; i < end; ++i) {
+    acc += (double)expf(l[i] - lse);
+    if (acc / tot > x) { idx = i; break; }
+  }
+  out[k] = idx < n ? idx : n - 1;
+}
+__global__ void set_kernel(float* __restrict__ l, const int64_t* __restrict__ idx, const float* __restrict__ v, int n) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) l[idx[k]] = v[k];
+}
+__global__ void get_kernel(const float* __restrict__ l, const int64_t* __restrict__ idx, float* __restrict__ v, int n) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) v[k] = l[idx[k]];
+}
+__global__ void fill_value_kernel(float* __restrict__ l, int64_t n, float v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) l[i] = v;
+}
+}  // namespace
+
+struct dqnb_logits {
+  int device = 0;
+  int64_t capacity = 0;
+  int nb = 0;
+  float* l = nullptr;
+  float* part = nullptr;      // [nb]
+  float* stat = nullptr;      // [0] max, [1] lse
+  double* dpart = nullptr;    // [nb] + [1] total
+  // small pinned/device scratch for index lists
+  int64_t io_cap = 0;
+  int64_t* d_idx = nullptr;
+  float* d_val = nullptr;
+  double* d_u = nullptr;
+  uint8_t* pinned = nullptr;  // io_cap * 16 bytes
+};
+
+namespace {
+int lse_passes(dqnb_logits* h, int64_t fill_at, double log_size, cudaStream_t st) {
+  max_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->part);
+  max_final_kernel<<<1, kThreads, 0, st>>>(h->part, h->nb, h->stat);
+  sumexp_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->stat, h->part);
+  lse_final_kernel<<<1, kThreads, 0, st>>>(h->part, h->nb, h->stat, h->l, fill_at, log_size);
+  DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+int ensure_io(dqnb_logits* h, int64_t n) {
+  if (n <= h->io_cap) return DQNB_OK;
+  DQNB_CUDA(cudaDeviceSynchronize());
+  cudaFree(h->d_idx); cudaFree(h->d_val); cudaFree(h->d_u);
+  if (h->pinned) cudaFreeHost(h->pinned);
+  h->io_cap = std::max<int64_t>(n, 1024);
+  DQNB_CUDA(cudaMalloc(&h->d_idx, sizeof(int64_t) * h->io_cap));
+  DQNB_CUDA(cudaMalloc(&h->d_val, sizeof(float) * h->io_cap));
+  DQNB_CUDA(cudaMalloc(&h->d_u, sizeof(double) * h->io_cap));
+  DQNB_CUDA(cudaMallocHost(&h->pinned, 16 * (size_t)h->io_cap));
+  return DQNB_OK;
+}
+int check_indices(dqnb_logits* h, const int64_t* idx, int64_t n) {
+  for (int64_t i = 0; i < n; ++i)
+    DQNB_REQUIRE(idx[i] >= 0 && idx[i] < h->capacity, "logit index %lld outside [0,%lld)", (long long)idx[i],
+                 (long long)h->capacity);
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_logits_create(int64_t capacity, int device, dqnb_logits** out) {
+  DQNB_REQUIRE(out && capacity >= 1 && capacity <= (int64_t)1 << 31, "bad capacity %lld", (long long)capacity);
+  DeviceGuard guard(device);
+  dqnb_logits* h = new dqnb_logits();
+  h->device = device; h->capacity = capacity;
+  h->nb = (int)((capacity + kBlk - 1) / kBlk);
+  DQNB_CUDA(cudaMalloc(&h->l, sizeof(float) * capacity));
+  DQNB_CUDA(cudaMalloc(&h->part, sizeof(float) * h->nb));
+  DQNB_CUDA(cudaMalloc(&h->stat, sizeof(float) * 4));
+  DQNB_CUDA(cudaMalloc(&h->dpart, sizeof(double) * (h->nb + 1)));
+  fill_value_kernel<<<(unsigned)((capacity + 255) / 256), 256>>>(h->l, capacity, -INFINITY);
+  DQNB_CUDA(cudaGetLastError());
+  DQNB_CUDA(cudaDeviceSynchronize());
+  *out = h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_logits_destroy(dqnb_logits* h) {
+  if (!h) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaDeviceSynchronize();
+  cudaFree(h->l); cudaFree(h->part); cudaFree(h->stat); cudaFree(h->dpart);
+  cudaFree(h->d_idx); cudaFree(h->d_val); cudaFree(h->d_u);
+  if (h->pinned) cudaFreeHost(h->pinned);
+  delete h;
+  return DQNB_OK;
+}
+
+// logits[index] = size == 0 ? 0 : logsumexp(all) - log(size)   (replay_circular.py:166-179, :526-533)
+extern "C" int dqnb_logits_fill(dqnb_logits* h, int64_t index, int64_t size, uintptr_t stream) {
+  DQNB_REQUIRE(h && index >= 0 && index < h->capacity && size >= 0, "bad argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  if (size == 0) {
+    fill_value_kernel<<<1, 32, 0, st>>>(h->l + index, 1, 0.0f);
+    DQNB_CUDA(cudaGetLastError());
+    return DQNB_OK;
+  }
+  return lse_passes(h, index, log((double)size), st);
+}
+
+extern "C" int dqnb_logits_set(dqnb_logits* h, const int64_t* indices, const float* values, int64_t n,
+                               uintptr_t stream) {
+  DQNB_REQUIRE(h && (n == 0 || (indices && values)), "null argument");
+  if (n == 0) return DQNB_OK;
+  DQNB_TRY(check_indices(h, indices, n));
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  if (n == 1) {   // the per-add case (popleft / explicit priority): by value, nothing to wait for
+    fill_value_kernel<<<1, 32, 0, st>>>(h->l + indices[0], 1, values[0]);
+    DQNB_CUDA(cudaGetLastError());
+    return DQNB_OK;
+  }
+  DQNB_TRY(ensure_io(h, n));
+  DQNB_CUDA(cudaStreamSynchronize(st));   // pinned scratch is reused call to call
+  int64_t* pi = reinterpret_cast<int64_t*>(h->pinned);
+  float* pv = reinterpret_cast<float*>(h->pinned + 8 * (size_t)h->io_cap);
+  memcpy(pi, indices, sizeof(int64_t) * n);
+  memcpy(pv, values, sizeof(float) * n);
+  DQNB_CUDA(cudaMemcpyAsync(h->d_idx, pi, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->d_val, pv, sizeof(float) * n, cudaMemcpyHostToDevice, st));
+  set_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->l, h->d_idx, h->d_val, (int)n);
+  DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_logits_get(dqnb_logits* h, const int64_t* indices, float* values, int64_t n, uintptr_t stream) {
+  DQNB_REQUIRE(h && (n == 0 || (indices && values)), "null argument");
+  if (n == 0) return DQNB_OK;
+  DQNB_TRY(check_indices(h, indices, n));
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(ensure_io(h, n));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  int64_t* pi = reinterpret_cast<int64_t*>(h->pinned);
+  float* pv = reinterpret_cast<float*>(h->pinned + 8 * (size_t)h->io_cap);
+  memcpy(pi, indices, sizeof(int64_t) * n);
+  DQNB_CUDA(cudaMemcpyAsync(h->d_idx, pi, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
+  get_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->l, h->d_idx, h->d_val, (int)n);
+  DQNB_CUDA(cudaGetLastError());
+  DQNB_CUDA(cudaMemcpyAsync(pv, h->d_val, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  memcpy(values, pv, sizeof(float) * n);
+  return DQNB_OK;
+}
+
+// Generator.choice(capacity, n, p=softmax(logits)) given the n doubles Generator.random(n) drew
+// (replay_circular.py:205-217); returns absolute slot indices.
+extern "C" int dqnb_logits_sample(dqnb_logits* h, const double* uniforms, int64_t n, int64_t* indices,
+                                  uintptr_t stream) {
+  DQNB_REQUIRE(h && (n == 0 || (uniforms && indices)), "null argument");
+  if (n == 0) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(ensure_io(h, n));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  double* pu = reinterpret_cast<double*>(h->pinned);
+  memcpy(pu, uniforms, sizeof(double) * n);
+  DQNB_CUDA(cudaMemcpyAsync(h->d_u, pu, sizeof(double) * n, cudaMemcpyHostToDevice, st));
+  DQNB_TRY(lse_passes(h, -1, 0.0, st));
+  psum_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->stat, h->dpart);
+  pscan_kernel<<<1, 32, 0, st>>>(h->dpart, h->nb, h->dpart + h->nb);
+  search_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(h->l, h->capacity, h->stat, h->dpart, h->nb,
+                                                         h->dpart + h->nb, h->d_u, (int)n, h->d_idx);
+  DQNB_CUDA(cudaGetLastError());
+  int64_t* pi = reinterpret_cast<int64_t*>(h->pinned + 8 * (size_t)h->io_cap);
+  DQNB_CUDA(cudaMemcpyAsync(pi, h->d_idx, sizeof(int64_t) * n, cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  memcpy(indices, pi, sizeof(int64_t) * n);
+  return DQNB_OK;
+}
+
+// whole-array host copies (get_state / set_state / experiments poking `_logits`); synchronous.
+extern "C" int dqnb_logits_read(dqnb_logits* h, float* host, int64_t n) {
+  DQNB_REQUIRE(h && host && n == h->capacity, "bad argument");
+  DeviceGuard guard(h->device);
+  DQNB_CUDA(cudaMemcpy(host, h->l, sizeof(float) * n, cudaMemcpyDeviceToHost));
+  return DQNB_OK;
+}
+extern "C" int dqnb_logits_write(dqnb_logits* h, const float* host, int64_t n) {
+  DQNB_REQUIRE(h && host && n == h->capacity, "bad argument");
+  DeviceGuard guard(h->device);
+  DQNB_CUDA(cudaMemcpy(h->l, host, sizeof(float) * n, cudaMemcpyHostToDevice));
+  return DQNB_OK;
+}
+extern "C" int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream) {
+  DQNB_REQUIRE(h && lse, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(lse_passes(h, -1, 0.0, st));
+  float stat[2];
+  DQNB_CUDA(cudaMemcpyAsync(stat, h->stat, sizeof(stat), cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  *lse = stat[1];
+  return DQNB_OK;
+}

@@ -1,0 +1,366 @@
+// K8b: MGSC meta_update (dqn_mgsc_batched/agent.py:152-220) on the device.
+//
+//   p = softmax(logits)                                        replay_circular.py:69-86
+//   g_i = grad of the batch-of-1 loss of meta transition i     agent.py:152-158 (clip acts on td itself)
+//   G = sum_i p_i g_i ; theta_exp = theta + u(G; mu, nu)       agent.py:171-179 (virtual RMSProp step)
+//   g2 = grad at theta_exp (target = theta) on the online transition ; theta_tgt = theta_exp + u(g2; mu1, nu1)
+//   L = |theta_exp - theta_tgt|^2 with theta_tgt a constant    agent.py:183-195 (stop_gradient)
+//   dL/dp_i = <v, g_i>,  v = 2 (theta_exp - theta_tgt) * du/dG  (SURVEY R12 identity)
+//   dL/dlogit_j = p_j (dL/dp_j - sum_i p_i dL/dp_i) ; Adam on the (M,) logits   agent.py:206-214
+//
+// The per-sample gradients are materialised like the reference's vmap does (M x 6.75 MB, in HBM):
+// an internal batch-of-1 learner with defer_apply runs once per meta transition on the same
+// kernels as the normal update.  Everything else is a handful of flat streaming kernels.
+#include <algorithm>
+#include <vector>
+
+#include "learner_internal.cuh"
+
+using namespace dqnb;
+
+namespace {
+constexpr int kDotBlocks = 64;     // partial sums per sample in the <v, g_i> reduction
+constexpr int kLossBlocks = 128;   // partial sums of the meta loss
+constexpr int kMaxMeta = 1024;
+
+__global__ void softmax_kernel(const float* __restrict__ logits, float* __restrict__ p, int M) {
+  __shared__ float red[256];
+  const int t = threadIdx.x;
+  float mx = -INFINITY;
+  for (int i = t; i < M; i += 256) mx = fmaxf(mx, logits[i]);
+  red[t] = mx;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (t < s) red[t] = fmaxf(red[t], red[t + s]); __syncthreads(); }
+  mx = red[0];
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = t; i < M; i += 256) sum += expf(logits[i] - mx);
+  red[t] = sum;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  const float lse = mx + logf(red[0]);
+  for (int i = t; i < M; i += 256) p[i] = expf(logits[i] - lse);
+}
+
+// G[j] = sum_i p[i] * per[i][j], i ascending.
+__global__ void weighted_sum_kernel(const float* __restrict__ per, const float* __restrict__ p, float* __restrict__ G,
+                                    int M, int64_t P) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P) return;
+  float acc = 0.f;
+  for (int i = 0; i < M; ++i) acc = fmaf(__ldg(p + i), per[(size_t)i * P + j], acc);
+  G[j] = acc;
+}
+
+// optax 0.1.2 rmsprop(centered) as a pure function: (theta, G, mu, nu) -> (theta_exp, mu1, nu1).
+__global__ void virtual_step_kernel(const float* __restrict__ theta, const float* __restrict__ G,
+                                    const float* __restrict__ mu, const float* __restrict__ nu,
+                                    float* __restrict__ theta_exp, float* __restrict__ mu1, float* __restrict__ nu1,
+                                    int64_t P, float lr, float decay, float eps) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P) return;
+  const float g = G[j], om = 1.0f - decay;
+  const float m = om * g + decay * mu[j];
+  const float v = om * (g * g) + decay * nu[j];
+  mu1[j] = m; nu1[j] = v;
+  theta_exp[j] = theta[j] + (-lr) * (g * rsqrtf(v - m * m + eps));
+}
+
+// Second virtual step and the meta-loss cotangent:
+//   u2 = -lr g2 rsqrt(nu2 - mu2^2 + eps) = theta_tgt - theta_exp ; L = sum u2^2 ; e = -2 u2
+//   v = e * du/dG,  du/dG = -lr s (1 - (1-d) G (G - mu1) s^2),  s = rsqrt(nu1 - mu1^2 + eps)
+__global__ void meta_v_kernel(const float* __restrict__ g2, const float* __restrict__ G, const float* __restrict__ mu1,
+                              const float* __restrict__ nu1, float* __restrict__ v, float* __restrict__ loss_part,
+                              int64_t P, float lr, float decay, float eps) {
+  __shared__ float red[256];
+  const float om = 1.0f - decay;
+  float acc = 0.f;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < P; j += (int64_t)gridDim.x * blockDim.x) {
+    const float g = g2[j], m1 = mu1[j], n1 = nu1[j], gg = G[j];
+    const float m2 = om * g + decay * m1;
+    const float n2 = om * (g * g) + decay * n1;
+    const float u2 = (-lr) * (g * rsqrtf(n2 - m2 * m2 + eps));
+    acc = fmaf(u2, u2, acc);
+    const float s = rsqrtf(n1 - m1 * m1 + eps);
+    const float du = (-lr) * s * (1.0f - om * gg * (gg - m1) * s * s);
+    v[j] = (-2.0f * u2) * du;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) loss_part[blockIdx.x] = red[0];
+}
+
+// part[i][b] = sum over chunk b of per[i][j] * v[j]   (grid = kDotBlocks x M)
+__global__ void dots_kernel(const float* __restrict__ per, const float* __restrict__ v, float* __restrict__ part,
+                            int64_t P) {
+  __shared__ float red[256];
+  const int i = blockIdx.y, b = blockIdx.x;
+  const int64_t chunk = (P + gridDim.x - 1) / gridDim.x;
+  const int64_t beg = (int64_t)b * chunk, end = beg + chunk < P ? beg + chunk : P;
+  const float* row = per + (size_t)i * P;
+  float acc = 0.f;
+  for (int64_t j = beg + threadIdx.x; j < end; j += 256) acc = fmaf(row[j], __ldg(v + j), acc);
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) part[(size_t)i * gridDim.x + b] = red[0];
+}
+
+// softmax backward + optax.adam (scale_by_adam bias-corrected, eps outside the sqrt) on the logits.
+// One block; M <= kMaxMeta.
+__global__ void logits_adam_kernel(const float* __restrict__ logits, const float* __restrict__ p,
+                                   const float* __restrict__ dot_part, const float* __restrict__ loss_part,
+                                   float* __restrict__ dldp, float* __restrict__ adam_m, float* __restrict__ adam_v,
+                                   float* __restrict__ out_logits, float* __restrict__ out_loss, int M, int count,
+                                   float lr, float b1, float b2, float eps) {
+  __shared__ float red[256];
+  __shared__ float d_s[kMaxMeta];
+  const int t = threadIdx.x;
+  float acc = 0.f;
+  for (int i = t; i < M; i += 256) {
+    float d = 0.f;
+    for (int b = 0; b < kDotBlocks; ++b) d += dot_part[(size_t)i * kDotBlocks + b];
+    d_s[i] = d;
+    dldp[i] = d;
+    acc = fmaf(p[i], d, acc);
+  }
+  red[t] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  const float mean = red[0];
+  const float c1 = 1.0f - powf(b1, (float)count), c2 = 1.0f - powf(b2, (float)count);
+  for (int i = t; i < M; i += 256) {
+    const float g = p[i] * (d_s[i] - mean);
+    const float m = (1.0f - b1) * g + b1 * adam_m[i];
+    const float v = (1.0f - b2) * (g * g) + b2 * adam_v[i];
+    adam_m[i] = m; adam_v[i] = v;
+    out_logits[i] = logits[i] + (-lr) * ((m / c1) / (sqrtf(v / c2) + eps));
+  }
+  if (t == 0) {
+    float l = 0.f;
+    for (int b = 0; b < kLossBlocks; ++b) l += loss_part[b];
+    *out_loss = l;
+  }
+}
+}  // namespace
+
+struct dqnb_mgsc {
+  dqnb_learner* main = nullptr;
+  dqnb_learner* sub = nullptr;     // batch-of-1, defer_apply: the per-sample gradient engine
+  dqnb_learner_config lcfg{};
+  dqnb_mgsc_config cfg{};
+  int device = 0, M = 0;
+  int64_t P = 0;
+  size_t img = 0;
+  // meta batch + online transition on the device
+  uint8_t *mb_s0 = nullptr, *mb_s1 = nullptr;
+  int32_t* mb_a = nullptr;
+  float *mb_r = nullptr, *mb_d = nullptr;
+  float *per = nullptr, *G = nullptr, *theta_exp = nullptr, *mu1 = nullptr, *nu1 = nullptr, *v = nullptr;
+  float *logits = nullptr, *p = nullptr, *dldp = nullptr, *dot_part = nullptr, *loss_part = nullptr;
+  float *adam_m = nullptr, *adam_v = nullptr, *out = nullptr;   // out: [M] new logits + [1] loss
+  float* pinned = nullptr;                                      // [2M + 8]
+  int32_t count = 0;                                            // Adam step count
+};
+
+namespace {
+template <class T>
+int dalloc(T** p, size_t count) {
+  DQNB_CUDA(cudaMalloc(p, sizeof(T) * std::max<size_t>(count, 4)));
+  DQNB_CUDA(cudaMemset(*p, 0, sizeof(T) * std::max<size_t>(count, 4)));
+  return DQNB_OK;
+}
+
+// Steps 3..11 of the header comment; the meta batch (M transitions) and the online transition
+// (index M) are already in h->mb_*; h->pinned[0..M) holds the incoming logits.
+int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host, cudaStream_t st) {
+  const int M = h->M;
+  const int64_t P = h->P;
+  const uintptr_t s = reinterpret_cast<uintptr_t>(st);
+  void *theta = nullptr, *theta_t = nullptr, *mu = nullptr, *nu = nullptr, *sub_grad = nullptr;
+  int64_t n = 0;
+  DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_ONLINE, &theta, &n));
+  DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_TARGET, &theta_t, &n));
+  DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_MU, &mu, &n));
+  DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_NU, &nu, &n));
+  DQNB_TRY(dqnb_learner_device_ptr(h->sub, DQNB_GRAD, &sub_grad, &n));
+  DQNB_CUDA(cudaMemcpyAsync(h->logits, h->pinned, sizeof(float) * M, cudaMemcpyHostToDevice, st));
+  softmax_kernel<<<1, 256, 0, st>>>(h->logits, h->p, M);
+  // per-sample gradients at (theta, theta_target)
+  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_ONLINE, static_cast<const float*>(theta), P, s));
+  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_TARGET, static_cast<const float*>(theta_t), P, s));
+  for (int i = 0; i < M; ++i) {
+    DQNB_TRY(dqnb_learner_update(h->sub, h->mb_s0 + i * h->img, h->mb_a + i, h->mb_r + i, h->mb_d + i,
+                                 h->mb_s1 + i * h->img, s));
+    DQNB_CUDA(cudaMemcpyAsync(h->per + (size_t)i * P, sub_grad, sizeof(float) * P, cudaMemcpyDeviceToDevice, st));
+  }
+  const unsigned pb = (unsigned)((P + 255) / 256);
+  weighted_sum_kernel<<<pb, 256, 0, st>>>(h->per, h->p, h->G, M, P);
+  virtual_step_kernel<<<pb, 256, 0, st>>>(static_cast<const float*>(theta), h->G, static_cast<const float*>(mu),
+                                          static_cast<const float*>(nu), h->theta_exp, h->mu1, h->nu1, P,
+                                          h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
+  // gradient at theta_exp against the *online* parameters as target, on the online transition
+  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_ONLINE, h->theta_exp, P, s));
+  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_TARGET, static_cast<const float*>(theta), P, s));
+  DQNB_TRY(dqnb_learner_update(h->sub, h->mb_s0 + M * h->img, h->mb_a + M, h->mb_r + M, h->mb_d + M,
+                               h->mb_s1 + M * h->img, s));
+  meta_v_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->v,
+                                             h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
+  dots_kernel<<<dim3(kDotBlocks, M), 256, 0, st>>>(h->per, h->v, h->dot_part, P);
+  h->count += 1;
+  logits_adam_kernel<<<1, 256, 0, st>>>(h->logits, h->p, h->dot_part, h->loss_part, h->dldp, h->adam_m, h->adam_v,
+                                        h->out, h->out + M, M, h->count, h->cfg.learning_rate, h->cfg.b1,
+                                        h->cfg.b2, h->cfg.eps);
+  DQNB_CUDA(cudaGetLastError());
+  DQNB_CUDA(cudaMemcpyAsync(h->pinned + M, h->out, sizeof(float) * (M + 1), cudaMemcpyDeviceToHost, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));
+  memcpy(new_logits_host, h->pinned + M, sizeof(float) * M);
+  if (meta_loss_host) *meta_loss_host = h->pinned[2 * M];
+  return DQNB_OK;
+}
+
+int stage_online_transition(dqnb_mgsc* h, const uint8_t* s_tm1, int32_t a, float r, float disc, const uint8_t* s_t,
+                            cudaStream_t st) {
+  const int M = h->M;
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s0 + M * h->img, s_tm1, h->img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s1 + M * h->img, s_t, h->img, cudaMemcpyHostToDevice, st));
+  // scalars travel by value through the pinned block (tail), then one small copy each
+  int32_t* pa = reinterpret_cast<int32_t*>(h->pinned + 2 * M + 4);
+  pa[0] = a;
+  h->pinned[2 * M + 5] = r;
+  h->pinned[2 * M + 6] = disc;
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_a + M, pa, 4, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_r + M, h->pinned + 2 * M + 5, 4, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_d + M, h->pinned + 2 * M + 6, 4, cudaMemcpyHostToDevice, st));
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* cfg, dqnb_mgsc** out) {
+  DQNB_REQUIRE(learner && cfg && out, "null argument");
+  DQNB_REQUIRE(cfg->meta_batch_size >= 1 && cfg->meta_batch_size <= kMaxMeta, "meta_batch_size %d not in 1..%d",
+               cfg->meta_batch_size, kMaxMeta);
+  dqnb_mgsc* h = new dqnb_mgsc();
+  h->main = learner;
+  h->cfg = *cfg;
+  h->M = cfg->meta_batch_size;
+  int rc = dqnb_learner_get_config(learner, &h->lcfg, &h->device);
+  if (rc == DQNB_OK && h->lcfg.double_q) {
+    set_error("MGSC uses the q_learning loss (dqn_mgsc_batched/agent.py:104-127): create the learner with double_q=0");
+    rc = DQNB_EINVAL;
+  }
+  if (rc != DQNB_OK) { delete h; return rc; }
+  dqnb_learner_config sc = h->lcfg;
+  sc.batch_size = 1; sc.loss_mean_over = 1; sc.double_q = 0; sc.defer_apply = 1;
+  rc = dqnb_learner_create(&sc, h->device, &h->sub);
+  if (rc != DQNB_OK) { delete h; return rc; }
+  DeviceGuard guard(h->device);
+  DQNB_TRY(dqnb_learner_num_params(learner, &h->P));
+  h->img = 84 * 84 * 4;
+  const size_t M1 = (size_t)h->M + 1, P = (size_t)h->P;
+  DQNB_TRY(dalloc(&h->mb_s0, M1 * h->img)); DQNB_TRY(dalloc(&h->mb_s1, M1 * h->img));
+  DQNB_TRY(dalloc(&h->mb_a, M1)); DQNB_TRY(dalloc(&h->mb_r, M1)); DQNB_TRY(dalloc(&h->mb_d, M1));
+  DQNB_TRY(dalloc(&h->per, (size_t)h->M * P));
+  DQNB_TRY(dalloc(&h->G, P)); DQNB_TRY(dalloc(&h->theta_exp, P)); DQNB_TRY(dalloc(&h->mu1, P));
+  DQNB_TRY(dalloc(&h->nu1, P)); DQNB_TRY(dalloc(&h->v, P));
+  DQNB_TRY(dalloc(&h->logits, M1)); DQNB_TRY(dalloc(&h->p, M1)); DQNB_TRY(dalloc(&h->dldp, M1));
+  DQNB_TRY(dalloc(&h->dot_part, (size_t)h->M * kDotBlocks)); DQNB_TRY(dalloc(&h->loss_part, kLossBlocks));
+  DQNB_TRY(dalloc(&h->adam_m, M1)); DQNB_TRY(dalloc(&h->adam_v, M1)); DQNB_TRY(dalloc(&h->out, M1 + 1));
+  DQNB_CUDA(cudaMallocHost(&h->pinned, sizeof(float) * (2 * M1 + 8)));
+  *out = h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_mgsc_destroy(dqnb_mgsc* h) {
+  if (!h) return DQNB_OK;
+  DeviceGuard guard(h->device);
+  cudaDeviceSynchronize();
+  if (h->sub) dqnb_learner_destroy(h->sub);
+  void* bufs[] = {h->mb_s0, h->mb_s1, h->mb_a, h->mb_r, h->mb_d, h->per, h->G, h->theta_exp, h->mu1, h->nu1, h->v,
+                  h->logits, h->p, h->dldp, h->dot_part, h->loss_part, h->adam_m, h->adam_v, h->out};
+  for (void* b : bufs) cudaFree(b);
+  if (h->pinned) cudaFreeHost(h->pinned);
+  delete h;
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_mgsc_meta_update_host(dqnb_mgsc* h, const uint8_t* s_tm1, const int32_t* a, const float* r,
+                                          const float* disc, const uint8_t* s_t, const float* logits,
+                                          const uint8_t* on_s_tm1, int32_t on_a, float on_r, float on_disc,
+                                          const uint8_t* on_s_t, float* new_logits, float* meta_loss,
+                                          uintptr_t stream) {
+  DQNB_REQUIRE(h && s_tm1 && a && r && disc && s_t && logits && on_s_tm1 && on_s_t && new_logits, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const size_t M = h->M;
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s0, s_tm1, M * h->img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s1, s_t, M * h->img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_a, a, 4 * M, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_r, r, 4 * M, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_d, disc, 4 * M, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaStreamSynchronize(st));   // caller buffers are pageable: do not hold on to them
+  memcpy(h->pinned, logits, sizeof(float) * M);
+  DQNB_TRY(stage_online_transition(h, on_s_tm1, on_a, on_r, on_disc, on_s_t, st));
+  return run_meta_update(h, new_logits, meta_loss, st);
+}
+
+extern "C" int dqnb_mgsc_meta_update(dqnb_mgsc* h, dqnb_replay* replay, const int64_t* slots_host,
+                                     const float* logits, const uint8_t* on_s_tm1, int32_t on_a, float on_r,
+                                     float on_disc, const uint8_t* on_s_t, float* new_logits, float* meta_loss,
+                                     uintptr_t stream) {
+  DQNB_REQUIRE(h && replay && slots_host && logits && on_s_tm1 && on_s_t && new_logits, "null argument");
+  int H, W, S;
+  replay_frame_shape(replay, &H, &W, &S);
+  DQNB_REQUIRE(H == 84 && W == 84 && S == 4, "replay frames %dx%dx%d are not 84x84x4", H, W, S);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(replay_gather_into(replay, slots_host, h->M, h->mb_s0, h->mb_s1, h->mb_a, h->mb_r, h->mb_d, st));
+  memcpy(h->pinned, logits, sizeof(float) * h->M);
+  DQNB_TRY(stage_online_transition(h, on_s_tm1, on_a, on_r, on_disc, on_s_t, st));
+  return run_meta_update(h, new_logits, meta_loss, st);
+}
+
+namespace {
+int mgsc_locate(dqnb_mgsc* h, int which, float** p, int64_t* n) {
+  switch (which) {
+    case DQNB_MGSC_ADAM_M: *p = h->adam_m; *n = h->M; break;
+    case DQNB_MGSC_ADAM_V: *p = h->adam_v; *n = h->M; break;
+    case DQNB_MGSC_P: *p = h->p; *n = h->M; break;
+    case DQNB_MGSC_DL_DP: *p = h->dldp; *n = h->M; break;
+    case DQNB_MGSC_G: *p = h->G; *n = h->P; break;
+    case DQNB_MGSC_V: *p = h->v; *n = h->P; break;
+    case DQNB_MGSC_THETA_EXP: *p = h->theta_exp; *n = h->P; break;
+    default: set_error("unknown MGSC array %d", which); return DQNB_EINVAL;
+  }
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_mgsc_read(dqnb_mgsc* h, int which, float* host, int64_t n) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DeviceGuard guard(h->device);
+  float* p; int64_t len;
+  DQNB_TRY(mgsc_locate(h, which, &p, &len));
+  DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
+  DQNB_CUDA(cudaMemcpy(host, p, sizeof(float) * n, cudaMemcpyDeviceToHost));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_mgsc_write(dqnb_mgsc* h, int which, const float* host, int64_t n) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DQNB_REQUIRE(which == DQNB_MGSC_ADAM_M || which == DQNB_MGSC_ADAM_V, "MGSC array %d is read-only", which);
+  DeviceGuard guard(h->device);
+  float* p; int64_t len;
+  DQNB_TRY(mgsc_locate(h, which, &p, &len));
+  DQNB_REQUIRE(n == len, "length %lld != %lld", (long long)n, (long long)len);
+  DQNB_CUDA(cudaMemcpy(p, host, sizeof(float) * n, cudaMemcpyHostToDevice));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_mgsc_adam_count(dqnb_mgsc* h, int32_t* get, const int32_t* set) {
+  DQNB_REQUIRE(h, "null argument");
+  if (set) h->count = *set;
+  if (get) *get = h->count;
+  return DQNB_OK;
+}

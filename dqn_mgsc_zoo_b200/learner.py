@@ -15,7 +15,8 @@ class LearnerConfig(ctypes.Structure):
                 ("double_q", ctypes.c_int32), ("batch_size", ctypes.c_int32),
                 ("loss_mean_over", ctypes.c_int32), ("precision", ctypes.c_int32),
                 ("learning_rate", ctypes.c_float), ("decay", ctypes.c_float),
-                ("eps", ctypes.c_float), ("grad_error_bound", ctypes.c_float)]
+                ("eps", ctypes.c_float), ("grad_error_bound", ctypes.c_float),
+                ("defer_apply", ctypes.c_int32)]
 
 
 def param_shapes(num_actions, shared_bias=False):
@@ -45,13 +46,14 @@ def unflatten_params(flat, num_actions, shared_bias=False):
 class Learner:
     def __init__(self, num_actions, batch_size, shared_bias=False, double_q=False, learning_rate=0.00025,
                  decay=0.95, eps=0.01 / 32 ** 2, grad_error_bound=1.0 / 32, precision="fp32", device=0,
-                 stream=0, loss_mean_over=0):
+                 stream=0, loss_mean_over=0, defer_apply=False):
         self.num_actions, self.batch_size = int(num_actions), int(batch_size)
         self.shared_bias, self.double_q = bool(shared_bias), bool(double_q)
         self.device, self.stream = device, stream
         cfg = LearnerConfig(self.num_actions, int(self.shared_bias), int(self.double_q), self.batch_size,
                             int(loss_mean_over), PRECISIONS[precision], learning_rate, decay, eps,
-                            grad_error_bound)
+                            grad_error_bound, int(bool(defer_apply)))
+        self.defer_apply = bool(defer_apply)
         h = ctypes.c_void_p()
         _lib.call("dqnb_learner_create", ctypes.byref(cfg), device, ctypes.byref(h))
         self._h = h
@@ -101,6 +103,16 @@ class Learner:
 
     def loss(self):
         return float(self.read(LOSS)[0])
+
+    def device_ptr(self, which):
+        """(device address, length) of a state array - e.g. the flat gradient arena for NCCL."""
+        ptr, n = ctypes.c_void_p(), ctypes.c_int64()
+        _lib.call("dqnb_learner_device_ptr", self._h, which, ctypes.byref(ptr), ctypes.byref(n))
+        return ptr.value, n.value
+
+    def apply_grads(self):
+        """optimizer.update + apply_updates on the gradient arena (second half of a deferred update)."""
+        _lib.call("dqnb_learner_apply_grads", self._h, self.stream)
 
     def loss_post(self):
         """Queues a read-back of the latest update's loss behind it (does not wait)."""
@@ -174,3 +186,99 @@ class Learner:
 
     def synchronize(self):
         _lib.call("dqnb_stream_sync", self.stream)
+
+
+class MgscConfig(ctypes.Structure):
+    _fields_ = [("meta_batch_size", ctypes.c_int32), ("learning_rate", ctypes.c_float),
+                ("b1", ctypes.c_float), ("b2", ctypes.c_float), ("eps", ctypes.c_float)]
+
+
+MGSC_ADAM_M, MGSC_ADAM_V, MGSC_P, MGSC_DL_DP, MGSC_G, MGSC_V, MGSC_THETA_EXP = range(7)
+
+
+class MetaLearner:
+    """`meta_update` of dqn_mgsc_batched/agent.py:160-220 over libdqnb200 (dqnb_mgsc_*).
+
+    Reads the learner's params / RMSProp state (virtual steps only), owns the optax.adam state of
+    the (meta_batch_size,) logits vector.
+    """
+
+    def __init__(self, learner: Learner, meta_batch_size, learning_rate=0.00025, b1=0.9, b2=0.999, eps=1e-8):
+        if learner.double_q:
+            raise ValueError("MGSC uses the q_learning loss: the learner must have double_q=False")
+        self.learner, self.meta_batch_size = learner, int(meta_batch_size)
+        cfg = MgscConfig(self.meta_batch_size, learning_rate, b1, b2, eps)
+        h = ctypes.c_void_p()
+        _lib.call("dqnb_mgsc_create", learner._h, ctypes.byref(cfg), ctypes.byref(h))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            _lib.call("dqnb_mgsc_destroy", self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _online(transition):
+        s0 = np.ascontiguousarray(transition[0], dtype=np.uint8)
+        s1 = np.ascontiguousarray(transition[4], dtype=np.uint8)
+        if s0.shape != (84, 84, 4) or s1.shape != (84, 84, 4):
+            raise ValueError("online transition stacks must be (84, 84, 4) uint8, got %s / %s" % (s0.shape, s1.shape))
+        return s0, int(transition[1]), float(transition[2]), float(transition[3]), s1
+
+    def meta_update(self, transitions, logits, online_transition):
+        """Host meta batch (stacked NumPy fields).  Returns (new_logits float32 [M], meta_loss)."""
+        M = self.meta_batch_size
+        s0 = np.ascontiguousarray(transitions[0], dtype=np.uint8)
+        s1 = np.ascontiguousarray(transitions[4], dtype=np.uint8)
+        a = np.ascontiguousarray(transitions[1], dtype=np.int32)
+        r = np.ascontiguousarray(transitions[2], dtype=np.float32)
+        d = np.ascontiguousarray(transitions[3], dtype=np.float32)
+        lg = np.ascontiguousarray(logits, dtype=np.float32)
+        if s0.shape != (M, 84, 84, 4) or s1.shape != s0.shape or a.shape != (M,) or lg.shape != (M,):
+            raise ValueError("meta batch shapes %s %s %s do not match meta_batch_size=%d"
+                             % (s0.shape, a.shape, lg.shape, M))
+        o0, oa, orr, od, o1 = self._online(online_transition)
+        out, loss = np.empty(M, dtype=np.float32), ctypes.c_float()
+        _lib.call("dqnb_mgsc_meta_update_host", self._h, s0.ctypes.data, a.ctypes.data, r.ctypes.data,
+                  d.ctypes.data, s1.ctypes.data, lg.ctypes.data, o0.ctypes.data, oa, orr, od, o1.ctypes.data,
+                  out.ctypes.data, ctypes.byref(loss), self.learner.stream)
+        return out, float(loss.value)
+
+    def meta_update_from_replay(self, frame_store, slots, logits, online_transition):
+        """Meta batch gathered on the device from replay slots."""
+        M = self.meta_batch_size
+        sl = np.ascontiguousarray(slots, dtype=np.int64)
+        lg = np.ascontiguousarray(logits, dtype=np.float32)
+        if sl.shape != (M,) or lg.shape != (M,):
+            raise ValueError("need %d slots and logits, got %s / %s" % (M, sl.shape, lg.shape))
+        o0, oa, orr, od, o1 = self._online(online_transition)
+        out, loss = np.empty(M, dtype=np.float32), ctypes.c_float()
+        _lib.call("dqnb_mgsc_meta_update", self._h, frame_store.handle, sl.ctypes.data, lg.ctypes.data,
+                  o0.ctypes.data, oa, orr, od, o1.ctypes.data, out.ctypes.data, ctypes.byref(loss),
+                  self.learner.stream)
+        return out, float(loss.value)
+
+    def read(self, which):
+        n = self.meta_batch_size if which <= MGSC_DL_DP else self.learner.num_params
+        out = np.empty(n, dtype=np.float32)
+        _lib.call("dqnb_mgsc_read", self._h, which, out.ctypes.data, n)
+        return out
+
+    def get_state(self):
+        """(count, mu, nu) like optax ScaleByAdamState."""
+        c = ctypes.c_int32()
+        _lib.call("dqnb_mgsc_adam_count", self._h, ctypes.byref(c), None)
+        return {"count": int(c.value), "mu": self.read(MGSC_ADAM_M), "nu": self.read(MGSC_ADAM_V)}
+
+    def set_state(self, state):
+        for which, key in ((MGSC_ADAM_M, "mu"), (MGSC_ADAM_V, "nu")):
+            v = np.ascontiguousarray(state[key], dtype=np.float32)
+            _lib.call("dqnb_mgsc_write", self._h, which, v.ctypes.data, v.size)
+        c = ctypes.c_int32(int(state["count"]))
+        _lib.call("dqnb_mgsc_adam_count", self._h, None, ctypes.byref(c))

@@ -107,6 +107,9 @@ typedef struct dqnb_learner_config {
   float decay;              /* optax.rmsprop decay */
   float eps;                /* optax.rmsprop eps (inside the rsqrt) */
   float grad_error_bound;   /* rlax.clip_gradient bound */
+  int32_t defer_apply;      /* 1: update() stops after the gradient (DQNB_GRAD holds it); the optimiser
+                               step runs in dqnb_learner_apply_grads - the seam for the data-parallel
+                               all-reduce and for the MGSC per-sample gradients */
 } dqnb_learner_config;
 
 /* state arrays addressable by read/write */
@@ -127,6 +130,14 @@ int dqnb_learner_num_params(dqnb_learner* h, int64_t* n);
 /* host <-> device copies of a state array (synchronous); n must equal the array length. */
 int dqnb_learner_write(dqnb_learner* h, int which, const float* host, int64_t n, uintptr_t stream);
 int dqnb_learner_read(dqnb_learner* h, int which, float* host, int64_t n, uintptr_t stream);
+/* device pointer + length of a state array (library-owned; valid until destroy).  Lets the
+ * caller hand the flat gradient arena to NCCL, or alias state into its own tensors. */
+int dqnb_learner_device_ptr(dqnb_learner* h, int which, void** ptr, int64_t* n);
+/* device -> device write of a state array (same rules as dqnb_learner_write; asynchronous). */
+int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* dev_src, int64_t n, uintptr_t stream);
+/* optimizer.update + apply_updates (dqn/agent.py:115-116) on whatever DQNB_GRAD holds; the second
+ * half of an update for learners created with defer_apply = 1. */
+int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream);
 /* one `update` on a batch that is already in device memory (asynchronous). */
 int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, const int32_t* a_dev,
                         const float* r_dev, const float* disc_dev, const uint8_t* s_t_dev,
@@ -163,6 +174,68 @@ int dqnb_learner_loss_post(dqnb_learner* h, uintptr_t stream);
 int dqnb_learner_loss_take(dqnb_learner* h, float* loss);
 /* number of kernel launches (graph nodes) one update issues. */
 int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n);
+
+/* the configuration and device a learner was created with. */
+int dqnb_learner_get_config(dqnb_learner* h, dqnb_learner_config* cfg, int* device);
+
+/* ---------------------------------------------------------------------------------------------
+ * MGSC meta_update (dqn_mgsc_batched/agent.py:160-220; meta optimiser optax.adam,
+ * dqn_mgsc_batched/run_atari.py:241-243, state shape (meta_batch_size,) agent.py:80).
+ * Reads the learner's online/target params and RMSProp state without advancing them (virtual
+ * steps), returns the updated logits of the meta batch and advances its own Adam state.
+ * The learner must use the q_learning loss (double_q = 0).  Synchronous.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct dqnb_mgsc dqnb_mgsc;
+typedef struct dqnb_mgsc_config {
+  int32_t meta_batch_size;   /* M */
+  float learning_rate;       /* optax.adam learning_rate */
+  float b1, b2, eps;         /* optax.adam defaults 0.9, 0.999, 1e-8 */
+} dqnb_mgsc_config;
+#define DQNB_MGSC_ADAM_M 0      /* [M] Adam first moment (read/write) */
+#define DQNB_MGSC_ADAM_V 1      /* [M] Adam second moment (read/write) */
+#define DQNB_MGSC_P 2           /* [M] softmax(logits) of the last call */
+#define DQNB_MGSC_DL_DP 3       /* [M] dL/dp_i of the last call */
+#define DQNB_MGSC_G 4           /* [params] sum_i p_i g_i */
+#define DQNB_MGSC_V 5           /* [params] dL/dG */
+#define DQNB_MGSC_THETA_EXP 6   /* [params] expected online params */
+int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* cfg, dqnb_mgsc** out);
+int dqnb_mgsc_destroy(dqnb_mgsc* h);
+/* meta batch = M replay slots gathered on the device (replay_circular.py:1270-1275), online
+ * transition and logits from host memory; new_logits[M] and *meta_loss (nullable) to host. */
+int dqnb_mgsc_meta_update(dqnb_mgsc* h, dqnb_replay* replay, const int64_t* slots_host, const float* logits,
+                          const uint8_t* on_s_tm1, int32_t on_a, float on_r, float on_disc,
+                          const uint8_t* on_s_t, float* new_logits, float* meta_loss, uintptr_t stream);
+/* same with the meta batch in host arrays ([M,84,84,4] uint8 stacks, [M] scalars). */
+int dqnb_mgsc_meta_update_host(dqnb_mgsc* h, const uint8_t* s_tm1, const int32_t* a, const float* r,
+                               const float* disc, const uint8_t* s_t, const float* logits,
+                               const uint8_t* on_s_tm1, int32_t on_a, float on_r, float on_disc,
+                               const uint8_t* on_s_t, float* new_logits, float* meta_loss, uintptr_t stream);
+int dqnb_mgsc_read(dqnb_mgsc* h, int which, float* host, int64_t n);
+int dqnb_mgsc_write(dqnb_mgsc* h, int which, const float* host, int64_t n);
+/* Adam step count: *get receives it (nullable), *set overwrites it (nullable). */
+int dqnb_mgsc_adam_count(dqnb_mgsc* h, int32_t* get, const int32_t* set);
+
+/* ---------------------------------------------------------------------------------------------
+ * MGSC logit ring in device memory (replay_circular.py:148-248 CircularLogitBuffer; the logits of
+ * MGSCReservoirDistribution :500-560).  The array of `capacity` float32 logits (-inf = empty) lives
+ * in HBM; ring heads, sizes and the NumPy Generator stay with the caller.  Indices are ABSOLUTE.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct dqnb_logits dqnb_logits;
+int dqnb_logits_create(int64_t capacity, int device, dqnb_logits** out);
+int dqnb_logits_destroy(dqnb_logits* h);
+/* logits[index] = size == 0 ? 0 : logsumexp(all logits) - log(size)  (add(), :166-179; reservoir
+ * replace :526-533 after the slot was set to -inf).  Asynchronous, no host round trip. */
+int dqnb_logits_fill(dqnb_logits* h, int64_t index, int64_t size, uintptr_t stream);
+int dqnb_logits_set(dqnb_logits* h, const int64_t* indices, const float* values, int64_t n, uintptr_t stream);
+int dqnb_logits_get(dqnb_logits* h, const int64_t* indices, float* values, int64_t n, uintptr_t stream);
+/* Generator.choice(capacity, n, p=softmax(logits)) for the n doubles the caller drew with
+ * Generator.random(n) (what choice() consumes, :205-217): float32 softmax, float64 CDF,
+ * searchsorted(side='right').  Synchronous. */
+int dqnb_logits_sample(dqnb_logits* h, const double* uniforms, int64_t n, int64_t* indices, uintptr_t stream);
+int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream);
+/* whole-array copies for get_state / set_state / `_logits` pokes; n must equal capacity. */
+int dqnb_logits_read(dqnb_logits* h, float* host, int64_t n);
+int dqnb_logits_write(dqnb_logits* h, const float* host, int64_t n);
 
 /* Test hook (not part of the drop-in surface): C[M,N] = A*B^T through the tcgen05 tile GEMM on
  * fp32 device matrices (operands rounded to bf16); *_mn_major selects [K,M]/[K,N] storage. */
