@@ -41,6 +41,10 @@ def parse_args():
     ap.add_argument("--gather-n", type=int, default=4096)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="replicas", choices=["replicas", "dp"],
+                    help="N>1: independent agent replicas (weak scaling, the reference's way) or one "
+                         "data-parallel learner on a fixed global batch (strong scaling, NCCL all-reduce)")
+    ap.add_argument("--global-batch", type=int, default=4096, help="dp mode: global batch")
     ap.add_argument("--precision", default="tf32", choices=["tf32", "fp32"],
                     help="arithmetic of the conv/dense GEMMs: tf32 = tcgen05 tensor cores, fp32 = SIMT")
     return ap.parse_args()
@@ -366,6 +370,124 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+UPDATE_FLOP_PER_SAMPLE = 86_906_880     # double-Q update, A=6
+
+
+def run_dp(args, rank, world, local_rank):
+    """one learner, fixed global batch, rows sharded over the ranks, one NCCL
+    all-reduce of the flat 6.75 MB gradient arena per update.  Replay replicated on every rank."""
+    import torch
+    import torch.distributed as dist
+    from dqn_mgsc_zoo_b200 import learner as lrn
+    from dqn_mgsc_zoo_b200 import networks, parallel
+    from dqn_mgsc_zoo_b200 import replay as rp
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    G = args.global_batch
+    capacity = min(args.capacity, 200_000)     # replicated ring; sampling pattern, not size, matters here
+    replay = rp.TransitionReplay(capacity, rp.Transition(None, None, None, None, None),
+                                 np.random.RandomState(0), device=local_rank)      # same seed: replicas
+    src = EpisodeSource(1000)
+    for _ in range(capacity):
+        replay.add(rp.Transition(*src.next()))
+    store = replay.frame_store
+    store.flush()
+    dp = parallel.make_nccl_learner(NUM_ACTIONS, G, local_rank, rank, world, shared_bias=True, double_q=True,
+                                    precision=args.precision)
+    L = dp.learner
+    init = networks.init_params(np.random.default_rng(0), NUM_ACTIONS, shared_bias=True)
+    L.set_params(init, lrn.ONLINE)
+    L.set_params(init, lrn.TARGET)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        dp.update_from_replay(store, replay.sample_slots(G))      # identical draw on every rank
+
+    pending = []
+
+    def e2e_step():
+        for _ in range(ADDS_PER_LEARN):
+            replay.add(rp.Transition(*pending.pop()))
+        device_step()
+        return L.loss_lagged()
+
+    def timed(fn, steps):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    steps = min(args.steps, 300)
+    for _ in range(max(3, min(args.warmup, 10))):
+        device_step()
+    with ClockSampler(local_rank) as clocks:
+        ms = timed(device_step, steps)
+    value = steps / (ms * 1e-3)
+    e2e_steps = min(steps, 100)
+    pending.extend(src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + 5)))
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, e2e_steps)
+    L.loss_take()
+    params = L.read(lrn.ONLINE)
+    digest = float(np.abs(params).sum())
+    same = True
+    if world > 1:     # replicas must hold bit-identical parameters after the run
+        t = torch.tensor([digest], device="cuda", dtype=torch.float64)
+        lo, hi = t.clone(), t.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool(lo.item() == hi.item())
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        tf = UPDATE_FLOP_PER_SAMPLE * G * value / 1e12
+        peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1398.4))
+        line = {
+            "metric": "learner_updates_per_s", "value": value, "unit": "updates/s", "n_gpus": world, "steps": steps,
+            "warmup": max(3, min(args.warmup, 10)), "ms_per_step": ms / steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else args.precision,
+            "data": "synthetic",
+            "config": {"workload": "data-parallel double_q learner, Nature CNN, GLOBAL batch %d (%d per GPU), "
+                                   "replicated %d-transition FIFO replay, one NCCL all-reduce of the 6.75 MB "
+                                   "gradient arena per update" % (G, G // world, capacity),
+                       "global_batch": G, "parallelism": "dp%d" % world,
+                       "l2": "random slots from a %.1f GB plane pool every step" % (capacity * 7056 / 1e9)},
+            "clocks": clocks.summary(), "samples_per_s": value * G,
+            "e2e": {"value": e2e_steps / (ms_e2e * 1e-3), "unit": "updates/s",
+                    "h2d_bytes_per_step": ADDS_PER_LEARN * (PLANE + 64) + G * 8, "d2h_bytes_per_step": 4,
+                    "what": "4 replicated replay.add + sample_slots(global batch) + sharded update + all-reduce "
+                            "+ apply + lagged loss read"},
+            "gpu_launches": int((L.launches_per_update() + 2) * steps),
+            "roofline": {"bound": "tensor", "achieved": tf / world, "peak": peak, "unit": "TFLOP/s",
+                         "frac": tf / world / peak, "traffic": None,
+                         "note": "per-GPU algorithmic flops (86.9 MFLOP x rows) / step time vs measured dense "
+                                 "bf16 peak; kind::tf32 nominal peak is half of bf16"},
+            "cpu_baseline": None, "replicas_identical": same,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -373,6 +495,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.mode == "dp":
+        run_dp(args, rank, world, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 
