@@ -29,6 +29,7 @@ TARGET_SYNC_UPDATES = 7500         # 1.2e5 frames / 16 (double_q/run_atari.py:86
 PLANE = 84 * 84
 GATHER_BYTES_PER_TRANSITION = 13 * PLANE + 12     # 5 planes read + 8 written + scalars
 UPDATE_BYTES = 49.05e6             # params/opt-state touched once + batch
+NCU_GATHER_TRAFFIC_BYTES = 309.9e6 # dram__bytes_read.sum + dram__bytes_write.sum of gather_stack4 at n=4096 (r01b)
 
 
 def parse_args():
@@ -308,11 +309,12 @@ def run_ours(args, rank, world, local_rank):
     ai = torch.empty(n, dtype=torch.int32, device="cuda")
     rf, df = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
     rs = np.random.RandomState(99 + rank)
-    slot_sets = [rs.randint(args.capacity, size=n).astype(np.int64) for _ in range(24)]
+    # slot lists pre-uploaded (int32, device): the timed region is the gather kernel alone
+    slot_sets = [torch.from_numpy(rs.randint(args.capacity, size=n).astype(np.int32)).cuda() for _ in range(24)]
 
     def gather_step(i=[0]):
-        store.gather(slot_sets[i[0] % len(slot_sets)], bufs[0].data_ptr(), bufs[1].data_ptr(), ai.data_ptr(),
-                     rf.data_ptr(), df.data_ptr())
+        store.gather_dev(slot_sets[i[0] % len(slot_sets)].data_ptr(), n, bufs[0].data_ptr(), bufs[1].data_ptr(),
+                         ai.data_ptr(), rf.data_ptr(), df.data_ptr())
         i[0] += 1
     for _ in range(4):
         gather_step()
@@ -326,9 +328,14 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
     achieved = n * GATHER_BYTES_PER_TRANSITION / (ms_g * 1e-3) / 1e9
     roofline = {"kernel": "gather_stack4", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC_BYTES, "peak_source": peak_src,
                 "transitions_per_launch": n, "us_per_launch": ms_g * 1e3,
-                "note": "timed with CUDA events around %d launches incl. the 16 KB slot-index upload each" % greps}
+                "algorithmic_bytes_per_launch": n * GATHER_BYTES_PER_TRANSITION,
+                "note": "CUDA events around %d back-to-back launches on the launching stream, slot lists already on "
+                        "the device; 24 different random slot lists over a %.1f GB plane pool (>> L2). traffic = "
+                        "dram read+write per launch from profiles/r01b_ncu_full_summary.csv (ncu --set full, "
+                        "60k-transition pool; write-back of the last lines is still in L2 when the kernel ends)"
+                        % (greps, store.stats()["hbm_bytes"] / 1e9)}
     ms_upd = ms / args.steps
     roofline_update = {"bound": "hbm", "achieved": UPDATE_BYTES / (ms_upd * 1e-3) / 1e9, "peak": peak,
                        "unit": "GB/s", "frac": UPDATE_BYTES / (ms_upd * 1e-3) / 1e9 / peak,

@@ -66,6 +66,11 @@ class FrameStore:
         _lib.call("dqnb_replay_gather", self._h, _ptr(slots), slots.size, s_tm1_ptr, s_t_ptr, a_ptr, r_ptr,
                   d_ptr, self.stream if stream is None else stream)
 
+    def gather_dev(self, slots_dev_ptr, n, s_tm1_ptr, s_t_ptr, a_ptr, r_ptr, d_ptr, stream=None):
+        """Same with the int32 slot list already in device memory (no upload): the bare kernel."""
+        _lib.call("dqnb_replay_gather_dev", self._h, slots_dev_ptr, int(n), s_tm1_ptr, s_t_ptr, a_ptr, r_ptr,
+                  d_ptr, self.stream if stream is None else stream)
+
     def set_gather_splits(self, splits):
         _lib.call("dqnb_replay_set_gather_splits", self._h, int(splits))
 
