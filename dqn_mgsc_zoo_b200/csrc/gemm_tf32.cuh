@@ -176,6 +176,12 @@ struct T32Map {
 // K range are issued before the first use so they share one memory round trip.
 template <class P, class = void> struct t32_a_reg : std::false_type {};
 template <class P> struct t32_a_reg<P, std::enable_if_t<P::A_REG>> : std::true_type {};
+//   static constexpr bool A_ROW16 = true;  const uint8_t* a_row16(z, m) const;  int a_kb_off(kb) const;
+// K-major uint8 A whose k-block of a row is 32 contiguous source bytes (conv1: one kernel row of the
+// patch = 8 px x 4 ch): thread t owns half a row (16 bytes = one LDG.128) of every k-block, i.e.
+// 4x fewer loads than the word-per-chunk path; the 4 widened chunks go to swizzled smem.
+template <class P, class = void> struct t32_a_row16 : std::false_type {};
+template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::true_type {};
 
 // Retire this thread's commit groups oldest-first: when group I has landed, make it visible to
 // the tensor core (async proxy) and arrive on k-block I's barrier.
@@ -246,7 +252,32 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         for (int ur = 0; ur < MB::NROW; ++ur) p.b_put(brow[ur], col, tile + MB::offset(t, ur, uc));
       }
     };
-    if constexpr (t32_a_reg<P>::value) {
+    if constexpr (t32_a_row16<P>::value) {
+      static_assert(!P::A_MN_MAJOR, "A_ROW16 is a K-major path");
+      const int row = t >> 1, half = t & 1;
+      const uint8_t* rp = p.a_row16(z, m0 + row);
+      uint4 w[KB];
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+        w[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (i < nkb && rp != nullptr) w[i] = __ldg(reinterpret_cast<const uint4*>(rp + p.a_kb_off(kb_beg + i) + half * 16));
+      }
+#pragma unroll 1
+      for (int i = 0; i < nkb; ++i) {
+        stage_b(i);
+        cp_commit();
+      }
+      const uint32_t row_off = (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+        if (i < nkb) {
+          const uint32_t base = smem + i * A_TILE + row_off;
+          const uint32_t wd[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) p.a_store(base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
+        }
+      }
+    } else if constexpr (t32_a_reg<P>::value) {
       constexpr int NW = MA::NROW * MA::NCOL;
       uint32_t word[KB * NW];
 #pragma unroll

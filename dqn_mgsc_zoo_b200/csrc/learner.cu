@@ -474,14 +474,14 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   bool fused = false;
   if (B <= kT32BK && !h->cfg.defer_apply) {
     fused = true;
-    if (live && !h->profiling) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
+    if (live && !h->profiling && !getenv("DQNB_NO_STAGGER")) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
     DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2)));
   }
   else DQNB_TRY((t32_dense_wgrad<4, 128>(h, B, false, s2)));
   DQNB_TRY((t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1)));
-  DQNB_TRY((t32_conv_dgrad<Conv2, 8>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
+  DQNB_TRY((t32_conv_dgrad<Conv2, 4>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
   if (live) DQNB_TRY(fork(h->ev[6], st, s1));
-  DQNB_TRY((t32_conv_wgrad<Conv1, uint8_t, 8, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1)));
+  DQNB_TRY((t32_conv_wgrad<Conv1, uint8_t, 4, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1)));
   if (live) {
     DQNB_TRY(fork(h->ev[3], s1, st));
     DQNB_TRY(fork(h->ev[4], s2, st));

@@ -15,8 +15,14 @@
 
 namespace dqnb {
 
+// 4 packed uint8 -> 4 floats without I2F (a quarter-rate conversion: 32 K of them per conv1 tile were
+// the producers' bottleneck): PRMT drops byte k into the mantissa of 2^23, one FADD removes the 2^23.
+__device__ __forceinline__ float t32_u8_to_float(uint32_t w, uint32_t selector) {
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, selector)) - 8388608.0f;
+}
 __device__ __forceinline__ void t32_widen4(uint32_t dst, uint32_t w) {
-  st16(dst, (float)(w & 0xFF), (float)((w >> 8) & 0xFF), (float)((w >> 16) & 0xFF), (float)(w >> 24));
+  st16(dst, t32_u8_to_float(w, 0x7650), t32_u8_to_float(w, 0x7651), t32_u8_to_float(w, 0x7652),
+       t32_u8_to_float(w, 0x7653));
 }
 template <class T> struct InScale { static constexpr float value = 1.0f; };
 template <> struct InScale<uint8_t> { static constexpr float value = 1.0f / 255.0f; };
@@ -48,11 +54,14 @@ struct T32ConvFwd {
   static constexpr int BN = L::COUT, KB_MAX = sizeof(TIn) == 1 ? 4 : 8;
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
   static constexpr bool A_REG = sizeof(TIn) == 1;   // uint8 frames (conv1): 4 packed bytes per chunk
+  static constexpr bool A_ROW16 = sizeof(TIn) == 1 && L::ROWLEN == 32;   // k-block = one 32-byte patch row
   int M, N, K;
   const TIn* x[kMaxNets];
   const float* w[kMaxNets];
   const float* bias[kMaxNets];
   float* y[kMaxNets];
+  __device__ const uint8_t* a_row16(int z, int m) const { return reinterpret_cast<const uint8_t*>(a_row(z, m)); }
+  __device__ int a_kb_off(int kb) const { return kb * (L::WIN * L::CIN); }
   using ARow = const TIn*;    // &x[b, i*s, j*s, 0] or null
   using ACol = int;           // offset of (kh, kw, c) inside the patch or -1
   using BRow = T32MatKN::Row;
@@ -96,6 +105,9 @@ struct T32ConvFwdDoubleQ {
   static constexpr int BN = 2 * L::COUT, KB_MAX = 8;
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
   static constexpr bool A_REG = sizeof(TIn) == 1;
+  static constexpr bool A_ROW16 = sizeof(TIn) == 1 && L::ROWLEN == 32;
+  __device__ const uint8_t* a_row16(int z, int m) const { return reinterpret_cast<const uint8_t*>(a_row(z, m)); }
+  __device__ int a_kb_off(int kb) const { return kb * (L::WIN * L::CIN); }
   int M, N, K, Mh;          // M = 2 * Mh, N = 2 * COUT
   const TIn* x[2];          // s_tm1, s_t
   const float* w[2];        // online, target

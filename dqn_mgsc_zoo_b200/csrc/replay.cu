@@ -55,6 +55,11 @@ struct dqnb_replay {
   bool idx_busy[kIdxRing] = {};
   int idx_cur = 0;
   int idx_pending = -1;                  // ring entry handed to the next gather without a copy
+  // small commits run on a side stream so they overlap whatever follows the last gather on the
+  // caller's stream (the learner's update graph): ordered after that gather, before the next one
+  cudaStream_t side = nullptr;
+  cudaEvent_t gather_done = nullptr;
+  bool have_gather = false;
   uint8_t* d_out = nullptr;
   int64_t out_cap = 0;
   int gather_splits = 0;
@@ -103,13 +108,21 @@ int flush(dqnb_replay* h, cudaStream_t st) {
     DQNB_CUDA(cudaEventRecord(s.copied, st));
   }
   int grid = s.n_planes + (s.n_records + kCommitThreads - 1) / kCommitThreads;
-  commit_kernel<<<grid, kCommitThreads, 0, st>>>(
+  // Readers of what this commit overwrites (evicted slot records, recycled planes) are gathers
+  // already enqueued on `st`; everything enqueued after the last of them (the update graph) does
+  // not touch the replay, so a small commit may run beside it.
+  cudaStream_t cs = (zero_copy && h->side != nullptr) ? h->side : st;
+  if (cs != st && h->have_gather) DQNB_CUDA(cudaStreamWaitEvent(cs, h->gather_done, 0));
+  commit_kernel<<<grid, kCommitThreads, 0, cs>>>(
       h->d_planes, h->plane_stride, h->plane_bytes, src + h->hdr_bytes,
       reinterpret_cast<const int32_t*>(src + h->hdr_records), s.n_planes,
       reinterpret_cast<const SlotRecord*>(src), s.n_records, h->d_slot_ids, h->d_actions,
       h->d_rewards, h->d_discounts);
   DQNB_CUDA(cudaGetLastError());
-  if (zero_copy) DQNB_CUDA(cudaEventRecord(s.copied, st));   // staging is free once the kernel has read it
+  if (zero_copy) {
+    DQNB_CUDA(cudaEventRecord(s.copied, cs));   // staging is free once the kernel has read it
+    if (cs != st) DQNB_CUDA(cudaStreamWaitEvent(st, s.copied, 0));   // later work on st sees the commit
+  }
   s.in_flight = true;
   for (int i = 0; i < s.n_records; ++i) h->slot_staged[h->rec_of(s)[i].slot] = 0;
   // planes released during this batch may be handed out again only now (stream order
@@ -232,6 +245,8 @@ extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int s
     DQNB_CUDA(cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
   }
   for (int i = 0; i < kIdxRing; ++i) DQNB_CUDA(cudaEventCreateWithFlags(&h->idx_ev[i], cudaEventDisableTiming));
+  DQNB_CUDA(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+  DQNB_CUDA(cudaEventCreateWithFlags(&h->gather_done, cudaEventDisableTiming));
   if (initial_planes <= 0) initial_planes = capacity + capacity / 8 + 64;
   DQNB_TRY(grow_pool(h, initial_planes));
   h->n_growths = 0;
@@ -254,6 +269,8 @@ extern "C" int dqnb_replay_destroy(dqnb_replay* h) {
     if (s.copied) cudaEventDestroy(s.copied);
   }
   for (int i = 0; i < kIdxRing; ++i) if (h->idx_ev[i]) cudaEventDestroy(h->idx_ev[i]);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->gather_done) cudaEventDestroy(h->gather_done);
   delete h;
   return DQNB_OK;
 }
@@ -352,6 +369,8 @@ int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* 
     gather_generic<<<(unsigned)n, 128, 0, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
   }
   DQNB_CUDA(cudaGetLastError());
+  DQNB_CUDA(cudaEventRecord(h->gather_done, st));
+  h->have_gather = true;
   if (h->idx_pending >= 0) {
     DQNB_CUDA(cudaEventRecord(h->idx_ev[h->idx_pending], st));
     h->idx_busy[h->idx_pending] = true;
