@@ -120,6 +120,11 @@ __device__ __forceinline__ float4 ld_cluster_f4(uint32_t addr) {
   asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
 // this CTA's own shared::cta address as a shared::cluster address
 __device__ __forceinline__ uint32_t local_as_cluster(uint32_t local_smem_addr) {
   uint32_t rank;
@@ -370,7 +375,7 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
     constexpr int G4 = BN / 4;
-    const int nsum = clustered ? splits : 1;
+    const int nsum = splits;   // used by the clustered path only
     const int R = clustered ? (kT32BM + splits - 1) / splits : kT32BM;
     const int row_beg = clustered ? split * R : 0;
     const int row_end = min(min(kT32BM, row_beg + R), p.M - m0);
@@ -378,10 +383,20 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
     for (int item = t; item < (row_end - row_beg) * G4; item += kT32Producers) {
       const int r = row_beg + item / G4, c4 = item % G4;
       const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int q = 0; q < nsum; ++q) {
-        const float4 x = ld_cluster_f4(clustered ? cluster_map(local, (uint32_t)q) : local_as_cluster(local));
-        v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+      float4 v;
+      if (!clustered) {
+        v = ld_shared_f4(local);
+      } else {
+        // all partial tiles' loads in flight together (a DSMEM load is a few hundred cycles), then the
+        // sum in split order
+        float4 x[kT32MaxCluster];
+#pragma unroll
+        for (int q = 0; q < kT32MaxCluster; ++q)
+          if (q < nsum) x[q] = ld_cluster_f4(cluster_map(local, (uint32_t)q));
+        v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < kT32MaxCluster; ++q)
+          if (q < nsum) { v.x += x[q].x; v.y += x[q].y; v.z += x[q].z; v.w += x[q].w; }
       }
       if (n0 + c4 * 4 < p.N) p.store4(z, split, m0 + r, n0 + c4 * 4, v);
     }

@@ -8,7 +8,7 @@ import bench
 from dqn_mgsc_zoo_b200 import learner as lrn, networks, replay as rp
 
 precision = sys.argv[1] if len(sys.argv) > 1 else "tf32"
-CAP = 100_000
+CAP = int(sys.argv[2]) if len(sys.argv) > 2 else 100_000
 replay = rp.TransitionReplay(CAP, rp.Transition(None, None, None, None, None), np.random.RandomState(0), device=0)
 src = bench.EpisodeSource(1000)
 for _ in range(CAP):
