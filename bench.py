@@ -10,6 +10,7 @@ an independent agent replica (own replay, params, RNG) - the way the reference s
 arrays); no data-path collective; value = total updates of all ranks / max-over-ranks time.
 """
 import argparse
+import collections
 import json
 import os
 import subprocess
@@ -241,13 +242,13 @@ def run_ours(args, rank, world, local_rank):
 
     def e2e_step():
         for _ in range(ADDS_PER_LEARN):
-            replay.add(rp.Transition(*pending.pop()))
+            replay.add(rp.Transition(*pending.popleft()))   # in arrival order: s_tm1 is the previous s_t
         device_step()
         return L.loss_lagged()   # queue this step's loss D2H, return the previous step's (already landed)
 
     def e2e_step_sync():
         for _ in range(ADDS_PER_LEARN):
-            replay.add(rp.Transition(*pending.pop()))
+            replay.add(rp.Transition(*pending.popleft()))   # in arrival order: s_tm1 is the previous s_t
         device_step()
         return L.loss()          # blocking D2H read of this step's loss
 
@@ -275,7 +276,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- e2e: new transitions arrive from host memory every step, loss is read back
     e2e_steps = min(args.steps, 1000)
     sync_steps = min(args.steps, 300)
-    pending = [src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + sync_steps + 10))]
+    pending = collections.deque(src.next() for _ in range(ADDS_PER_LEARN * (e2e_steps + sync_steps + 10)))
     for _ in range(5):
         e2e_step()
     up0 = store.stats()["planes_uploaded"]
@@ -416,11 +417,11 @@ def run_dp(args, rank, world, local_rank):
     def device_step():
         dp.update_from_replay(store, replay.sample_slots(G))      # identical draw on every rank
 
-    pending = []
+    pending = collections.deque()
 
     def e2e_step():
         for _ in range(ADDS_PER_LEARN):
-            replay.add(rp.Transition(*pending.pop()))
+            replay.add(rp.Transition(*pending.popleft()))   # in arrival order: s_tm1 is the previous s_t
         device_step()
         return L.loss_lagged()
 

@@ -235,6 +235,9 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   __syncthreads();
   t32_fence_after();
   const uint32_t tmem = tmem_slot;
+  // everything above touched only this CTA's shared memory / TMEM; from here on the kernel reads
+  // what its predecessors wrote
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (dbg && t == 0) sk.dbg[1] = clock64();     // setup done
 
   if (warp < 8) {
@@ -372,6 +375,11 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   // handed to p.store4 (bias / relu / mask / partial-buffer placement live there).
   const bool clustered = !P::DEFER_REDUCE && splits > 1;
   if (clustered) cluster_sync_all(); else __syncthreads();
+  // Programmatic dependent launch: the MMAs are done and only the store loop is left, so let the
+  // next kernel of the stream get its CTAs placed and run its prologue (barriers, TMEM) now; it
+  // blocks at its griddepcontrol.wait until this grid has completed.  Triggering earlier parks idle
+  // CTAs on SMs the side-branch kernels need.  (No-ops for launches without the attribute.)
+  asm volatile("griddepcontrol.launch_dependents;");
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
     constexpr int G4 = BN / 4;
@@ -428,7 +436,8 @@ inline int t32_splits_for(const P& p, int Z, int want_ctas = 120) {
 template <class P>
 // `priority`: CUDA launch priority (lower = scheduled first); kernels of the dependent chain get
 // the device's greatest priority so that side-branch kernels do not take their SMs.
-inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cudaStream_t st, int priority = 0) {
+inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cudaStream_t st, int priority = 0,
+                                    bool pdl = false) {
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tf32<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, t32_smem_bytes<P>());
@@ -451,8 +460,12 @@ inline cudaError_t launch_gemm_tf32(const P& p, int Z, int splits, SplitK sk, cu
   cfg.blockDim = dim3(kT32Threads);
   cfg.dynamicSmemBytes = t32_smem_bytes<P>();
   cfg.stream = st;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   unsigned na = 0;
+  if (pdl) {   // may start before the previous kernel of `st` has finished (see griddepcontrol.wait)
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na++].val.programmaticStreamSerializationAllowed = 1;
+  }
   attr[na].id = cudaLaunchAttributePriority;
   attr[na++].val.priority = priority;
   if (clustered) {

@@ -97,6 +97,8 @@ struct dqnb_learner {
   cudaStream_t side[3] = {};
   cudaStream_t chain = nullptr;   // stream of the dependent kernel chain in the enqueue in progress
   int prio_hi = 0;                // greatest launch priority of the device
+  bool pdl = false;               // programmatic dependent launch between consecutive chain kernels
+  bool boost = false;             // next side-branch launch gets the chain's priority
   cudaEvent_t ev[8] = {};
   int64_t updates = 0;
   int64_t launches_per_update = 0;
@@ -315,7 +317,9 @@ int run_t32(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
     DQNB_TRY(mark(h, st, "(twin)"));
   }
   if (h->profiling && h->dbg_clocks) sk.dbg = h->dbg_clocks + 8 * h->prof_n;
-  DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, st == h->chain ? h->prio_hi : 0));
+  const bool on_chain = st == h->chain;
+  DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, (on_chain || h->boost) ? h->prio_hi : 0,
+                             on_chain && !h->profiling && h->pdl));
   return mark(h, st, P::NAME);
 }
 
@@ -382,9 +386,14 @@ int t32_conv_wgrad(dqnb_learner* h, int rows, const TIn* x, const float* dy, int
   if (!BIAS_ROW) {
     h->launches_per_update++;
     if (!h->sizing) {
-      bias_colsum_kernel<L::COUT><<<splits, 256, 0, bias_st>>>(dy, p.K, p.gpart, P::PART, (size_t)L::KCOL * L::COUT,
-                                                               h->next_tl("bias_colsum"));
-      DQNB_CUDA(cudaGetLastError());
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(splits); cfg.blockDim = dim3(256); cfg.stream = bias_st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributePriority;
+      attr[0].val.priority = h->boost ? h->prio_hi : 0;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      DQNB_CUDA(cudaLaunchKernelEx(&cfg, bias_colsum_kernel<L::COUT>, dy, p.K, p.gpart, (size_t)P::PART,
+                                   (size_t)L::KCOL * L::COUT, h->next_tl("bias_colsum")));
       DQNB_TRY(mark(h, bias_st, "bias_colsum"));
     }
   }
@@ -474,14 +483,26 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   bool fused = false;
   if (B <= kT32BK && !h->cfg.defer_apply) {
     fused = true;
-    if (live && !h->profiling && !getenv("DQNB_NO_STAGGER")) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
-    DQNB_TRY((t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2)));
+    if (live && !h->profiling && !h->pdl && !getenv("DQNB_NO_STAGGER")) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
+    // With dependent launches the chain always has CTAs pending, so a low-priority kernel would only
+    // run after the chain; this one is the longest side branch (bandwidth-bound, ~10 us) and must
+    // start as soon as its inputs exist.
+    h->boost = h->pdl;
+    int rc_w = t32_dense_wgrad<1, 32>(h, B, /*fuse=*/true, s2);
+    h->boost = false;
+    DQNB_TRY(rc_w);
   }
   else DQNB_TRY((t32_dense_wgrad<4, 128>(h, B, false, s2)));
-  DQNB_TRY((t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1)));
+  h->boost = h->pdl;   // see the fc1 wgrad above: conv2's wgrad and both bias column sums would otherwise wait for the chain
+  int rc_c2 = t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1);
+  h->boost = false;
+  DQNB_TRY(rc_c2);
   DQNB_TRY((t32_conv_dgrad<Conv2, 4>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
   if (live) DQNB_TRY(fork(h->ev[6], st, s1));
-  DQNB_TRY((t32_conv_wgrad<Conv1, uint8_t, 4, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1)));
+  h->boost = h->pdl;
+  int rc_c1 = t32_conv_wgrad<Conv1, uint8_t, 4, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1);
+  h->boost = false;
+  DQNB_TRY(rc_c1);
   if (live) {
     DQNB_TRY(fork(h->ev[3], s1, st));
     DQNB_TRY(fork(h->ev[4], s2, st));
@@ -573,6 +594,7 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
     int least = 0, greatest = 0;
     DQNB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     h->prio_hi = greatest;
+    h->pdl = getenv("DQNB_NO_PDL") == nullptr;
   }
   for (auto& e : h->ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   DQNB_CUDA(cudaEventCreateWithFlags(&h->pinned_free, cudaEventDisableTiming));
