@@ -101,18 +101,47 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
   if (t < kMaxNets * kMaxActions) (&q_s[0][0])[t] = -INFINITY;
   // (2) fc2: q[z][a] = sum_k h1[z][k] w2[z][k][a].  Thread t covers k = 4t..4t+3, whose weights
   // are 4A consecutive floats (coalesced across the CTA); warp shuffle, then 4 warp partials.
-#pragma unroll 2
-  for (int a = 0; a < A; ++a) {
+  // Actions go in groups of kGroup: all weight loads of a group are issued first (one L2 round trip
+  // instead of one per action), then the FMAs, then kGroup * nets independent shuffle trees.
+  constexpr int kGroup = 6;
+  for (int a0 = 0; a0 < A; a0 += kGroup) {
+    float wv[kMaxNets][kGroup][4];
 #pragma unroll
     for (int z = 0; z < kMaxNets; ++z) {
-      if (z < nets) {
-        const float* w2 = g.w2[z] + (size_t)(4 * t) * A + a;
-        float s = hv[z].x * __ldg(w2);
-        s = fmaf(hv[z].y, __ldg(w2 + A), s);
-        s = fmaf(hv[z].z, __ldg(w2 + 2 * A), s);
-        s = fmaf(hv[z].w, __ldg(w2 + 3 * A), s);
-        s = warp_sum(s);
-        if (lane == 0) red_s[warp][z][a] = s;
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const bool on = z < nets && a0 + u < A;
+        const float* w2 = g.w2[z < nets ? z : 0] + (size_t)(4 * t) * A + (on ? a0 + u : 0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) wv[z][u][j] = on ? __ldg(w2 + j * A) : 0.f;
+      }
+    }
+    float part[kMaxNets][kGroup];
+#pragma unroll
+    for (int z = 0; z < kMaxNets; ++z) {
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        float s = hv[z < nets ? z : 0].x * wv[z][u][0];
+        s = fmaf(hv[z < nets ? z : 0].y, wv[z][u][1], s);
+        s = fmaf(hv[z < nets ? z : 0].z, wv[z][u][2], s);
+        s = fmaf(hv[z < nets ? z : 0].w, wv[z][u][3], s);
+        part[z][u] = s;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int z = 0; z < kMaxNets; ++z) {
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) part[z][u] += __shfl_xor_sync(0xffffffffu, part[z][u], o);
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int z = 0; z < kMaxNets; ++z) {
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u)
+          if (z < nets && a0 + u < A) red_s[warp][z][a0 + u] = part[z][u];
       }
     }
   }

@@ -352,7 +352,7 @@ ReplayDeviceView view_of(const dqnb_replay* h) {
 }
 
 int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* s_tm1, uint8_t* s_t,
-                  int32_t* a, float* r, float* d, cudaStream_t st) {
+                  int32_t* a, float* r, float* d, cudaStream_t st, const InlineSlots* inl = nullptr) {
   if (n == 0) return DQNB_OK;
   ReplayDeviceView v = view_of(h);
   if (h->S == 4 && h->plane_bytes % 16 == 0) {
@@ -363,8 +363,9 @@ int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* 
     chunk = std::min(chunk, 16 * 1024);
     splits = (h->plane_bytes + chunk - 1) / chunk;
     dim3 grid(splits, (unsigned)n);
+    static const InlineSlots no_inline{};
     gather_stack4<kGatherThreads><<<grid, kGatherThreads, 8 * (size_t)chunk, st>>>(
-        v, slots_dev, (int)n, chunk, s_tm1, s_t, a, r, d);
+        v, slots_dev, inl ? *inl : no_inline, (int)n, chunk, s_tm1, s_t, a, r, d);
   } else {
     gather_generic<<<(unsigned)n, 128, 0, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
   }
@@ -434,6 +435,18 @@ extern "C" int dqnb_replay_gather(dqnb_replay* h, const int64_t* slots_host, int
   DQNB_REQUIRE(n >= 0 && n < 65536 * 16, "n=%lld out of range", (long long)n);
   if (n == 0) return DQNB_OK;
   DeviceGuard guard(h->device);
+  if (n <= kInlineSlots && h->S == 4 && h->plane_bytes % 16 == 0) {   // slot list by value, no upload
+    DQNB_REQUIRE(s_tm1_dev && s_t_dev && a_dev && r_dev && disc_dev, "null argument");
+    InlineSlots inl{};
+    for (int64_t i = 0; i < n; ++i) {
+      DQNB_REQUIRE(slots_host[i] >= 0 && slots_host[i] < h->capacity, "slot %lld outside [0,%lld)",
+                   (long long)slots_host[i], (long long)h->capacity);
+      inl.v[i] = (int32_t)slots_host[i];
+    }
+    cudaStream_t st = as_stream(stream);
+    DQNB_TRY(flush(h, st));
+    return launch_gather(h, nullptr, n, s_tm1_dev, s_t_dev, a_dev, r_dev, disc_dev, st, &inl);
+  }
   const int32_t* dslots = nullptr;
   DQNB_TRY(upload_slots(h, slots_host, n, as_stream(stream), &dslots));
   return dqnb_replay_gather_dev(h, dslots, n, s_tm1_dev, s_t_dev, a_dev, r_dev, disc_dev, stream);

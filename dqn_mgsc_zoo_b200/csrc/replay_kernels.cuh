@@ -77,16 +77,21 @@ __device__ __forceinline__ uint4 interleave4(uint32_t w0, uint32_t w1, uint32_t 
 // blockIdx.x = split, blockIdx.y = batch row.  Unique planes only are fetched (a chained
 // transition shares 3 of its 8 plane references), each with one bulk async copy that
 // completes on an mbarrier; threads then emit both stacks with 16-byte stores.
+// Small batches (the learner's sample of 32) carry their slot list in the kernel parameters:
+// no index upload, i.e. no copy-engine operation between the kernels of the training stream.
+constexpr int kInlineSlots = 64;
+struct InlineSlots { int32_t v[kInlineSlots]; };
+
 template <int kThreads>
 __global__ void __launch_bounds__(kThreads)
-gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, int n, int chunk,
-              uint8_t* __restrict__ s_tm1_out, uint8_t* __restrict__ s_t_out,
+gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __grid_constant__ InlineSlots inl, int n,
+              int chunk, uint8_t* __restrict__ s_tm1_out, uint8_t* __restrict__ s_t_out,
               int32_t* __restrict__ a_out, float* __restrict__ r_out, float* __restrict__ d_out) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ int buf_of[8];   // smem buffer index per plane reference, -1 = zeros
   const int row = blockIdx.y, split = blockIdx.x;
-  const int slot = slots[row];
+  const int slot = slots != nullptr ? slots[row] : inl.v[row];
   const int px0 = split * chunk;
   const int len = min(chunk, v.plane_bytes - px0);   // multiple of 16 by construction
 
