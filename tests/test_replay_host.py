@@ -1,0 +1,194 @@
+"""The reference's own replay tests, run against the drop-in classes (host side, no GPU):
+dqn_zoo/replay_test.py:39-175 (UniformDistributionTest, TransitionReplayTest) and the reservoir
+inclusion statistics of dqn_zoo/dqn_reservoir/run_reservoir_test.py:26-47.  Items here are the
+reference tests' `Pair(a, b)` of Python ints, which the product keeps in a host list exactly like
+the reference does (frames go to HBM: tests/test_replay_gpu.py)."""
+import collections
+import copy
+
+import numpy as np
+import pytest
+
+from dqn_mgsc_zoo_b200 import replay as replay_lib
+
+Pair = collections.namedtuple('Pair', ['a', 'b'])
+
+
+def assert_trees_equal(a, b):
+    if isinstance(a, dict):
+        assert set(a) == set(b)
+        for k in a:
+            assert_trees_equal(a[k], b[k])
+    elif isinstance(a, (list, tuple)):
+        assert len(a) == len(b)
+        for x, y in zip(a, b):
+            assert_trees_equal(x, y)
+    elif isinstance(a, np.random.RandomState):
+        sa, sb = a.get_state(), b.get_state()
+        assert sa[0] == sb[0] and np.array_equal(sa[1], sb[1]) and sa[2:] == sb[2:]
+    else:
+        assert np.array_equal(a, b)
+
+
+# ---- UniformDistributionTest (replay_test.py:39-100)
+@pytest.fixture
+def dist():
+    return replay_lib.UniformDistribution(np.random.RandomState(seed=1))
+
+
+def test_add_and_sample_one(dist):
+    dist.add([2])
+    assert dist.sample(1) == 2
+    assert dist.check_valid()[0]
+
+
+def test_adding_existing_id_raises_an_error(dist):
+    dist.add([2, 5])
+    with pytest.raises(IndexError, match='Cannot add ID'):
+        dist.add([6, 5])
+
+
+def test_remove(dist):
+    dist.add([2, 5, 7])
+    dist.remove([5])
+    assert 5 not in dist.sample(100)
+    assert dist.check_valid()[0]
+
+
+def test_remove_final_id(dist):
+    dist.add([2, 5, 7])
+    dist.remove([7])
+    assert dist.size == 2
+    assert 7 not in dist.sample(100)
+    assert dist.check_valid()[0]
+
+
+def test_removing_nonexistent_id_raises_an_error(dist):
+    dist.add([2, 5])
+    with pytest.raises(IndexError, match='Cannot remove ID'):
+        dist.remove([7])
+
+
+def test_distribution_size(dist):
+    dist.add([2, 5, 3])
+    assert dist.size == 3
+    dist.remove([5])
+    assert dist.size == 2
+
+
+def test_distribution_get_state_and_set_state(dist):
+    dist.add([2, 5, 3, 8])
+    dist.remove([5])
+    assert dist.check_valid()[0]
+    state = copy.deepcopy(dist.get_state())
+    new_dist = replay_lib.UniformDistribution(np.random.RandomState(seed=1))
+    new_dist.set_state(state)
+    assert new_dist.check_valid()[0]
+    assert new_dist.size == dist.size
+    assert_trees_equal(state, new_dist.get_state())
+
+
+# ---- TransitionReplayTest (replay_test.py:103-175)
+CAPACITY = 10
+ITEMS = [Pair(a=1, b=2), Pair(a=11, b=22), Pair(a=111, b=222), Pair(a=1111, b=2222)]
+
+
+@pytest.fixture
+def replay():
+    r = replay_lib.TransitionReplay(capacity=CAPACITY, structure=Pair(a=None, b=None),
+                                    random_state=np.random.RandomState(1))
+    for item in ITEMS:
+        r.add(item)
+    return r
+
+
+def test_size_and_capacity(replay):
+    assert replay.size == len(ITEMS)
+    assert replay.capacity == CAPACITY
+
+
+def test_sample(replay):
+    samples = replay.sample(2)
+    assert samples.a.shape == (2,)
+    assert np.array_equal(samples.b, 2 * samples.a)
+
+
+def test_invariants():
+    capacity, num_samples = 10, 3
+    replay = replay_lib.TransitionReplay(capacity=capacity, structure=Pair(a=None, b=None),
+                                         random_state=np.random.RandomState(1))
+    for i in range(31):
+        replay.add(Pair(a=i, b=2 * i))
+        assert replay.size <= capacity
+        if i > 2:
+            assert replay.sample(num_samples).a.shape == (num_samples,)
+        ids = list(replay.ids())
+        assert len(ids) == min(i + 1, capacity)
+        assert ids == sorted(ids)
+        assert ids[0] + len(ids) - 1 == ids[-1]
+        assert [p.a for p in replay.get(ids)] == ids          # FIFO: id i holds the i-th item
+
+
+def test_get_state_and_set_state():
+    make = lambda: replay_lib.TransitionReplay(capacity=CAPACITY, structure=Pair(a=None, b=None),
+                                               random_state=np.random.RandomState(1))
+    replay = make()
+    for i in range(100):
+        replay.add(Pair(a=i, b=i))
+    replay.sample(10)
+    assert replay.check_valid()[0]
+    state = copy.deepcopy(replay.get_state())
+    new_replay = make()
+    new_replay.set_state(state)
+    assert new_replay.check_valid()[0]
+    assert new_replay.size == replay.size
+    assert_trees_equal(state, new_replay.get_state())
+    # both continue identically (same ids, same items) after the restore
+    replay.add(Pair(a=100, b=100))
+    new_replay.add(Pair(a=100, b=100))
+    assert list(replay.ids()) == list(new_replay.ids())
+    assert [p.a for p in replay.get(replay.ids())] == [p.a for p in new_replay.get(new_replay.ids())]
+
+
+def test_empty_and_oversized_sample():
+    replay = replay_lib.TransitionReplay(4, Pair(None, None), np.random.RandomState(0))
+    with pytest.raises(ValueError):            # RandomState.randint(0): the reference raises the same
+        replay.sample(1)
+    replay.add(Pair(1, 2))
+    assert replay.sample(5).a.tolist() == [1] * 5          # sampling is with replacement
+
+
+# ---- reservoir inclusion statistics (dqn_reservoir/run_reservoir_test.py:26-47, fewer epochs)
+def test_reservoir_keeps_every_item_with_probability_capacity_over_n():
+    epochs, capacity, n, eps = 1500, 50, 200, 0.045
+    structure = replay_lib.Transition(None, None, None, None, None)
+    transitions = [replay_lib.Transition(i, i, i, i, i) for i in range(n)]
+    counts = collections.Counter()
+    for epoch in range(epochs):
+        replay = replay_lib.ReservoirTransitionReplay(capacity, structure, np.random.RandomState(epoch), None, None)
+        for tr in transitions:
+            replay.add(tr)
+        assert replay.size == capacity
+        for tr in replay.get(replay.ids()):
+            counts[tr.a_tm1] += 1
+    expected = capacity / n
+    freq = np.array([counts[i] / epochs for i in range(n)])
+    assert np.all(np.abs(freq - expected) <= eps), (freq.min(), freq.max())
+
+
+def test_transition_accumulator_pairs_consecutive_timesteps():
+    # replay.py:1163-1197 (the agents' accumulator; the n-step one is out of scope)
+    from dqn_mgsc_zoo_b200 import synthetic
+    acc = replay_lib.TransitionAccumulator()
+    obs = [np.full((2, 2), i, np.uint8) for i in range(4)]
+    first = synthetic.TimeStep(0, None, None, obs[0])
+    assert list(acc.step(first, 3)) == []
+    mid = synthetic.TimeStep(1, 0.5, 0.9, obs[1])
+    (t,) = list(acc.step(mid, 4))
+    assert t.s_tm1 is obs[0] and t.s_t is obs[1] and t.a_tm1 == 3 and t.r_t == 0.5 and t.discount_t == 0.9
+    last = synthetic.TimeStep(2, 1.0, 0.0, obs[2])
+    (t,) = list(acc.step(last, 5))
+    assert t.s_tm1 is obs[1] and t.a_tm1 == 4 and t.discount_t == 0.0
+    acc.reset()
+    with pytest.raises(ValueError, match='Expected FIRST timestep'):
+        list(acc.step(mid, 0))
