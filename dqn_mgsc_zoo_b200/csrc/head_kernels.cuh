@@ -239,6 +239,56 @@ __global__ void fc2_wgrad_kernel(int batch, int A, int shared_bias, float inv_me
   tl_end(tl);
 }
 
+// Large batches: the serial batch loop above becomes the critical path, so slice q of the batch
+// (blockIdx.y) leaves its partial in part[q][512*A] and the optimiser kernel sums the slices in order.
+// Block (0, 0) also produces the bias gradient and the loss exactly like fc2_wgrad_kernel.
+__global__ void fc2_wgrad_sliced_kernel(int batch, int A, int shared_bias, float inv_mean, const float* __restrict__ h1,
+                                        const int32_t* __restrict__ action, const float* __restrict__ dq_taken,
+                                        const float* __restrict__ row_loss, float* __restrict__ part,
+                                        float* __restrict__ gb2, float* __restrict__ loss, LossRing ring,
+                                        unsigned long long* tl) {
+  tl_begin(tl);
+  const int n = kFc1Out * A, e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int q = blockIdx.y, nq = gridDim.y;
+  const int beg = (int)((int64_t)batch * q / nq), end = (int)((int64_t)batch * (q + 1) / nq);
+  if (e < n) {
+    int k = e / A, a = e - k * A;
+    float s = 0.f;
+#pragma unroll 4
+    for (int b = beg; b < end; ++b)
+      if (__ldg(action + b) == a) s = fmaf(__ldg(h1 + (size_t)b * kFc1Out + k), __ldg(dq_taken + b), s);
+    part[(size_t)q * n + e] = s;
+  }
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 32) {
+    int lane = threadIdx.x;
+    if (shared_bias) {
+      float s = 0.f;
+      for (int b = lane; b < batch; b += 32) s += dq_taken[b];
+      s = warp_sum(s);
+      if (lane == 0) gb2[0] = s;
+    } else if (lane < A) {
+      float s = 0.f;
+      for (int b = 0; b < batch; ++b)
+        if (action[b] == lane) s += dq_taken[b];
+      gb2[lane] = s;
+    }
+    float l = 0.f;
+    for (int b = lane; b < batch; b += 32) l += row_loss[b];
+    l = warp_sum(l);
+    if (lane == 0) {
+      const float mean = l * inv_mean;
+      *loss = mean;
+      if (ring.ring != nullptr) {
+        const unsigned seq = *ring.seq + 1;
+        *ring.seq = seq;
+        ring.ring[seq & (kLossRing - 1)] = ((unsigned long long)seq << 32) | __float_as_uint(mean);
+        __threadfence_system();
+      }
+    }
+  }
+  tl_end(tl);
+}
+
 // K5: optax.rmsprop(centered=True) + apply_updates, one pass over the flat arena
 // (op order of Digraph.gv:711-752; eps inside the rsqrt).
 __global__ void rmsprop_kernel(float* __restrict__ p, float* __restrict__ mu, float* __restrict__ nu,
@@ -281,10 +331,11 @@ __global__ void rmsprop_kernel(float* __restrict__ p, float* __restrict__ mu, fl
 // APPLY=false only materialises g (the data-parallel learner all-reduces it before the update).
 struct GradRegion {
   int64_t off, count;      // floats; both multiples of 4
-  const float* part;
+  const float* part;       // split q's partial of this region starts at part + q * stride
+  int64_t stride;
   int splits;
 };
-constexpr int kMaxGradRegions = 4;
+constexpr int kMaxGradRegions = 8;
 struct GradRegions {
   GradRegion r[kMaxGradRegions];
   int n;
@@ -323,7 +374,7 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
         for (int q = sub; q < regs.r[r].splits; q += 8) {
-          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].count));
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].stride));
           gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
         }
         summed = true;

@@ -11,6 +11,7 @@
 #include "head_kernels.cuh"
 #include "learner_internal.cuh"
 #include "nature_tf32.cuh"
+#include "gemm_tf32_stream.cuh"
 
 using namespace dqnb;
 
@@ -99,6 +100,7 @@ struct dqnb_learner {
   int prio_hi = 0;                // greatest launch priority of the device
   bool pdl = false;               // programmatic dependent launch between consecutive chain kernels
   bool boost = false;             // next side-branch launch gets the chain's priority
+  bool stream = false;            // large batch: GEMMs go to the persistent ring kernel (gemm_tf32_stream.cuh)
   cudaEvent_t ev[8] = {};
   int64_t updates = 0;
   int64_t launches_per_update = 0;
@@ -123,11 +125,14 @@ struct dqnb_learner {
     return sk;
   }
   // partial-gradient buffer for one wgrad op; registers the arena region it reduces into
-  float* take_part(int64_t arena_off, int64_t count, int splits) {
+  // `splits` partials of `stride` floats each; the first `count` of every partial belong to the arena
+  // range [arena_off, arena_off + count), which the optimiser kernel sums in split order.
+  float* take_part(int64_t arena_off, int64_t count, int splits, int64_t stride = 0) {
+    if (stride == 0) stride = count;
     float* ptr = gpart ? gpart + part_off : nullptr;
-    part_off += (size_t)count * splits;
+    part_off += (size_t)stride * splits;
     GradRegion& r = regions.r[regions.n++];
-    r.off = arena_off; r.count = count; r.part = ptr; r.splits = splits;
+    r.off = arena_off; r.count = count; r.part = ptr; r.stride = stride; r.splits = splits;
     return ptr;
   }
 };
@@ -306,6 +311,7 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------ TF32 tensor-core path
+constexpr int kStreamMinBatch = 256;   // below this the one-tile-per-CTA slab kernel (latency) wins
 template <class P>
 int run_t32(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
   SplitK sk = h->take_scratch(gemm_tf32_ws_floats(p, Z, splits), gemm_tf32_tiles(p, Z));
@@ -318,9 +324,18 @@ int run_t32(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
   }
   if (h->profiling && h->dbg_clocks) sk.dbg = h->dbg_clocks + 8 * h->prof_n;
   const bool on_chain = st == h->chain;
-  DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, (on_chain || h->boost) ? h->prio_hi : 0,
-                             on_chain && !h->profiling && h->pdl));
+  if (h->stream) DQNB_CUDA(launch_gemm_tf32_stream(p, Z, splits, sk, st, on_chain ? h->prio_hi : 0));
+  else
+    DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, (on_chain || h->boost) ? h->prio_hi : 0,
+                               on_chain && !h->profiling && h->pdl));
   return mark(h, st, P::NAME);
+}
+
+// Split-K factor of a TF32 GEMM: latency mode spreads one short tile's K over a cluster; stream mode
+// splits only deferred-reduction problems, just enough to occupy every SM.
+template <class P>
+int t32_splits(const dqnb_learner* h, const P& p, int Z, int want_ctas = 120) {
+  return h->stream ? t32s_splits_for(p, Z) : t32_splits_for(p, Z, want_ctas);
 }
 
 template <class L, class TIn>
@@ -332,7 +347,7 @@ int t32_conv_fwd(dqnb_learner* h, int nets, int rows, const TIn* const* x, const
     int zz = std::min(z, nets - 1);
     p.x[z] = x[zz]; p.w[z] = wts[zz] + w_off; p.bias[z] = params[zz] + b_off; p.y[z] = y[zz];
   }
-  return run_t32(h, p, nets, t32_splits_for(p, nets), st);
+  return run_t32(h, p, nets, t32_splits(h, p, nets), st);
 }
 
 // `params`: fp32 arenas (biases); `wts`: their tf32-rounded shadows (GEMM weight operands).
@@ -348,7 +363,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
     p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
     p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
     for (int z = 0; z < kMaxNets; ++z) p.y[z] = h->a1[z];
-    DQNB_TRY(run_t32(h, p, 1, t32_splits_for(p, 1), st));
+    DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
   } else {
     DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
   }
@@ -363,7 +378,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
     int zz = std::min(z, nets - 1);
     p.x[z] = in4[zz]; p.w[z] = wts[zz] + h->L.fw1;
   }
-  p.splits = t32_splits_for(p, Z, kNumSMs);
+  p.splits = t32_splits(h, p, Z, kNumSMs);
   h->fc1_splits = p.splits;
   h->fc1_rows = rows;
   const size_t need = (size_t)nets * p.splits * rows * kFc1Out;
@@ -381,19 +396,25 @@ int t32_conv_wgrad(dqnb_learner* h, int rows, const TIn* x, const float* dy, int
   P p;
   p.M = P::ROWS; p.N = L::COUT; p.K = rows * L::HOUT * L::WOUT;
   p.x = x; p.dy = dy;
-  const int splits = t32_splits_for(p, 1);
-  p.gpart = h->take_part(w_off, (int64_t)P::PART, splits);
+  const int splits = t32_splits(h, p, 1);
+  // Stream mode has a handful of long splits, far too few blocks for the bias column sums: those get
+  // their own partial buffer (one row of COUT per block) and their own region.
+  const bool own_bias = !BIAS_ROW && h->stream;
+  p.gpart = h->take_part(w_off, own_bias ? (int64_t)L::KCOL * L::COUT : (int64_t)P::PART, splits, (int64_t)P::PART);
   if (!BIAS_ROW) {
     h->launches_per_update++;
+    const int blocks = own_bias ? std::max(1, std::min(4 * kNumSMs, p.K / 64)) : splits;
+    float* bpart = own_bias ? h->take_part(w_off + (int64_t)L::KCOL * L::COUT, L::COUT, blocks) : p.gpart;
     if (!h->sizing) {
       cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(splits); cfg.blockDim = dim3(256); cfg.stream = bias_st;
+      cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(256); cfg.stream = bias_st;
       cudaLaunchAttribute attr[1];
       attr[0].id = cudaLaunchAttributePriority;
       attr[0].val.priority = h->boost ? h->prio_hi : 0;
       cfg.attrs = attr; cfg.numAttrs = 1;
-      DQNB_CUDA(cudaLaunchKernelEx(&cfg, bias_colsum_kernel<L::COUT>, dy, p.K, p.gpart, (size_t)P::PART,
-                                   (size_t)L::KCOL * L::COUT, h->next_tl("bias_colsum")));
+      DQNB_CUDA(cudaLaunchKernelEx(&cfg, bias_colsum_kernel<L::COUT>, dy, p.K, bpart,
+                                   own_bias ? (size_t)L::COUT : (size_t)P::PART,
+                                   own_bias ? (size_t)0 : (size_t)L::KCOL * L::COUT, h->next_tl("bias_colsum")));
       DQNB_TRY(mark(h, bias_st, "bias_colsum"));
     }
   }
@@ -408,7 +429,7 @@ int t32_conv_dgrad(dqnb_learner* h, int rows, const float* dy, const float* w, c
   p.K = T32ConvDgrad<L, KB>::T * T32ConvDgrad<L, KB>::T * L::COUT;
   p.dy = dy; p.w = w; p.act_in = act_in; p.dx = dx;
   const int Z = L::STRIDE * L::STRIDE;
-  return run_t32(h, p, Z, t32_splits_for(p, Z), st);
+  return run_t32(h, p, Z, t32_splits(h, p, Z), st);
 }
 
 template <int KB, int BN>
@@ -416,7 +437,7 @@ int t32_dense_wgrad(dqnb_learner* h, int rows, bool fuse, cudaStream_t st) {
   T32DenseWgrad<KB, BN> p;
   p.M = kFc1In + 1; p.N = kFc1Out; p.K = rows;
   p.x = h->a3[0]; p.dy = h->dh1;
-  const int splits = t32_splits_for(p, 1);
+  const int splits = t32_splits(h, p, 1);
   p.fuse = FusedRmsProp{nullptr, nullptr, nullptr, nullptr, nullptr, 0.f, 0.f, 0.f};
   p.gpart = nullptr;
   if (fuse && splits == 1) {
@@ -457,12 +478,20 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   }
   if (live) DQNB_TRY(fork(h->ev[0], st, s1));
   h->launches_per_update++;
+  float* fc2_part = nullptr;
+  constexpr int kFc2Slices = 32;
+  if (h->stream) fc2_part = h->take_part(h->L.fw2, (int64_t)kFc1Out * h->A, kFc2Slices);
   if (live) {
     int n = kFc1Out * h->A;
-    fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
-                                                     h->dq_taken, h->row_loss, h->grad + h->L.fw2,
-                                                     h->grad + h->L.fb2, h->loss, LossRing{h->loss_ring, h->d_seq},
-                                                     h->next_tl("fc2_wgrad"));
+    if (h->stream)
+      fc2_wgrad_sliced_kernel<<<dim3((n + 255) / 256, kFc2Slices), 256, 0, s1>>>(
+          B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act, h->dq_taken, h->row_loss, fc2_part,
+          h->grad + h->L.fb2, h->loss, LossRing{h->loss_ring, h->d_seq}, h->next_tl("fc2_wgrad"));
+    else
+      fc2_wgrad_kernel<<<(n + 255) / 256, 256, 0, s1>>>(B, h->A, h->cfg.shared_bias, g.inv_mean, h->h1[0], h->act,
+                                                       h->dq_taken, h->row_loss, h->grad + h->L.fw2,
+                                                       h->grad + h->L.fb2, h->loss, LossRing{h->loss_ring, h->d_seq},
+                                                       h->next_tl("fc2_wgrad"));
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, s1, "fc2_wgrad"));
   }
@@ -470,7 +499,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     T32DenseDgrad p;
     p.M = B; p.N = kFc1In; p.K = kFc1Out;
     p.dy = h->dh1; p.w = h->online_r + h->L.fw1; p.act = h->a3[0]; p.dx = h->dy3;
-    DQNB_TRY(run_t32(h, p, 1, t32_splits_for(p, 1), st));
+    DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
   }
   if (live) DQNB_TRY(fork(h->ev[1], st, s3));
   DQNB_TRY((t32_conv_wgrad<Conv3, float, 8, true>(h, B, h->a2[0], h->dy3, h->L.w3, s3)));
@@ -481,7 +510,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
   // kernels (conv2 dgrad, conv1 wgrad) leave room for its small CTAs beside their own on every SM.
   bool fused = false;
-  if (B <= kT32BK && !h->cfg.defer_apply) {
+  if (B <= kT32BK && !h->cfg.defer_apply && !h->stream) {
     fused = true;
     if (live && !h->profiling && !h->pdl && !getenv("DQNB_NO_STAGGER")) { stagger_kernel<<<1, 32, 0, s2>>>(); DQNB_CUDA(cudaGetLastError()); }
     // With dependent launches the chain always has CTAs pending, so a low-priority kernel would only
@@ -510,7 +539,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   }
   h->launches_per_update++;
   if (live) {
-    const int64_t split_end = fused ? h->L.fw1 : h->L.fw2;
+    const int64_t split_end = fused ? h->L.fw1 : (h->stream ? h->L.fb2 : h->L.fw2);   // stream: fc2's slices too
     const int64_t skip_lo = fused ? h->L.fw1 : 0, skip_hi = fused ? h->L.fw2 : 0;
     if (h->cfg.defer_apply)   // sum the split-K partials into DQNB_GRAD, nothing else
       rmsprop_reduce_kernel<false><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
@@ -572,6 +601,10 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   h->device = device;
   h->B = cfg->batch_size; h->A = cfg->num_actions; h->nets = cfg->double_q ? 3 : 2;
   h->tf32 = cfg->precision == DQNB_TF32;
+  {
+    const char* e = getenv("DQNB_STREAM_MIN_BATCH");   // testing knob: batch size from which the ring kernel is used
+    h->stream = h->tf32 && cfg->batch_size >= (e ? atoi(e) : kStreamMinBatch);
+  }
   h->L = make_layout(h->A, cfg->shared_bias);
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));

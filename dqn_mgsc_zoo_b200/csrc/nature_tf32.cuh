@@ -55,6 +55,7 @@ struct T32ConvFwd {
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
   static constexpr bool A_REG = sizeof(TIn) == 1;   // uint8 frames (conv1): 4 packed bytes per chunk
   static constexpr bool A_ROW16 = sizeof(TIn) == 1 && L::ROWLEN == 32;   // k-block = one 32-byte patch row
+  static constexpr int B_RESIDENT_KB = (L::KCOL + kT32BK - 1) / kT32BK;   // stream kernel: the filters stay in smem
   int M, N, K;
   const TIn* x[kMaxNets];
   const float* w[kMaxNets];
@@ -106,9 +107,12 @@ struct T32ConvFwdDoubleQ {
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = false;
   static constexpr bool A_REG = sizeof(TIn) == 1;
   static constexpr bool A_ROW16 = sizeof(TIn) == 1 && L::ROWLEN == 32;
+  static constexpr int B_RESIDENT_KB = (L::KCOL + kT32BK - 1) / kT32BK;
   __device__ const uint8_t* a_row16(int z, int m) const { return reinterpret_cast<const uint8_t*>(a_row(z, m)); }
   __device__ int a_kb_off(int kb) const { return kb * (L::WIN * L::CIN); }
   int M, N, K, Mh;          // M = 2 * Mh, N = 2 * COUT
+  // (the two-entry arrays below are only ever read through selects: a dynamically indexed kernel
+  // parameter array would be copied to local memory)
   const TIn* x[2];          // s_tm1, s_t
   const float* w[2];        // online, target
   const float* bias[2];
@@ -122,7 +126,7 @@ struct T32ConvFwdDoubleQ {
     const int half = m >= Mh, mm = m - half * Mh;
     int b = mm / (L::HOUT * L::WOUT), r = mm - b * (L::HOUT * L::WOUT);
     int i = r / L::WOUT, j = r - i * L::WOUT;
-    return x[half] + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
+    return (half ? x[1] : x[0]) + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
   }
   __device__ ACol a_col(int, int k) const {
     if (k >= K) return -1;
@@ -141,14 +145,14 @@ struct T32ConvFwdDoubleQ {
   __device__ BCol b_col(int, int k) const { return k < K ? k : -1; }
   __device__ void b_put(const BRow& r, BCol c, uint32_t dst) const {
     const bool ok = r.n >= 0 && c >= 0;
-    cp16(dst, ok ? w[r.which] + (size_t)c * L::COUT + r.n : w[0], ok);
+    cp16(dst, ok ? (r.which ? w[1] : w[0]) + (size_t)c * L::COUT + r.n : w[0], ok);
   }
   __device__ void store4(int, int, int m, int n, float4 v) const {
     const int half = m >= Mh, which = n >= L::COUT;
     if (!half && which) return;
     const int nn = n - which * L::COUT;
     float* dst = half ? (which ? y[1] : y[2]) : y[0];
-    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[which] + nn));
+    const float4 b = __ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + nn));
     constexpr float s = InScale<TIn>::value;
     *reinterpret_cast<float4*>(dst + (size_t)(m - half * Mh) * L::COUT + nn) =
         tf32_rn4(make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
@@ -167,6 +171,7 @@ struct T32ConvWgrad {
   static constexpr int BN = L::COUT, KB_MAX = KB_;
   static constexpr bool A_MN_MAJOR = true, B_MN_MAJOR = true, DEFER_REDUCE = true;
   static constexpr bool A_REG = sizeof(TIn) == 1;
+  static constexpr bool B_REG = sizeof(TIn) == 1 && L::COUT == 32;   // conv1 (stream kernel): dy rides the register prefetch too
   static constexpr int ROWS = L::KCOL + (BIAS_ROW ? 1 : 0);
   static constexpr size_t PART = (size_t)(L::KCOL + 1) * L::COUT;   // floats per split in gpart
   int M, N, K;              // M = ROWS, N = COUT, K = B*HOUT*WOUT
@@ -202,6 +207,9 @@ struct T32ConvWgrad {
   __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
   __device__ BCol b_col(int, int k) const { return T32MatKN::col(dy, k, K, N); }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, dy); }
+  __device__ float4 b_get(BRow r, BCol c) const {
+    return (c != nullptr && r >= 0) ? __ldg(reinterpret_cast<const float4*>(c + r)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   __device__ void store4(int, int split, int m, int n, float4 v) const {
     const float s = m < L::KCOL ? InScale<TIn>::value : 1.0f;
     *reinterpret_cast<float4*>(gpart + (size_t)split * PART + (size_t)m * N + n) =

@@ -10,6 +10,7 @@ struct T32ConvDgrad {
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
   static constexpr int S = L::STRIDE, T = L::KS / L::STRIDE;
   static constexpr int NY = (L::HIN + S - 1) / S, NX = (L::WIN + S - 1) / S;
+  static constexpr int B_RESIDENT_KB = (T * T * L::COUT + kT32BK - 1) / kT32BK;   // per parity class z
   static_assert(L::KS % L::STRIDE == 0, "taps per parity class must be uniform");
   int M, N, K;              // M = B*NY*NX, N = CIN, K = T*T*COUT
   const float* dy;          // [B,HOUT,WOUT,COUT], already relu-masked
