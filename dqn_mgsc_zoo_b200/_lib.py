@@ -44,6 +44,7 @@ SIGNATURES = {
     "dqnb_learner_device_ptr": [c_vp, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_i64)],
     "dqnb_learner_write_dev": [c_vp, c_int, c_vp, c_i64, STREAM],
     "dqnb_learner_apply_grads": [c_vp, STREAM],
+    "dqnb_learner_adjoint_dots": [c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_get_config": [c_vp, c_vp, ctypes.POINTER(c_int)],
     "dqnb_mgsc_create": [c_vp, c_vp, ctypes.POINTER(c_vp)],
     "dqnb_mgsc_destroy": [c_vp],

@@ -436,4 +436,51 @@ inline unsigned rmsprop_reduce_blocks(int64_t n, int64_t split_end, int64_t skip
   return (unsigned)((threads + 255) / 256);
 }
 
+// MGSC adjoint dots (dqn_mgsc_batched/agent.py:171-214): for row i of the last update,
+//   out[i] = <v, d loss_i / d theta> = sum over layers l of <dy_l[i], V_l * x_l[i] + vb_l>
+// with dy_l the saved pre-activation cotangents of the backward pass and z_l = V_l * x_l + vb_l the
+// layer-local forward products of the direction v (z1..z4, computed by the forward GEMMs with v in
+// the weight slot and no ReLU).  fc2's term is formed here.  One CTA per row, float64 partials,
+// fixed summation order.
+struct AdjointArgs {
+  int num_actions, shared_bias;
+  const float *dy1, *z1, *dy2, *z2, *dy3, *z3, *dh1, *z4;   // [batch, n_l]
+  int n1, n2, n3, n4;
+  const float* h1;          // [batch,512] relu(fc1) of the online net
+  const float* dq_taken;    // [batch]
+  const int32_t* action;
+  const float* v_w2;        // [512,A] slice of v
+  const float* v_b2;        // [A] or [1]
+  float* out;               // [batch]
+};
+
+__device__ __forceinline__ double dot_span(const float* __restrict__ a, const float* __restrict__ b, int n, int t) {
+  double acc = 0.0;
+  const float4* a4 = reinterpret_cast<const float4*>(a);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+  for (int i = t; i < (n >> 2); i += 256) {
+    const float4 x = a4[i], y = b4[i];
+    acc += (double)x.x * y.x + (double)x.y * y.y + (double)x.z * y.z + (double)x.w * y.w;
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(256) adjoint_dot_kernel(AdjointArgs g) {
+  __shared__ double red[256];
+  const int row = blockIdx.x, t = threadIdx.x;
+  double acc = dot_span(g.dy1 + (size_t)row * g.n1, g.z1 + (size_t)row * g.n1, g.n1, t);
+  acc += dot_span(g.dy2 + (size_t)row * g.n2, g.z2 + (size_t)row * g.n2, g.n2, t);
+  acc += dot_span(g.dy3 + (size_t)row * g.n3, g.z3 + (size_t)row * g.n3, g.n3, t);
+  acc += dot_span(g.dh1 + (size_t)row * g.n4, g.z4 + (size_t)row * g.n4, g.n4, t);
+  const int act = g.action[row];
+  const double dq = (double)g.dq_taken[row];
+  for (int k = t; k < g.n4; k += 256)
+    acc += dq * (double)g.h1[(size_t)row * g.n4 + k] * (double)g.v_w2[(size_t)k * g.num_actions + act];
+  if (t == 0) acc += dq * (double)g.v_b2[g.shared_bias ? 0 : act];
+  red[t] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  if (t == 0) g.out[row] = (float)red[0];
+}
+
 }  // namespace dqnb

@@ -165,8 +165,9 @@ int run_gemm(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
 
 template <class L, class TIn, int BM>
 int conv_fwd(dqnb_learner* h, int nets, int rows, const TIn* const* x, const float* const* params,
-             int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st) {
+             int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st, bool linear = false) {
   ConvFwd<L, TIn, BM> p;
+  p.linear = linear;
   p.M = rows * L::HOUT * L::WOUT; p.N = L::COUT; p.K = L::KCOL;
   for (int z = 0; z < nets; ++z) {
     p.x[z] = x[z]; p.w[z] = params[z] + w_off; p.bias[z] = params[z] + b_off; p.y[z] = y[z];
@@ -204,7 +205,7 @@ HeadArgs head_args(dqnb_learner* h, int rows, const float* const* params, int ne
     int zz = std::min(z, nets - 1);
     g.b1[z] = params[zz] + h->L.fb1; g.h1_out[z] = h->h1[zz];
   }
-  g.action = h->act; g.reward = h->rew; g.discount = h->disc; g.row_weight = nullptr;
+  g.action = h->act; g.reward = h->rew; g.discount = h->disc; g.row_weight = h->row_weight;   // null unless cfg.row_weighted
   g.td = h->td; g.row_loss = h->row_loss; g.dq_taken = h->dq_taken; g.dh1 = h->dh1;
   return g;
 }
@@ -562,6 +563,41 @@ int enqueue_any(dqnb_learner* h, cudaStream_t st) {
   return rc;
 }
 
+// MGSC adjoint dots: the four layer-local forward products of the direction `v` (an arena laid out
+// like the parameters) on the activations the last update saved, into the dead target-net
+// activation buffers, then one dot kernel.  fp32 SIMT GEMMs in both precision modes.
+int enqueue_adjoint(dqnb_learner* h, const float* v, float* out, cudaStream_t st) {
+  h->ws_off = h->cnt_off = 0;
+  const int B = h->B;
+  const uint8_t* x1[kMaxNets] = {h->s_tm1, nullptr, nullptr};
+  const float* x2[kMaxNets] = {h->a1[0], nullptr, nullptr};
+  const float* x3[kMaxNets] = {h->a2[0], nullptr, nullptr};
+  const float* vp[kMaxNets] = {v, nullptr, nullptr};
+  float* z1[kMaxNets] = {h->a1[1], nullptr, nullptr};
+  float* z2[kMaxNets] = {h->a2[1], nullptr, nullptr};
+  float* z3[kMaxNets] = {h->a3[1], nullptr, nullptr};
+  DQNB_TRY((conv_fwd<Conv1, uint8_t, 64>(h, 1, B, x1, vp, h->L.w1, h->L.b1, z1, st, true)));
+  DQNB_TRY((conv_fwd<Conv2, float, 32>(h, 1, B, x2, vp, h->L.w2, h->L.b2, z2, st, true)));
+  DQNB_TRY((conv_fwd<Conv3, float, 32>(h, 1, B, x3, vp, h->L.w3, h->L.b3, z3, st, true)));
+  DenseFwd p;
+  p.linear = 1;
+  p.M = B; p.N = kFc1Out; p.K = kFc1In;
+  p.x[0] = h->a3[0]; p.w[0] = v + h->L.fw1; p.bias[0] = v + h->L.fb1; p.y[0] = h->h1[1];
+  DQNB_TRY(run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st));
+  if (h->sizing) return DQNB_OK;
+  AdjointArgs g;
+  g.num_actions = h->A; g.shared_bias = h->cfg.shared_bias;
+  g.dy1 = h->dy1; g.z1 = h->a1[1]; g.n1 = Conv1::OUT_PER_IMG;
+  g.dy2 = h->dy2; g.z2 = h->a2[1]; g.n2 = Conv2::OUT_PER_IMG;
+  g.dy3 = h->dy3; g.z3 = h->a3[1]; g.n3 = Conv3::OUT_PER_IMG;
+  g.dh1 = h->dh1; g.z4 = h->h1[1]; g.n4 = kFc1Out;
+  g.h1 = h->h1[0]; g.dq_taken = h->dq_taken; g.action = h->act;
+  g.v_w2 = v + h->L.fw2; g.v_b2 = v + h->L.fb2; g.out = out;
+  adjoint_dot_kernel<<<B, 256, 0, st>>>(g);
+  DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+
 int build_graph(dqnb_learner* h) {
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
@@ -613,6 +649,11 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));
   DQNB_TRY(dmalloc(&h->act, B)); DQNB_TRY(dmalloc(&h->rew, B)); DQNB_TRY(dmalloc(&h->disc, B));
   DQNB_TRY(dmalloc(&h->d_slots, B));
+  if (cfg->row_weighted) {
+    DQNB_TRY(dmalloc(&h->row_weight, B));
+    std::vector<float> ones(B, 1.0f);
+    DQNB_CUDA(cudaMemcpy(h->row_weight, ones.data(), sizeof(float) * B, cudaMemcpyHostToDevice));
+  }
   for (int z = 0; z < h->nets; ++z) {
     DQNB_TRY(dmalloc(&h->a1[z], B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->a2[z], B * Conv2::OUT_PER_IMG));
     DQNB_TRY(dmalloc(&h->a3[z], B * Conv3::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->h1[z], B * kFc1Out));
@@ -640,8 +681,14 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   // size the split-K scratch with a dry pass, then record the graph
   h->sizing = true;
   DQNB_TRY(enqueue_any(h, nullptr));
-  h->sizing = false;
   h->ws_cap = h->ws_off; h->cnt_cap = h->cnt_off; h->part_cap = h->part_off;
+  if (cfg->row_weighted) {   // the adjoint-dot GEMMs borrow the same split-K scratch
+    const int64_t launches = h->launches_per_update;
+    DQNB_TRY(enqueue_adjoint(h, nullptr, nullptr, nullptr));
+    h->launches_per_update = launches;
+    h->ws_cap = std::max(h->ws_cap, h->ws_off); h->cnt_cap = std::max(h->cnt_cap, h->cnt_off);
+  }
+  h->sizing = false;
   DQNB_TRY(dmalloc(&h->ws, h->ws_cap)); DQNB_TRY(dmalloc(&h->counters, h->cnt_cap));
   if (h->part_cap) DQNB_TRY(dmalloc(&h->gpart, h->part_cap));
   if (h->fc1_part_cap) DQNB_TRY(dmalloc(&h->fc1_part, h->fc1_part_cap));
@@ -658,7 +705,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   cudaDeviceSynchronize();
   if (h->graph) cudaGraphExecDestroy(h->graph);
   float* fl[] = {h->online, h->target, h->mu, h->nu, h->grad, h->rew, h->disc, h->dh1, h->dy3, h->dy2, h->dy1,
-                 h->td, h->row_loss, h->dq_taken, h->loss, h->ws, h->gpart, h->fc1_part, h->online_r, h->target_r};
+                 h->td, h->row_loss, h->dq_taken, h->loss, h->ws, h->gpart, h->fc1_part, h->online_r, h->target_r,
+                 h->row_weight};
   for (float* p : fl) cudaFree(p);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
   cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
@@ -700,6 +748,9 @@ int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
     case DQNB_Q_T: DQNB_REQUIRE(h->nets == 3, "Q_T only exists for double-Q learners"); *p = h->q[2]; *n = BA; break;
     case DQNB_TD: *p = h->td; *n = h->B; break;
     case DQNB_LOSS: *p = h->loss; *n = 1; break;
+    case DQNB_ROW_WEIGHT:
+      DQNB_REQUIRE(h->row_weight, "row weights only exist for learners created with row_weighted = 1");
+      *p = h->row_weight; *n = h->B; break;
     // undocumented debug taps (activation gradients / activations of the online net)
     case 100: *p = h->dh1; *n = (int64_t)h->B * kFc1Out; break;
     case 101: *p = h->dy3; *n = (int64_t)h->B * Conv3::OUT_PER_IMG; break;
@@ -742,7 +793,7 @@ extern "C" int dqnb_learner_device_ptr(dqnb_learner* h, int which, void** ptr, i
 
 extern "C" int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* dev_src, int64_t n, uintptr_t stream) {
   DQNB_REQUIRE(h && dev_src, "null argument");
-  DQNB_REQUIRE(which >= DQNB_ONLINE && which <= DQNB_GRAD, "state array %d is read-only", which);
+  DQNB_REQUIRE((which >= DQNB_ONLINE && which <= DQNB_GRAD) || which == DQNB_ROW_WEIGHT, "state array %d is read-only", which);
   DeviceGuard guard(h->device);
   float* p; int64_t len;
   DQNB_TRY(locate(h, which, &p, &len));
@@ -772,6 +823,14 @@ extern "C" int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream) {
   }
   DQNB_CUDA(cudaGetLastError());
   return DQNB_OK;
+}
+
+extern "C" int dqnb_learner_adjoint_dots(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream) {
+  DQNB_REQUIRE(h && v_dev && out_dev, "null argument");
+  DQNB_REQUIRE(h->row_weight, "adjoint dots need a learner created with row_weighted = 1");
+  DQNB_REQUIRE(h->nets == 2, "adjoint dots are defined for the q_learning loss (double_q = 0)");
+  DeviceGuard guard(h->device);
+  return enqueue_adjoint(h, v_dev, out_dev, as_stream(stream));
 }
 
 extern "C" int dqnb_learner_read(dqnb_learner* h, int which, float* host, int64_t n, uintptr_t stream) {
@@ -902,6 +961,7 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
   else DQNB_TRY(forward_torso(h, 1, n, xin, params, st));
   HeadArgs g = head_args(h, n, params, 2);
   g.h1[1] = g.h1[0]; g.q[1] = h->q[1];   // head also evaluates a dummy target row; harmless
+  g.row_weight = nullptr;
   if (h->tf32) {   // one net's partials; the dummy second net re-reads them
     g.fc1_part = h->fc1_part; g.fc1_splits = h->fc1_splits;
   }

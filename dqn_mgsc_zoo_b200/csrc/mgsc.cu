@@ -8,9 +8,12 @@
 //   dL/dp_i = <v, g_i>,  v = 2 (theta_exp - theta_tgt) * du/dG  (SURVEY R12 identity)
 //   dL/dlogit_j = p_j (dL/dp_j - sum_i p_i dL/dp_i) ; Adam on the (M,) logits   agent.py:206-214
 //
-// The per-sample gradients are materialised like the reference's vmap does (M x 6.75 MB, in HBM):
-// an internal batch-of-1 learner with defer_apply runs once per meta transition on the same
-// kernels as the normal update.  Everything else is a handful of flat streaming kernels.
+// The vmapped per-sample gradients are never materialised (the reference holds M x 6.75 MB): an
+// internal batch-of-M learner (`bat`: defer_apply, row_weighted, loss over 1 row) runs ONE batched
+// forward/backward whose row cotangents are p_i * clip(td_i), so its gradient arena is G; the
+// inner products <v, g_i> come from the same pass's saved activations and cotangents
+// (dqnb_learner_adjoint_dots: <v, p_i g_i> = sum_l <dy_l[i], V_l x_l[i]>), divided by p_i.
+// A batch-of-1 learner (`sub`) takes the gradient at theta_exp on the online transition.
 #include <algorithm>
 #include <vector>
 
@@ -19,7 +22,6 @@
 using namespace dqnb;
 
 namespace {
-constexpr int kDotBlocks = 64;     // partial sums per sample in the <v, g_i> reduction
 constexpr int kLossBlocks = 128;   // partial sums of the meta loss
 constexpr int kMaxMeta = 1024;
 
@@ -40,16 +42,6 @@ __global__ void softmax_kernel(const float* __restrict__ logits, float* __restri
   for (int s = 128; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
   const float lse = mx + logf(red[0]);
   for (int i = t; i < M; i += 256) p[i] = expf(logits[i] - lse);
-}
-
-// G[j] = sum_i p[i] * per[i][j], i ascending.
-__global__ void weighted_sum_kernel(const float* __restrict__ per, const float* __restrict__ p, float* __restrict__ G,
-                                    int M, int64_t P) {
-  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= P) return;
-  float acc = 0.f;
-  for (int i = 0; i < M; ++i) acc = fmaf(__ldg(p + i), per[(size_t)i * P + j], acc);
-  G[j] = acc;
 }
 
 // optax 0.1.2 rmsprop(centered) as a pure function: (theta, G, mu, nu) -> (theta_exp, mu1, nu1).
@@ -91,26 +83,12 @@ __global__ void meta_v_kernel(const float* __restrict__ g2, const float* __restr
   if (threadIdx.x == 0) loss_part[blockIdx.x] = red[0];
 }
 
-// part[i][b] = sum over chunk b of per[i][j] * v[j]   (grid = kDotBlocks x M)
-__global__ void dots_kernel(const float* __restrict__ per, const float* __restrict__ v, float* __restrict__ part,
-                            int64_t P) {
-  __shared__ float red[256];
-  const int i = blockIdx.y, b = blockIdx.x;
-  const int64_t chunk = (P + gridDim.x - 1) / gridDim.x;
-  const int64_t beg = (int64_t)b * chunk, end = beg + chunk < P ? beg + chunk : P;
-  const float* row = per + (size_t)i * P;
-  float acc = 0.f;
-  for (int64_t j = beg + threadIdx.x; j < end; j += 256) acc = fmaf(row[j], __ldg(v + j), acc);
-  red[threadIdx.x] = acc;
-  __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
-  if (threadIdx.x == 0) part[(size_t)i * gridDim.x + b] = red[0];
-}
-
 // softmax backward + optax.adam (scale_by_adam bias-corrected, eps outside the sqrt) on the logits.
 // One block; M <= kMaxMeta.
+// `wdot[i]` = <v, p_i g_i>: dL/dp_i = wdot[i] / p_i.  A p_i that underflowed leaves dL/dp_i = 0: its
+// logit gradient p_i (dL/dp_i - mean) vanishes for any finite dL/dp_i.
 __global__ void logits_adam_kernel(const float* __restrict__ logits, const float* __restrict__ p,
-                                   const float* __restrict__ dot_part, const float* __restrict__ loss_part,
+                                   const float* __restrict__ wdot, const float* __restrict__ loss_part,
                                    float* __restrict__ dldp, float* __restrict__ adam_m, float* __restrict__ adam_v,
                                    float* __restrict__ out_logits, float* __restrict__ out_loss, int M, int count,
                                    float lr, float b1, float b2, float eps) {
@@ -119,8 +97,7 @@ __global__ void logits_adam_kernel(const float* __restrict__ logits, const float
   const int t = threadIdx.x;
   float acc = 0.f;
   for (int i = t; i < M; i += 256) {
-    float d = 0.f;
-    for (int b = 0; b < kDotBlocks; ++b) d += dot_part[(size_t)i * kDotBlocks + b];
+    const float d = p[i] > 1e-30f ? wdot[i] / p[i] : 0.f;
     d_s[i] = d;
     dldp[i] = d;
     acc = fmaf(p[i], d, acc);
@@ -147,7 +124,8 @@ __global__ void logits_adam_kernel(const float* __restrict__ logits, const float
 
 struct dqnb_mgsc {
   dqnb_learner* main = nullptr;
-  dqnb_learner* sub = nullptr;     // batch-of-1, defer_apply: the per-sample gradient engine
+  dqnb_learner* bat = nullptr;     // batch-of-M, defer_apply + row_weighted: G and the adjoint dots in one pass
+  dqnb_learner* sub = nullptr;     // batch-of-1, defer_apply: gradient at theta_exp on the online transition
   dqnb_learner_config lcfg{};
   dqnb_mgsc_config cfg{};
   int device = 0, M = 0;
@@ -157,7 +135,7 @@ struct dqnb_mgsc {
   uint8_t *mb_s0 = nullptr, *mb_s1 = nullptr;
   int32_t* mb_a = nullptr;
   float *mb_r = nullptr, *mb_d = nullptr;
-  float *per = nullptr, *G = nullptr, *theta_exp = nullptr, *mu1 = nullptr, *nu1 = nullptr, *v = nullptr;
+  float *G = nullptr, *theta_exp = nullptr, *mu1 = nullptr, *nu1 = nullptr, *v = nullptr;
   float *logits = nullptr, *p = nullptr, *dldp = nullptr, *dot_part = nullptr, *loss_part = nullptr;
   float *adam_m = nullptr, *adam_v = nullptr, *out = nullptr;   // out: [M] new logits + [1] loss
   float* pinned = nullptr;                                      // [2M + 8]
@@ -178,25 +156,23 @@ int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host,
   const int M = h->M;
   const int64_t P = h->P;
   const uintptr_t s = reinterpret_cast<uintptr_t>(st);
-  void *theta = nullptr, *theta_t = nullptr, *mu = nullptr, *nu = nullptr, *sub_grad = nullptr;
+  void *theta = nullptr, *theta_t = nullptr, *mu = nullptr, *nu = nullptr, *sub_grad = nullptr, *bat_grad = nullptr;
   int64_t n = 0;
   DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_ONLINE, &theta, &n));
   DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_TARGET, &theta_t, &n));
   DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_MU, &mu, &n));
   DQNB_TRY(dqnb_learner_device_ptr(h->main, DQNB_NU, &nu, &n));
   DQNB_TRY(dqnb_learner_device_ptr(h->sub, DQNB_GRAD, &sub_grad, &n));
+  DQNB_TRY(dqnb_learner_device_ptr(h->bat, DQNB_GRAD, &bat_grad, &n));
   DQNB_CUDA(cudaMemcpyAsync(h->logits, h->pinned, sizeof(float) * M, cudaMemcpyHostToDevice, st));
   softmax_kernel<<<1, 256, 0, st>>>(h->logits, h->p, M);
-  // per-sample gradients at (theta, theta_target)
-  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_ONLINE, static_cast<const float*>(theta), P, s));
-  DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_TARGET, static_cast<const float*>(theta_t), P, s));
-  for (int i = 0; i < M; ++i) {
-    DQNB_TRY(dqnb_learner_update(h->sub, h->mb_s0 + i * h->img, h->mb_a + i, h->mb_r + i, h->mb_d + i,
-                                 h->mb_s1 + i * h->img, s));
-    DQNB_CUDA(cudaMemcpyAsync(h->per + (size_t)i * P, sub_grad, sizeof(float) * P, cudaMemcpyDeviceToDevice, st));
-  }
+  // G = sum_i p_i g_i at (theta, theta_target): one batched pass with row weights p
+  DQNB_TRY(dqnb_learner_write_dev(h->bat, DQNB_ROW_WEIGHT, h->p, M, s));
+  DQNB_TRY(dqnb_learner_write_dev(h->bat, DQNB_ONLINE, static_cast<const float*>(theta), P, s));
+  DQNB_TRY(dqnb_learner_write_dev(h->bat, DQNB_TARGET, static_cast<const float*>(theta_t), P, s));
+  DQNB_TRY(dqnb_learner_update(h->bat, h->mb_s0, h->mb_a, h->mb_r, h->mb_d, h->mb_s1, s));
+  DQNB_CUDA(cudaMemcpyAsync(h->G, bat_grad, sizeof(float) * P, cudaMemcpyDeviceToDevice, st));
   const unsigned pb = (unsigned)((P + 255) / 256);
-  weighted_sum_kernel<<<pb, 256, 0, st>>>(h->per, h->p, h->G, M, P);
   virtual_step_kernel<<<pb, 256, 0, st>>>(static_cast<const float*>(theta), h->G, static_cast<const float*>(mu),
                                           static_cast<const float*>(nu), h->theta_exp, h->mu1, h->nu1, P,
                                           h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
@@ -207,7 +183,7 @@ int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host,
                                h->mb_s1 + M * h->img, s));
   meta_v_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->v,
                                              h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
-  dots_kernel<<<dim3(kDotBlocks, M), 256, 0, st>>>(h->per, h->v, h->dot_part, P);
+  DQNB_TRY(dqnb_learner_adjoint_dots(h->bat, h->v, h->dot_part, s));
   h->count += 1;
   logits_adam_kernel<<<1, 256, 0, st>>>(h->logits, h->p, h->dot_part, h->loss_part, h->dldp, h->adam_m, h->adam_v,
                                         h->out, h->out + M, M, h->count, h->cfg.learning_rate, h->cfg.b1,
@@ -255,17 +231,19 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
   sc.batch_size = 1; sc.loss_mean_over = 1; sc.double_q = 0; sc.defer_apply = 1;
   rc = dqnb_learner_create(&sc, h->device, &h->sub);
   if (rc != DQNB_OK) { delete h; return rc; }
+  sc.batch_size = h->M; sc.row_weighted = 1;
+  rc = dqnb_learner_create(&sc, h->device, &h->bat);
+  if (rc != DQNB_OK) { dqnb_learner_destroy(h->sub); delete h; return rc; }
   DeviceGuard guard(h->device);
   DQNB_TRY(dqnb_learner_num_params(learner, &h->P));
   h->img = 84 * 84 * 4;
   const size_t M1 = (size_t)h->M + 1, P = (size_t)h->P;
   DQNB_TRY(dalloc(&h->mb_s0, M1 * h->img)); DQNB_TRY(dalloc(&h->mb_s1, M1 * h->img));
   DQNB_TRY(dalloc(&h->mb_a, M1)); DQNB_TRY(dalloc(&h->mb_r, M1)); DQNB_TRY(dalloc(&h->mb_d, M1));
-  DQNB_TRY(dalloc(&h->per, (size_t)h->M * P));
   DQNB_TRY(dalloc(&h->G, P)); DQNB_TRY(dalloc(&h->theta_exp, P)); DQNB_TRY(dalloc(&h->mu1, P));
   DQNB_TRY(dalloc(&h->nu1, P)); DQNB_TRY(dalloc(&h->v, P));
   DQNB_TRY(dalloc(&h->logits, M1)); DQNB_TRY(dalloc(&h->p, M1)); DQNB_TRY(dalloc(&h->dldp, M1));
-  DQNB_TRY(dalloc(&h->dot_part, (size_t)h->M * kDotBlocks)); DQNB_TRY(dalloc(&h->loss_part, kLossBlocks));
+  DQNB_TRY(dalloc(&h->dot_part, M1)); DQNB_TRY(dalloc(&h->loss_part, kLossBlocks));
   DQNB_TRY(dalloc(&h->adam_m, M1)); DQNB_TRY(dalloc(&h->adam_v, M1)); DQNB_TRY(dalloc(&h->out, M1 + 1));
   DQNB_CUDA(cudaMallocHost(&h->pinned, sizeof(float) * (2 * M1 + 8)));
   *out = h;
@@ -277,7 +255,8 @@ extern "C" int dqnb_mgsc_destroy(dqnb_mgsc* h) {
   DeviceGuard guard(h->device);
   cudaDeviceSynchronize();
   if (h->sub) dqnb_learner_destroy(h->sub);
-  void* bufs[] = {h->mb_s0, h->mb_s1, h->mb_a, h->mb_r, h->mb_d, h->per, h->G, h->theta_exp, h->mu1, h->nu1, h->v,
+  if (h->bat) dqnb_learner_destroy(h->bat);
+  void* bufs[] = {h->mb_s0, h->mb_s1, h->mb_a, h->mb_r, h->mb_d, h->G, h->theta_exp, h->mu1, h->nu1, h->v,
                   h->logits, h->p, h->dldp, h->dot_part, h->loss_part, h->adam_m, h->adam_v, h->out};
   for (void* b : bufs) cudaFree(b);
   if (h->pinned) cudaFreeHost(h->pinned);

@@ -55,8 +55,10 @@ struct ConvFwd {
   __device__ BCol b_col(int z, int n) const { return {n < N ? w[z] + n : nullptr}; }
   __device__ float b(const BCol& c, int k) const { return (c.p && k < K) ? c.p[(size_t)k * N] : 0.f; }
   __device__ void store(int z, int m, int n, float acc) const {
-    y[z][(size_t)m * N + n] = fmaxf(acc + bias[z][n], 0.f);
+    const float v = acc + bias[z][n];
+    y[z][(size_t)m * N + n] = linear ? v : fmaxf(v, 0.f);
   }
+  int linear = 0;           // 1: no ReLU (the layer-local products of the MGSC adjoint dots)
 };
 
 // ---------------------------------------------------------------- conv weight gradient
@@ -160,8 +162,10 @@ struct DenseFwd {
   __device__ BCol b_col(int z, int n) const { return {n < N ? w[z] + n : nullptr}; }
   __device__ float b(const BCol& c, int k) const { return (c.p && k < K) ? c.p[(size_t)k * N] : 0.f; }
   __device__ void store(int z, int m, int n, float acc) const {
-    y[z][(size_t)m * N + n] = fmaxf(acc + bias[z][n], 0.f);
+    const float v = acc + bias[z][n];
+    y[z][(size_t)m * N + n] = linear ? v : fmaxf(v, 0.f);
   }
+  int linear = 0;
 };
 
 // dW[m'=k_in, n] = sum_b x[b,m'] * dy[b,n];  row m' == IN is ones -> bias gradient.

@@ -16,7 +16,7 @@ class LearnerConfig(ctypes.Structure):
                 ("loss_mean_over", ctypes.c_int32), ("precision", ctypes.c_int32),
                 ("learning_rate", ctypes.c_float), ("decay", ctypes.c_float),
                 ("eps", ctypes.c_float), ("grad_error_bound", ctypes.c_float),
-                ("defer_apply", ctypes.c_int32)]
+                ("defer_apply", ctypes.c_int32), ("row_weighted", ctypes.c_int32)]
 
 
 def param_shapes(num_actions, shared_bias=False):
@@ -46,13 +46,13 @@ def unflatten_params(flat, num_actions, shared_bias=False):
 class Learner:
     def __init__(self, num_actions, batch_size, shared_bias=False, double_q=False, learning_rate=0.00025,
                  decay=0.95, eps=0.01 / 32 ** 2, grad_error_bound=1.0 / 32, precision="fp32", device=0,
-                 stream=0, loss_mean_over=0, defer_apply=False):
+                 stream=0, loss_mean_over=0, defer_apply=False, row_weighted=False):
         self.num_actions, self.batch_size = int(num_actions), int(batch_size)
         self.shared_bias, self.double_q = bool(shared_bias), bool(double_q)
         self.device, self.stream = device, stream
         cfg = LearnerConfig(self.num_actions, int(self.shared_bias), int(self.double_q), self.batch_size,
                             int(loss_mean_over), PRECISIONS[precision], learning_rate, decay, eps,
-                            grad_error_bound, int(bool(defer_apply)))
+                            grad_error_bound, int(bool(defer_apply)), int(bool(row_weighted)))
         self.defer_apply = bool(defer_apply)
         h = ctypes.c_void_p()
         _lib.call("dqnb_learner_create", ctypes.byref(cfg), device, ctypes.byref(h))

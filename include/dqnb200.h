@@ -109,7 +109,10 @@ typedef struct dqnb_learner_config {
   float grad_error_bound;   /* rlax.clip_gradient bound */
   int32_t defer_apply;      /* 1: update() stops after the gradient (DQNB_GRAD holds it); the optimiser
                                step runs in dqnb_learner_apply_grads - the seam for the data-parallel
-                               all-reduce and for the MGSC per-sample gradients */
+                               all-reduce and for the MGSC weighted gradient */
+  int32_t row_weighted;     /* 1: every row's clipped cotangent is multiplied by DQNB_ROW_WEIGHT[row] (initially
+                               1) - with loss_mean_over = 1 the gradient is sum_i w_i grad(loss_i), the
+                               vmapped weighted_grads of dqn_mgsc_batched/agent.py:171-176 as ONE batched pass */
 } dqnb_learner_config;
 
 /* state arrays addressable by read/write */
@@ -123,6 +126,7 @@ typedef struct dqnb_learner_config {
 #define DQNB_Q_T 7        /* [batch, A] online q(s_t) (double-Q only) */
 #define DQNB_TD 8         /* [batch] td errors */
 #define DQNB_LOSS 9       /* [1] mean loss */
+#define DQNB_ROW_WEIGHT 10 /* [batch] per-row cotangent weights (row_weighted learners; device-writable) */
 
 int dqnb_learner_create(const dqnb_learner_config* cfg, int device, dqnb_learner** out);
 int dqnb_learner_destroy(dqnb_learner* h);
@@ -138,6 +142,12 @@ int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* dev_src, int
 /* optimizer.update + apply_updates (dqn/agent.py:115-116) on whatever DQNB_GRAD holds; the second
  * half of an update for learners created with defer_apply = 1. */
 int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream);
+/* row_weighted learners, after an update: out_dev[i] = <v, w_i * d loss_i / d theta> for every row i of
+ * that update's batch, v_dev a device vector laid out like the parameters.  Computed as the sum over
+ * layers of <saved cotangent of row i, layer-local forward product of v> - four forward GEMMs and
+ * one dot kernel instead of `batch` materialised per-sample gradients (the reference's
+ * jax.vmap(weighted_grads), dqn_mgsc_batched/agent.py:171, holds M x 6.75 MB).  Asynchronous. */
+int dqnb_learner_adjoint_dots(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream);
 /* one `update` on a batch that is already in device memory (asynchronous). */
 int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, const int32_t* a_dev,
                         const float* r_dev, const float* disc_dev, const uint8_t* s_t_dev,

@@ -141,7 +141,7 @@ def _meta_case(A, shared, M, seed):
 # flip, which moves single-sample gradients by ~1e-2 (test_learner_gpu.py conditions on the device's
 # own masks for that reason); the meta-gradient is an inner product of such gradients.
 @pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("tf32", 1e-1)])
-@pytest.mark.parametrize("A,shared,M", [(6, False, 5), (4, True, 9)])
+@pytest.mark.parametrize("A,shared,M", [(6, False, 5), (4, True, 9), (6, False, 40)])
 def test_meta_update_matches_oracle(precision, tol, A, shared, M):
     params, target, mu, nu, batch, online_tr, logits = _meta_case(A, shared, M, 17 + M)
     L = lrn.Learner(A, 32, shared_bias=shared, double_q=False, precision=precision)
