@@ -78,6 +78,9 @@ __device__ __forceinline__ void t32_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
+__device__ __forceinline__ void t32_commit_a(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void t32_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void t32_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 template <int kCols>
@@ -196,7 +199,7 @@ __device__ __forceinline__ void t32_retire_groups(int nkb, uint64_t* full_bar) {
     if (I < nkb) {
       cp_wait<KB - 1 - I>();
       fence_proxy_async_smem();
-      mbar_arrive(&full_bar[I]);
+      mbar_arrive_warp(&full_bar[I]);
     }
     t32_retire_groups<KB, I + 1>(nkb, full_bar);
   }
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   const int nkb = max(kb_end - kb_beg, 0);
 
   if (t == 0) {
-    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], kT32Producers);
+    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], kT32Producers / 32);
     mbar_init(&done_bar, 1);
     fence_mbar_init();
   }

@@ -46,17 +46,32 @@ template <class P>
 __host__ __device__ constexpr int t32s_stage_bytes() {
   return t32_tile_bytes(kT32BM, P::A_MN_MAJOR) + (t32_b_resident<P>::value ? 0 : t32_tile_bytes(P::BN, P::B_MN_MAJOR));
 }
+// A_ROW16 problems (uint8 rows of 32 source bytes per k-block): the raw bytes are prefetched with
+// cp.async into a byte ring of kT32SByteDepth k-blocks x 4 KB behind the operand ring; thread t reads
+// back the 16 bytes it copied itself, widens them and stores the tf32 chunks.  cp.async groups retire
+// in order (wait_group counts), which plain LDG prefetches do not: eight loads in flight share the
+// warp's six scoreboards, so waiting for the oldest also waited for the newest.
+constexpr int kT32SByteDepth = 8;
+template <class P>
+__host__ __device__ constexpr int t32s_byte_ring() { return t32_a_row16<P>::value ? kT32SByteDepth * 4096 : 0; }
 template <class P>
 __host__ __device__ constexpr int t32s_stages() {
-  return (208 * 1024 - t32s_resident_bytes<P>()) / t32s_stage_bytes<P>() > 8
+  return (208 * 1024 - t32s_resident_bytes<P>() - t32s_byte_ring<P>()) / t32s_stage_bytes<P>() > 8
              ? 8
-             : (208 * 1024 - t32s_resident_bytes<P>()) / t32s_stage_bytes<P>();
+             : (208 * 1024 - t32s_resident_bytes<P>() - t32s_byte_ring<P>()) / t32s_stage_bytes<P>();
 }
 template <class P>
 __host__ __device__ constexpr int t32s_smem_bytes() {
-  return t32s_resident_bytes<P>() + t32s_stages<P>() * t32s_stage_bytes<P>() + 1024;
+  return t32s_resident_bytes<P>() + t32s_stages<P>() * t32s_stage_bytes<P>() + t32s_byte_ring<P>() + 1024;
 }
 
+// Timing knobs and the event trace exist only in builds that define DQNB_STREAM_KNOBS (the micro
+// harnesses): every knob is a load + branch on the serial path of a ring stage.
+#ifdef DQNB_STREAM_KNOBS
+#define T32S_KNOB(w, bit) ((w).dbg & (bit))
+#else
+#define T32S_KNOB(w, bit) 0
+#endif
 struct T32Work {
   int tiles_m, tiles_n, splits, per, kblocks, items;   // per = k-blocks per split; items = Z*tiles*splits
   int dbg;   // timing experiments only (DQNB_STREAM_DBG): 1 = no epilogue stores, 2 = no A st.shared, 4 = no A loads
@@ -78,6 +93,9 @@ __device__ __forceinline__ T32Item t32s_item(const T32Work& w, int item) {
 // Optional event trace (scripts/micro/stream_trace.cu): CTA 0 writes clock64() of event `idx` of series
 // `series` to sk.dbg[series * 256 + idx].  sk.dbg is null in the product.
 __device__ __forceinline__ void t32s_trace(long long* trace, int series, uint32_t idx) {
+#ifndef DQNB_STREAM_KNOBS
+  return;
+#endif
   if (trace != nullptr && blockIdx.x == 0 && idx < 256) trace[series * 256 + idx] = clock64();
 }
 
@@ -96,16 +114,16 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
   constexpr int A_TILE = t32_tile_bytes(kT32BM, P::A_MN_MAJOR), B_TILE = t32_tile_bytes(BN, P::B_MN_MAJOR);
   constexpr int STAGE = t32s_stage_bytes<P>(), RING = t32s_resident_bytes<P>();   // ring starts behind resident B
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t full_bar[S], empty_bar[S], acc_full[2], acc_empty[2], b_full;
+  __shared__ uint64_t bars[2 * S + 5];   // full[S], empty[S], acc_full[2], acc_empty[2], b_full
   __shared__ uint32_t tmem_slot;
 
   const int t = threadIdx.x, warp = t >> 5;
   const unsigned long long tl_t0 = tl_begin(sk.tl);
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   if (t == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], kT32Producers); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 128); }
-    mbar_init(&b_full, kT32Producers);
+    for (int s = 0; s < S; ++s) { mbar_init(&bars[s], kT32Producers / 32); mbar_init(&bars[S + s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&bars[2 * S + a], 1); mbar_init(&bars[2 * S + 2 + a], 4); }
+    mbar_init(&bars[2 * S + 4], kT32Producers / 32);
     fence_mbar_init();
   }
   if (warp == kT32SMmaWarp) t32_alloc<2 * COLS>(&tmem_slot);
@@ -113,6 +131,9 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
   __syncthreads();
   t32_fence_after();
   const uint32_t tmem = tmem_slot;
+  // shared-space addresses of the barriers, computed once
+  const uint32_t full_bar = smem_u32(bars), empty_bar = full_bar + 8 * S, acc_full = full_bar + 16 * S,
+                 acc_empty = acc_full + 16, b_full = acc_full + 32;
 
   if (warp < 8) {
     // ------------------------------------------------------------------ producers
@@ -135,14 +156,14 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     };
     auto acquire = [&]() -> uint32_t {   // the ring slot of stage q, once the tensor core has released it
       const uint32_t s = q % S;
-      if (q >= (uint32_t)S) mbar_wait(&empty_bar[s], ((q / S) - 1) & 1);
+      if (q >= (uint32_t)S) mbar_wait_a(empty_bar + 8 * s, ((q / S) - 1) & 1);
       if (t == 0) t32s_trace(sk.dbg, 0, q);   // series 0: producer holds slot of stage q
       return smem + RING + s * STAGE;
     };
     auto publish = [&]() {   // stage q issued: hand the oldest unpublished stage (landed by now) to the tensor core
       if constexpr (NO_CP) {   // everything was written with st.shared: publish at once
-        if (!(w.dbg & 8)) fence_proxy_async_smem();
-        mbar_arrive(&full_bar[q % S]);
+        if (!T32S_KNOB(w, 8)) fence_proxy_async_smem();
+        mbar_arrive_warp_a(full_bar + 8 * (q % S));
         pub = ++q;
         return;
       }
@@ -151,14 +172,14 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       if (q - pub > (uint32_t)D) {
         cp_wait<D>();
         fence_proxy_async_smem();
-        mbar_arrive(&full_bar[pub % S]);
+        mbar_arrive_warp_a(full_bar + 8 * (pub % S));
         ++pub;
       }
     };
     auto flush = [&]() {   // publish everything issued
       cp_wait<0>();
       fence_proxy_async_smem();
-      for (; pub < q; ++pub) mbar_arrive(&full_bar[pub % S]);
+      for (; pub < q; ++pub) mbar_arrive_warp_a(full_bar + 8 * (pub % S));
     };
     // (brow must describe `it`.)  Resident mode: make B of this item's (z, tile_n) the resident one.
     auto open_b = [&](const T32Item& it) {
@@ -167,21 +188,22 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         if (key == b_key) return;
         b_key = key;
         flush();
-        if (q > 0) mbar_wait(&empty_bar[(q - 1) % S], ((q - 1) / S) & 1);   // every MMA on the old B has retired
+        if (q > 0) mbar_wait_a(empty_bar + 8 * ((q - 1) % S), ((q - 1) / S) & 1);   // every MMA on the old B has retired
         for (int kb = 0; kb < w.kblocks; ++kb) put_b(it, kb, smem + kb * B_TILE);
         cp_commit();
         cp_wait<0>();
         fence_proxy_async_smem();
-        mbar_arrive(&b_full);
+        mbar_arrive_warp_a(b_full);
       }
     };
     if constexpr (t32_a_reg<P>::value) {
       // uint8 A through registers: the load cursor runs RD k-blocks ahead of the store cursor
       constexpr bool ROW16 = t32_a_row16<P>::value;
       constexpr int NW = ROW16 ? 4 : MA::NROW * MA::NCOL;
-      constexpr int RD = ROW16 ? 8 : 6;
+      constexpr int RD = ROW16 ? kT32SByteDepth : 6;
       const int row = t >> 1, half = t & 1;   // ROW16: this thread's half row of the tile
-      uint32_t wreg[RD][NW];
+      const uint32_t stg = smem + RING + S * STAGE + t * 16;   // ROW16: this thread's 16 bytes of byte-ring slot 0
+      uint32_t wreg[ROW16 ? 1 : RD][NW];
       float4 breg[B_REG ? RD : 1];
       static_assert(!B_REG || MB::NROW * MB::NCOL == 1, "B_REG: one B chunk per producer thread and k-block");
       int l_item = blockIdx.x, l_i = 0;
@@ -199,18 +221,21 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
           for (int u = 0; u < MA::NROW; ++u) l_arow[u] = p.a_row(l_it.z, l_it.m0 + MA::row_index(t, u));
         }
       };
-      auto l_next = [&](uint32_t (&dst)[NW], float4& bdst) {
+      auto l_next = [&](uint32_t (&dst)[NW], float4& bdst, int slot) {
+        if constexpr (ROW16) {   // one cp.async group per k-block, also past the end (the wait counts stay static)
+          const bool on = l_item < w.items && !T32S_KNOB(w, 4);
+          const bool ok = on && l_rp != nullptr;
+          cp16(stg + slot * 4096, ok ? l_rp + p.a_kb_off(l_it.kb_beg + l_i) + half * 16 : reinterpret_cast<const uint8_t*>(p.x[0]), ok);
+          cp_commit();
+          if (l_item < w.items && ++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); }
+          return;
+        }
 #pragma unroll
         for (int j = 0; j < NW; ++j) dst[j] = 0u;
         if (l_item >= w.items) return;
-        if (w.dbg & 4) { if (++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); } return; }
+        if (T32S_KNOB(w, 4)) { if (++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); } return; }
         if constexpr (B_REG) bdst = p.b_get(l_brow, p.b_col(l_it.z, (l_it.kb_beg + l_i) * kT32BK + MB::col_index(t, 0)));
-        if constexpr (ROW16) {
-          if (l_rp != nullptr) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(l_rp + p.a_kb_off(l_it.kb_beg + l_i) + half * 16));
-            dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
-          }
-        } else {
+        {
 #pragma unroll
           for (int uc = 0; uc < MA::NCOL; ++uc) {
             typename P::ACol col = p.a_col(l_it.z, (l_it.kb_beg + l_i) * kT32BK + MA::col_index(t, uc));
@@ -222,7 +247,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       };
       l_open();
 #pragma unroll
-      for (int u = 0; u < RD; ++u) l_next(wreg[u], breg[B_REG ? u : 0]);
+      for (int u = 0; u < RD; ++u) l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
       int s_item = blockIdx.x, s_i = 0;
       T32Item s_it = {};
       auto s_open = [&]() {
@@ -238,11 +263,14 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         for (int u = 0; u < RD; ++u) {
           if (s_item < w.items) {
             const uint32_t base = acquire();
-            if (w.dbg & 2) {
+            if (T32S_KNOB(w, 2)) {
             } else if constexpr (ROW16) {
+              cp_wait<RD - 1>();   // this thread's bytes of the oldest k-block have landed
+              uint32_t wd[4];
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[0]), "=r"(wd[1]), "=r"(wd[2]), "=r"(wd[3]) : "r"(stg + u * 4096) : "memory");
               const uint32_t row_base = base + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-              for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wreg[u][j]);
+              for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
             } else {
 #pragma unroll
               for (int uc = 0; uc < MA::NCOL; ++uc)
@@ -253,7 +281,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
               const float4 bv = breg[u];
               st16(base + A_TILE + MB::offset(t, 0, 0), bv.x, bv.y, bv.z, bv.w);
             }
-            l_next(wreg[u], breg[B_REG ? u : 0]);
+            l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
             stage_b(s_it, s_i, base);
             publish();
             if (++s_i == s_it.nkb) { s_i = 0; s_item += gridDim.x; s_open(); }
@@ -309,19 +337,19 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       if constexpr (RKB > 0) {   // (tiles_n == 1, splits == 1: the key is z = item / tiles_m)
         if (item >= key_end) {
           key_end = (item / w.tiles_m + 1) * w.tiles_m;
-          mbar_wait(&b_full, nb & 1);
+          mbar_wait_a(b_full, nb & 1);
           ++nb;
         }
       }
       const uint32_t a = n & 1;
-      if (n >= 2) mbar_wait(&acc_empty[a], ((n >> 1) - 1) & 1);   // the epilogue has drained this accumulator
+      if (n >= 2) mbar_wait_a(acc_empty + 8 * a, ((n >> 1) - 1) & 1);   // the epilogue has drained this accumulator
       t32_fence_after();
       t32s_trace(sk.dbg, 1, n);   // series 1: accumulator of tile n available
       const uint32_t d_tmem = tmem + a * COLS;
       uint32_t b_lo_res = (uint32_t)b_d0 + (uint32_t)kb_beg * (B_TILE >> 4);
 #pragma unroll 1
       for (int i = 0; i < nkb; ++i) {
-        mbar_wait(&full_bar[s], ph);
+        mbar_wait_a(full_bar + 8 * s, ph);
         t32_fence_after();
         t32s_trace(sk.dbg, 2, n * nkb + i);   // series 2: stage seen full by the MMA thread (uniform nkb only)
         const uint32_t a_lo = (uint32_t)a_d0 + s * (STAGE >> 4);
@@ -330,11 +358,11 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         for (int ks = 0; ks < kT32BK / 8; ++ks)
           t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
                   i > 0 || ks > 0);
-        t32_commit(&empty_bar[s]);   // slot free once these MMAs have read it
+        t32_commit_a(empty_bar + 8 * s);   // slot free once these MMAs have read it
         b_lo_res += B_TILE >> 4;
         if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
       }
-      t32_commit(&acc_full[a]);
+      t32_commit_a(acc_full + 8 * a);
       t32s_trace(sk.dbg, 3, n);   // series 3: tile n fully issued
     }
   } else if (warp >= kT32SEpiWarp && warp < kT32SEpiWarp + 4) {
@@ -344,7 +372,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     for (int item = blockIdx.x; item < w.items; item += gridDim.x, ++n) {
       const T32Item it = t32s_item<BN>(w, item);
       const uint32_t a = n & 1;
-      mbar_wait(&acc_full[a], (n >> 1) & 1);
+      mbar_wait_a(acc_full + 8 * a, (n >> 1) & 1);
       t32_fence_after();
       if (t == kT32SEpiWarp * 32) t32s_trace(sk.dbg, 4, n);   // series 4: epilogue sees tile n complete
       const uint32_t lane_addr = tmem + a * COLS + ((uint32_t)(quarter * 32) << 16);
@@ -356,11 +384,11 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         if (m < p.M) {
 #pragma unroll
           for (int i = 0; i < 16; i += 4)
-            if (it.n0 + c + i < p.N && !(w.dbg & 1)) p.store4(it.z, it.split, m, it.n0 + c + i, make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+            if (it.n0 + c + i < p.N && !T32S_KNOB(w, 1)) p.store4(it.z, it.split, m, it.n0 + c + i, make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
         }
       }
       t32_fence_before();
-      mbar_arrive(&acc_empty[a]);
+      mbar_arrive_warp_a(acc_empty + 8 * a);
       if (t == kT32SEpiWarp * 32) t32s_trace(sk.dbg, 5, n);   // series 5: epilogue done with tile n
     }
   }

@@ -1,6 +1,7 @@
 // Standalone harness for the stream kernel: conv1 double-Q forward at batch B (argv[1], default 1024) on
 // random frames, timed with CUDA events, plus the event trace of CTA 0 (see t32s_trace).
 //   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -I dqn_mgsc_zoo_b200/csrc -o /tmp/stream_trace scripts/micro/stream_trace.cu
+#define DQNB_STREAM_KNOBS 1
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
