@@ -93,6 +93,20 @@ struct dqnb_learner {
   size_t fc1_part_cap = 0;
   int fc1_splits = 0, fc1_rows = 0;
   GradRegions regions;
+  // Second batch-buffer set + its own graph (small batches): update_from_replay alternates between
+  // the two, so the gather of update n+1 runs on `gather_st` beside update n instead of after it.
+  uint8_t *alt_s_tm1 = nullptr, *alt_s_t = nullptr;
+  int32_t* alt_act = nullptr;
+  float *alt_rew = nullptr, *alt_disc = nullptr;
+  cudaGraphExec_t graph_alt = nullptr;
+  cudaStream_t gather_st = nullptr;
+  cudaEvent_t set_free[2] = {}, gathered = nullptr;   // set_free[k]: last reader of buffer set k has finished
+  bool set_used[2] = {false, false};
+  int flip = 0;
+  void swap_sets() {
+    std::swap(s_tm1, alt_s_tm1); std::swap(s_t, alt_s_t); std::swap(act, alt_act);
+    std::swap(rew, alt_rew); std::swap(disc, alt_disc);
+  }
   // graph
   cudaGraphExec_t graph = nullptr;
   cudaStream_t side[3] = {};
@@ -598,7 +612,7 @@ int enqueue_adjoint(dqnb_learner* h, const float* v, float* out, cudaStream_t st
   return DQNB_OK;
 }
 
-int build_graph(dqnb_learner* h) {
+int build_graph(dqnb_learner* h, cudaGraphExec_t* out) {
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
   DQNB_CUDA(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
@@ -608,7 +622,7 @@ int build_graph(dqnb_learner* h) {
   if (rc != DQNB_OK) { if (graph) cudaGraphDestroy(graph); cudaStreamDestroy(cap); return rc; }
   DQNB_CUDA(e);
   // Per-node priorities: the kernels of the dependent chain outrank the side-branch kernels.
-  DQNB_CUDA(cudaGraphInstantiateWithFlags(&h->graph, graph, cudaGraphInstantiateFlagUseNodePriority));
+  DQNB_CUDA(cudaGraphInstantiateWithFlags(out, graph, cudaGraphInstantiateFlagUseNodePriority));
   DQNB_CUDA(cudaGraphDestroy(graph));
   DQNB_CUDA(cudaStreamDestroy(cap));
   return DQNB_OK;
@@ -693,8 +707,19 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   if (h->part_cap) DQNB_TRY(dmalloc(&h->gpart, h->part_cap));
   if (h->fc1_part_cap) DQNB_TRY(dmalloc(&h->fc1_part, h->fc1_part_cap));
   DQNB_CUDA(cudaMalloc(&h->d_tl, sizeof(unsigned long long) * kTlSlot * 64));
-  DQNB_TRY(build_graph(h));
+  DQNB_TRY(build_graph(h, &h->graph));
   h->tl_graph_n = h->tl_n;
+  if (!h->stream && getenv("DQNB_NO_GATHER_OVERLAP") == nullptr) {
+    DQNB_TRY(dmalloc(&h->alt_s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->alt_s_t, B * Conv1::IN_PER_IMG));
+    DQNB_TRY(dmalloc(&h->alt_act, B)); DQNB_TRY(dmalloc(&h->alt_rew, B)); DQNB_TRY(dmalloc(&h->alt_disc, B));
+    h->swap_sets();
+    int rc = build_graph(h, &h->graph_alt);
+    h->swap_sets();
+    DQNB_TRY(rc);
+    DQNB_CUDA(cudaStreamCreateWithFlags(&h->gather_st, cudaStreamNonBlocking));
+    for (auto& e : h->set_free) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    DQNB_CUDA(cudaEventCreateWithFlags(&h->gathered, cudaEventDisableTiming));
+  }
   *out = h;
   return DQNB_OK;
 }
@@ -704,6 +729,11 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   DeviceGuard guard(h->device);
   cudaDeviceSynchronize();
   if (h->graph) cudaGraphExecDestroy(h->graph);
+  if (h->graph_alt) cudaGraphExecDestroy(h->graph_alt);
+  if (h->gather_st) cudaStreamDestroy(h->gather_st);
+  for (auto& e : h->set_free) if (e) cudaEventDestroy(e);
+  if (h->gathered) cudaEventDestroy(h->gathered);
+  cudaFree(h->alt_s_tm1); cudaFree(h->alt_s_t); cudaFree(h->alt_act); cudaFree(h->alt_rew); cudaFree(h->alt_disc);
   float* fl[] = {h->online, h->target, h->mu, h->nu, h->grad, h->rew, h->disc, h->dh1, h->dy3, h->dy2, h->dy1,
                  h->td, h->row_loss, h->dq_taken, h->loss, h->ws, h->gpart, h->fc1_part, h->online_r, h->target_r,
                  h->row_weight};
@@ -859,6 +889,7 @@ extern "C" int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, co
     DQNB_CUDA(cudaMemcpyAsync(h->disc, disc_dev, 4 * B, cudaMemcpyDeviceToDevice, st));
   }
   DQNB_CUDA(cudaGraphLaunch(h->graph, st));
+  if (h->graph_alt) { DQNB_CUDA(cudaEventRecord(h->set_free[0], st)); h->set_used[0] = true; }
   h->updates++;
   h->seq_host++;
   return DQNB_OK;
@@ -893,8 +924,26 @@ extern "C" int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* rep
   replay_frame_shape(replay, &H, &W, &S);
   DQNB_REQUIRE(H == Conv1::HIN && W == Conv1::WIN && S == Conv1::CIN, "replay frames %dx%dx%d are not 84x84x4", H, W, S);
   DeviceGuard guard(h->device);
-  DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->s_tm1, h->s_t, h->act, h->rew, h->disc, as_stream(stream)));
-  return dqnb_learner_update(h, h->s_tm1, h->act, h->rew, h->disc, h->s_t, stream);
+  if (h->graph_alt == nullptr) {
+    DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->s_tm1, h->s_t, h->act, h->rew, h->disc, as_stream(stream)));
+    return dqnb_learner_update(h, h->s_tm1, h->act, h->rew, h->disc, h->s_t, stream);
+  }
+  // Gather into the buffer set the running update is NOT reading, on the gather stream: it waits only
+  // for the last reader of that set (two updates ago) and for the replay's own commits.
+  cudaStream_t st = as_stream(stream), gs = h->gather_st;
+  const int k = h->flip;
+  if (h->set_used[k]) DQNB_CUDA(cudaStreamWaitEvent(gs, h->set_free[k], 0));
+  if (k) DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->alt_s_tm1, h->alt_s_t, h->alt_act, h->alt_rew, h->alt_disc, gs));
+  else DQNB_TRY(replay_gather_into(replay, slots_host, h->B, h->s_tm1, h->s_t, h->act, h->rew, h->disc, gs));
+  DQNB_CUDA(cudaEventRecord(h->gathered, gs));
+  DQNB_CUDA(cudaStreamWaitEvent(st, h->gathered, 0));
+  DQNB_CUDA(cudaGraphLaunch(k ? h->graph_alt : h->graph, st));
+  DQNB_CUDA(cudaEventRecord(h->set_free[k], st));
+  h->set_used[k] = true;
+  h->flip ^= 1;
+  h->updates++;
+  h->seq_host++;
+  return DQNB_OK;
 }
 
 extern "C" int dqnb_learner_loss_post(dqnb_learner* h, uintptr_t) {
@@ -968,6 +1017,7 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
   g.td = h->td; g.dh1 = h->dh1;
   head_td_kernel<<<n, kHeadThreads, 0, st>>>(g);
   DQNB_CUDA(cudaGetLastError());
+  if (h->graph_alt) { DQNB_CUDA(cudaEventRecord(h->set_free[0], st)); h->set_used[0] = true; }
   DQNB_CUDA(cudaMemcpyAsync(q_host, h->q[0], sizeof(float) * n * h->A, cudaMemcpyDeviceToHost, st));
   DQNB_CUDA(cudaStreamSynchronize(st));
   return DQNB_OK;

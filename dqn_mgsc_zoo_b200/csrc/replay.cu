@@ -59,6 +59,11 @@ struct dqnb_replay {
   // caller's stream (the learner's update graph): ordered after that gather, before the next one
   cudaStream_t side = nullptr;
   cudaEvent_t gather_done = nullptr;
+  // callers may gather on different streams (the learner prefetches on its own gather stream): a
+  // gather on another stream than its predecessor / than the last commit's waits for them first
+  cudaStream_t gather_stream = nullptr, commit_stream = nullptr;
+  cudaEvent_t committed = nullptr;
+  bool have_commit = false;
   bool have_gather = false;
   uint8_t* d_out = nullptr;
   int64_t out_cap = 0;
@@ -112,7 +117,7 @@ int flush(dqnb_replay* h, cudaStream_t st) {
   // already enqueued on `st`; everything enqueued after the last of them (the update graph) does
   // not touch the replay, so a small commit may run beside it.
   cudaStream_t cs = (zero_copy && h->side != nullptr) ? h->side : st;
-  if (cs != st && h->have_gather) DQNB_CUDA(cudaStreamWaitEvent(cs, h->gather_done, 0));
+  if (h->have_gather && (cs != st || st != h->gather_stream)) DQNB_CUDA(cudaStreamWaitEvent(cs, h->gather_done, 0));
   commit_kernel<<<grid, kCommitThreads, 0, cs>>>(
       h->d_planes, h->plane_stride, h->plane_bytes, src + h->hdr_bytes,
       reinterpret_cast<const int32_t*>(src + h->hdr_records), s.n_planes,
@@ -123,6 +128,9 @@ int flush(dqnb_replay* h, cudaStream_t st) {
     DQNB_CUDA(cudaEventRecord(s.copied, cs));   // staging is free once the kernel has read it
     if (cs != st) DQNB_CUDA(cudaStreamWaitEvent(st, s.copied, 0));   // later work on st sees the commit
   }
+  DQNB_CUDA(cudaEventRecord(h->committed, cs));   // gathers issued on any other stream wait for this
+  h->commit_stream = st;
+  h->have_commit = true;
   s.in_flight = true;
   for (int i = 0; i < s.n_records; ++i) h->slot_staged[h->rec_of(s)[i].slot] = 0;
   // planes released during this batch may be handed out again only now (stream order
@@ -247,6 +255,7 @@ extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int s
   for (int i = 0; i < kIdxRing; ++i) DQNB_CUDA(cudaEventCreateWithFlags(&h->idx_ev[i], cudaEventDisableTiming));
   DQNB_CUDA(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   DQNB_CUDA(cudaEventCreateWithFlags(&h->gather_done, cudaEventDisableTiming));
+  DQNB_CUDA(cudaEventCreateWithFlags(&h->committed, cudaEventDisableTiming));
   if (initial_planes <= 0) initial_planes = capacity + capacity / 8 + 64;
   DQNB_TRY(grow_pool(h, initial_planes));
   h->n_growths = 0;
@@ -271,6 +280,7 @@ extern "C" int dqnb_replay_destroy(dqnb_replay* h) {
   for (int i = 0; i < kIdxRing; ++i) if (h->idx_ev[i]) cudaEventDestroy(h->idx_ev[i]);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->gather_done) cudaEventDestroy(h->gather_done);
+  if (h->committed) cudaEventDestroy(h->committed);
   delete h;
   return DQNB_OK;
 }
@@ -354,6 +364,9 @@ ReplayDeviceView view_of(const dqnb_replay* h) {
 int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* s_tm1, uint8_t* s_t,
                   int32_t* a, float* r, float* d, cudaStream_t st, const InlineSlots* inl = nullptr) {
   if (n == 0) return DQNB_OK;
+  if (h->have_gather && st != h->gather_stream) DQNB_CUDA(cudaStreamWaitEvent(st, h->gather_done, 0));
+  if (h->have_commit && st != h->commit_stream) DQNB_CUDA(cudaStreamWaitEvent(st, h->committed, 0));
+  h->gather_stream = st;
   ReplayDeviceView v = view_of(h);
   if (h->S == 4 && h->plane_bytes % 16 == 0) {
     // enough CTAs to cover the 148 SMs twice for small batches; whole planes for big ones
