@@ -30,7 +30,12 @@ constexpr int kT32SMmaWarp = 12;
 // (z, tile_n) a CTA meets, i.e. a few times per launch - and the ring carries A only: a third less
 // staging work and shared-memory fill per k-block for the convolutions.
 template <class P, class = void> struct t32_b_resident : std::integral_constant<int, 0> {};
-template <class P> struct t32_b_resident<P, std::enable_if_t<(P::B_RESIDENT_KB > 0)>> : std::integral_constant<int, P::B_RESIDENT_KB> {};
+// Filters above kT32SResidentMax would leave the ring two or three k-blocks of A (conv2 / conv3 forward,
+// conv3 dgrad: 128-144 KB): those stream B with A instead, which buys two k-blocks per stage and a deeper ring.
+constexpr int kT32SResidentMax = 96 * 1024;
+template <class P>
+struct t32_b_resident<P, std::enable_if_t<(P::B_RESIDENT_KB > 0 && P::B_RESIDENT_KB * t32_tile_bytes(P::BN, P::B_MN_MAJOR) <= kT32SResidentMax)>>
+    : std::integral_constant<int, P::B_RESIDENT_KB> {};
 
 //   static constexpr bool B_REG = true;  float4 b_get(const BRow&, const BCol&) const;
 // (only with A_REG, and only when a producer thread owns a single B chunk per k-block): B also travels
@@ -40,12 +45,14 @@ template <class P> struct t32_b_resident<P, std::enable_if_t<(P::B_RESIDENT_KB >
 template <class P, class = void> struct t32_b_reg : std::false_type {};
 template <class P> struct t32_b_reg<P, std::enable_if_t<P::B_REG>> : std::true_type {};
 
+// k-blocks per ring stage.  A stage costs every producer warp a fixed serial latency (~500 clocks of
+// barrier wait, address arithmetic, MEMBAR and arrive) whatever it carries, and the MMA thread one
+// wait + commit: two k-blocks per stage halve that overhead per unit of K.  Work items are cut at
+// multiples of that many k-blocks (loaders zero-fill k >= K).
+// Only where the ring keeps at least three such stages: problems whose resident B leaves little shared
+// memory (conv2 / conv3 forward) stay at one k-block per stage.
 template <class P>
 __host__ __device__ constexpr int t32s_resident_bytes() { return t32_b_resident<P>::value * t32_tile_bytes(P::BN, P::B_MN_MAJOR); }
-template <class P>
-__host__ __device__ constexpr int t32s_stage_bytes() {
-  return t32_tile_bytes(kT32BM, P::A_MN_MAJOR) + (t32_b_resident<P>::value ? 0 : t32_tile_bytes(P::BN, P::B_MN_MAJOR));
-}
 // A_ROW16 problems (uint8 rows of 32 source bytes per k-block): the raw bytes are prefetched with
 // cp.async into a byte ring of kT32SByteDepth k-blocks x 4 KB behind the operand ring; thread t reads
 // back the 16 bytes it copied itself, widens them and stores the tf32 chunks.  cp.async groups retire
@@ -54,6 +61,16 @@ __host__ __device__ constexpr int t32s_stage_bytes() {
 constexpr int kT32SByteDepth = 8;
 template <class P>
 __host__ __device__ constexpr int t32s_byte_ring() { return t32_a_row16<P>::value ? kT32SByteDepth * 4096 : 0; }
+template <class P>
+__host__ __device__ constexpr int t32s_kb_bytes() {
+  return t32_tile_bytes(kT32BM, P::A_MN_MAJOR) + (t32_b_resident<P>::value ? 0 : t32_tile_bytes(P::BN, P::B_MN_MAJOR));
+}
+template <class P>
+__host__ __device__ constexpr int t32s_kps() {
+  return (208 * 1024 - t32s_resident_bytes<P>() - t32s_byte_ring<P>()) / (2 * t32s_kb_bytes<P>()) >= 3 ? 2 : 1;
+}
+template <class P>
+__host__ __device__ constexpr int t32s_stage_bytes() { return t32s_kps<P>() * t32s_kb_bytes<P>(); }
 template <class P>
 __host__ __device__ constexpr int t32s_stages() {
   return (208 * 1024 - t32s_resident_bytes<P>() - t32s_byte_ring<P>()) / t32s_stage_bytes<P>() > 8
@@ -72,7 +89,28 @@ __host__ __device__ constexpr int t32s_smem_bytes() {
 #else
 #define T32S_KNOB(w, bit) 0
 #endif
+// Division by a launch constant as multiply-high + shifts (Granlund-Montgomery): decoding a work item
+// sits on the serial path of every tile boundary in all three roles, and a runtime 32-bit division is
+// a ~100-instruction dependent chain.
+struct T32FastDiv {
+  uint32_t d, m, s1, s2;
+  __device__ __forceinline__ uint32_t div(uint32_t n) const {
+    const uint32_t t = __umulhi(m, n);
+    return (t + ((n - t) >> s1)) >> s2;
+  }
+};
+inline T32FastDiv t32s_fastdiv(uint32_t d) {
+  uint32_t l = 0;
+  while ((1ull << l) < d) ++l;
+  T32FastDiv f;
+  f.d = d;
+  f.m = (uint32_t)(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+  f.s1 = l < 1 ? l : 1;
+  f.s2 = l > 0 ? l - 1 : 0;
+  return f;
+}
 struct T32Work {
+  T32FastDiv fd_splits, fd_tn, fd_tm;
   int tiles_m, tiles_n, splits, per, kblocks, items;   // per = k-blocks per split; items = Z*tiles*splits
   int dbg;   // timing experiments only (DQNB_STREAM_DBG): 1 = no epilogue stores, 2 = no A st.shared, 4 = no A loads
 };
@@ -81,12 +119,13 @@ struct T32Item {
 };
 template <int BN>
 __device__ __forceinline__ T32Item t32s_item(const T32Work& w, int item) {
-  const int split = item % w.splits;
-  int r = item / w.splits;
-  const int tn = r % w.tiles_n;
-  r /= w.tiles_n;
-  const int tm = r % w.tiles_m, z = r / w.tiles_m;
-  const int kb_beg = split * w.per, kb_end = min(w.kblocks, kb_beg + w.per);
+  uint32_t r = w.fd_splits.div((uint32_t)item);
+  const int split = item - (int)r * w.splits;
+  uint32_t r2 = w.fd_tn.div(r);
+  const int tn = (int)(r - r2 * (uint32_t)w.tiles_n);
+  const int z = (int)w.fd_tm.div(r2);
+  const int tm = (int)r2 - z * w.tiles_m;
+  const int kb_beg = split * w.per, kb_end = min(w.kblocks, kb_beg + w.per);   // both multiples of the problem's k-blocks per stage
   return {z, split, tm * kT32BM, tn * BN, kb_beg, kb_end - kb_beg};
 }
 
@@ -151,8 +190,9 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         for (int ur = 0; ur < MB::NROW; ++ur) p.b_put(brow[ur], col, tile + MB::offset(t, ur, uc));
       }
     };
-    auto stage_b = [&](const T32Item& it, int i, uint32_t base) {
-      if constexpr (RKB == 0 && !B_REG) put_b(it, it.kb_beg + i, base + A_TILE);
+    constexpr int KPS = t32s_kps<P>();
+    auto stage_b = [&](const T32Item& it, int i, uint32_t base, int sub) {   // k-block i of the item = sub-block `sub` of its stage
+      if constexpr (RKB == 0 && !B_REG) put_b(it, it.kb_beg + i, base + KPS * A_TILE + sub * B_TILE);
     };
     auto acquire = [&]() -> uint32_t {   // the ring slot of stage q, once the tensor core has released it
       const uint32_t s = q % S;
@@ -258,33 +298,40 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         open_b(s_it);
       };
       s_open();
+      static_assert(RD % KPS == 0, "prefetch depth must be a whole number of stages");
       while (s_item < w.items) {
 #pragma unroll
-        for (int u = 0; u < RD; ++u) {
+        for (int u0 = 0; u0 < RD; u0 += KPS) {
           if (s_item < w.items) {
             const uint32_t base = acquire();
-            if (T32S_KNOB(w, 2)) {
-            } else if constexpr (ROW16) {
-              cp_wait<RD - 1>();   // this thread's bytes of the oldest k-block have landed
-              uint32_t wd[4];
-              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[0]), "=r"(wd[1]), "=r"(wd[2]), "=r"(wd[3]) : "r"(stg + u * 4096) : "memory");
-              const uint32_t row_base = base + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-              for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
-            } else {
+            for (int sub = 0; sub < KPS; ++sub) {
+              const int u = u0 + sub;
+              const uint32_t abase = base + sub * A_TILE;
+              if (T32S_KNOB(w, 2)) {
+              } else if constexpr (ROW16) {
+                cp_wait<RD - 1>();   // this thread's bytes of the oldest k-block have landed
+                uint32_t wd[4];
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[0]), "=r"(wd[1]), "=r"(wd[2]), "=r"(wd[3]) : "r"(stg + u * 4096) : "memory");
+                const uint32_t row_base = abase + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-              for (int uc = 0; uc < MA::NCOL; ++uc)
+                for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
+              } else {
 #pragma unroll
-                for (int ur = 0; ur < MA::NROW; ++ur) p.a_store(base + MA::offset(t, ur, uc), wreg[u][uc * MA::NROW + ur]);
+                for (int uc = 0; uc < MA::NCOL; ++uc)
+#pragma unroll
+                  for (int ur = 0; ur < MA::NROW; ++ur) p.a_store(abase + MA::offset(t, ur, uc), wreg[u][uc * MA::NROW + ur]);
+              }
+              if constexpr (B_REG) {
+                const float4 bv = breg[u];
+                st16(base + KPS * A_TILE + sub * B_TILE + MB::offset(t, 0, 0), bv.x, bv.y, bv.z, bv.w);
+              }
+              l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
+              stage_b(s_it, s_i + sub, base, sub);
             }
-            if constexpr (B_REG) {
-              const float4 bv = breg[u];
-              st16(base + A_TILE + MB::offset(t, 0, 0), bv.x, bv.y, bv.z, bv.w);
-            }
-            l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
-            stage_b(s_it, s_i, base);
             publish();
-            if (++s_i == s_it.nkb) { s_i = 0; s_item += gridDim.x; s_open(); }
+            s_i += KPS;
+            if (s_i == s_it.nkb) { s_i = 0; s_item += gridDim.x; s_open(); }
           }
         }
       }
@@ -298,16 +345,19 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         for (int u = 0; u < MB::NROW; ++u) brow[u] = p.b_row(it.z, it.n0 + MB::row_index(t, u));
         open_b(it);
 #pragma unroll 1
-        for (int i = 0; i < it.nkb; ++i) {
+        for (int i = 0; i < it.nkb; i += KPS) {
           const uint32_t base = acquire();
-          const int k0 = (it.kb_beg + i) * kT32BK;
 #pragma unroll
-          for (int uc = 0; uc < MA::NCOL; ++uc) {
-            typename P::ACol col = p.a_col(it.z, k0 + MA::col_index(t, uc));
+          for (int sub = 0; sub < KPS; ++sub) {
+            const int k0 = (it.kb_beg + i + sub) * kT32BK;
 #pragma unroll
-            for (int ur = 0; ur < MA::NROW; ++ur) p.a_put(arow[ur], col, base + MA::offset(t, ur, uc));
+            for (int uc = 0; uc < MA::NCOL; ++uc) {
+              typename P::ACol col = p.a_col(it.z, k0 + MA::col_index(t, uc));
+#pragma unroll
+              for (int ur = 0; ur < MA::NROW; ++ur) p.a_put(arow[ur], col, base + sub * A_TILE + MA::offset(t, ur, uc));
+            }
+            stage_b(it, i + sub, base, sub);
           }
-          stage_b(it, i, base);
           publish();
         }
       }
@@ -321,8 +371,8 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     // < 256 KB, so no carry leaves the field); ring slot and phase are counters, not divisions.
     const uint32_t idesc = t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     const uint64_t a_d0 = P::A_MN_MAJOR ? t32_desc(smem + RING, 4096, 512, 1) : t32_desc(smem + RING, 16, 1024);
-    const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(RKB > 0 ? smem : smem + RING + A_TILE, 4096, 512, 1)
-                                        : t32_desc(RKB > 0 ? smem : smem + RING + A_TILE, 16, 1024);
+    const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(RKB > 0 ? smem : smem + RING + t32s_kps<P>() * A_TILE, 4096, 512, 1)
+                                        : t32_desc(RKB > 0 ? smem : smem + RING + t32s_kps<P>() * A_TILE, 16, 1024);
     const uint32_t a_hi = (uint32_t)(a_d0 >> 32), b_hi = (uint32_t)(b_d0 >> 32);
     constexpr uint32_t A_KS = (P::A_MN_MAJOR ? 1024 : 32) >> 4, B_KS = (P::B_MN_MAJOR ? 1024 : 32) >> 4;
     uint32_t s = 0, ph = 0, n = 0, nb = 0;   // ring slot + its phase / tile / resident-B sequence numbers
@@ -336,7 +386,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       }
       if constexpr (RKB > 0) {   // (tiles_n == 1, splits == 1: the key is z = item / tiles_m)
         if (item >= key_end) {
-          key_end = (item / w.tiles_m + 1) * w.tiles_m;
+          key_end = ((int)w.fd_tm.div((uint32_t)item) + 1) * w.tiles_m;
           mbar_wait_a(b_full, nb & 1);
           ++nb;
         }
@@ -348,18 +398,21 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       const uint32_t d_tmem = tmem + a * COLS;
       uint32_t b_lo_res = (uint32_t)b_d0 + (uint32_t)kb_beg * (B_TILE >> 4);
 #pragma unroll 1
-      for (int i = 0; i < nkb; ++i) {
+      for (int i = 0; i < nkb; i += t32s_kps<P>()) {
         mbar_wait_a(full_bar + 8 * s, ph);
         t32_fence_after();
-        t32s_trace(sk.dbg, 2, n * nkb + i);   // series 2: stage seen full by the MMA thread (uniform nkb only)
-        const uint32_t a_lo = (uint32_t)a_d0 + s * (STAGE >> 4);
-        const uint32_t b_lo = RKB > 0 ? b_lo_res : (uint32_t)b_d0 + s * (STAGE >> 4);
+        t32s_trace(sk.dbg, 2, (n * nkb + i) / t32s_kps<P>());   // series 2: stage seen full by the MMA thread (uniform nkb only)
 #pragma unroll
-        for (int ks = 0; ks < kT32BK / 8; ++ks)
-          t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
-                  i > 0 || ks > 0);
+        for (int sub = 0; sub < t32s_kps<P>(); ++sub) {
+          const uint32_t a_lo = (uint32_t)a_d0 + s * (STAGE >> 4) + sub * (A_TILE >> 4);
+          const uint32_t b_lo = RKB > 0 ? b_lo_res : (uint32_t)b_d0 + s * (STAGE >> 4) + sub * (B_TILE >> 4);
+#pragma unroll
+          for (int ks = 0; ks < kT32BK / 8; ++ks)
+            t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
+                    i > 0 || sub > 0 || ks > 0);
+          b_lo_res += B_TILE >> 4;
+        }
         t32_commit_a(empty_bar + 8 * s);   // slot free once these MMAs have read it
-        b_lo_res += B_TILE >> 4;
         if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
       }
       t32_commit_a(acc_full + 8 * a);
@@ -399,16 +452,19 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
   tl_end(sk.tl, tl_t0);
 }
 
+template <class P>
+inline int t32s_round_kb(int kb) { return (kb + t32s_kps<P>() - 1) / t32s_kps<P>() * t32s_kps<P>(); }
+
 // Split-K only for DEFER_REDUCE problems, and only as far as it takes to give every SM an item.
 template <class P>
 inline int t32s_splits_for(const P& p, int Z) {
   if (!P::DEFER_REDUCE) return 1;
-  const int kblocks = (p.K + kT32BK - 1) / kT32BK;
+  const int kblocks = t32s_round_kb<P>((p.K + kT32BK - 1) / kT32BK);
   const int tiles = ((p.M + kT32BM - 1) / kT32BM) * ((p.N + P::BN - 1) / P::BN) * Z;
   int s = kNumSMs / (tiles > 0 ? tiles : 1);
   const int cap = kblocks / 8 > 1 ? kblocks / 8 : 1;   // at least 8 k-blocks per split
   s = s < 1 ? 1 : (s > cap ? cap : s);
-  const int per = (kblocks + s - 1) / s;
+  const int per = t32s_round_kb<P>((kblocks + s - 1) / s);
   return (kblocks + per - 1) / per;
 }
 
@@ -424,7 +480,8 @@ inline cudaError_t launch_gemm_tf32_stream(const P& p, int Z, int splits, SplitK
     configured = true;
   }
   static_assert(t32s_smem_bytes<P>() <= 227 * 1024, "ring does not fit in shared memory");
-  static_assert(t32s_stages<P>() >= 3, "ring too short");
+  static_assert(t32s_stages<P>() >= 2, "ring too short");
+  static_assert(t32_b_resident<P>::value % t32s_kps<P>() == 0, "resident B must hold whole stages");
   if (splits < 1 || (splits > 1 && !P::DEFER_REDUCE)) return cudaErrorInvalidValue;
   if (t32_b_resident<P>::value > 0 &&
       (splits != 1 || p.N > P::BN || (p.K + kT32BK - 1) / kT32BK > t32_b_resident<P>::value))
@@ -432,10 +489,11 @@ inline cudaError_t launch_gemm_tf32_stream(const P& p, int Z, int splits, SplitK
   T32Work w;
   w.tiles_m = (p.M + kT32BM - 1) / kT32BM;
   w.tiles_n = (p.N + P::BN - 1) / P::BN;
-  w.kblocks = (p.K + kT32BK - 1) / kT32BK;
-  w.per = (w.kblocks + splits - 1) / splits;
+  w.kblocks = t32s_round_kb<P>((p.K + kT32BK - 1) / kT32BK);   // whole stages; loaders zero-fill k >= K
+  w.per = t32s_round_kb<P>((w.kblocks + splits - 1) / splits);
   if (w.kblocks < 1 || (w.kblocks + w.per - 1) / w.per != splits) return cudaErrorInvalidValue;   // no empty splits
   w.splits = splits;
+  w.fd_splits = t32s_fastdiv((uint32_t)splits); w.fd_tn = t32s_fastdiv((uint32_t)w.tiles_n); w.fd_tm = t32s_fastdiv((uint32_t)w.tiles_m);
   const long long items = (long long)w.tiles_m * w.tiles_n * splits * Z;
   if (items < 1 || items > 0x7fffffffLL) return cudaErrorInvalidValue;
   w.items = (int)items;
