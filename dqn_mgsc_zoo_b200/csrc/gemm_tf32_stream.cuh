@@ -58,9 +58,18 @@ __host__ __device__ constexpr int t32s_resident_bytes() { return t32_b_resident<
 // back the 16 bytes it copied itself, widens them and stores the tf32 chunks.  cp.async groups retire
 // in order (wait_group counts), which plain LDG prefetches do not: eight loads in flight share the
 // warp's six scoreboards, so waiting for the oldest also waited for the newest.
+// A_COL16 problems (conv1 weight gradient: MN-major uint8 A whose 4 consecutive mn-chunks of one k are 16
+// contiguous source bytes, plus one fp32 B chunk per thread) send both operands through the same ring:
+//   static constexpr bool A_COL16 = true;
+//   const uint8_t* a_src16(int m0, int k, int c16) const;   16 bytes of mn-chunks 4*c16..4*c16+3 at k, or null
+//   const float* b_src(const BRow&, const BCol&) const;     the thread's B chunk, or null
 constexpr int kT32SByteDepth = 8;
+template <class P, class = void> struct t32_a_col16 : std::false_type {};
+template <class P> struct t32_a_col16<P, std::enable_if_t<P::A_COL16>> : std::true_type {};
 template <class P>
-__host__ __device__ constexpr int t32s_byte_ring() { return t32_a_row16<P>::value ? kT32SByteDepth * 4096 : 0; }
+__host__ __device__ constexpr int t32s_byte_slot() { return t32_a_row16<P>::value ? 4096 : t32_a_col16<P>::value ? 8192 : 0; }
+template <class P>
+__host__ __device__ constexpr int t32s_byte_ring() { return kT32SByteDepth * t32s_byte_slot<P>(); }
 template <class P>
 __host__ __device__ constexpr int t32s_kb_bytes() {
   return t32_tile_bytes(kT32BM, P::A_MN_MAJOR) + (t32_b_resident<P>::value ? 0 : t32_tile_bytes(P::BN, P::B_MN_MAJOR));
@@ -238,13 +247,15 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     };
     if constexpr (t32_a_reg<P>::value) {
       // uint8 A through registers: the load cursor runs RD k-blocks ahead of the store cursor
-      constexpr bool ROW16 = t32_a_row16<P>::value;
+      constexpr bool ROW16 = t32_a_row16<P>::value, COL16 = t32_a_col16<P>::value, BYTES = ROW16 || COL16;
+      constexpr int SLOT = t32s_byte_slot<P>();
+      static_assert(!COL16 || (P::A_MN_MAJOR && B_REG), "A_COL16: MN-major A and a one-chunk-per-thread B");
       constexpr int NW = ROW16 ? 4 : MA::NROW * MA::NCOL;
-      constexpr int RD = ROW16 ? kT32SByteDepth : 6;
+      constexpr int RD = BYTES ? kT32SByteDepth : 6;
       const int row = t >> 1, half = t & 1;   // ROW16: this thread's half row of the tile
       const uint32_t stg = smem + RING + S * STAGE + t * 16;   // ROW16: this thread's 16 bytes of byte-ring slot 0
-      uint32_t wreg[ROW16 ? 1 : RD][NW];
-      float4 breg[B_REG ? RD : 1];
+      uint32_t wreg[BYTES ? 1 : RD][NW];
+      float4 breg[B_REG && !BYTES ? RD : 1];
       static_assert(!B_REG || MB::NROW * MB::NCOL == 1, "B_REG: one B chunk per producer thread and k-block");
       int l_item = blockIdx.x, l_i = 0;
       T32Item l_it = {};
@@ -256,7 +267,8 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         l_it = t32s_item<BN>(w, l_item);
         if constexpr (B_REG) l_brow = p.b_row(l_it.z, l_it.n0 + MB::row_index(t, 0));
         if constexpr (ROW16) l_rp = p.a_row16(l_it.z, l_it.m0 + row);
-        else {
+        else if constexpr (COL16) {
+        } else {
 #pragma unroll
           for (int u = 0; u < MA::NROW; ++u) l_arow[u] = p.a_row(l_it.z, l_it.m0 + MA::row_index(t, u));
         }
@@ -266,6 +278,17 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
           const bool on = l_item < w.items && !T32S_KNOB(w, 4);
           const bool ok = on && l_rp != nullptr;
           cp16(stg + slot * 4096, ok ? l_rp + p.a_kb_off(l_it.kb_beg + l_i) + half * 16 : reinterpret_cast<const uint8_t*>(p.x[0]), ok);
+          cp_commit();
+          if (l_item < w.items && ++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); }
+          return;
+        }
+        if constexpr (COL16) {   // A bytes and the B chunk of one k-block = one cp.async group
+          const bool on = l_item < w.items && !T32S_KNOB(w, 4);
+          const int k0 = (l_it.kb_beg + l_i) * kT32BK;
+          const uint8_t* a = on ? p.a_src16(l_it.m0, k0 + (t >> 3), t & 7) : nullptr;
+          cp16(stg + slot * SLOT, a != nullptr ? a : reinterpret_cast<const uint8_t*>(p.x), a != nullptr);
+          const float* b = on ? p.b_src(l_brow, p.b_col(l_it.z, k0 + MB::col_index(t, 0))) : nullptr;
+          cp16(stg + slot * SLOT + 4096, b != nullptr ? reinterpret_cast<const void*>(b) : reinterpret_cast<const void*>(p.x), b != nullptr);
           cp_commit();
           if (l_item < w.items && ++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); }
           return;
@@ -287,7 +310,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       };
       l_open();
 #pragma unroll
-      for (int u = 0; u < RD; ++u) l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
+      for (int u = 0; u < RD; ++u) l_next(wreg[BYTES ? 0 : u], breg[B_REG && !BYTES ? u : 0], u);
       int s_item = blockIdx.x, s_i = 0;
       T32Item s_it = {};
       auto s_open = [&]() {
@@ -299,35 +322,63 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       };
       s_open();
       static_assert(RD % KPS == 0, "prefetch depth must be a whole number of stages");
+      static_assert(!BYTES || RKB > 0 || B_REG, "byte-ring paths publish without cp.async waits: B must be resident or ride the ring");
       while (s_item < w.items) {
 #pragma unroll
         for (int u0 = 0; u0 < RD; u0 += KPS) {
           if (s_item < w.items) {
             const uint32_t base = acquire();
+            if constexpr (BYTES) {
+              // the whole stage at once: one wait, all read-backs, then the widening stores, then the
+              // next prefetches - a shorter dependent chain per stage than k-block by k-block
+              cp_wait<RD - KPS>();
+              uint32_t wd[KPS][4];
+              float4 bv[COL16 ? KPS : 1];
 #pragma unroll
-            for (int sub = 0; sub < KPS; ++sub) {
-              const int u = u0 + sub;
-              const uint32_t abase = base + sub * A_TILE;
-              if (T32S_KNOB(w, 2)) {
-              } else if constexpr (ROW16) {
-                cp_wait<RD - 1>();   // this thread's bytes of the oldest k-block have landed
-                uint32_t wd[4];
-                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[0]), "=r"(wd[1]), "=r"(wd[2]), "=r"(wd[3]) : "r"(stg + u * 4096) : "memory");
-                const uint32_t row_base = abase + (row >> 3) * 1024 + (row & 7) * 128;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
-              } else {
-#pragma unroll
-                for (int uc = 0; uc < MA::NCOL; ++uc)
-#pragma unroll
-                  for (int ur = 0; ur < MA::NROW; ++ur) p.a_store(abase + MA::offset(t, ur, uc), wreg[u][uc * MA::NROW + ur]);
+              for (int sub = 0; sub < KPS; ++sub) {
+                const uint32_t src = stg + (u0 + sub) * SLOT;
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[sub][0]), "=r"(wd[sub][1]), "=r"(wd[sub][2]), "=r"(wd[sub][3]) : "r"(src) : "memory");
+                if constexpr (COL16) bv[sub] = ld_shared_f4(src + 4096);
               }
-              if constexpr (B_REG) {
-                const float4 bv = breg[u];
-                st16(base + KPS * A_TILE + sub * B_TILE + MB::offset(t, 0, 0), bv.x, bv.y, bv.z, bv.w);
+#pragma unroll
+              for (int sub = 0; sub < KPS; ++sub) {
+                const uint32_t abase = base + sub * A_TILE;
+                if (T32S_KNOB(w, 2)) {
+                } else if constexpr (ROW16) {
+                  const uint32_t row_base = abase + (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[sub][j]);
+                } else {
+                  const int kk = t >> 3, c16 = t & 7;   // SWIZZLE_128B_BASE32B atom: see T32Map::offset
+                  const uint32_t kbase = abase + (kk >> 2) * 512 + (kk & 3) * 128;
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    const int cc = 4 * c16 + j;
+                    p.a_store(kbase + (cc >> 3) * 4096 + ((((cc >> 1) & 3) ^ (kk & 3)) << 5) + ((cc & 1) << 4), wd[sub][j]);
+                  }
+                  st16(base + KPS * A_TILE + sub * B_TILE + MB::offset(t, 0, 0), bv[sub].x, bv[sub].y, bv[sub].z, bv[sub].w);
+                }
               }
-              l_next(wreg[ROW16 ? 0 : u], breg[B_REG ? u : 0], u);
-              stage_b(s_it, s_i + sub, base, sub);
+#pragma unroll
+              for (int sub = 0; sub < KPS; ++sub) l_next(wreg[0], breg[0], u0 + sub);
+            } else {
+#pragma unroll
+              for (int sub = 0; sub < KPS; ++sub) {
+                const int u = u0 + sub;
+                const uint32_t abase = base + sub * A_TILE;
+                if (!T32S_KNOB(w, 2)) {
+#pragma unroll
+                  for (int uc = 0; uc < MA::NCOL; ++uc)
+#pragma unroll
+                    for (int ur = 0; ur < MA::NROW; ++ur) p.a_store(abase + MA::offset(t, ur, uc), wreg[u][uc * MA::NROW + ur]);
+                }
+                if constexpr (B_REG) {
+                  const float4 bvv = breg[u];
+                  st16(base + KPS * A_TILE + sub * B_TILE + MB::offset(t, 0, 0), bvv.x, bvv.y, bvv.z, bvv.w);
+                }
+                l_next(wreg[u], breg[B_REG ? u : 0], u);
+                stage_b(s_it, s_i + sub, base, sub);
+              }
             }
             publish();
             s_i += KPS;

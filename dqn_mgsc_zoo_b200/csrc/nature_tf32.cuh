@@ -172,6 +172,14 @@ struct T32ConvWgrad {
   static constexpr bool A_MN_MAJOR = true, B_MN_MAJOR = true, DEFER_REDUCE = true;
   static constexpr bool A_REG = sizeof(TIn) == 1;
   static constexpr bool B_REG = sizeof(TIn) == 1 && L::COUT == 32;   // conv1 (stream kernel): dy rides the register prefetch too
+  // conv1 (stream kernel): both operands ride the in-order cp.async byte ring (gemm_tf32_stream.cuh)
+  static constexpr bool A_COL16 = sizeof(TIn) == 1 && L::ROWLEN == 32 && L::COUT == 32 && !BIAS_ROW;
+  __device__ const uint8_t* a_src16(int m0, int k, int c16) const {
+    ACol c = a_col(0, k);
+    if (c == nullptr) return nullptr;
+    return reinterpret_cast<const uint8_t*>(c) + (m0 / L::ROWLEN + (c16 >> 1)) * (L::WIN * L::CIN) + (c16 & 1) * 16;
+  }
+  __device__ const float* b_src(int r, const float* c) const { return (c != nullptr && r >= 0) ? c + r : nullptr; }
   static constexpr int ROWS = L::KCOL + (BIAS_ROW ? 1 : 0);
   static constexpr size_t PART = (size_t)(L::KCOL + 1) * L::COUT;   // floats per split in gpart
   int M, N, K;              // M = ROWS, N = COUT, K = B*HOUT*WOUT
