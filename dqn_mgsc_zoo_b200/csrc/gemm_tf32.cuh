@@ -74,6 +74,21 @@ __device__ __forceinline__ void t32_mma(uint32_t tmem_d, uint64_t adesc, uint64_
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)acc)
       : "memory");
 }
+// kind::f16 twin (fp16 operands, fp32 accumulate): K = 16 per instruction, i.e. the same 32 bytes of a
+// K-major SWIZZLE_128B row as kind::tf32's K = 8, so descriptors and their k-step are shared.
+__device__ __forceinline__ uint32_t t32_idesc_f16(int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kT32BM >> 4) << 24);   // D = f32, A = B = F16, K-major
+}
+__device__ __forceinline__ void t32_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool acc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)acc)
+      : "memory");
+}
 __device__ __forceinline__ void t32_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
@@ -189,6 +204,25 @@ template <class P> struct t32_a_reg<P, std::enable_if_t<P::A_REG>> : std::true_t
 // patch = 8 px x 4 ch): thread t owns half a row (16 bytes = one LDG.128) of every k-block, i.e.
 // 4x fewer loads than the word-per-chunk path; the 4 widened chunks go to swizzled smem.
 template <class P, class = void> struct t32_a_row16 : std::false_type {};
+//   static constexpr bool F16 = true;  both operands are fp16, K-major; a k-block is 64 halves (128 bytes per
+//   row, like 32 floats) and p.K counts 32-bit words.  With A_ROW16H the uint8 A rows (two 32-byte patch
+//   rows per k-block) are widened to halves: thread t owns bytes [16 half, 16 half + 16) of both.
+template <class P, class = void> struct t32_f16 : std::false_type {};
+template <class P> struct t32_f16<P, std::enable_if_t<P::F16>> : std::true_type {};
+template <class P, class = void> struct t32_a_row16h : std::false_type {};
+template <class P> struct t32_a_row16h<P, std::enable_if_t<P::A_ROW16H>> : std::true_type {};
+// 8 packed uint8 (two words) -> 8 halves without conversions: PRMT drops a byte into the mantissa of 1024
+// (0x6400 | b is 1024 + b exactly), HSUB2 removes the 1024.
+__device__ __forceinline__ uint32_t t32_u8x2_to_half2(uint32_t w, uint32_t selector) {
+  uint32_t r;
+  asm("{\n.reg .b32 t, c;\nmov.b32 c, 0x64006400;\nprmt.b32 t, %1, 0x64646464, %2;\nsub.f16x2 %0, t, c;\n}\n" : "=r"(r) : "r"(w), "r"(selector));
+  return r;
+}
+__device__ __forceinline__ void t32_widen8h(uint32_t dst, uint32_t w0, uint32_t w1) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(t32_u8x2_to_half2(w0, 0x4140)),
+               "r"(t32_u8x2_to_half2(w0, 0x4342)), "r"(t32_u8x2_to_half2(w1, 0x4140)), "r"(t32_u8x2_to_half2(w1, 0x4342))
+               : "memory");
+}
 template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::true_type {};
 
 // Retire this thread's commit groups oldest-first: when group I has landed, make it visible to
@@ -263,7 +297,39 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         for (int ur = 0; ur < MB::NROW; ++ur) p.b_put(brow[ur], col, tile + MB::offset(t, ur, uc));
       }
     };
-    if constexpr (t32_a_row16<P>::value) {
+    if constexpr (t32_a_row16h<P>::value) {
+      static_assert(!P::A_MN_MAJOR && t32_f16<P>::value, "A_ROW16H is the K-major fp16 path");
+      const int row = t >> 1, half = t & 1;
+      const uint8_t* rp = p.a_row16(z, m0 + row);
+      uint4 w[KB][2];
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          w[i][s] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < nkb && rp != nullptr)
+            w[i][s] = __ldg(reinterpret_cast<const uint4*>(rp + p.a_kb_off(2 * (kb_beg + i) + s) + half * 16));
+        }
+      }
+#pragma unroll 1
+      for (int i = 0; i < nkb; ++i) {
+        stage_b(i);
+        cp_commit();
+      }
+      const uint32_t row_off = (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+        if (i < nkb) {
+          const uint32_t base = smem + i * A_TILE + row_off;
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            const uint32_t c = s * 4 + half * 2;   // 16-byte chunk (8 halves) inside the 128-byte row
+            t32_widen8h(base + ((c ^ (uint32_t)(row & 7)) << 4), w[i][s].x, w[i][s].y);
+            t32_widen8h(base + (((c + 1) ^ (uint32_t)(row & 7)) << 4), w[i][s].z, w[i][s].w);
+          }
+        }
+      }
+    } else if constexpr (t32_a_row16<P>::value) {
       static_assert(!P::A_MN_MAJOR, "A_ROW16 is a K-major path");
       const int row = t >> 1, half = t & 1;
       const uint8_t* rp = p.a_row16(z, m0 + row);
@@ -336,7 +402,7 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
     if (dbg && t == 0) sk.dbg[3] = clock64();     // this thread's copies landed
   } else if (t == kT32Producers) {
     // ---- MMA issuer
-    const uint32_t idesc = t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
+    const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     for (int i = 0; i < nkb; ++i) {
       mbar_wait(&full_bar[i], 0);
       t32_fence_after();
@@ -345,7 +411,8 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
       for (int ks = 0; ks < kT32BK / 8; ++ks) {
         uint64_t ad = P::A_MN_MAJOR ? t32_desc(a_addr + ks * 1024, 4096, 512, 1) : t32_desc(a_addr + ks * 32, 16, 1024);
         uint64_t bd = P::B_MN_MAJOR ? t32_desc(b_addr + ks * 1024, 4096, 512, 1) : t32_desc(b_addr + ks * 32, 16, 1024);
-        t32_mma(tmem, ad, bd, idesc, i > 0 || ks > 0);
+        if constexpr (t32_f16<P>::value) t32_mma_f16(tmem, ad, bd, idesc, i > 0 || ks > 0);
+        else t32_mma(tmem, ad, bd, idesc, i > 0 || ks > 0);
       }
     }
     t32_commit(&done_bar);

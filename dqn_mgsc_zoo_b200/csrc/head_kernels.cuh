@@ -1,5 +1,6 @@
 // K4 (TD / loss, warp-shuffle reductions), fc2 forward+backward, K5 fused centered RMSProp.
 #pragma once
+#include <cuda_fp16.h>
 #include "nature_problems.cuh"
 
 namespace dqnb {
@@ -356,8 +357,21 @@ __device__ __forceinline__ void rmsprop4(float4& pv, float4& mv, float4& nv, con
 // butterfly adds the 8 lane sums (every lane performs the same commutative additions, so the
 // result is reproducible).  Elements [skip_lo, skip_hi) are updated elsewhere (fc1's fused
 // weight-gradient epilogue) and are not visited.  The rest: one thread per float4, g read as is.
+// fp16, transposed copy of the conv1 filters (arena offset 0, [K][N] -> h16[n][k]); see H16ConvFwdDoubleQ
+struct H16Shadow {
+  __half* dst;      // null = off
+  int K, N;
+  __device__ __forceinline__ void put4(int64_t i, const float4& v) const {
+    if (dst == nullptr || i >= (int64_t)K * N) return;
+    const int k = (int)i / N, n = (int)i - k * N;
+    dst[(size_t)n * K + k] = __float2half_rn(v.x);
+    dst[(size_t)(n + 1) * K + k] = __float2half_rn(v.y);
+    dst[(size_t)(n + 2) * K + k] = __float2half_rn(v.z);
+    dst[(size_t)(n + 3) * K + k] = __float2half_rn(v.w);
+  }
+};
 template <bool APPLY>
-__global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, float* __restrict__ mu,
+__global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
                                       float* __restrict__ nu, float* __restrict__ g, int64_t n, GradRegions regs, int64_t split_end,
                                       int64_t skip_lo, int64_t skip_hi, float lr, float decay, float eps,
                                       unsigned long long* tl) {
@@ -398,6 +412,7 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
         reinterpret_cast<float4*>(nu)[i4] = nv;
         reinterpret_cast<float4*>(p)[i4] = pv;
         if (p_r != nullptr) reinterpret_cast<float4*>(p_r)[i4] = tf32_rn4(pv);
+        h16.put4(i, pv);
       }
     }
   } else if (APPLY) {
@@ -413,6 +428,7 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
       reinterpret_cast<float4*>(nu)[i4] = nv;
       reinterpret_cast<float4*>(p)[i4] = pv;
       if (p_r != nullptr) reinterpret_cast<float4*>(p_r)[i4] = tf32_rn4(pv);
+      h16.put4(i, pv);
     } else if (i4 == n4) {   // scalar tail
       const float om = 1.0f - decay;
       for (int64_t k = n4 << 2; k < n; ++k) {

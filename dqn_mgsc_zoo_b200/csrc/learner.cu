@@ -55,6 +55,8 @@ struct dqnb_learner {
   // parameter / optimiser arenas (flat fp32, oracle leaf order)
   float *online = nullptr, *target = nullptr, *mu = nullptr, *nu = nullptr, *grad = nullptr;
   float *online_r = nullptr, *target_r = nullptr;   // TF32 mode: weights rounded to tf32 (GEMM operands)
+  __half* conv1_h16 = nullptr;   // TF32 mode, small batches: fp16 K-major conv1 filters [online 32 | target 32][256]
+  H16Shadow h16_online() const { return H16Shadow{conv1_h16, Conv1::KCOL, Conv1::COUT}; }
   // batch
   uint8_t *s_tm1 = nullptr, *s_t = nullptr;
   int32_t* act = nullptr;
@@ -371,14 +373,25 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
   const float* in2[kMaxNets]; const float* in3[kMaxNets]; const float* in4[kMaxNets];
   for (int z = 0; z < nets; ++z) { in2[z] = h->a1[z]; in3[z] = h->a2[z]; in4[z] = h->a3[z]; }
   if (nets == 3 && x[1] == x[2] && wts[0] == wts[2]) {   // double-Q update: one merged conv1 GEMM
-    T32ConvFwdDoubleQ<Conv1, uint8_t> p;
-    p.Mh = rows * Conv1::HOUT * Conv1::WOUT;
-    p.M = 2 * p.Mh; p.N = 2 * Conv1::COUT; p.K = Conv1::KCOL;
-    p.x[0] = x[0]; p.x[1] = x[1];
-    p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
-    p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
-    for (int z = 0; z < kMaxNets; ++z) p.y[z] = h->a1[z];
-    DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
+    auto fill = [&](auto& p) {
+      p.Mh = rows * Conv1::HOUT * Conv1::WOUT;
+      p.M = 2 * p.Mh; p.N = 2 * Conv1::COUT; p.K = Conv1::KCOL;
+      p.x[0] = x[0]; p.x[1] = x[1];
+      p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
+      p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
+      for (int z = 0; z < kMaxNets; ++z) p.y[z] = h->a1[z];
+    };
+    if (h->conv1_h16 != nullptr && wts[0] == h->online_r && wts[1] == h->target_r) {   // fp16 operands: one wave at batch 32
+      H16ConvFwdDoubleQ<Conv1, uint8_t> p;
+      fill(p);
+      p.K = Conv1::KCOL / 2;   // 32-bit words
+      p.w16 = h->conv1_h16;
+      DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
+    } else {
+      T32ConvFwdDoubleQ<Conv1, uint8_t> p;
+      fill(p);
+      DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
+    }
   } else {
     DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
   }
@@ -558,11 +571,11 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     const int64_t skip_lo = fused ? h->L.fw1 : 0, skip_hi = fused ? h->L.fw2 : 0;
     if (h->cfg.defer_apply)   // sum the split-K partials into DQNB_GRAD, nothing else
       rmsprop_reduce_kernel<false><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
-          h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+          h->online, h->online_r, H16Shadow{nullptr, 0, 0}, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
           h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("grad_reduce"));
     else
       rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
-          h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+          h->online, h->online_r, h->h16_online(), h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
           h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce"));
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, st, "rmsprop_reduce"));
@@ -659,6 +672,8 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
   if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
+  if (h->tf32 && !h->stream && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
+    DQNB_TRY(dmalloc(&h->conv1_h16, (size_t)2 * Conv1::COUT * Conv1::KCOL));
   DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));
   DQNB_TRY(dmalloc(&h->act, B)); DQNB_TRY(dmalloc(&h->rew, B)); DQNB_TRY(dmalloc(&h->disc, B));
@@ -740,6 +755,7 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   for (float* p : fl) cudaFree(p);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
   cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
+  cudaFree(h->conv1_h16);
   for (auto& s : h->side) if (s) cudaStreamDestroy(s);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->pinned_free) cudaEventDestroy(h->pinned_free);
@@ -807,6 +823,9 @@ extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host,
   if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
     float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
     round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
+    if (h->conv1_h16 != nullptr)
+      conv1_h16_kernel<<<(Conv1::KCOL * Conv1::COUT + 255) / 256, 256, 0, as_stream(stream)>>>(
+          p + h->L.w1, h->conv1_h16 + (which == DQNB_ONLINE ? 0 : Conv1::COUT * Conv1::KCOL), Conv1::KCOL, Conv1::COUT);
     DQNB_CUDA(cudaGetLastError());
   }
   DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
@@ -832,6 +851,9 @@ extern "C" int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* d
   if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
     float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
     round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
+    if (h->conv1_h16 != nullptr)
+      conv1_h16_kernel<<<(Conv1::KCOL * Conv1::COUT + 255) / 256, 256, 0, as_stream(stream)>>>(
+          p + h->L.w1, h->conv1_h16 + (which == DQNB_ONLINE ? 0 : Conv1::COUT * Conv1::KCOL), Conv1::KCOL, Conv1::COUT);
     DQNB_CUDA(cudaGetLastError());
   }
   return DQNB_OK;
@@ -844,7 +866,7 @@ extern "C" int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream) {
   if (h->tf32) {
     GradRegions none{};
     rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, 0, 0, 0), 256, 0, st>>>(
-        h->online, h->online_r, h->mu, h->nu, h->grad, h->L.total, none, 0, 0, 0, h->cfg.learning_rate,
+        h->online, h->online_r, h->h16_online(), h->mu, h->nu, h->grad, h->L.total, none, 0, 0, 0, h->cfg.learning_rate,
         h->cfg.decay, h->cfg.eps, nullptr);
   } else {
     int64_t n4 = (h->L.total >> 2) + 1;
@@ -988,6 +1010,9 @@ extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
   if (h->tf32)
     DQNB_CUDA(cudaMemcpyAsync(h->target_r, h->online_r, sizeof(float) * h->L.total, cudaMemcpyDeviceToDevice,
                               as_stream(stream)));
+  if (h->conv1_h16 != nullptr)
+    DQNB_CUDA(cudaMemcpyAsync(h->conv1_h16 + Conv1::COUT * Conv1::KCOL, h->conv1_h16,
+                              sizeof(__half) * Conv1::COUT * Conv1::KCOL, cudaMemcpyDeviceToDevice, as_stream(stream)));
   return DQNB_OK;
 }
 

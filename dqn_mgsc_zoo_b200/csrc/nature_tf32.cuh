@@ -9,6 +9,8 @@
 // Weight gradients leave their split-K partials in gpart[split][...] (arena layout, bias row
 // right behind the weights); rmsprop_reduce_kernel sums them in split order.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "gemm_tf32.cuh"
 #include "head_kernels.cuh"
 #include "nature_problems.cuh"
@@ -159,6 +161,34 @@ struct T32ConvFwdDoubleQ {
                              fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f)));
   }
 };
+
+// The same GEMM with fp16 operands (slab kernel, small batches).  uint8 frames are exact in fp16 and
+// fp16 has tf32's 11-bit significand, so nothing is lost against the tf32 path; the operand slab
+// halves (96 KB: two CTAs per SM, so the 200 tiles of a batch-32 double-Q update run as ONE wave
+// instead of two) and every MMA covers K = 16.  B is the learner's fp16 copy of both nets' conv1
+// filters, transposed to K-major: w16[n][k], n < COUT online, n >= COUT target (conv1_h16_kernel).
+// K counts 32-bit words here (KCOL / 2).
+template <class L, class TIn>
+struct H16ConvFwdDoubleQ : T32ConvFwdDoubleQ<L, TIn> {
+  static constexpr int KB_MAX = 4;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
+  static constexpr bool F16 = true, A_ROW16H = true, A_ROW16 = false, A_REG = false;
+  static constexpr int B_RESIDENT_KB = 0;
+  const __half* w16;        // [2 * COUT][KCOL]
+  using BRow = int;         // n or -1
+  using BCol = int;         // word index k (2 halves each; first of 4) or -1
+  __device__ BRow b_row(int, int n) const { return n < this->N ? n : -1; }
+  __device__ BCol b_col(int, int k) const { return k < this->K ? k : -1; }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const {
+    const bool ok = r >= 0 && c >= 0;
+    cp16(dst, ok ? w16 + (size_t)r * L::KCOL + 2 * c : w16, ok);
+  }
+};
+// w[k][n] fp32 (one net's conv1 filters, HWIO) -> dst[n][k] fp16
+__global__ void conv1_h16_kernel(const float* __restrict__ w, __half* __restrict__ dst, int K, int N) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K * N) dst[(size_t)(i % N) * K + i / N] = __float2half_rn(w[i]);
+}
 
 // ---------------------------------------------------------------- conv weight gradient
 // dW[m'=(kh,kw,c), n] = scale * sum_{k'=(b,i,j)} x[...] * dy[k', n]; row m' == KCOL is all ones
