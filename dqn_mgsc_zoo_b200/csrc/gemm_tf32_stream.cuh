@@ -67,7 +67,9 @@ constexpr int kT32SByteDepth = 8;
 template <class P, class = void> struct t32_a_col16 : std::false_type {};
 template <class P> struct t32_a_col16<P, std::enable_if_t<P::A_COL16>> : std::true_type {};
 template <class P>
-__host__ __device__ constexpr int t32s_byte_slot() { return t32_a_row16<P>::value ? 4096 : t32_a_col16<P>::value ? 8192 : 0; }
+__host__ __device__ constexpr int t32s_byte_slot() {
+  return t32_a_row16<P>::value ? 4096 : (t32_a_col16<P>::value || t32_a_row16h<P>::value) ? 8192 : 0;
+}
 template <class P>
 __host__ __device__ constexpr int t32s_byte_ring() { return kT32SByteDepth * t32s_byte_slot<P>(); }
 template <class P>
@@ -247,7 +249,10 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     };
     if constexpr (t32_a_reg<P>::value) {
       // uint8 A through registers: the load cursor runs RD k-blocks ahead of the store cursor
-      constexpr bool ROW16 = t32_a_row16<P>::value, COL16 = t32_a_col16<P>::value, BYTES = ROW16 || COL16;
+      // ROW16H (fp16 operands): a k-block is 64 halves = two 32-byte patch rows; both 16-byte pieces of this
+      // thread's half ride one ring slot (piece s at +4096 s)
+      constexpr bool ROW16 = t32_a_row16<P>::value, COL16 = t32_a_col16<P>::value, ROW16H = t32_a_row16h<P>::value;
+      constexpr bool BYTES = ROW16 || COL16 || ROW16H;
       constexpr int SLOT = t32s_byte_slot<P>();
       static_assert(!COL16 || (P::A_MN_MAJOR && B_REG), "A_COL16: MN-major A and a one-chunk-per-thread B");
       constexpr int NW = ROW16 ? 4 : MA::NROW * MA::NCOL;
@@ -266,7 +271,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         if (l_item >= w.items) return;
         l_it = t32s_item<BN>(w, l_item);
         if constexpr (B_REG) l_brow = p.b_row(l_it.z, l_it.n0 + MB::row_index(t, 0));
-        if constexpr (ROW16) l_rp = p.a_row16(l_it.z, l_it.m0 + row);
+        if constexpr (ROW16 || ROW16H) l_rp = p.a_row16(l_it.z, l_it.m0 + row);
         else if constexpr (COL16) {
         } else {
 #pragma unroll
@@ -278,6 +283,17 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
           const bool on = l_item < w.items && !T32S_KNOB(w, 4);
           const bool ok = on && l_rp != nullptr;
           cp16(stg + slot * 4096, ok ? l_rp + p.a_kb_off(l_it.kb_beg + l_i) + half * 16 : reinterpret_cast<const uint8_t*>(p.x[0]), ok);
+          cp_commit();
+          if (l_item < w.items && ++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); }
+          return;
+        }
+        if constexpr (ROW16H) {
+          const bool on = l_item < w.items && !T32S_KNOB(w, 4);
+          const bool ok = on && l_rp != nullptr;
+#pragma unroll
+          for (int s = 0; s < 2; ++s)
+            cp16(stg + slot * SLOT + s * 4096,
+                 ok ? l_rp + p.a_kb_off(2 * (l_it.kb_beg + l_i) + s) + half * 16 : reinterpret_cast<const uint8_t*>(p.x[0]), ok);
           cp_commit();
           if (l_item < w.items && ++l_i == l_it.nkb) { l_i = 0; l_item += gridDim.x; l_open(); }
           return;
@@ -332,13 +348,15 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
               // the whole stage at once: one wait, all read-backs, then the widening stores, then the
               // next prefetches - a shorter dependent chain per stage than k-block by k-block
               cp_wait<RD - KPS>();
-              uint32_t wd[KPS][4];
+              uint32_t wd[KPS][4], wh[ROW16H ? KPS : 1][4];
               float4 bv[COL16 ? KPS : 1];
 #pragma unroll
               for (int sub = 0; sub < KPS; ++sub) {
                 const uint32_t src = stg + (u0 + sub) * SLOT;
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wd[sub][0]), "=r"(wd[sub][1]), "=r"(wd[sub][2]), "=r"(wd[sub][3]) : "r"(src) : "memory");
                 if constexpr (COL16) bv[sub] = ld_shared_f4(src + 4096);
+                if constexpr (ROW16H)
+                  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wh[sub][0]), "=r"(wh[sub][1]), "=r"(wh[sub][2]), "=r"(wh[sub][3]) : "r"(src + 4096) : "memory");
               }
 #pragma unroll
               for (int sub = 0; sub < KPS; ++sub) {
@@ -348,6 +366,13 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
                   const uint32_t row_base = abase + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
                   for (int j = 0; j < 4; ++j) p.a_store(row_base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[sub][j]);
+                } else if constexpr (ROW16H) {
+                  const uint32_t row_base = abase + (row >> 3) * 1024 + (row & 7) * 128, sw = (uint32_t)(row & 7);
+                  const uint32_t c0 = half * 2, c1 = 4 + half * 2;   // chunks of patch row s = 0 / 1
+                  t32_widen8h(row_base + ((c0 ^ sw) << 4), wd[sub][0], wd[sub][1]);
+                  t32_widen8h(row_base + (((c0 + 1) ^ sw) << 4), wd[sub][2], wd[sub][3]);
+                  t32_widen8h(row_base + ((c1 ^ sw) << 4), wh[sub][0], wh[sub][1]);
+                  t32_widen8h(row_base + (((c1 + 1) ^ sw) << 4), wh[sub][2], wh[sub][3]);
                 } else {
                   const int kk = t >> 3, c16 = t & 7;   // SWIZZLE_128B_BASE32B atom: see T32Map::offset
                   const uint32_t kbase = abase + (kk >> 2) * 512 + (kk & 3) * 128;
@@ -420,7 +445,7 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
     // is kept to a handful of instructions per k-block: descriptors are a constant high word plus a low
     // word that is advanced by adds (smem address >> 4 lives in bits 0-13, and the CTA's window is
     // < 256 KB, so no carry leaves the field); ring slot and phase are counters, not divisions.
-    const uint32_t idesc = t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
+    const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     const uint64_t a_d0 = P::A_MN_MAJOR ? t32_desc(smem + RING, 4096, 512, 1) : t32_desc(smem + RING, 16, 1024);
     const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(RKB > 0 ? smem : smem + RING + t32s_kps<P>() * A_TILE, 4096, 512, 1)
                                         : t32_desc(RKB > 0 ? smem : smem + RING + t32s_kps<P>() * A_TILE, 16, 1024);
@@ -458,9 +483,14 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
           const uint32_t a_lo = (uint32_t)a_d0 + s * (STAGE >> 4) + sub * (A_TILE >> 4);
           const uint32_t b_lo = RKB > 0 ? b_lo_res : (uint32_t)b_d0 + s * (STAGE >> 4) + sub * (B_TILE >> 4);
 #pragma unroll
-          for (int ks = 0; ks < kT32BK / 8; ++ks)
-            t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
-                    i > 0 || sub > 0 || ks > 0);
+          for (int ks = 0; ks < kT32BK / 8; ++ks) {
+            if constexpr (t32_f16<P>::value)
+              t32_mma_f16(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
+                          i > 0 || sub > 0 || ks > 0);
+            else
+              t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
+                      i > 0 || sub > 0 || ks > 0);
+          }
           b_lo_res += B_TILE >> 4;
         }
         t32_commit_a(empty_bar + 8 * s);   // slot free once these MMAs have read it

@@ -672,7 +672,7 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
   if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
-  if (h->tf32 && !h->stream && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
+  if (h->tf32 && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
     DQNB_TRY(dmalloc(&h->conv1_h16, (size_t)2 * Conv1::COUT * Conv1::KCOL));
   DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));

@@ -172,8 +172,8 @@ template <class L, class TIn>
 struct H16ConvFwdDoubleQ : T32ConvFwdDoubleQ<L, TIn> {
   static constexpr int KB_MAX = 4;
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
-  static constexpr bool F16 = true, A_ROW16H = true, A_ROW16 = false, A_REG = false;
-  static constexpr int B_RESIDENT_KB = 0;
+  static constexpr bool F16 = true, A_ROW16H = true, A_ROW16 = false, A_REG = true;
+  static constexpr int B_RESIDENT_KB = L::KCOL / 64;   // stream kernel: k-blocks of 64 halves
   const __half* w16;        // [2 * COUT][KCOL]
   using BRow = int;         // n or -1
   using BCol = int;         // word index k (2 halves each; first of 4) or -1
