@@ -69,6 +69,7 @@ SIGNATURES = {
     "dqnb_learner_launches_per_update": [c_vp, ctypes.POINTER(c_i64)],
     "dqnb_learner_profile": [c_vp, c_int, ctypes.c_char_p, c_sz, STREAM],
     "dqnb_learner_timeline": [c_vp, ctypes.c_char_p, c_sz, STREAM],
+    "dqnb_learner_relaunch": [c_vp, c_int, STREAM],
     "dqnb_selftest_tc_gemm": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, STREAM],
     "dqnb_selftest_tf32_gemm": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, STREAM],
 }

@@ -1048,6 +1048,18 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
   return DQNB_OK;
 }
 
+extern "C" int dqnb_learner_relaunch(dqnb_learner* h, int times, uintptr_t stream) {
+  DQNB_REQUIRE(h && times >= 0, "bad argument");
+  DeviceGuard guard(h->device);
+  for (int i = 0; i < times; ++i) {
+    DQNB_CUDA(cudaGraphLaunch(h->graph, as_stream(stream)));
+    h->updates++;
+    h->seq_host++;
+  }
+  if (h->graph_alt && times > 0) { DQNB_CUDA(cudaEventRecord(h->set_free[0], as_stream(stream))); h->set_used[0] = true; }
+  return DQNB_OK;
+}
+
 extern "C" int dqnb_learner_launches_per_update(dqnb_learner* h, int64_t* n) {
   DQNB_REQUIRE(h && n, "null argument");
   *n = h->launches_per_update;

@@ -174,6 +174,10 @@ int dqnb_learner_profile(dqnb_learner* h, int iters, char* report, size_t report
 /* Diagnostics: begin/end (us, from %globaltimer) of every kernel of one update as the CUDA graph
  * really runs it; text table into `report`.  Advances the state by 3 updates. */
 int dqnb_learner_timeline(dqnb_learner* h, char* report, size_t report_len, uintptr_t stream);
+/* Diagnostics: `times` more updates on the batch that is already in the learner's buffers (graph replays
+ * only: no copies, no gather) - the period of back-to-back updates minus the timeline's span is the
+ * graph-to-graph gap.  Advances the learner state like `times` updates.  Asynchronous. */
+int dqnb_learner_relaunch(dqnb_learner* h, int times, uintptr_t stream);
 /* Loss read-back that neither drains the stream nor uses a copy engine: every update writes
  * (sequence number, mean loss) into a pinned host ring of 8 entries.  `post` notes the sequence
  * number of the update launched last; `take` polls host memory until the OLDEST posted entry has

@@ -34,3 +34,13 @@ for _ in range(n):
 ev1.record()
 torch.cuda.synchronize()
 print("update_host loop: %.1f us/update" % (ev0.elapsed_time(ev1) * 1e3 / n))
+
+# graph replays only (batch resident, no copies, no gather): period of back-to-back updates
+torch.cuda.synchronize()
+_lib.call("dqnb_learner_relaunch", L._h, 50, L.stream)
+torch.cuda.synchronize()
+ev0.record()
+_lib.call("dqnb_learner_relaunch", L._h, 1000, L.stream)
+ev1.record()
+torch.cuda.synchronize()
+print("graph replay loop: %.2f us/update" % (ev0.elapsed_time(ev1)))
