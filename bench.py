@@ -30,7 +30,7 @@ TARGET_SYNC_UPDATES = 7500         # 1.2e5 frames / 16 (double_q/run_atari.py:86
 PLANE = 84 * 84
 GATHER_BYTES_PER_TRANSITION = 13 * PLANE + 12     # 5 planes read + 8 written + scalars
 UPDATE_BYTES = 49.05e6             # params/opt-state touched once + batch
-NCU_GATHER_TRAFFIC_BYTES = 309.9e6 # dram__bytes_read.sum + dram__bytes_write.sum of gather_stack4 at n=4096 (r01b)
+NCU_GATHER_TRAFFIC_BYTES = 308.5e6 # dram__bytes_read.sum + dram__bytes_write.sum of gather_stack4 at n=4096 (r01c)
 
 
 def parse_args():
@@ -334,7 +334,7 @@ def run_ours(args, rank, world, local_rank):
                 "algorithmic_bytes_per_launch": n * GATHER_BYTES_PER_TRANSITION,
                 "note": "CUDA events around %d back-to-back launches on the launching stream, slot lists already on "
                         "the device; 24 different random slot lists over a %.1f GB plane pool (>> L2). traffic = "
-                        "dram read+write per launch from profiles/r01b_ncu_full_summary.csv (ncu --set full, "
+                        "dram read+write per launch from profiles/r01c_ncu_gather_full.csv (ncu --set full, "
                         "60k-transition pool; write-back of the last lines is still in L2 when the kernel ends)"
                         % (greps, store.stats()["hbm_bytes"] / 1e9)}
     ms_upd = ms / args.steps
