@@ -498,6 +498,9 @@ def run_dp(args, rank, world, local_rank):
 
 def main():
     args = parse_args()
+    # NCCL logs to stdout: a NCCL_DEBUG=VERSION/INFO banner would precede the one JSON line this prints
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "INFO") and "NCCL_DEBUG_FILE" not in os.environ:
+        os.environ["NCCL_DEBUG"] = "WARN"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
