@@ -498,9 +498,9 @@ def run_dp(args, rank, world, local_rank):
 
 def main():
     args = parse_args()
-    # NCCL logs to stdout: a NCCL_DEBUG=VERSION/INFO banner would precede the one JSON line this prints
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "INFO") and "NCCL_DEBUG_FILE" not in os.environ:
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # NCCL logs to stdout (its version banner at any NCCL_DEBUG level above NONE): send that to stderr so
+    # that stdout carries the one JSON line only
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
