@@ -109,6 +109,11 @@ struct dqnb_learner {
     std::swap(s_tm1, alt_s_tm1); std::swap(s_t, alt_s_t); std::swap(act, alt_act);
     std::swap(rew, alt_rew); std::swap(disc, alt_disc);
   }
+  // Acting (q_values of ONE observation with the online net, every environment step): its own small
+  // graph - pinned observation -> s_tm1, the batch-1 forward, q -> pinned - built on first use.
+  cudaGraphExec_t act_graph = nullptr;
+  uint8_t* act_obs = nullptr;    // pinned [84*84*4]
+  float* act_q = nullptr;        // pinned [kMaxActions]
   // graph
   cudaGraphExec_t graph = nullptr;
   cudaStream_t side[3] = {};
@@ -745,6 +750,9 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   cudaDeviceSynchronize();
   if (h->graph) cudaGraphExecDestroy(h->graph);
   if (h->graph_alt) cudaGraphExecDestroy(h->graph_alt);
+  if (h->act_graph) cudaGraphExecDestroy(h->act_graph);
+  if (h->act_obs) cudaFreeHost(h->act_obs);
+  if (h->act_q) cudaFreeHost(h->act_q);
   if (h->gather_st) cudaStreamDestroy(h->gather_st);
   for (auto& e : h->set_free) if (e) cudaEventDestroy(e);
   if (h->gathered) cudaEventDestroy(h->gathered);
@@ -1016,15 +1024,10 @@ extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
   return DQNB_OK;
 }
 
-extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_host, int32_t n,
-                                     float* q_host, uintptr_t stream) {
-  DQNB_REQUIRE(h && s_host && q_host, "null argument");
-  DQNB_REQUIRE(n >= 1 && n <= h->B, "n=%d not in 1..batch_size", n);
-  DQNB_REQUIRE(which_params == 0 || which_params == 1, "which_params must be 0 (online) or 1 (target)");
-  DeviceGuard guard(h->device);
-  cudaStream_t st = as_stream(stream);
-  // acting runs between updates on the same stream, so net-0 buffers can be borrowed
-  DQNB_CUDA(cudaMemcpyAsync(h->s_tm1, s_host, (size_t)n * Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, st));
+namespace {
+// The forward of `n` observations already in h->s_tm1 through one net, q into h->q[0] (net-0 buffers
+// are borrowed: acting runs between updates on the same stream).
+int enqueue_q_forward(dqnb_learner* h, int which_params, int n, cudaStream_t st) {
   const uint8_t* xin[kMaxNets] = {h->s_tm1, h->s_tm1, h->s_tm1};
   const float* prm = which_params ? h->target : h->online;
   const float* params[kMaxNets] = {prm, prm, prm};
@@ -1042,6 +1045,57 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
   g.td = h->td; g.dh1 = h->dh1;
   head_td_kernel<<<n, kHeadThreads, 0, st>>>(g);
   DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+
+int build_act_graph(dqnb_learner* h) {
+  if (h->act_obs == nullptr) DQNB_CUDA(cudaMallocHost(&h->act_obs, Conv1::IN_PER_IMG));
+  if (h->act_q == nullptr) DQNB_CUDA(cudaMallocHost(&h->act_q, sizeof(float) * kMaxActions));
+  cudaStream_t cap;
+  DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+  DQNB_CUDA(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+  h->chain = cap;   // consecutive kernels: chain priority + programmatic dependent launch
+  int rc = DQNB_OK;
+  if (cudaMemcpyAsync(h->s_tm1, h->act_obs, Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, cap) != cudaSuccess) rc = DQNB_ECUDA;
+  if (rc == DQNB_OK) rc = enqueue_q_forward(h, 0, 1, cap);
+  if (rc == DQNB_OK && cudaMemcpyAsync(h->act_q, h->q[0], sizeof(float) * h->A, cudaMemcpyDeviceToHost, cap) != cudaSuccess)
+    rc = DQNB_ECUDA;
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(cap, &graph);
+  h->chain = nullptr;
+  if (rc != DQNB_OK || e != cudaSuccess) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaStreamDestroy(cap);
+    cudaGetLastError();
+    if (rc == DQNB_OK) { set_error("capture of the acting graph failed: %s", cudaGetErrorString(e)); rc = DQNB_ECUDA; }
+    return rc;
+  }
+  DQNB_CUDA(cudaGraphInstantiateWithFlags(&h->act_graph, graph, cudaGraphInstantiateFlagUseNodePriority));
+  DQNB_CUDA(cudaGraphDestroy(graph));
+  DQNB_CUDA(cudaStreamDestroy(cap));
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const uint8_t* s_host, int32_t n,
+                                     float* q_host, uintptr_t stream) {
+  DQNB_REQUIRE(h && s_host && q_host, "null argument");
+  DQNB_REQUIRE(n >= 1 && n <= h->B, "n=%d not in 1..batch_size", n);
+  DQNB_REQUIRE(which_params == 0 || which_params == 1, "which_params must be 0 (online) or 1 (target)");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  if (n == 1 && which_params == 0 && getenv("DQNB_NO_ACT_GRAPH") == nullptr) {
+    if (h->act_graph == nullptr) DQNB_TRY(build_act_graph(h));
+    memcpy(h->act_obs, s_host, Conv1::IN_PER_IMG);
+    DQNB_CUDA(cudaGraphLaunch(h->act_graph, st));
+    if (h->graph_alt) { DQNB_CUDA(cudaEventRecord(h->set_free[0], st)); h->set_used[0] = true; }
+    DQNB_CUDA(cudaStreamSynchronize(st));
+    memcpy(q_host, h->act_q, sizeof(float) * h->A);
+    return DQNB_OK;
+  }
+  // acting runs between updates on the same stream, so net-0 buffers can be borrowed
+  DQNB_CUDA(cudaMemcpyAsync(h->s_tm1, s_host, (size_t)n * Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, st));
+  DQNB_TRY(enqueue_q_forward(h, which_params, n, st));
   if (h->graph_alt) { DQNB_CUDA(cudaEventRecord(h->set_free[0], st)); h->set_used[0] = true; }
   DQNB_CUDA(cudaMemcpyAsync(q_host, h->q[0], sizeof(float) * n * h->A, cudaMemcpyDeviceToHost, st));
   DQNB_CUDA(cudaStreamSynchronize(st));

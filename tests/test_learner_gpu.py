@@ -168,6 +168,10 @@ def test_q_values_match_oracle():
     obs = rng.integers(0, 256, (7, 84, 84, 4), dtype=np.uint8)
     assert rel(L.q_values(obs), net.forward(online, obs)) < 1e-5
     assert rel(L.q_values(obs[0], lrn.TARGET), net.forward(target, obs[:1])) < 1e-5
+    # one observation through the online net = the acting graph (pinned in/out, one launch)
+    for i in (1, 2, 1):
+        assert rel(L.q_values(obs[i]), net.forward(online, obs[i:i + 1])) < 1e-5
+    assert np.array_equal(L.q_values(obs[3]), L.q_values(obs[3:4]))
 
 
 @pytest.mark.parametrize("B,A,shared,double_q", [(32, 6, False, False), (32, 18, True, True), (5, 4, False, True),
@@ -225,3 +229,8 @@ def test_tf32_update_from_replay_deterministic_and_q_values():
     obs = rng.integers(0, 256, (7, 84, 84, 4), dtype=np.uint8)
     params = {k: v.astype(np.float64) for k, v in L.get_params().items()}
     assert rel(L.q_values(obs), net.forward(params, obs)) < TOL["tf32"]
+    for i in (0, 5):     # acting graph (one observation, online net), also after further updates
+        assert rel(L.q_values(obs[i]), net.forward(params, obs[i:i + 1])) < TOL["tf32"]
+    L.update_from_replay(rep.frame_store, rep.sample_slots(B))
+    params = {k: v.astype(np.float64) for k, v in L.get_params().items()}
+    assert rel(L.q_values(obs[2]), net.forward(params, obs[2:3])) < TOL["tf32"]
