@@ -116,11 +116,21 @@ __global__ void pscan_kernel(double* __restrict__ part, int nb, double* __restri
   for (int i = beg; i < end; ++i) { acc += part[i]; part[i] = acc; }
   if (lane == 31) *total = incl;
 }
-// One thread per uniform: binary search over block prefixes, then an in-order scan of the block.
+// One warp per uniform: binary search over the block prefixes, then the hit block (kBlk logits) is
+// scanned by the warp - lane j sums its 32 consecutive entries in index order, a warp scan of the lane
+// totals gives every lane its offset, and each lane looks for the first entry whose cdf / total > x
+// (searchsorted(side='right') counts the entries <= x).  The exact float64 division is only evaluated
+// when the product test is within rounding of the boundary.
+__device__ __forceinline__ bool cdf_above(double acc, double tot, double x) {
+  const double t = x * tot;
+  if (acc > t * (1.0 + 1e-12)) return true;
+  if (acc < t * (1.0 - 1e-12)) return false;
+  return acc / tot > x;
+}
 __global__ void search_kernel(const float* __restrict__ l, int64_t n, const float* __restrict__ stat,
                               const double* __restrict__ prefix, int nb, const double* __restrict__ total,
                               const double* __restrict__ u, int count, int64_t* __restrict__ out) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (k >= count) return;
   const double tot = *total, x = u[k];
   const float lse = stat[1];
@@ -130,14 +140,32 @@ __global__ void search_kernel(const float* __restrict__ l, int64_t n, const floa
     const int mid = (lo + hi) >> 1;
     if (prefix[mid] / tot > x) hi = mid; else lo = mid + 1;
   }
-  double acc = lo > 0 ? prefix[lo - 1] : 0.0;
-  const int64_t beg = (int64_t)lo * kBlk, end = min(beg + kBlk, n);
-  int64_t idx = end;   // searchsorted(side='right'): number of cdf entries <= x
-  for (int64_t i = beg; i < end; ++i) {
-    acc += (double)expf(l[i] - lse);
-    if (acc / tot > x) { idx = i; break; }
+  const double base = lo > 0 ? prefix[lo - 1] : 0.0;
+  constexpr int RUN = kBlk / 32;
+  const int64_t beg = (int64_t)lo * kBlk + lane * RUN, end = min((int64_t)(lo + 1) * kBlk, n);
+  double p[RUN], run = 0.0;
+#pragma unroll
+  for (int i = 0; i < RUN; ++i) {
+    p[i] = beg + i < end ? (double)expf(l[beg + i] - lse) : 0.0;
+    run += p[i];
   }
-  out[k] = idx < n ? idx : n - 1;
+  double incl = run;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  double acc = base + (incl - run);
+  int64_t idx = -1;
+#pragma unroll
+  for (int i = 0; i < RUN; ++i) {
+    acc += p[i];
+    if (idx < 0 && beg + i < end && cdf_above(acc, tot, x)) idx = beg + i;
+  }
+  const unsigned hit = __ballot_sync(0xffffffffu, idx >= 0);
+  if (hit == 0u) idx = end;   // no entry above x in this block: searchsorted returns the block's end
+  else idx = __shfl_sync(0xffffffffu, idx, __ffs(hit) - 1);
+  if (lane == 0) out[k] = idx < n ? idx : n - 1;
 }
 __global__ void set_kernel(float* __restrict__ l, const int64_t* __restrict__ idx, const float* __restrict__ v, int n) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -300,7 +328,7 @@ extern "C" int dqnb_logits_sample(dqnb_logits* h, const double* uniforms, int64_
   DQNB_TRY(lse_passes(h, -1, 0.0, st));
   psum_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->stat, h->dpart);
   pscan_kernel<<<1, 32, 0, st>>>(h->dpart, h->nb, h->dpart + h->nb);
-  search_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(h->l, h->capacity, h->stat, h->dpart, h->nb,
+  search_kernel<<<(unsigned)((n + 1) / 2), 64, 0, st>>>(h->l, h->capacity, h->stat, h->dpart, h->nb,
                                                          h->dpart + h->nb, h->d_u, (int)n, h->d_idx);
   DQNB_CUDA(cudaGetLastError());
   int64_t* pi = reinterpret_cast<int64_t*>(h->pinned + 8 * (size_t)h->io_cap);
