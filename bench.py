@@ -187,7 +187,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": res["value"], "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, res_capacity=None):
@@ -373,7 +373,7 @@ def run_ours(args, rank, world, local_rank):
         "roofline": roofline, "roofline_update": roofline_update, "cpu_baseline": cpu,
         "other_precisions": other, "replay_gather_gbs": achieved, "replay_fill_seconds": t_fill, "replay_stats": store.stats(),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -491,16 +491,30 @@ def run_dp(args, rank, world, local_rank):
                                  "bf16 peak; kind::tf32 nominal peak is half of bf16"},
             "cpu_baseline": None, "replicas_identical": same,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    """The one JSON line, on the process's ORIGINAL stdout."""
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     args = parse_args()
-    # NCCL logs to stdout (its version banner at any NCCL_DEBUG level above NONE): send that to stderr so
-    # that stdout carries the one JSON line only
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # Libraries print to fd 1 behind Python's back (NCCL's version banner came out ahead of the JSON line
+    # whatever NCCL_DEBUG_FILE said): keep the original stdout for the JSON line only and point fd 1 at
+    # stderr for everything else.
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
