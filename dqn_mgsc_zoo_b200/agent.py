@@ -187,7 +187,7 @@ class MGSCDqn(Dqn):
 
     Per step (agent.py:252-278): meta-learn on the newest transition *before* it is added to the
     replay, then add, learn from a logit-weighted sample, sync.  `meta_update` (agent.py:160-220)
-    runs on the device (dqnb_mgsc_meta_update: per-sample gradients, two virtual RMSProp steps,
+    runs on the device (dqnb_mgsc_meta_update: one row-weighted batched backward, two virtual RMSProp steps,
     softmax backward, Adam on the logits); neither params nor RMSProp state advance in it.
     """
 

@@ -608,15 +608,27 @@ int enqueue_adjoint(dqnb_learner* h, const float* v, float* out, cudaStream_t st
   float* z1[kMaxNets] = {h->a1[1], nullptr, nullptr};
   float* z2[kMaxNets] = {h->a2[1], nullptr, nullptr};
   float* z3[kMaxNets] = {h->a3[1], nullptr, nullptr};
+  // the four products are independent: one per stream (each op owns its slice of the split-K scratch)
+  const bool live = !h->sizing;
+  cudaStream_t s1 = live ? h->side[0] : st, s2 = live ? h->side[1] : st, s3 = live ? h->side[2] : st;
+  if (live) {
+    DQNB_CUDA(cudaEventRecord(h->ev[0], st));
+    DQNB_CUDA(cudaStreamWaitEvent(s1, h->ev[0], 0));
+    DQNB_CUDA(cudaStreamWaitEvent(s2, h->ev[0], 0));
+    DQNB_CUDA(cudaStreamWaitEvent(s3, h->ev[0], 0));
+  }
   DQNB_TRY((conv_fwd<Conv1, uint8_t, 64>(h, 1, B, x1, vp, h->L.w1, h->L.b1, z1, st, true)));
-  DQNB_TRY((conv_fwd<Conv2, float, 32>(h, 1, B, x2, vp, h->L.w2, h->L.b2, z2, st, true)));
-  DQNB_TRY((conv_fwd<Conv3, float, 32>(h, 1, B, x3, vp, h->L.w3, h->L.b3, z3, st, true)));
+  DQNB_TRY((conv_fwd<Conv2, float, 32>(h, 1, B, x2, vp, h->L.w2, h->L.b2, z2, s1, true)));
+  DQNB_TRY((conv_fwd<Conv3, float, 32>(h, 1, B, x3, vp, h->L.w3, h->L.b3, z3, s2, true)));
   DenseFwd p;
   p.linear = 1;
   p.M = B; p.N = kFc1Out; p.K = kFc1In;
   p.x[0] = h->a3[0]; p.w[0] = v + h->L.fw1; p.bias[0] = v + h->L.fb1; p.y[0] = h->h1[1];
-  DQNB_TRY(run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st));
+  DQNB_TRY(run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), s3));
   if (h->sizing) return DQNB_OK;
+  DQNB_TRY(fork(h->ev[3], s1, st));
+  DQNB_TRY(fork(h->ev[4], s2, st));
+  DQNB_TRY(fork(h->ev[5], s3, st));
   AdjointArgs g;
   g.num_actions = h->A; g.shared_bias = h->cfg.shared_bias;
   g.dy1 = h->dy1; g.z1 = h->a1[1]; g.n1 = Conv1::OUT_PER_IMG;
