@@ -12,6 +12,7 @@
 #include "learner_internal.cuh"
 #include "nature_tf32.cuh"
 #include "gemm_tf32_stream.cuh"
+#include "act_kernel.cuh"
 
 using namespace dqnb;
 
@@ -113,7 +114,9 @@ struct dqnb_learner {
   // graph - pinned observation -> s_tm1, the batch-1 forward, q -> pinned - built on first use.
   cudaGraphExec_t act_graph = nullptr;
   uint8_t* act_obs = nullptr;    // pinned [84*84*4]
-  float* act_q = nullptr;        // pinned [kMaxActions]
+  float* act_q = nullptr;        // pinned + device-mapped [kMaxActions]: the kernel writes q straight into it
+  float* act_part = nullptr;     // fc1 partial sums of the acting kernel
+  GridBarrier* act_bar = nullptr;
   // graph
   cudaGraphExec_t graph = nullptr;
   cudaStream_t side[3] = {};
@@ -765,6 +768,7 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   if (h->act_graph) cudaGraphExecDestroy(h->act_graph);
   if (h->act_obs) cudaFreeHost(h->act_obs);
   if (h->act_q) cudaFreeHost(h->act_q);
+  cudaFree(h->act_part); cudaFree(h->act_bar);
   if (h->gather_st) cudaStreamDestroy(h->gather_st);
   for (auto& e : h->set_free) if (e) cudaEventDestroy(e);
   if (h->gathered) cudaEventDestroy(h->gathered);
@@ -1062,16 +1066,32 @@ int enqueue_q_forward(dqnb_learner* h, int which_params, int n, cudaStream_t st)
 
 int build_act_graph(dqnb_learner* h) {
   if (h->act_obs == nullptr) DQNB_CUDA(cudaMallocHost(&h->act_obs, Conv1::IN_PER_IMG));
-  if (h->act_q == nullptr) DQNB_CUDA(cudaMallocHost(&h->act_q, sizeof(float) * kMaxActions));
+  if (h->act_q == nullptr) DQNB_CUDA(cudaHostAlloc(&h->act_q, sizeof(float) * kMaxActions, cudaHostAllocMapped));
+  if (h->act_part == nullptr) DQNB_TRY(dmalloc(&h->act_part, (size_t)kActSlices * kFc1Out));
+  if (h->act_bar == nullptr) DQNB_TRY(dmalloc(&h->act_bar, 1));
+  int sms = 0, per_sm = 0;
+  DQNB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+  DQNB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, act_forward_kernel, kActThreads, 0));
+  DQNB_REQUIRE(per_sm >= 1 && sms >= 1, "acting kernel does not fit on an SM");
+  ActArgs a;
+  a.obs = h->s_tm1;
+  a.w1 = h->online + h->L.w1; a.b1 = h->online + h->L.b1; a.w2 = h->online + h->L.w2; a.b2 = h->online + h->L.b2;
+  a.w3 = h->online + h->L.w3; a.b3 = h->online + h->L.b3; a.fw1 = h->online + h->L.fw1; a.fb1 = h->online + h->L.fb1;
+  a.fw2 = h->online + h->L.fw2; a.fb2 = h->online + h->L.fb2;
+  a.a1 = h->a1[0]; a.a2 = h->a2[0]; a.a3 = h->a3[0]; a.part = h->act_part; a.q = h->q[0];
+  a.q_host = h->act_q;   // unified addressing: the pinned allocation is device-accessible at the same address
+  a.bar = h->act_bar; a.num_actions = h->A; a.shared_bias = h->cfg.shared_bias;
+  const int grid = std::min(sms, kNumSMs);
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
   DQNB_CUDA(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
   h->chain = cap;   // consecutive kernels: chain priority + programmatic dependent launch
   int rc = DQNB_OK;
   if (cudaMemcpyAsync(h->s_tm1, h->act_obs, Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, cap) != cudaSuccess) rc = DQNB_ECUDA;
-  if (rc == DQNB_OK) rc = enqueue_q_forward(h, 0, 1, cap);
-  if (rc == DQNB_OK && cudaMemcpyAsync(h->act_q, h->q[0], sizeof(float) * h->A, cudaMemcpyDeviceToHost, cap) != cudaSuccess)
-    rc = DQNB_ECUDA;
+  if (rc == DQNB_OK) {
+    act_forward_kernel<<<grid, kActThreads, 0, cap>>>(a);
+    if (cudaGetLastError() != cudaSuccess) rc = DQNB_ECUDA;
+  }
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(cap, &graph);
   h->chain = nullptr;

@@ -171,7 +171,7 @@ def test_q_values_match_oracle():
     # one observation through the online net = the acting graph (pinned in/out, one launch)
     for i in (1, 2, 1):
         assert rel(L.q_values(obs[i]), net.forward(online, obs[i:i + 1])) < 1e-5
-    assert np.array_equal(L.q_values(obs[3]), L.q_values(obs[3:4]))
+    assert rel(L.q_values(obs[3]), L.q_values(obs[3:5])[:1]) < 1e-5      # fused acting kernel vs the layer kernels
 
 
 @pytest.mark.parametrize("B,A,shared,double_q", [(32, 6, False, False), (32, 18, True, True), (5, 4, False, True),
