@@ -43,6 +43,8 @@ struct ActArgs {
   float* part;               // [49][512] fc1 partial sums
   float* q;                  // [A]
   float* q_host;             // optional pinned copy of q (null = off)
+  unsigned* seq_dev;         // launches executed so far (device counter)
+  volatile unsigned* done_host;   // pinned, device-mapped: receives the launch's sequence number after q_host is written
   GridBarrier* bar;
   int num_actions, shared_bias;
 };
@@ -165,6 +167,16 @@ __global__ void __launch_bounds__(kActThreads, 1) act_forward_kernel(ActArgs g) 
       const float v = acc + __ldg(g.fb2 + (g.shared_bias ? 0 : a));
       g.q[a] = v;
       if (g.q_host != nullptr) g.q_host[a] = v;
+    }
+  }
+  // completion flag for the host (it polls pinned memory instead of synchronising the stream)
+  if (g.done_host != nullptr) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned seq = *g.seq_dev + 1;
+      *g.seq_dev = seq;
+      *g.done_host = seq;
     }
   }
 }

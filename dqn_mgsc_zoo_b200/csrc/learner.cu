@@ -116,6 +116,9 @@ struct dqnb_learner {
   uint8_t* act_obs = nullptr;    // pinned [84*84*4]
   float* act_q = nullptr;        // pinned + device-mapped [kMaxActions]: the kernel writes q straight into it
   float* act_part = nullptr;     // fc1 partial sums of the acting kernel
+  unsigned* act_seq = nullptr;   // device: acting launches executed
+  unsigned* act_done = nullptr;  // pinned + mapped: sequence number of the last finished acting launch
+  unsigned act_launched = 0;
   GridBarrier* act_bar = nullptr;
   // graph
   cudaGraphExec_t graph = nullptr;
@@ -768,7 +771,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   if (h->act_graph) cudaGraphExecDestroy(h->act_graph);
   if (h->act_obs) cudaFreeHost(h->act_obs);
   if (h->act_q) cudaFreeHost(h->act_q);
-  cudaFree(h->act_part); cudaFree(h->act_bar);
+  cudaFree(h->act_part); cudaFree(h->act_bar); cudaFree(h->act_seq);
+  if (h->act_done) cudaFreeHost(h->act_done);
   if (h->gather_st) cudaStreamDestroy(h->gather_st);
   for (auto& e : h->set_free) if (e) cudaEventDestroy(e);
   if (h->gathered) cudaEventDestroy(h->gathered);
@@ -1069,6 +1073,11 @@ int build_act_graph(dqnb_learner* h) {
   if (h->act_q == nullptr) DQNB_CUDA(cudaHostAlloc(&h->act_q, sizeof(float) * kMaxActions, cudaHostAllocMapped));
   if (h->act_part == nullptr) DQNB_TRY(dmalloc(&h->act_part, (size_t)kActSlices * kFc1Out));
   if (h->act_bar == nullptr) DQNB_TRY(dmalloc(&h->act_bar, 1));
+  if (h->act_seq == nullptr) DQNB_TRY(dmalloc(&h->act_seq, 1));
+  if (h->act_done == nullptr) {
+    DQNB_CUDA(cudaHostAlloc(&h->act_done, sizeof(unsigned), cudaHostAllocMapped));
+    *h->act_done = 0;
+  }
   int sms = 0, per_sm = 0;
   DQNB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
   DQNB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, act_forward_kernel, kActThreads, 0));
@@ -1081,6 +1090,7 @@ int build_act_graph(dqnb_learner* h) {
   a.a1 = h->a1[0]; a.a2 = h->a2[0]; a.a3 = h->a3[0]; a.part = h->act_part; a.q = h->q[0];
   a.q_host = h->act_q;   // unified addressing: the pinned allocation is device-accessible at the same address
   a.bar = h->act_bar; a.num_actions = h->A; a.shared_bias = h->cfg.shared_bias;
+  a.seq_dev = h->act_seq; a.done_host = h->act_done;
   const int grid = std::min(sms, kNumSMs);
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
@@ -1121,7 +1131,18 @@ extern "C" int dqnb_learner_q_values(dqnb_learner* h, int which_params, const ui
     memcpy(h->act_obs, s_host, Conv1::IN_PER_IMG);
     DQNB_CUDA(cudaGraphLaunch(h->act_graph, st));
     if (h->graph_alt) { DQNB_CUDA(cudaEventRecord(h->set_free[0], st)); h->set_used[0] = true; }
-    DQNB_CUDA(cudaStreamSynchronize(st));
+    // poll the kernel's completion flag in pinned memory (a stream synchronise costs several us of wake-up)
+    const unsigned want = ++h->act_launched;
+    const volatile unsigned* done = h->act_done;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (uint64_t spins = 0; *done != want; ++spins) {
+      if ((spins & 4095) == 4095) {
+        if (cudaStreamQuery(st) != cudaErrorNotReady) break;   // finished (flag lands with it) or faulted
+        DQNB_REQUIRE(std::chrono::steady_clock::now() - t0 < std::chrono::seconds(30), "acting kernel timed out");
+      }
+    }
+    if (*done != want) DQNB_CUDA(cudaStreamSynchronize(st));
+    DQNB_REQUIRE(*done == want, "acting kernel finished without reporting (sequence %u, expected %u)", *done, want);
     memcpy(q_host, h->act_q, sizeof(float) * h->A);
     return DQNB_OK;
   }
