@@ -234,3 +234,32 @@ def test_tf32_update_from_replay_deterministic_and_q_values():
     L.update_from_replay(rep.frame_store, rep.sample_slots(B))
     params = {k: v.astype(np.float64) for k, v in L.get_params().items()}
     assert rel(L.q_values(obs[2]), net.forward(params, obs[2:3])) < TOL["tf32"]
+
+
+def test_tf32_target_sync_and_writes_refresh_the_fp16_conv1_filters():
+    """conv1's forward reads an fp16 K-major copy of both nets' filters (H16ConvFwdDoubleQ): every
+    writer of the weights - optimiser step, sync_target, set_params - has to refresh it.  After each
+    of them the next update's q-values must match the oracle forward of the learner's own
+    parameters."""
+    B, A = 32, 6
+    rng, online, target, L = setup(5, B, A, True, True, precision="tf32")
+    tol = TOL["tf32"]
+
+    def check(tag):
+        batch = synthetic.random_batch(rng, B, A)
+        on = {k: v.astype(np.float64) for k, v in L.get_params(lrn.ONLINE).items()}
+        tg = {k: v.astype(np.float64) for k, v in L.get_params(lrn.TARGET).items()}
+        L.update_host(*batch)
+        assert rel(L.read(lrn.Q_TM1), net.forward(on, batch[0])) < tol, tag
+        assert rel(L.read(lrn.Q_T), net.forward(on, batch[4])) < tol, tag
+        assert rel(L.read(lrn.Q_TARGET_T), net.forward(tg, batch[4])) < tol, tag
+
+    check("after set_params")
+    for _ in range(3):
+        check("after an optimiser step")
+    L.sync_target()
+    assert np.array_equal(L.read(lrn.TARGET), L.read(lrn.ONLINE))
+    check("after sync_target")
+    fresh = net.init_params(rng, A, True)
+    L.set_params(fresh, lrn.TARGET)
+    check("after set_params(TARGET)")

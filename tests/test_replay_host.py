@@ -192,3 +192,28 @@ def test_transition_accumulator_pairs_consecutive_timesteps():
     acc.reset()
     with pytest.raises(ValueError, match='Expected FIRST timestep'):
         list(acc.step(mid, 0))
+
+
+def test_uniform_distribution_id_mirror_tracks_the_list():
+    """sample() takes from an int64 mirror of `_ids`; adds, swap-removes and set_state must keep the
+    mirror equal to the list, and the draw must be the reference's (positions -> ids)."""
+    import numpy as np
+    from dqn_mgsc_zoo_b200 import replay as rp
+    d = rp.UniformDistribution(np.random.RandomState(4))
+    ref_rng = np.random.RandomState(4)
+    rng = np.random.default_rng(0)
+    next_id = 0
+    for step in range(5000):
+        if d.size < 3 or rng.random() < 0.6:
+            d.add([next_id]); next_id += 1
+        else:
+            d.remove([int(d._ids[int(rng.integers(d.size))])])
+        if step % 97 == 0:
+            assert np.array_equal(d._ids_np[:d.size], np.asarray(d._ids, dtype=np.int64))
+            got = d.sample(16)
+            want = np.asarray([d._ids[p] for p in ref_rng.randint(d.size, size=16)], dtype=np.int64)
+            assert got.dtype == np.int64 and np.array_equal(got, want)
+    e = rp.UniformDistribution(np.random.RandomState(4))
+    e.set_state(d.get_state())
+    assert np.array_equal(e._ids_np[:e.size], np.asarray(d._ids, dtype=np.int64))
+    assert d.check_valid()[0]
