@@ -24,5 +24,8 @@ for _ in range(3):
                  rf.data_ptr(), df.data_ptr())
 for _ in range(2):
     L.update_from_replay(store, replay.sample_slots(32))
+obs = np.random.default_rng(2).integers(0, 256, (84, 84, 4), dtype=np.uint8)
+for _ in range(2):
+    q = L.q_values(obs)        # acting graph: act_forward_kernel
 torch.cuda.synchronize()
-print("ok", L.loss())
+print("ok", L.loss(), q)
