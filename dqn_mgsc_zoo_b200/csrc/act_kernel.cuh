@@ -17,7 +17,8 @@ struct GridBarrier {
   unsigned count, gen;
 };
 // Self-resetting generation barrier (state persists across launches).  All CTAs of the grid must be
-// co-resident: grid = one CTA per SM, checked at launch with the occupancy API.
+// co-resident: grid = one CTA per SM, checked with the occupancy API, and the kernel is launched with
+// cudaLaunchAttributeCooperative so the grid is scheduled all-or-nothing.
 __device__ __forceinline__ void grid_barrier(GridBarrier* b) {
   __syncthreads();
   if (threadIdx.x == 0) {

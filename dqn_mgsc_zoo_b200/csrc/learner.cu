@@ -1099,8 +1099,15 @@ int build_act_graph(dqnb_learner* h) {
   int rc = DQNB_OK;
   if (cudaMemcpyAsync(h->s_tm1, h->act_obs, Conv1::IN_PER_IMG, cudaMemcpyHostToDevice, cap) != cudaSuccess) rc = DQNB_ECUDA;
   if (rc == DQNB_OK) {
-    act_forward_kernel<<<grid, kActThreads, 0, cap>>>(a);
-    if (cudaGetLastError() != cudaSuccess) rc = DQNB_ECUDA;
+    // cooperative launch: the grid barrier needs every CTA resident at once, and only a cooperative grid is
+    // scheduled all-or-nothing (two plain launches from different streams could each hold half the SMs)
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)grid); lc.blockDim = dim3(kActThreads); lc.stream = cap;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    lc.attrs = attr; lc.numAttrs = 1;
+    if (cudaLaunchKernelEx(&lc, act_forward_kernel, a) != cudaSuccess) { cudaGetLastError(); rc = DQNB_ECUDA; set_error("cooperative launch of the acting kernel failed"); }
   }
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(cap, &graph);
