@@ -139,6 +139,7 @@ struct dqnb_mgsc {
   float *logits = nullptr, *p = nullptr, *dldp = nullptr, *dot_part = nullptr, *loss_part = nullptr;
   float *adam_m = nullptr, *adam_v = nullptr, *out = nullptr;   // out: [M] new logits + [1] loss
   float* pinned = nullptr;                                      // [2M + 8]
+  uint8_t* pinned_on = nullptr;                                 // [2 * img]: the online transition's stacks
   int32_t count = 0;                                            // Adam step count
 };
 
@@ -199,8 +200,12 @@ int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host,
 int stage_online_transition(dqnb_mgsc* h, const uint8_t* s_tm1, int32_t a, float r, float disc, const uint8_t* s_t,
                             cudaStream_t st) {
   const int M = h->M;
-  DQNB_CUDA(cudaMemcpyAsync(h->mb_s0 + M * h->img, s_tm1, h->img, cudaMemcpyHostToDevice, st));
-  DQNB_CUDA(cudaMemcpyAsync(h->mb_s1 + M * h->img, s_t, h->img, cudaMemcpyHostToDevice, st));
+  // through pinned staging (a pageable source makes each copy a blocking, double-hop transfer); the
+  // buffer is free again when run_meta_update returns (it synchronises the stream)
+  memcpy(h->pinned_on, s_tm1, h->img);
+  memcpy(h->pinned_on + h->img, s_t, h->img);
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s0 + M * h->img, h->pinned_on, h->img, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->mb_s1 + M * h->img, h->pinned_on + h->img, h->img, cudaMemcpyHostToDevice, st));
   // scalars travel by value through the pinned block (tail), then one small copy each
   int32_t* pa = reinterpret_cast<int32_t*>(h->pinned + 2 * M + 4);
   pa[0] = a;
@@ -246,6 +251,7 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
   DQNB_TRY(dalloc(&h->dot_part, M1)); DQNB_TRY(dalloc(&h->loss_part, kLossBlocks));
   DQNB_TRY(dalloc(&h->adam_m, M1)); DQNB_TRY(dalloc(&h->adam_v, M1)); DQNB_TRY(dalloc(&h->out, M1 + 1));
   DQNB_CUDA(cudaMallocHost(&h->pinned, sizeof(float) * (2 * M1 + 8)));
+  DQNB_CUDA(cudaMallocHost(&h->pinned_on, 2 * h->img));
   *out = h;
   return DQNB_OK;
 }
@@ -260,6 +266,7 @@ extern "C" int dqnb_mgsc_destroy(dqnb_mgsc* h) {
                   h->logits, h->p, h->dldp, h->dot_part, h->loss_part, h->adam_m, h->adam_v, h->out};
   for (void* b : bufs) cudaFree(b);
   if (h->pinned) cudaFreeHost(h->pinned);
+  if (h->pinned_on) cudaFreeHost(h->pinned_on);
   delete h;
   return DQNB_OK;
 }
