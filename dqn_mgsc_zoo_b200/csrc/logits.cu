@@ -80,6 +80,7 @@ __global__ void lse_final_kernel(const float* __restrict__ part, int nb, float* 
   if (threadIdx.x == 0) {
     const float lse = stat[0] + logf(s);
     stat[1] = lse;
+    stat[2] = (s != s) ? 1.f : 0.f;   // a NaN logit (fmaxf drops it from the max, expf carries it into the sum)
     // np.float32 lse minus np.log(int) (float64), rounded when stored into the float32 array
     if (fill_at >= 0) l[fill_at] = (float)((double)lse - log_size);
   }
@@ -163,9 +164,17 @@ __global__ void search_kernel(const float* __restrict__ l, int64_t n, const floa
     if (idx < 0 && beg + i < end && cdf_above(acc, tot, x)) idx = beg + i;
   }
   const unsigned hit = __ballot_sync(0xffffffffu, idx >= 0);
-  if (hit == 0u) idx = end;   // no entry above x in this block: searchsorted returns the block's end
-  else idx = __shfl_sync(0xffffffffu, idx, __ffs(hit) - 1);
-  if (lane == 0) out[k] = idx < n ? idx : n - 1;
+  if (hit != 0u) {
+    idx = __shfl_sync(0xffffffffu, idx, __ffs(hit) - 1);
+  } else if (lane == 0) {
+    // The block's own re-summation came out a last-ulp short of the prefix that selected it.  searchsorted on
+    // the reference's cdf then lands on the next entry that carries probability (the cdf is flat over empty
+    // -inf slots, which it can never return); past the end of the array, on the last such entry.
+    idx = end;
+    while (idx < n && !(expf(l[idx] - lse) > 0.f)) ++idx;
+    if (idx >= n) { idx = n - 1; while (idx > 0 && !(expf(l[idx] - lse) > 0.f)) --idx; }
+  }
+  if (lane == 0) out[k] = idx;
 }
 __global__ void set_kernel(float* __restrict__ l, const int64_t* __restrict__ idx, const float* __restrict__ v, int n) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -333,7 +342,11 @@ extern "C" int dqnb_logits_sample(dqnb_logits* h, const double* uniforms, int64_
   DQNB_CUDA(cudaGetLastError());
   int64_t* pi = reinterpret_cast<int64_t*>(h->pinned + 8 * (size_t)h->io_cap);
   DQNB_CUDA(cudaMemcpyAsync(pi, h->d_idx, sizeof(int64_t) * n, cudaMemcpyDeviceToHost, st));
+  float* pflag = reinterpret_cast<float*>(h->pinned);   // the uniforms were consumed by the copy above
+  DQNB_CUDA(cudaMemcpyAsync(pflag, h->stat + 2, sizeof(float), cudaMemcpyDeviceToHost, st));
   DQNB_CUDA(cudaStreamSynchronize(st));
+  // Generator.choice raises ValueError('probabilities contain NaN') in the reference (replay_circular.py:205-217)
+  DQNB_REQUIRE(*pflag == 0.f, "probabilities contain NaN");
   memcpy(indices, pi, sizeof(int64_t) * n);
   return DQNB_OK;
 }

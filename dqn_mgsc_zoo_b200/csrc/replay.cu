@@ -62,6 +62,7 @@ struct dqnb_replay {
   // callers may gather on different streams (the learner prefetches on its own gather stream): a
   // gather on another stream than its predecessor / than the last commit's waits for them first
   cudaStream_t gather_stream = nullptr, commit_stream = nullptr;
+  cudaStream_t commit_ran_on = nullptr;   // the stream the last commit kernel really ran on (side or caller's)
   cudaEvent_t committed = nullptr;
   bool have_commit = false;
   bool have_gather = false;
@@ -118,6 +119,9 @@ int flush(dqnb_replay* h, cudaStream_t st) {
   // not touch the replay, so a small commit may run beside it.
   cudaStream_t cs = (zero_copy && h->side != nullptr) ? h->side : st;
   if (h->have_gather && (cs != st || st != h->gather_stream)) DQNB_CUDA(cudaStreamWaitEvent(cs, h->gather_done, 0));
+  // Commits must land in issue order (two batches may write the same slot: small capacities, reservoir
+  // replacements): a commit on another stream than its predecessor waits for it.
+  if (h->have_commit && cs != h->commit_ran_on) DQNB_CUDA(cudaStreamWaitEvent(cs, h->committed, 0));
   commit_kernel<<<grid, kCommitThreads, 0, cs>>>(
       h->d_planes, h->plane_stride, h->plane_bytes, src + h->hdr_bytes,
       reinterpret_cast<const int32_t*>(src + h->hdr_records), s.n_planes,
@@ -130,6 +134,7 @@ int flush(dqnb_replay* h, cudaStream_t st) {
   }
   DQNB_CUDA(cudaEventRecord(h->committed, cs));   // gathers issued on any other stream wait for this
   h->commit_stream = st;
+  h->commit_ran_on = cs;
   h->have_commit = true;
   s.in_flight = true;
   for (int i = 0; i < s.n_records; ++i) h->slot_staged[h->rec_of(s)[i].slot] = 0;

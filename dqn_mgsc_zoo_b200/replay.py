@@ -44,6 +44,16 @@ def is_frame_item(item) -> bool:
     return bool(ok and np.ndim(a) == 0 and np.ndim(r) == 0 and np.ndim(d) == 0)
 
 
+def _scalar_dtype(value, kind):
+    """Host dtype of a per-slot scalar column: what np.stack gives the reference for Python scalars
+    (int64 actions, float64 rewards / discounts, replay.py:204-205) - never narrower because the FIRST
+    item happened to carry an int reward (a synthetic env's `0`), which would truncate later floats."""
+    dt = np.asarray(value).dtype
+    if kind == 'f':
+        return dt if dt.kind == 'f' else np.dtype(np.float64)
+    return dt if dt.kind in 'iu' and isinstance(value, np.generic) else np.dtype(np.int64)
+
+
 class ItemStorage:
     """slot -> item.  Frame items on the device, anything else in a host list."""
 
@@ -63,7 +73,8 @@ class ItemStorage:
                 h, w, s = item[0].shape
                 self.frames = FrameStore(self.capacity, h, w, s, self.device, self.stream,
                                          self.initial_planes)
-                self.scalars = [np.zeros(self.capacity, dtype=np.asarray(item[k]).dtype) for k in (1, 2, 3)]
+                self.scalars = [np.zeros(self.capacity, dtype=_scalar_dtype(item[k], kind))
+                                for k, kind in ((1, 'i'), (2, 'f'), (3, 'f'))]
             else:
                 self.host_items = [None] * self.capacity
         if self.frames is not None:
@@ -131,8 +142,11 @@ class UniformDistribution:
                 self._ids_np[pos] = tail
                 self._id_to_index[tail] = pos
 
+    def _draw(self, high, size):
+        return self._random_state.randint(high, size=size)          # replay.py:121
+
     def sample(self, size: int) -> np.ndarray:
-        positions = self._random_state.randint(self.size, size=size)
+        positions = self._draw(self.size, size)
         return self._ids_np[positions]
 
     def ids(self):
@@ -166,13 +180,14 @@ class UniformDistribution:
 
 class _UniformReplayBase:
     """Shared sampling / state code of the FIFO and reservoir replays."""
+    _DISTRIBUTION = UniformDistribution
 
     def __init__(self, capacity, structure, random_state, encoder=None, decoder=None, device=0,
                  stream=0, initial_planes=0):
         self._capacity = capacity
         self._structure = structure
         self._random_state = random_state
-        self._distribution = UniformDistribution(random_state=random_state)
+        self._distribution = self._DISTRIBUTION(random_state=random_state)
         self._storage = ItemStorage(capacity, structure, encoder, decoder, device, stream, initial_planes)
         self._live = collections.OrderedDict()   # id -> slot, insertion-ordered like the reference dict
         self._t = 0
@@ -256,9 +271,12 @@ class TransitionReplay(_UniformReplayBase):
 class ReservoirTransitionReplay(_UniformReplayBase):
     """Uniform replay with Algorithm-R insertion (replay.py:246-333); slot = id."""
 
+    def _draw_replacement(self):
+        return self._random_state.randint(0, self._t)   # same draw as replay.py:270
+
     def add(self, item) -> None:
         if self.size == self._capacity:
-            j = self._random_state.randint(0, self._t)   # same draw as replay.py:270
+            j = self._draw_replacement()
             if j < self.size:
                 self._storage.put(int(j), item)
         else:
@@ -292,3 +310,73 @@ class TransitionAccumulator:
     def reset(self) -> None:
         self._timestep_tm1 = None
         self._a_tm1 = None
+
+
+def _build_n_step_transition(transitions):
+    """Builds a single n-step transition from n 1-step transitions (replay.py:1200-1215)."""
+    r_t = 0.0
+    discount_t = 1.0
+    for transition in transitions:
+        r_t += discount_t * transition.r_t
+        discount_t *= transition.discount_t
+    return Transition(s_tm1=transitions[0].s_tm1, a_tm1=transitions[0].a_tm1, r_t=r_t, discount_t=discount_t,
+                      s_t=transitions[-1].s_t)
+
+
+class NStepTransitionAccumulator:
+    """Accumulates timesteps to form n-step transitions (replay.py:1218-1284): nothing on FIRST, one
+    n-step transition per MID once n are buffered, all remaining n..1-step ones on LAST."""
+
+    def __init__(self, n):
+        self._transitions = collections.deque(maxlen=n)
+        self.reset()
+
+    def step(self, timestep_t, a_t):
+        if timestep_t.first():
+            self.reset()
+        if self._timestep_tm1 is None:
+            assert self._a_tm1 is None
+            if not timestep_t.first():
+                raise ValueError('Expected FIRST timestep, got %s.' % str(timestep_t))
+            self._timestep_tm1, self._a_tm1 = timestep_t, a_t
+            return
+        self._transitions.append(Transition(
+            s_tm1=self._timestep_tm1.observation, a_tm1=self._a_tm1, r_t=timestep_t.reward,
+            discount_t=timestep_t.discount, s_t=timestep_t.observation))
+        self._timestep_tm1, self._a_tm1 = timestep_t, a_t
+        if timestep_t.last():
+            while self._transitions:
+                yield _build_n_step_transition(self._transitions)
+                self._transitions.popleft()
+        else:
+            if len(self._transitions) < self._transitions.maxlen:
+                return
+            yield _build_n_step_transition(self._transitions)
+
+    def reset(self) -> None:
+        self._transitions.clear()
+        self._timestep_tm1 = None
+        self._a_tm1 = None
+
+
+# The reference runners snappy-compress every stack before it enters the host replay
+# (replay.py:1287-1296, dqn/run_atari.py:178-190) to fit 1 M transitions in 25 GB of RAM.  Frame items
+# never pass through encoder/decoder here (HBM holds the raw bytes, 7 GB deduplicated), so the codec only
+# has to round-trip for callers that still invoke it: snappy when the package exists, else raw bytes.
+try:
+    import snappy as _snappy
+except ImportError:      # not in this image
+    _snappy = None
+
+
+def compress_array(array: np.ndarray):
+    """(bytes, shape, dtype) - replay.py:1287-1289."""
+    raw = np.ascontiguousarray(array)
+    return (_snappy.compress(raw) if _snappy is not None else raw.tobytes()), array.shape, array.dtype
+
+
+def uncompress_array(compressed) -> np.ndarray:
+    """replay.py:1292-1296."""
+    compressed_array, shape, dtype = compressed
+    byte_string = _snappy.uncompress(compressed_array) if _snappy is not None else compressed_array
+    return np.frombuffer(byte_string, dtype=dtype).reshape(shape)

@@ -24,11 +24,91 @@ from typing import Optional
 import numpy as np
 
 from dqn_mgsc_zoo_b200 import _lib
-from dqn_mgsc_zoo_b200.replay import ItemStorage, Transition  # noqa: F401  (re-exported like the reference)
+from dqn_mgsc_zoo_b200 import replay as _uniform
+from dqn_mgsc_zoo_b200.replay import (ItemStorage, Transition, TransitionAccumulator,  # noqa: F401  (re-exported:
+                                      NStepTransitionAccumulator, compress_array,     # the MGSC runners import this
+                                      uncompress_array)                               # module as `replay_lib`)
 
 
 def _i64(a):
     return np.ascontiguousarray(a, dtype=np.int64)
+
+
+class CircularBuffer:
+    """Host ring of arbitrary items (replay_circular.py:90-146); the MGSC replays here keep frame items in
+    the HBM store instead, this class is the module-surface twin for code that uses it directly."""
+
+    def __init__(self, capacity: int):
+        self._list = [None] * capacity
+        self._capacity = capacity
+        self._size = 0
+        self._left_head = 0
+        self._right_head = 0
+
+    @property
+    def capacity(self) -> int:
+        return self._capacity
+
+    @property
+    def size(self) -> int:
+        return self._size
+
+    def is_full(self) -> bool:
+        return self._size == self._capacity
+
+    def add(self, item) -> None:
+        if self.is_full():
+            raise BufferError("Buffer is full and cannot be added to. Pop an item first.")
+        self._list[self._right_head] = item
+        self._right_head = (self._right_head + 1) % self._capacity
+        self._size += 1
+
+    def popleft(self):
+        if self._size == 0:
+            raise BufferError("Buffer is empty and cannot be popped from. Add an item first.")
+        item = self._list[self._left_head]
+        self._left_head = (self._left_head + 1) % self._capacity
+        self._size -= 1
+        return item
+
+    def __getitem__(self, key: int):
+        if self._size == 0:
+            raise BufferError("Buffer is empty and cannot be indexed. Add an item first.")
+        return self._list[(self._left_head + key) % self._capacity]
+
+    def __len__(self):
+        return self._size
+
+    def get_state(self):
+        return {'list': self._list, 'capacity': self._capacity, 'size': self._size,
+                'left_head': self._left_head, 'right_head': self._right_head}
+
+    def set_state(self, state) -> None:
+        self._list = state['list']
+        self._capacity = state['capacity']
+        self._size = state['size']
+        self._left_head = state['left_head']
+        self._right_head = state['right_head']
+
+
+class UniformDistribution(_uniform.UniformDistribution):
+    """replay_circular.py:251-324: the `np.random.Generator` twin (`integers` instead of `randint`)."""
+
+    def _draw(self, high, size):
+        return self._random_state.integers(high, size=size)          # replay_circular.py:285
+
+
+class TransitionReplay(_uniform.TransitionReplay):
+    """replay_circular.py:327-407 (FIFO, Generator)."""
+    _DISTRIBUTION = UniformDistribution
+
+
+class ReservoirTransitionReplay(_uniform.ReservoirTransitionReplay):
+    """replay_circular.py:410-497 (Algorithm R, Generator)."""
+    _DISTRIBUTION = UniformDistribution
+
+    def _draw_replacement(self):
+        return self._random_state.integers(0, self._t)                # replay_circular.py:436
 
 
 class _DeviceLogits:
@@ -68,7 +148,12 @@ class _DeviceLogits:
     def sample(self, uniforms):
         u = np.ascontiguousarray(uniforms, dtype=np.float64)
         out = np.empty(u.shape, dtype=np.int64)
-        _lib.call("dqnb_logits_sample", self._h, u.ctypes.data, u.size, out.ctypes.data, self.stream)
+        try:
+            _lib.call("dqnb_logits_sample", self._h, u.ctypes.data, u.size, out.ctypes.data, self.stream)
+        except _lib.DqnbError as e:
+            if "NaN" in str(e):     # what Generator.choice raises for NaN probabilities in the reference
+                raise ValueError("probabilities contain NaN") from e
+            raise
         return out
 
     def lse(self):

@@ -62,7 +62,9 @@ class UniformIds:
         return len(self.table)
 
     def sample(self, n):
-        pos = self.rs.randint(self.size, size=n)
+        # replay.py:121 draws with RandomState.randint, the replay_circular.py:285 twin with Generator.integers
+        pos = self.rs.integers(self.size, size=n) if isinstance(self.rs, np.random.Generator) \
+            else self.rs.randint(self.size, size=n)
         return np.array([self.table[p] for p in pos], dtype=np.int64)
 
 
@@ -113,7 +115,8 @@ class ReservoirReplay:
 
     def add(self, item):
         if len(self.items) == self.capacity:
-            j = int(self.rs.randint(0, self.t))
+            j = int(self.rs.integers(0, self.t) if isinstance(self.rs, np.random.Generator)
+                    else self.rs.randint(0, self.t))       # replay.py:270 / replay_circular.py:436
             if j < self.capacity:
                 self.items[j] = item
                 self.last_decision = j

@@ -21,6 +21,7 @@ from tests import replay_scenarios as sc  # noqa: E402
 def reference_factory(kind):
     r, rc = ref_shim.load("replay"), ref_shim.load("replay_circular")
     cls = {"fifo": r.TransitionReplay, "reservoir": r.ReservoirTransitionReplay,
+           "gen_fifo": rc.TransitionReplay, "gen_reservoir": rc.ReservoirTransitionReplay,
            "mgsc_fifo": rc.MGSCFiFoTransitionReplay,
            "mgsc_reservoir": rc.MGSCReservoirTransitionReplay}[kind]
     return lambda capacity, structure, rng: cls(capacity, structure, rng)

@@ -16,9 +16,10 @@ def _crc(arr):
     return zlib.crc32(np.ascontiguousarray(arr).tobytes())
 
 
-def pairs_uniform(make, seed, capacity, n_add, sample_every, batch):
-    """FIFO / reservoir with a RandomState: record every sampled `a` column."""
-    rs = np.random.RandomState(seed)
+def pairs_uniform(make, seed, capacity, n_add, sample_every, batch, generator=False):
+    """FIFO / reservoir with a RandomState (replay.py) or a Generator (the replay_circular.py twins):
+    record every sampled `a` column."""
+    rs = np.random.default_rng(seed) if generator else np.random.RandomState(seed)
     rep = make(capacity, Pair(None, None), rs)
     drawn, sizes = [], []
     for i in range(n_add):
@@ -29,7 +30,8 @@ def pairs_uniform(make, seed, capacity, n_add, sample_every, batch):
             drawn.append(np.asarray(s.a, dtype=np.int64))
             sizes.append(rep.size)
     # the caller shares the RandomState with the replay: its next draw is part of the contract
-    return {"drawn": np.stack(drawn), "sizes": np.array(sizes), "next_draw": rs.randint(1 << 30)}
+    return {"drawn": np.stack(drawn), "sizes": np.array(sizes),
+            "next_draw": rs.integers(1 << 30) if generator else rs.randint(1 << 30)}
 
 
 def pairs_mgsc(make, seed, capacity, n_add, every, batch, meta):
@@ -74,6 +76,8 @@ SCENARIOS = {
     "fifo_pairs": dict(kind="fifo", fn="pairs_uniform", args=dict(seed=7, capacity=37, n_add=180, sample_every=3, batch=8)),
     "fifo_pairs_tiny": dict(kind="fifo", fn="pairs_uniform", args=dict(seed=1, capacity=4, n_add=40, sample_every=1, batch=5)),
     "reservoir_pairs": dict(kind="reservoir", fn="pairs_uniform", args=dict(seed=11, capacity=50, n_add=600, sample_every=4, batch=8)),
+    "gen_fifo_pairs": dict(kind="gen_fifo", fn="pairs_uniform", args=dict(seed=19, capacity=23, n_add=150, sample_every=3, batch=8, generator=True)),
+    "gen_reservoir_pairs": dict(kind="gen_reservoir", fn="pairs_uniform", args=dict(seed=23, capacity=40, n_add=500, sample_every=4, batch=8, generator=True)),
     "mgsc_fifo_pairs": dict(kind="mgsc_fifo", fn="pairs_mgsc", args=dict(seed=3, capacity=24, n_add=90, every=2, batch=6, meta=5)),
     "mgsc_reservoir_pairs": dict(kind="mgsc_reservoir", fn="pairs_mgsc", args=dict(seed=5, capacity=24, n_add=140, every=2, batch=6, meta=5)),
     "fifo_frames": dict(kind="fifo", fn="frames_uniform", args=dict(seed=13, capacity=64, n_add=260, sample_every=10, batch=16)),

@@ -19,6 +19,7 @@ GOLDEN = np.load(os.path.join(os.path.dirname(__file__), "golden", "replay_golde
 
 def oracle_factory(kind):
     cls = {"fifo": ro.FifoReplay, "reservoir": ro.ReservoirReplay,
+           "gen_fifo": ro.FifoReplay, "gen_reservoir": ro.ReservoirReplay,
            "mgsc_fifo": ro.MgscFifoReplay, "mgsc_reservoir": ro.MgscReservoirReplay}[kind]
     return lambda capacity, structure, rng: cls(capacity, structure, rng)
 

@@ -11,11 +11,13 @@ from tests.test_oracle_replay import check_against_golden
 
 pytestmark = pytest.mark.gpu
 
-UNIFORM = [n for n, s in sc.SCENARIOS.items() if s["kind"] in ("fifo", "reservoir")]
+UNIFORM = [n for n, s in sc.SCENARIOS.items() if s["kind"] in ("fifo", "reservoir", "gen_fifo", "gen_reservoir")]
 
 
 def product_factory(kind):
-    cls = {"fifo": rp.TransitionReplay, "reservoir": rp.ReservoirTransitionReplay}[kind]
+    from dqn_mgsc_zoo_b200 import replay_circular as rc
+    cls = {"fifo": rp.TransitionReplay, "reservoir": rp.ReservoirTransitionReplay,
+           "gen_fifo": rc.TransitionReplay, "gen_reservoir": rc.ReservoirTransitionReplay}[kind]
     return lambda capacity, structure, rng: cls(capacity, structure, rng)
 
 
@@ -89,3 +91,28 @@ def test_gather_split_settings_agree():
         p.frame_store.set_gather_splits(splits)
         for x, y in zip(base, p.frame_store.gather_host(slots)):
             assert np.array_equal(x, y), splits
+
+
+def test_commit_order_large_then_small_batches_same_slots():
+    """A >128 KB staged batch is committed on the caller's stream, a small one on the store's side
+    stream; with capacity 4 both write the same slots, so the commits must land in issue order
+    (the older SlotRecord could land last).  Non-chained puts: 8 new planes each."""
+    cap = 4
+    rng = np.random.default_rng(21)
+    p = rp.TransitionReplay(cap, rp.Transition(None, None, None, None, None), np.random.RandomState(0))
+    o = ro.FifoReplay(cap, ro.Transition(None, None, None, None, None), np.random.RandomState(0))
+
+    def item():
+        s0 = rng.integers(1, 256, size=(84, 84, 4), dtype=np.uint8)
+        s1 = rng.integers(1, 256, size=(84, 84, 4), dtype=np.uint8)
+        return (s0, int(rng.integers(6)), float(rng.integers(-1, 2)), 0.99, s1)
+
+    for rounds in range(6):
+        for n in (70, 3, 2, 33, 1):      # big staged batches (copied) followed by small (zero-copy) ones
+            for _ in range(n):
+                it = item()
+                p.add(rp.Transition(*it))
+                o.add(ro.Transition(*it))
+            a, b = o.sample(8), p.sample(8)
+            for x, y, name in zip(a, b, a._fields):
+                assert np.array_equal(x, y), (rounds, n, name)

@@ -217,3 +217,68 @@ def test_uniform_distribution_id_mirror_tracks_the_list():
     e.set_state(d.get_state())
     assert np.array_equal(e._ids_np[:e.size], np.asarray(d._ids, dtype=np.int64))
     assert d.check_valid()[0]
+
+
+# ---- golden fixtures made by the unmodified reference, product classes on generic (host) items
+@pytest.mark.parametrize("name", ["fifo_pairs", "fifo_pairs_tiny", "reservoir_pairs", "gen_fifo_pairs",
+                                  "gen_reservoir_pairs"])
+def test_product_pairs_match_reference_golden(name):
+    from dqn_mgsc_zoo_b200 import replay_circular as rc
+    from tests import replay_scenarios as sc
+    from tests.test_oracle_replay import check_against_golden
+    spec = sc.SCENARIOS[name]
+    cls = {"fifo": replay_lib.TransitionReplay, "reservoir": replay_lib.ReservoirTransitionReplay,
+           "gen_fifo": rc.TransitionReplay, "gen_reservoir": rc.ReservoirTransitionReplay}[spec["kind"]]
+    got = sc.pairs_uniform(lambda capacity, structure, rng: cls(capacity, structure, rng), **spec["args"])
+    check_against_golden(name, got)
+
+
+def test_replay_circular_module_surface_of_the_mgsc_runner():
+    """dqn_mgsc_batched/run_atari.py:185-232 imports replay_circular as replay_lib and touches exactly these."""
+    from dqn_mgsc_zoo_b200 import replay_circular as rc
+    for name in ("Transition", "TransitionAccumulator", "NStepTransitionAccumulator", "compress_array",
+                 "uncompress_array", "CircularBuffer", "CircularLogitBuffer", "UniformDistribution",
+                 "TransitionReplay", "ReservoirTransitionReplay", "MGSCReservoirDistribution",
+                 "MGSCFiFoTransitionReplay", "MGSCReservoirTransitionReplay"):
+        assert hasattr(rc, name), name
+    a = np.arange(84 * 84 * 4, dtype=np.uint8).reshape(84, 84, 4)
+    t = rc.Transition(s_tm1=a, a_tm1=1, r_t=0.0, discount_t=0.99, s_t=a + 1)
+    enc = t._replace(s_tm1=rc.compress_array(t.s_tm1), s_t=rc.compress_array(t.s_t))       # the runner's encoder
+    dec = enc._replace(s_tm1=rc.uncompress_array(enc.s_tm1), s_t=rc.uncompress_array(enc.s_t))
+    assert np.array_equal(dec.s_tm1, t.s_tm1) and np.array_equal(dec.s_t, t.s_t)
+    buf = rc.CircularBuffer(3)
+    with pytest.raises(BufferError):
+        buf.popleft()
+    for i in range(3):
+        buf.add(i)
+    with pytest.raises(BufferError):
+        buf.add(9)
+    assert buf.popleft() == 0 and buf[0] == 1 and len(buf) == 2
+    buf.add(7)
+    assert [buf[k] for k in range(3)] == [1, 2, 7]
+    st = buf.get_state()
+    other = rc.CircularBuffer(3)
+    other.set_state(st)
+    assert [other[k] for k in range(3)] == [1, 2, 7]
+
+
+def test_n_step_accumulator_matches_reference_semantics():
+    """replay_test.py:177-360 (NStepTransitionAccumulatorTest): n-step returns and episode-end flush."""
+    import collections
+    TS = collections.namedtuple("TS", "step_type reward discount observation")
+    TS.first = lambda self: self.step_type == 0
+    TS.last = lambda self: self.step_type == 2
+    acc = replay_lib.NStepTransitionAccumulator(3)
+    steps = [TS(0, None, None, 0)] + [TS(1, float(k), 0.5, k) for k in range(1, 5)] + [TS(2, 5.0, 0.0, 5)]
+    out = []
+    for k, ts in enumerate(steps):
+        out.append(list(acc.step(ts, a_t=k)))
+    assert [len(o) for o in out] == [0, 0, 0, 1, 1, 3]
+    first = out[3][0]
+    assert (first.s_tm1, first.a_tm1, first.s_t) == (0, 0, 3)
+    assert first.r_t == 1.0 + 0.5 * 2.0 + 0.25 * 3.0 and first.discount_t == 0.125
+    tail = out[5]
+    assert [(t.s_tm1, t.s_t) for t in tail] == [(2, 5), (3, 5), (4, 5)]
+    assert tail[-1].r_t == 5.0 and tail[-1].discount_t == 0.0
+    with pytest.raises(ValueError, match="Expected FIRST"):
+        replay_lib.NStepTransitionAccumulator(2).step(TS(1, 0.0, 1.0, 0), 0).__next__()
