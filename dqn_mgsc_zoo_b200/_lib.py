@@ -45,6 +45,10 @@ SIGNATURES = {
     "dqnb_learner_write_dev": [c_vp, c_int, c_vp, c_i64, STREAM],
     "dqnb_learner_apply_grads": [c_vp, STREAM],
     "dqnb_learner_adjoint_dots": [c_vp, c_vp, c_vp, STREAM],
+    "dqnb_dp_unique_id": [c_vp],
+    "dqnb_dp_init": [c_vp, c_vp, c_int, c_int],
+    "dqnb_dp_allreduce": [c_vp, STREAM],
+    "dqnb_dp_info": [c_vp, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int)],
     "dqnb_learner_get_config": [c_vp, c_vp, ctypes.POINTER(c_int)],
     "dqnb_mgsc_create": [c_vp, c_vp, ctypes.POINTER(c_vp)],
     "dqnb_mgsc_destroy": [c_vp],
@@ -54,6 +58,7 @@ SIGNATURES = {
                                    c_vp, ctypes.POINTER(c_f32), STREAM],
     "dqnb_mgsc_read": [c_vp, c_int, c_vp, c_i64],
     "dqnb_mgsc_write": [c_vp, c_int, c_vp, c_i64],
+    "dqnb_mgsc_read_learner": [c_vp, c_int, c_int, c_vp, c_i64],
     "dqnb_mgsc_adam_count": [c_vp, ctypes.POINTER(c_i32), ctypes.POINTER(c_i32)],
     "dqnb_logits_create": [c_i64, c_int, ctypes.POINTER(c_vp)],
     "dqnb_logits_destroy": [c_vp],

@@ -443,6 +443,45 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
   }
   tl_end(tl);
 }
+// Sums the split-K partials of the arena range [lo, hi) (multiples of 4) into g, with the very additions of
+// rmsprop_reduce_kernel (8 lanes per float4, xor butterfly): the data-parallel learner materialises the gradient
+// in two pieces so that the first (fc1 + fc2, 95 % of the bytes) can be all-reduced while the convolution
+// backward still runs.  Elements without a registered region keep what the producing kernel wrote into g.
+__global__ void grad_reduce_range_kernel(float* __restrict__ g, GradRegions regs, int64_t lo, int64_t hi,
+                                         unsigned long long* tl) {
+  tl_begin(tl);
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t i4 = (lo >> 2) + (gid >> 3), i = i4 << 2;
+  const int sub = (int)(gid & 7);
+  const bool live = i < hi;
+  float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool summed = false;
+  if (live) {
+#pragma unroll
+    for (int r = 0; r < kMaxGradRegions; ++r) {
+      if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
+        const float* src = regs.r[r].part + (i - regs.r[r].off);
+        for (int q = sub; q < regs.r[r].splits; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].stride));
+          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
+        }
+        summed = true;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    gv.x += __shfl_xor_sync(0xffffffffu, gv.x, o);
+    gv.y += __shfl_xor_sync(0xffffffffu, gv.y, o);
+    gv.z += __shfl_xor_sync(0xffffffffu, gv.z, o);
+    gv.w += __shfl_xor_sync(0xffffffffu, gv.w, o);
+  }
+  if (live && summed && sub == 0) reinterpret_cast<float4*>(g)[i4] = gv;
+  tl_end(tl);
+}
+inline unsigned grad_reduce_range_blocks(int64_t lo, int64_t hi) {
+  return (unsigned)((((hi - lo + 3) >> 2) * 8 + 255) / 256);
+}
 __global__ void round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t n) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[i] = tf32_rn(src[i]);

@@ -13,6 +13,7 @@
 #include "nature_tf32.cuh"
 #include "gemm_tf32_stream.cuh"
 #include "act_kernel.cuh"
+#include "nccl_dyn.cuh"
 
 using namespace dqnb;
 
@@ -131,6 +132,14 @@ struct dqnb_learner {
   cudaEvent_t ev[8] = {};
   int64_t updates = 0;
   int64_t launches_per_update = 0;
+  // Data-parallel mode (dqnb_dp_init): the update graph itself all-reduces the gradient arena over NCCL - the
+  // fc1 + fc2 part as soon as their weight gradients exist, the convolution part at the end - and then applies
+  // the optimiser step, so one graph launch per rank is the whole data-parallel update.
+  NcclComm dp_comm = nullptr;
+  int dp_rank = 0, dp_world = 1;
+  cudaStream_t dp_stream = nullptr;      // carries the collectives (high priority: NCCL's few CTAs must not queue behind whole GEMM grids)
+  cudaEvent_t dp_ev[4] = {};
+  bool dp_on() const { return dp_comm != nullptr; }
   // pinned staging for host-batch updates and slot uploads
   uint8_t* pinned = nullptr;
   size_t pinned_bytes = 0;
@@ -325,7 +334,15 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
     DQNB_TRY(fork(h->ev[4], s2, st));
     DQNB_TRY(fork(h->ev[5], s3, st));
   }
-  if (h->cfg.defer_apply) return DQNB_OK;
+  if (h->cfg.defer_apply && !h->dp_on()) return DQNB_OK;
+  if (h->dp_on()) {   // fp32 mode: one collective over the whole arena (the tf32 path chunks it)
+    h->launches_per_update++;
+    if (live) {
+      const NcclApi* nccl = nccl_api();
+      DQNB_REQUIRE(nccl != nullptr, "NCCL went away");
+      DQNB_NCCL(nccl, nccl->AllReduce(h->grad, h->grad, (size_t)h->L.total, kNcclFloat32, kNcclSum, h->dp_comm, st));
+    }
+  }
   h->launches_per_update++;
   if (live) {
     int64_t n4 = (h->L.total >> 2) + 1;
@@ -561,6 +578,25 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     DQNB_TRY(rc_w);
   }
   else DQNB_TRY((t32_dense_wgrad<4, 128>(h, B, false, s2)));
+  const int64_t dp_split_end = h->stream ? h->L.fb2 : h->L.fw2;
+  const bool dp_live = live && h->dp_on();
+  cudaStream_t sd = h->profiling ? st : h->dp_stream;
+  if (h->dp_on()) h->launches_per_update += 2;
+  if (dp_live) {
+    // chunk 1 = [fc1.w, end of arena): both producers (fc1 wgrad on s2, fc2 wgrad first on s1) are enqueued;
+    // sum their split-K partials and start the collective while conv2 dgrad / conv2 wgrad / conv1 wgrad run
+    const NcclApi* nccl = nccl_api();
+    DQNB_REQUIRE(nccl != nullptr, "NCCL went away");
+    DQNB_TRY(fork(h->dp_ev[0], s1, sd));
+    DQNB_TRY(fork(h->dp_ev[1], s2, sd));
+    grad_reduce_range_kernel<<<grad_reduce_range_blocks(h->L.fw1, dp_split_end), 256, 0, sd>>>(
+        h->grad, h->regions, h->L.fw1, dp_split_end, h->next_tl("grad_reduce_fc"));
+    DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(mark(h, sd, "grad_reduce_fc"));
+    DQNB_NCCL(nccl, nccl->AllReduce(h->grad + h->L.fw1, h->grad + h->L.fw1, (size_t)(h->L.total - h->L.fw1),
+                                    kNcclFloat32, kNcclSum, h->dp_comm, sd));
+    DQNB_TRY(mark(h, sd, "allreduce_fc"));
+  }
   h->boost = h->pdl;   // see the fc1 wgrad above: conv2's wgrad and both bias column sums would otherwise wait for the chain
   int rc_c2 = t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1);
   h->boost = false;
@@ -575,6 +611,30 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     DQNB_TRY(fork(h->ev[3], s1, st));
     DQNB_TRY(fork(h->ev[4], s2, st));
     DQNB_TRY(fork(h->ev[5], s3, st));
+  }
+  if (h->dp_on()) {
+    // chunk 2 = the convolution gradients [0, fc1.w): reduce, all-reduce behind chunk 1 on the collective
+    // stream, then the optimiser step over the whole (now global) gradient
+    h->launches_per_update += 3;
+    if (live) {
+      const NcclApi* nccl = nccl_api();
+      DQNB_REQUIRE(nccl != nullptr, "NCCL went away");
+      grad_reduce_range_kernel<<<grad_reduce_range_blocks(0, h->L.fw1), 256, 0, st>>>(
+          h->grad, h->regions, 0, h->L.fw1, h->next_tl("grad_reduce_conv"));
+      DQNB_CUDA(cudaGetLastError());
+      DQNB_TRY(mark(h, st, "grad_reduce_conv"));
+      DQNB_TRY(fork(h->dp_ev[2], st, sd));
+      DQNB_NCCL(nccl, nccl->AllReduce(h->grad, h->grad, (size_t)h->L.fw1, kNcclFloat32, kNcclSum, h->dp_comm, sd));
+      DQNB_TRY(mark(h, sd, "allreduce_conv"));
+      DQNB_TRY(fork(h->dp_ev[3], sd, st));
+      GradRegions none{};
+      rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, 0, 0, 0), 256, 0, st>>>(
+          h->online, h->online_r, h->h16_online(), h->mu, h->nu, h->grad, h->L.total, none, 0, 0, 0,
+          h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop"));
+      DQNB_CUDA(cudaGetLastError());
+      DQNB_TRY(mark(h, st, "rmsprop"));
+    }
+    return DQNB_OK;
   }
   h->launches_per_update++;
   if (live) {
@@ -768,6 +828,9 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   cudaDeviceSynchronize();
   if (h->graph) cudaGraphExecDestroy(h->graph);
   if (h->graph_alt) cudaGraphExecDestroy(h->graph_alt);
+  if (h->dp_comm) { const NcclApi* nccl = nccl_api(); if (nccl) nccl->CommDestroy(h->dp_comm); }
+  if (h->dp_stream) cudaStreamDestroy(h->dp_stream);
+  for (auto& e : h->dp_ev) if (e) cudaEventDestroy(e);
   if (h->act_graph) cudaGraphExecDestroy(h->act_graph);
   if (h->act_obs) cudaFreeHost(h->act_obs);
   if (h->act_q) cudaFreeHost(h->act_q);
@@ -889,6 +952,10 @@ extern "C" int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* d
 
 extern "C" int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream) {
   DQNB_REQUIRE(h, "null argument");
+  if (h->dp_on()) {
+    set_error("this learner is data-parallel (dqnb_dp_init): its update already all-reduces and applies the gradient");
+    return DQNB_ESTATE;
+  }
   DeviceGuard guard(h->device);
   cudaStream_t st = as_stream(stream);
   if (h->tf32) {
@@ -902,6 +969,76 @@ extern "C" int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream) {
                                                                h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, nullptr);
   }
   DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}
+
+// ------------------------------------------------------------------ data-parallel learner
+extern "C" int dqnb_dp_unique_id(uint8_t* id128) {
+  DQNB_REQUIRE(id128, "null argument");
+  const NcclApi* nccl = nccl_api();
+  if (!nccl) return DQNB_ESTATE;
+  NcclUniqueId id;
+  DQNB_NCCL(nccl, nccl->GetUniqueId(&id));
+  memcpy(id128, id.internal, sizeof(id.internal));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_dp_init(dqnb_learner* h, const uint8_t* id128, int rank, int world) {
+  DQNB_REQUIRE(h && id128, "null argument");
+  DQNB_REQUIRE(world >= 1 && rank >= 0 && rank < world, "rank %d not in a world of %d", rank, world);
+  DQNB_REQUIRE(h->cfg.defer_apply, "create the learner with defer_apply = 1 (and loss_mean_over = the global batch)");
+  DQNB_REQUIRE(!h->dp_on(), "dqnb_dp_init was already called on this learner");
+  const NcclApi* nccl = nccl_api();
+  if (!nccl) return DQNB_ESTATE;
+  DeviceGuard guard(h->device);
+  DQNB_CUDA(cudaDeviceSynchronize());
+  NcclUniqueId id;
+  memcpy(id.internal, id128, sizeof(id.internal));
+  NcclComm comm = nullptr;
+  DQNB_NCCL(nccl, nccl->CommInitRank(&comm, world, id, rank));
+  h->dp_comm = comm; h->dp_rank = rank; h->dp_world = world;
+  DQNB_CUDA(cudaStreamCreateWithPriority(&h->dp_stream, cudaStreamNonBlocking, h->prio_hi));
+  for (auto& e : h->dp_ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  // one eager collective first: NCCL sets up its channels / buffers on the first call, which must not happen
+  // inside a stream capture
+  DQNB_NCCL(nccl, nccl->AllReduce(h->grad, h->grad, (size_t)h->L.total, kNcclFloat32, kNcclSum, h->dp_comm, h->dp_stream));
+  DQNB_CUDA(cudaStreamSynchronize(h->dp_stream));
+  DQNB_CUDA(cudaMemsetAsync(h->grad, 0, sizeof(float) * h->L.total, h->dp_stream));
+  DQNB_CUDA(cudaStreamSynchronize(h->dp_stream));
+  // re-record the update graph(s): backward -> [reduce + all-reduce] x 2 -> optimiser step
+  if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+  DQNB_TRY(build_graph(h, &h->graph));
+  h->tl_graph_n = h->tl_n;
+  if (h->graph_alt) {
+    cudaGraphExecDestroy(h->graph_alt); h->graph_alt = nullptr;
+    h->swap_sets();
+    int rc = build_graph(h, &h->graph_alt);
+    h->swap_sets();
+    DQNB_TRY(rc);
+  }
+  return DQNB_OK;
+}
+
+// The collectives of one data-parallel update alone (same two chunks, same stream), for timing.
+extern "C" int dqnb_dp_allreduce(dqnb_learner* h, uintptr_t stream) {
+  DQNB_REQUIRE(h && h->dp_on(), "not a data-parallel learner (dqnb_dp_init)");
+  const NcclApi* nccl = nccl_api();
+  if (!nccl) return DQNB_ESTATE;
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_NCCL(nccl, nccl->AllReduce(h->grad + h->L.fw1, h->grad + h->L.fw1, (size_t)(h->L.total - h->L.fw1),
+                                  kNcclFloat32, kNcclSum, h->dp_comm, st));
+  DQNB_NCCL(nccl, nccl->AllReduce(h->grad, h->grad, (size_t)h->L.fw1, kNcclFloat32, kNcclSum, h->dp_comm, st));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_dp_info(dqnb_learner* h, int* rank, int* world, int* nccl_version) {
+  DQNB_REQUIRE(h && rank && world && nccl_version, "null argument");
+  *rank = h->dp_rank; *world = h->dp_world; *nccl_version = 0;
+  if (h->dp_on()) {
+    const NcclApi* nccl = nccl_api();
+    if (nccl) nccl->GetVersion(nccl_version);
+  }
   return DQNB_OK;
 }
 

@@ -333,6 +333,14 @@ extern "C" int dqnb_mgsc_read(dqnb_mgsc* h, int which, float* host, int64_t n) {
   return DQNB_OK;
 }
 
+// Test hook: a state array (or debug tap) of the internal batch-of-M (0) / batch-of-1 (1) learner as the
+// last meta_update left it - the parity tests take the device's own ReLU masks and td errors from here.
+extern "C" int dqnb_mgsc_read_learner(dqnb_mgsc* h, int which_learner, int which, float* host, int64_t n) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DQNB_REQUIRE(which_learner == 0 || which_learner == 1, "which_learner must be 0 (meta batch) or 1 (online transition)");
+  return dqnb_learner_read(which_learner == 0 ? h->bat : h->sub, which, host, n, 0);
+}
+
 extern "C" int dqnb_mgsc_write(dqnb_mgsc* h, int which, const float* host, int64_t n) {
   DQNB_REQUIRE(h && host, "null argument");
   DQNB_REQUIRE(which == DQNB_MGSC_ADAM_M || which == DQNB_MGSC_ADAM_V, "MGSC array %d is read-only", which);

@@ -114,6 +114,24 @@ class Learner:
         """optimizer.update + apply_updates on the gradient arena (second half of a deferred update)."""
         _lib.call("dqnb_learner_apply_grads", self._h, self.stream)
 
+    def dp_init(self, unique_id, rank, world):
+        """Joins the NCCL communicator described by rank 0's 128-byte ncclUniqueId; afterwards every update of
+        this (defer_apply) learner all-reduces the gradient arena inside its own CUDA graph and applies it."""
+        uid = np.ascontiguousarray(unique_id, dtype=np.uint8)
+        if uid.size != 128:
+            raise ValueError("ncclUniqueId is 128 bytes, got %d" % uid.size)
+        _lib.call("dqnb_dp_init", self._h, uid.ctypes.data, int(rank), int(world))
+
+    def dp_allreduce(self):
+        _lib.call("dqnb_dp_allreduce", self._h, self.stream)
+
+    def dp_info(self):
+        """(rank, world, 'major.minor.patch' of the NCCL in use)"""
+        r, w, v = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        _lib.call("dqnb_dp_info", self._h, ctypes.byref(r), ctypes.byref(w), ctypes.byref(v))
+        ver = v.value
+        return r.value, w.value, "%d.%d.%d" % (ver // 10000, (ver // 100) % 100, ver % 100)
+
     def loss_post(self):
         """Queues a read-back of the latest update's loss behind it (does not wait)."""
         _lib.call("dqnb_learner_loss_post", self._h, self.stream)
@@ -268,6 +286,12 @@ class MetaLearner:
         n = self.meta_batch_size if which <= MGSC_DL_DP else self.learner.num_params
         out = np.empty(n, dtype=np.float32)
         _lib.call("dqnb_mgsc_read", self._h, which, out.ctypes.data, n)
+        return out
+
+    def read_learner(self, which_learner, which, n):
+        """Test hook: array `which` (n floats) of the internal batch-of-M (0) / batch-of-1 (1) learner."""
+        out = np.empty(n, dtype=np.float32)
+        _lib.call("dqnb_mgsc_read_learner", self._h, which_learner, which, out.ctypes.data, n)
         return out
 
     def get_state(self):

@@ -142,6 +142,24 @@ int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* dev_src, int
 /* optimizer.update + apply_updates (dqn/agent.py:115-116) on whatever DQNB_GRAD holds; the second
  * half of an update for learners created with defer_apply = 1. */
 int dqnb_learner_apply_grads(dqnb_learner* h, uintptr_t stream);
+/* ---- data-parallel learner (north_star: "large-batch data-parallel learner with an NCCL allreduce of the ~1.7M-
+ * parameter gradient over NVLink"; the reference has no multi-device code, this is how its `update`,
+ * dqn/agent.py:109-117, is spread over GPUs).  One process per GPU; every rank creates a learner with
+ * batch_size = its share of the rows, loss_mean_over = the GLOBAL batch and defer_apply = 1, then:
+ *   rank 0: dqnb_dp_unique_id(id) -> the 128 bytes reach the other ranks by any side channel
+ *   all   : dqnb_dp_init(learner, id, rank, world)   (collective: blocks until every rank has called it)
+ * From then on ONE dqnb_learner_update* call per rank is the whole data-parallel update: its CUDA graph runs
+ * forward / TD / backward on the local rows, sums the split-K partials of [fc1.w, end) and all-reduces them
+ * (ncclAllReduce, sum, fp32) on a side stream while the convolution backward still runs, all-reduces the
+ * convolution gradients behind it, and applies the optimiser step.  Every rank must issue the same sequence of
+ * updates.  NCCL is loaded with dlopen (the process's own libnccl.so.2 if one is mapped, e.g. PyTorch's; else
+ * the system one; DQNB_NCCL_LIB overrides). */
+int dqnb_dp_unique_id(uint8_t* id128);
+int dqnb_dp_init(dqnb_learner* h, const uint8_t* id128, int rank, int world);
+/* the two collectives of one update alone on `stream` (timing aid; contents of DQNB_GRAD are summed in place). */
+int dqnb_dp_allreduce(dqnb_learner* h, uintptr_t stream);
+int dqnb_dp_info(dqnb_learner* h, int* rank, int* world, int* nccl_version);
+
 /* row_weighted learners, after an update: out_dev[i] = <v, w_i * d loss_i / d theta> for every row i of
  * that update's batch, v_dev a device vector laid out like the parameters.  Computed as the sum over
  * layers of <saved cotangent of row i, layer-local forward product of v> - four forward GEMMs and
@@ -226,6 +244,9 @@ int dqnb_mgsc_meta_update_host(dqnb_mgsc* h, const uint8_t* s_tm1, const int32_t
                                const uint8_t* on_s_t, float* new_logits, float* meta_loss, uintptr_t stream);
 int dqnb_mgsc_read(dqnb_mgsc* h, int which, float* host, int64_t n);
 int dqnb_mgsc_write(dqnb_mgsc* h, int which, const float* host, int64_t n);
+/* Test hook: dqnb_learner_read on the internal batch-of-M (which_learner 0) or batch-of-1 (1) learner, as the
+ * last meta_update left it (activations / td errors the parity tests condition the oracle on). */
+int dqnb_mgsc_read_learner(dqnb_mgsc* h, int which_learner, int which, float* host, int64_t n);
 /* Adam step count: *get receives it (nullable), *set overwrites it (nullable). */
 int dqnb_mgsc_adam_count(dqnb_mgsc* h, int32_t* get, const int32_t* set);
 

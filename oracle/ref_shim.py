@@ -19,11 +19,24 @@ import types
 
 import numpy as np
 
-REFERENCE_ROOT = os.environ.get("DQNB_REFERENCE_ROOT", "/root/reference")
+# The read-only reference tree in the build container, else the byte-identical copies oracle/build_ref.py
+# staged under the git-ignored oracle/_ref/ (they travel to the GPU box with the snapshot).
+_CANDIDATES = (os.environ.get("DQNB_REFERENCE_ROOT", "/root/reference"),
+               os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref"))
+
+
+def _root():
+    for root in _CANDIDATES:
+        if os.path.isfile(os.path.join(root, "dqn_zoo", "replay.py")):
+            return root
+    return None
+
+
+REFERENCE_ROOT = _root() or _CANDIDATES[0]
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "dqn_zoo", "replay.py"))
+    return _root() is not None
 
 
 def _stub_modules():
@@ -64,12 +77,12 @@ def load(name: str):
     if name in _cache:
         return _cache[name]
     if not available():
-        raise FileNotFoundError("reference tree not present at %s" % REFERENCE_ROOT)
+        raise FileNotFoundError("reference tree not present at %s" % (_CANDIDATES,))
     stubs = _stub_modules()
     saved = {k: sys.modules.get(k) for k in stubs}
     sys.modules.update(stubs)
     try:
-        path = os.path.join(REFERENCE_ROOT, "dqn_zoo", name + ".py")
+        path = os.path.join(_root(), "dqn_zoo", name + ".py")
         spec = importlib.util.spec_from_file_location("_dqnref_" + name, path)
         mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(mod)

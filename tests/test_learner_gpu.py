@@ -9,8 +9,19 @@ from dqn_mgsc_zoo_b200 import synthetic
 from oracle import learner_oracle as net
 from oracle import update_oracle as upd
 
+from tests import cond
+
 pytestmark = pytest.mark.gpu
-TOL = {"fp32": 1e-5, "tf32": 2e-3}
+# north_star: rel 1e-5 (fp32), rel 1e-3 (reduced precision).  rel = max|x - ref| / max|ref| per tensor.
+TOL = {"fp32": 1e-5, "tf32": 1e-3}
+# tf32 bounds that are NOT 1e-3, with their derivation:
+#  * raw (unconditioned) gradients: a forward perturbation of 5e-4 flips the ReLU mask of units whose
+#    pre-activation is within that of zero; each flip changes a gradient entry by O(|dy| * |x|), which at batch 32
+#    measures up to 1.5e-2 of max|g| - a property of the function (discontinuous), bounded here at 5e-2;
+#  * the parameter step g * rsqrt(nu - mu^2 + eps): where nu ~ mu^2 the rsqrt amplifies a relative gradient
+#    error e by up to (1 + g^2/(nu - mu^2 + eps)) ~ 2 at the test's state: 2e-3.
+TF32_RAW_GRAD = 5e-2
+TF32_PARAM_STEP = 2e-3
 
 
 def rel(x, ref):
@@ -22,24 +33,8 @@ def conditioned_grads(L, online, batch, B, A):
     """Oracle backward through the *device's own* forward activations: relu masks, clip and
     argmax decisions are taken from what the learner computed, so the comparison checks the
     backward kernels without the discontinuities a near-zero pre-activation introduces."""
-    s_tm1, a = batch[0], np.asarray(batch[1])
-    dt = np.float64
-    x0 = s_tm1.astype(dt) / 255.0
-    acts = {"conv1": L.read(113).reshape(B, 20, 20, 32).astype(dt), "conv2": L.read(112).reshape(B, 9, 9, 64).astype(dt),
-            "conv3": L.read(111).reshape(B, 7, 7, 64).astype(dt)}
-    cache = {"x0": x0}
-    x = x0
-    for name, k, s, _, _ in net.LAYERS:
-        p = net._patches(x, k, s)
-        cache[name + ".cols"] = p.reshape(p.shape[0] * p.shape[1] * p.shape[2], -1)
-        x = acts[name]
-        cache[name + ".out"] = x
-    cache["h0"] = x.reshape(B, -1)
-    cache["h1"] = L.read(110).reshape(B, 512).astype(dt)
-    td = L.read(lrn.TD).astype(dt)
-    dq = np.zeros((B, A))
-    dq[np.arange(B), a] = -np.clip(td / B, -1.0 / 32, 1.0 / 32)
-    return net.flatten(net.backward({k: v.astype(dt) for k, v in online.items()}, cache, dq))
+    cache = cond.device_cache(L.read, batch[0], B)
+    return cond.grads(online, cache, L.read(lrn.TD).astype(np.float64), batch[1], B)
 
 
 def setup(seed, B, A, shared, double_q, precision="fp32"):
@@ -203,14 +198,75 @@ def test_single_update_tf32_matches_oracle(B, A, shared, double_q):
     ref_g = lrn.unflatten_params(g_ref, A, shared)
     for k in ref_g:
         errs["grad." + k] = rel(got_g[k], ref_g[k])
+        errs["rawgrad." + k] = rel(got_g[k], want["grads"][k])     # no conditioning: bounds a broken backward
     p2, mu2, nu2 = upd.rmsprop_step(net.flatten(online), L.read(lrn.GRAD).astype(np.float64),
                                     mu.astype(np.float64), nu.astype(np.float64))
     errs["mu"], errs["nu"] = rel(L.read(lrn.MU), mu2), rel(L.read(lrn.NU), nu2)
     errs["param_step"] = rel(L.read(lrn.ONLINE).astype(np.float64) - net.flatten(online), p2 - net.flatten(online))
     print("tf32 B%d A%d:" % (B, A), {k: "%.1e" % v for k, v in errs.items()})
     for k, v in errs.items():
-        lim = 1e-5 if k in ("mu", "nu") else (2e-3 if k == "param_step" else tol)
+        lim = 1e-5 if k in ("mu", "nu") else TF32_PARAM_STEP if k == "param_step" else \
+            TF32_RAW_GRAD if k.startswith("rawgrad.") else tol
         assert v < lim, (k, v)
+
+
+def test_chained_updates_teacher_forced_tf32():
+    """The tf32 twin of test_chained_updates_teacher_forced: 60 chained tensor-core updates with a target
+    sync, each checked as a one-step parity test from the state the learner is really in.  Covers what only
+    shows over many optimiser steps: the tf32 weight shadows, the fp16 conv1 filter copy and the fused fc1
+    wgrad+RMSProp epilogue must all follow the fp32 master weights."""
+    B, A, steps = 32, 6, 60
+    rng, online, target, L = setup(2, B, A, True, True, precision="tf32")
+    worst = {}
+    for step in range(steps):
+        online = {k: v.astype(np.float64) for k, v in L.get_params().items()}
+        mu, nu = L.read(lrn.MU).astype(np.float64), L.read(lrn.NU).astype(np.float64)
+        batch = synthetic.random_batch(rng, B, A)
+        want = upd.update(online, target, mu, nu, batch, True)
+        L.update_host(*batch)
+        g_dev = L.read(lrn.GRAD).astype(np.float64)
+        p2, mu2, nu2 = upd.rmsprop_step(net.flatten(online), g_dev, mu, nu)    # optimiser on the device's gradient
+        errs = {"loss": abs(L.loss() - want["loss"]) / max(1.0, abs(want["loss"])),
+                "q_tm1": rel(L.read(lrn.Q_TM1), want["q_tm1"]), "q_t": rel(L.read(lrn.Q_T), want["q_sel_t"]),
+                "q_target_t": rel(L.read(lrn.Q_TARGET_T), want["q_target_t"]),
+                "grad": rel(g_dev, conditioned_grads(L, online, batch, B, A)),
+                "mu": rel(L.read(lrn.MU), mu2), "nu": rel(L.read(lrn.NU), nu2),
+                "param_step": rel(L.read(lrn.ONLINE).astype(np.float64) - net.flatten(online), p2 - net.flatten(online))}
+        for k, v in errs.items():
+            worst[k] = max(worst.get(k, 0.0), v)
+            lim = 1e-5 if k in ("mu", "nu") else TF32_PARAM_STEP if k == "param_step" else TOL["tf32"]
+            assert v < lim, (step, k, v)
+        if step == 24:
+            L.sync_target()
+            assert np.array_equal(L.read(lrn.TARGET), L.read(lrn.ONLINE))
+            target = {k: v.astype(np.float64) for k, v in L.get_params(lrn.TARGET).items()}
+    print("tf32 chain worst:", {k: "%.1e" % v for k, v in worst.items()})
+
+
+def test_chained_updates_free_running_tf32():
+    """100 free-running tf32 updates against the free-running float64 oracle (after 1 and after 100
+    updates).  Mask flips make the trajectories drift apart (see test_chained_updates_free_running), so the
+    bound after 100 steps is on the loss trajectory and a loose one on the parameters."""
+    B, A, steps = 32, 6, 100
+    rng, online, target, L = setup(2, B, A, True, True, precision="tf32")
+    P = L.num_params
+    mu, nu = np.zeros(P), np.zeros(P)
+    for step in range(steps):
+        batch = synthetic.random_batch(rng, B, A)
+        out = upd.update(online, target, mu, nu, batch, True)
+        online, mu, nu = out["params"], out["mu"], out["nu"]
+        L.update_host(*batch)
+        assert abs(L.loss() - out["loss"]) < 2e-2 * max(1.0, abs(out["loss"])), step
+        if step == 0:
+            got = L.get_params()
+            for k in online:
+                assert rel(got[k], online[k]) < TOL["tf32"], (k, "1 step")
+        if step == 49:
+            target = {k: v.copy() for k, v in online.items()}
+            L.sync_target()
+    got = L.get_params()
+    for k in online:
+        assert rel(got[k], online[k]) < 1e-1, k
 
 
 def test_tf32_update_from_replay_deterministic_and_q_values():

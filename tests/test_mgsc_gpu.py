@@ -136,10 +136,48 @@ def _meta_case(A, shared, M, seed):
     return params, target, mu, nu, batch, online_tr, logits
 
 
-# fp32 is the parity mode.  In tf32 mode the per-sample (batch-of-1) gradients are compared RAW with
-# the float64 oracle: a handful of ReLU units whose pre-activation is within tf32 rounding of zero
-# flip, which moves single-sample gradients by ~1e-2 (test_learner_gpu.py conditions on the device's
-# own masks for that reason); the meta-gradient is an inner product of such gradients.
+def conditioned_meta_update(meta, logits, batch, params, target, online_tr, mu, nu, adam_m, adam_v, count):
+    """oracle.update_oracle.meta_update with every backward pass run through the DEVICE's own forward
+    (activations => ReLU masks, td errors) of the batch-of-M and batch-of-1 learners - tests/cond.py.  Same
+    formulas, same order (dqn_mgsc_batched/agent.py:160-220); only the discontinuous decisions are the device's."""
+    from tests import cond
+    A, shared = params["fc2.w"].shape[1], params["fc2.b"].shape == (1,)
+    M = len(batch[1])
+    size = {110: 512, 111: 3136, 112: 5184, 113: 12800}
+    f64 = {k: v.astype(np.float64) for k, v in params.items()}
+    p = upd.softmax(np.asarray(logits, np.float64))
+    cache = cond.device_cache(lambda tap: meta.read_learner(0, tap, M * size[tap]), batch[0], M)
+    td = meta.read_learner(0, lrn.TD, M).astype(np.float64)
+    per = np.stack([cond.grads(f64, cond.row_cache(cache, i), td[i:i + 1], batch[1][i:i + 1], 1) for i in range(M)])
+    G = p @ per
+    theta = net.flatten(f64)
+    theta_exp, mu1, nu1 = upd.rmsprop_step(theta, G, mu, nu)
+    cache1 = cond.device_cache(lambda tap: meta.read_learner(1, tap, size[tap]), online_tr[0][None], 1)
+    td1 = meta.read_learner(1, lrn.TD, 1).astype(np.float64)
+    g2 = cond.grads(net.unflatten(theta_exp, A, shared), cache1, td1, [online_tr[1]], 1)
+    theta_tgt, _, _ = upd.rmsprop_step(theta_exp, g2, mu1, nu1)
+    h = upd.DQN_RMSPROP
+    e = 2.0 * (theta_exp - theta_tgt)
+    sdev = 1.0 / np.sqrt(nu1 - mu1 * mu1 + h.eps)
+    v = e * (-h.lr * sdev * (1.0 - (1.0 - h.decay) * G * (G - mu1) * sdev * sdev))
+    dL_dp = per @ v
+    new_logits, m2, v2, c2 = upd.adam_step(np.asarray(logits, np.float64), p * (dL_dp - np.dot(p, dL_dp)),
+                                           adam_m, adam_v, count)
+    return {"logits": new_logits, "adam_m": m2, "adam_v": v2, "adam_count": c2,
+            "loss": np.sum((theta_exp - theta_tgt) ** 2), "p": p, "G": G, "v": v, "dL_dp": dL_dp,
+            "theta_exp": theta_exp}
+
+
+# fp32 is compared RAW with the float64 oracle at 2e-5.  tf32 is compared (a) conditioned on the device's own
+# forward decisions (conditioned_meta_update) at the bounds below, and (b) raw at 1e-1: a handful of ReLU units
+# whose pre-activation is within tf32 rounding of zero flip, which moves single-sample gradients by ~1e-2, and the
+# meta-gradient is an inner product of such gradients.  Conditioned bounds: G is a p-weighted sum of per-sample
+# gradients (1e-3 class, like the learner's); theta_exp - theta and v go through g * rsqrt(nu - mu^2 + eps), which
+# doubles a relative error where nu ~ mu^2 (2e-3 class, cf. TF32_PARAM_STEP); dL/dp_i = <g_i, v> sums products of
+# two such vectors with cancellation, bounded at 5e-3.
+TF32_META = {"p": 1e-5, "G": 1e-3, "theta_exp": 2e-3, "v": 3e-3, "dL_dp": 5e-3, "loss": 3e-3}
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("tf32", 1e-1)])
 @pytest.mark.parametrize("A,shared,M", [(6, False, 5), (4, True, 9), (6, False, 40)])
 def test_meta_update_matches_oracle(precision, tol, A, shared, M):
@@ -165,6 +203,18 @@ def test_meta_update_matches_oracle(precision, tol, A, shared, M):
         print("meta %s A%d M%d it%d:" % (precision, A, M, it), {k: "%.1e" % v for k, v in errs.items()})
         for k, v in errs.items():
             assert v < tol, (it, k, v)
+        if precision == "tf32":
+            cw = conditioned_meta_update(meta, cur, batch, params, target, online_tr, mu.astype(np.float64),
+                                         nu.astype(np.float64), adam_m, adam_v, count)
+            cerrs = {"p": rel(meta.read(lrn.MGSC_P), cw["p"]), "G": rel(meta.read(lrn.MGSC_G), cw["G"]),
+                     "theta_exp": rel(meta.read(lrn.MGSC_THETA_EXP) - net.flatten(params),
+                                      cw["theta_exp"] - net.flatten(f64(params))),
+                     "v": rel(meta.read(lrn.MGSC_V), cw["v"]), "dL_dp": rel(meta.read(lrn.MGSC_DL_DP), cw["dL_dp"]),
+                     "loss": abs(loss - cw["loss"]) / cw["loss"]}
+            print("meta tf32 conditioned A%d M%d it%d:" % (A, M, it), {k: "%.1e" % v for k, v in cerrs.items()})
+            for k, v in cerrs.items():
+                assert v < TF32_META[k], (it, k, v)
+            assert np.abs(got - cw["logits"]).max() < 5.1e-4      # one Adam step is 2.5e-4 whatever |g| is: a sign flip of a ~0 entry
         # logits are float32 of magnitude ~1 and one Adam step is 2.5e-4: compare the values
         assert np.abs(got - want["logits"]).max() < (2e-7 if precision == "fp32" else 5e-4)
         adam_m, adam_v, count = want["adam_m"], want["adam_v"], want["adam_count"]
