@@ -39,6 +39,7 @@ SIGNATURES = {
     "dqnb_learner_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_update_host": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_update_from_replay": [c_vp, c_vp, c_vp, STREAM],
+    "dqnb_learner_update_from_replay_weighted": [c_vp, c_vp, c_vp, c_vp, STREAM],
     "dqnb_learner_sync_target": [c_vp, STREAM],
     "dqnb_learner_q_values": [c_vp, c_int, c_vp, c_i32, c_vp, STREAM],
     "dqnb_learner_device_ptr": [c_vp, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_i64)],
@@ -69,6 +70,12 @@ SIGNATURES = {
     "dqnb_logits_lse": [c_vp, ctypes.POINTER(c_f32), STREAM],
     "dqnb_logits_read": [c_vp, c_vp, c_i64],
     "dqnb_logits_write": [c_vp, c_vp, c_i64],
+    "dqnb_sumtree_create": [c_i64, c_int, ctypes.POINTER(c_vp)],
+    "dqnb_sumtree_destroy": [c_vp],
+    "dqnb_sumtree_set": [c_vp, c_vp, c_vp, c_i64, STREAM],
+    "dqnb_sumtree_query": [c_vp, c_vp, c_i64, c_int, c_vp, ctypes.POINTER(ctypes.c_double), STREAM],
+    "dqnb_sumtree_read": [c_vp, c_vp, c_i64],
+    "dqnb_sumtree_write": [c_vp, c_vp, c_i64],
     "dqnb_learner_loss_post": [c_vp, STREAM],
     "dqnb_learner_loss_take": [c_vp, ctypes.POINTER(ctypes.c_float)],
     "dqnb_learner_launches_per_update": [c_vp, ctypes.POINTER(c_i64)],

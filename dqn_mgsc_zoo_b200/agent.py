@@ -35,6 +35,7 @@ class Dqn(parts.Agent):
     """Deep Q-Network agent (dqn/agent.py:40)."""
 
     _DOUBLE_Q = False
+    _ROW_WEIGHTED = 0
 
     def __init__(
         self,
@@ -52,8 +53,11 @@ class Dqn(parts.Agent):
         grad_error_bound: float,
         rng_key,
         device: int = 0,
-        precision: str = "fp32",
+        precision: str = "tf32",
     ):
+        """`device`, `precision`: this implementation's two extra keywords.  precision="tf32" (default) runs every
+        conv / dense GEMM on the tcgen05 tensor cores (fp32 storage, tf32 operands, fp32 accumulate; parity class
+        rel 1e-3, the mode bench.py reports); precision="fp32" is the CUDA-core path held to rel 1e-5, 3.5x slower."""
         if not optimizer.centered:
             raise ValueError("the CUDA learner implements optax.rmsprop(centered=True) only "
                              "(dqn/run_atari.py:208-213)")
@@ -69,6 +73,7 @@ class Dqn(parts.Agent):
         self._learn_period = learn_period
         self._target_network_update_period = target_network_update_period
         self._network = network
+        self.precision = precision
 
         # jax.random.split(rng_key) -> (agent key, network init key) in the reference.
         seeds = np.random.SeedSequence(networks.key_to_seed(rng_key)).spawn(2)
@@ -76,7 +81,8 @@ class Dqn(parts.Agent):
         self._learner = lrn.Learner(
             network.num_actions, batch_size, shared_bias=network.shared_bias, double_q=self._DOUBLE_Q,
             learning_rate=optimizer.learning_rate, decay=optimizer.decay, eps=optimizer.eps,
-            grad_error_bound=grad_error_bound, precision=precision, device=device)
+            grad_error_bound=grad_error_bound, precision=precision, device=device,
+            row_weighted=self._ROW_WEIGHTED)
         init = networks.init_params(np.random.default_rng(seeds[1]), network.num_actions, network.shared_bias)
         self._learner.set_params(init, lrn.ONLINE)
         self._learner.sync_target()           # self._target_params = self._online_params
@@ -175,6 +181,82 @@ class DoubleDqn(Dqn):
     the target net values it (rlax.double_q_learning, double_q/agent.py:85-111)."""
 
     _DOUBLE_Q = True
+
+
+class PrioritizedDqn(Dqn):
+    """Prioritized Experience Replay (proportional variant) DQN agent (prioritized/agent.py:40-262).
+
+    Same constructor keywords as the reference; `replay` is a `replay.PrioritizedTransitionReplay`.  Differences
+    from `DoubleDqn` follow the reference line by line: new transitions enter with the largest priority seen so
+    far (:147), `_learn` (:215-236) samples (transitions, ids, importance weights), runs the double-Q update with
+    loss = mean(w * 0.5 td^2) - the weight multiplies the cotangent before rlax.clip_gradient (:85-108;
+    `row_weighted = 2` in the learner) - and writes |td| back as the new priorities.  The td errors come back to
+    the host every step (32 floats), as in the reference (`jax.device_get(priorities)`, :230): the next
+    sample depends on them, so this agent is host-synchronous by construction.
+    """
+
+    _DOUBLE_Q = True
+    _ROW_WEIGHTED = 2
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self._max_seen_priority = 1.0
+
+    def step(self, timestep) -> parts.Action:
+        self._frame_t += 1
+
+        timestep = self._preprocessor(timestep)
+
+        if timestep is None:  # Repeat action.
+            if self._action is None:
+                raise RuntimeError('Cannot repeat if action has never been selected.')
+            action = self._action
+        else:
+            action = self._action = self._act(timestep)
+            for transition in self._transition_accumulator.step(timestep, action):
+                self._replay.add(transition, priority=self._max_seen_priority)
+
+        if self._replay.size < self._min_replay_capacity:
+            return action
+
+        if self._frame_t % self._learn_period == 0:
+            self._learn()
+
+        if self._frame_t % self._target_network_update_period == 0:
+            self._learner.sync_target()
+
+        return action
+
+    def _learn(self) -> None:
+        store = getattr(self._replay, "frame_store", None)
+        if store is not None and hasattr(self._replay, "sample_slots_ids_weights"):
+            slots, indices, weights = self._replay.sample_slots_ids_weights(self._batch_size)
+            self._learner.update_from_replay(store, slots, weights=weights)
+        else:
+            t, indices, weights = self._replay.sample(self._batch_size)
+            self._learner.set_row_weights(weights)
+            self._learner.update_host(t.s_tm1, t.a_tm1, t.r_t, t.discount_t, t.s_t)
+        priorities = np.abs(self._learner.read(lrn.TD))
+        max_priority = priorities.max()
+        self._max_seen_priority = np.max([self._max_seen_priority, max_priority])
+        self._replay.update_priorities(indices, priorities)
+
+    @property
+    def importance_sampling_exponent(self) -> float:
+        return self._replay.importance_sampling_exponent
+
+    @property
+    def max_seen_priority(self) -> float:
+        return self._max_seen_priority
+
+    def get_state(self) -> Mapping[str, Any]:
+        state = dict(super().get_state())
+        state['max_seen_priority'] = self._max_seen_priority
+        return state
+
+    def set_state(self, state: Mapping[str, Any]) -> None:
+        super().set_state(state)
+        self._max_seen_priority = state['max_seen_priority']
 
 
 ScaleByAdamState = collections.namedtuple("ScaleByAdamState", "count mu nu")

@@ -24,6 +24,8 @@ struct HeadArgs {
   const float* reward;
   const float* discount;
   const float* row_weight;  // optional per-row weight on the cotangent (MGSC), may be null
+  int weight_inside;        // 1: the weight is an importance-sampling weight of the loss (prioritized replay): it
+                            // multiplies the cotangent before the clip and the row loss
   float* q[kMaxNets];       // [batch,A] outputs
   float* td;                // [batch]
   float* row_loss;          // [batch] 0.5*td^2
@@ -164,12 +166,14 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
     const int act = g.action[row];
     const float q_taken = q_s[0][act];
     const float td = g.reward[row] + g.discount[row] * q_next - q_taken;
-    float cot = fminf(fmaxf(td * g.inv_mean, -g.grad_bound), g.grad_bound);
-    if (g.row_weight) cot *= g.row_weight[row];
+    const float wrow = g.row_weight ? g.row_weight[row] : 1.0f;
+    const float win = g.weight_inside ? wrow : 1.0f;
+    float cot = fminf(fmaxf(td * g.inv_mean * win, -g.grad_bound), g.grad_bound);
+    if (!g.weight_inside) cot *= wrow;
     const float dq = -cot;
     if (lane == 0) {
       g.td[row] = td;
-      g.row_loss[row] = 0.5f * td * td;
+      g.row_loss[row] = 0.5f * td * td * win;
       g.dq_taken[row] = dq;
       dq_s = dq;
       act_s = act;

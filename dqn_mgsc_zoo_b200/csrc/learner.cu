@@ -147,6 +147,10 @@ struct dqnb_learner {
   cudaEvent_t pinned_free = nullptr;
   bool pinned_busy = false;
   float* pinned_loss = nullptr;
+  float* pinned_w = nullptr;                 // [kWRing][B] row weights on their way to the device (weighted updates)
+  cudaEvent_t w_ev[4] = {};
+  bool w_busy[4] = {};
+  int w_cur = 0;
   // loss read-back without copies: the update writes (seq, loss) into a pinned ring (LossRing)
   unsigned long long* loss_ring = nullptr;   // pinned, device-mapped, kLossRing entries
   unsigned* d_seq = nullptr;                 // device: updates executed so far
@@ -237,6 +241,7 @@ HeadArgs head_args(dqnb_learner* h, int rows, const float* const* params, int ne
     g.h1[z] = h->h1[zz]; g.w2[z] = params[zz] + h->L.fw2; g.b2[z] = params[zz] + h->L.fb2; g.q[z] = h->q[zz];
   }
   g.fc1_part = nullptr; g.fc1_splits = 0; g.tl = nullptr; g.round_tf32 = 0;
+  g.weight_inside = h->cfg.row_weighted == 2;
   for (int z = 0; z < kMaxNets; ++z) {
     int zz = std::min(z, nets - 1);
     g.b1[z] = params[zz] + h->L.fb1; g.h1_out[z] = h->h1[zz];
@@ -787,6 +792,10 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   h->pinned_bytes = 2 * B * Conv1::IN_PER_IMG + 16 * B;
   DQNB_CUDA(cudaMallocHost(&h->pinned, h->pinned_bytes));
   DQNB_CUDA(cudaMallocHost(&h->pinned_loss, 64));
+  if (cfg->row_weighted) {
+    DQNB_CUDA(cudaMallocHost(&h->pinned_w, sizeof(float) * 4 * B));
+    for (auto& e : h->w_ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
   DQNB_CUDA(cudaHostAlloc(&h->loss_ring, sizeof(unsigned long long) * kLossRing, cudaHostAllocMapped));
   memset(h->loss_ring, 0, sizeof(unsigned long long) * kLossRing);
   DQNB_TRY(dmalloc(&h->d_seq, 1));
@@ -794,7 +803,7 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   h->sizing = true;
   DQNB_TRY(enqueue_any(h, nullptr));
   h->ws_cap = h->ws_off; h->cnt_cap = h->cnt_off; h->part_cap = h->part_off;
-  if (cfg->row_weighted) {   // the adjoint-dot GEMMs borrow the same split-K scratch
+  if (cfg->row_weighted == 1) {   // the adjoint-dot GEMMs borrow the same split-K scratch
     const int64_t launches = h->launches_per_update;
     DQNB_TRY(enqueue_adjoint(h, nullptr, nullptr, nullptr));
     h->launches_per_update = launches;
@@ -852,6 +861,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   if (h->pinned_free) cudaEventDestroy(h->pinned_free);
   if (h->pinned) cudaFreeHost(h->pinned);
   if (h->pinned_loss) cudaFreeHost(h->pinned_loss);
+  if (h->pinned_w) cudaFreeHost(h->pinned_w);
+  for (auto& e : h->w_ev) if (e) cudaEventDestroy(e);
   if (h->loss_ring) cudaFreeHost(h->loss_ring);
   cudaFree(h->d_seq);
   delete h;
@@ -905,7 +916,7 @@ int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
 
 extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host, int64_t n, uintptr_t stream) {
   DQNB_REQUIRE(h && host, "null argument");
-  DQNB_REQUIRE(which >= DQNB_ONLINE && which <= DQNB_NU, "state array %d is read-only", which);
+  DQNB_REQUIRE((which >= DQNB_ONLINE && which <= DQNB_NU) || which == DQNB_ROW_WEIGHT, "state array %d is read-only", which);
   DeviceGuard guard(h->device);
   float* p; int64_t len;
   DQNB_TRY(locate(h, which, &p, &len));
@@ -1131,6 +1142,25 @@ extern "C" int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* rep
   h->updates++;
   h->seq_host++;
   return DQNB_OK;
+}
+
+// `_learn` of the prioritized agent (prioritized/agent.py:215-236): as update_from_replay, with this batch's
+// importance-sampling weights (host float32 [batch]) staged into DQNB_ROW_WEIGHT ahead of the step.
+extern "C" int dqnb_learner_update_from_replay_weighted(dqnb_learner* h, dqnb_replay* replay, const int64_t* slots_host,
+                                                        const float* weights_host, uintptr_t stream) {
+  DQNB_REQUIRE(h && weights_host, "null argument");
+  DQNB_REQUIRE(h->row_weight && h->pinned_w, "row weights need a learner created with row_weighted = 1 or 2");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  const int k = h->w_cur;
+  h->w_cur = (k + 1) & 3;
+  if (h->w_busy[k]) DQNB_CUDA(cudaEventSynchronize(h->w_ev[k]));
+  float* pw = h->pinned_w + (size_t)k * h->B;
+  memcpy(pw, weights_host, sizeof(float) * h->B);
+  DQNB_CUDA(cudaMemcpyAsync(h->row_weight, pw, sizeof(float) * h->B, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaEventRecord(h->w_ev[k], st));
+  h->w_busy[k] = true;
+  return dqnb_learner_update_from_replay(h, replay, slots_host, stream);
 }
 
 extern "C" int dqnb_learner_loss_post(dqnb_learner* h, uintptr_t) {

@@ -6,7 +6,7 @@ import numpy as np
 
 from dqn_mgsc_zoo_b200 import _lib
 
-ONLINE, TARGET, MU, NU, GRAD, Q_TM1, Q_TARGET_T, Q_T, TD, LOSS = range(10)
+ONLINE, TARGET, MU, NU, GRAD, Q_TM1, Q_TARGET_T, Q_T, TD, LOSS, ROW_WEIGHT = range(11)
 PRECISIONS = {"fp32": 0, "tf32": 2}
 
 
@@ -52,7 +52,7 @@ class Learner:
         self.device, self.stream = device, stream
         cfg = LearnerConfig(self.num_actions, int(self.shared_bias), int(self.double_q), self.batch_size,
                             int(loss_mean_over), PRECISIONS[precision], learning_rate, decay, eps,
-                            grad_error_bound, int(bool(defer_apply)), int(bool(row_weighted)))
+                            grad_error_bound, int(bool(defer_apply)), int(row_weighted))
         self.defer_apply = bool(defer_apply)
         h = ctypes.c_void_p()
         _lib.call("dqnb_learner_create", ctypes.byref(cfg), device, ctypes.byref(h))
@@ -150,6 +150,11 @@ class Learner:
         self.loss_post()
         return self.loss_take() if self._loss_outstanding > 1 else None
 
+    def set_row_weights(self, weights):
+        """Host write of DQNB_ROW_WEIGHT (synchronous): the weights the next update(s) will use."""
+        w = np.ascontiguousarray(weights, dtype=np.float32)
+        _lib.call("dqnb_learner_write", self._h, ROW_WEIGHT, w.ctypes.data, w.size, self.stream)
+
     def update_host(self, s_tm1, a_tm1, r_t, discount_t, s_t):
         """`update(transitions)` with NumPy inputs, like the reference's jit dispatch."""
         s0 = np.ascontiguousarray(s_tm1, dtype=np.uint8)
@@ -167,11 +172,19 @@ class Learner:
     def update_device(self, s_tm1_ptr, a_ptr, r_ptr, d_ptr, s_t_ptr):
         _lib.call("dqnb_learner_update", self._h, s_tm1_ptr, a_ptr, r_ptr, d_ptr, s_t_ptr, self.stream)
 
-    def update_from_replay(self, frame_store, slots):
+    def update_from_replay(self, frame_store, slots, weights=None):
+        """`weights`: per-row weights of this batch (row_weighted learners; prioritized replay's importance weights)."""
         slots = np.ascontiguousarray(slots, dtype=np.int64)
         if slots.size != self.batch_size:
             raise ValueError("need %d slots, got %d" % (self.batch_size, slots.size))
-        _lib.check(self._update_from_replay(self._h, frame_store.handle, slots.ctypes.data, self.stream))
+        if weights is None:
+            _lib.check(self._update_from_replay(self._h, frame_store.handle, slots.ctypes.data, self.stream))
+            return
+        w = np.ascontiguousarray(weights, dtype=np.float32)
+        if w.shape != (self.batch_size,):
+            raise ValueError("need %d weights, got %s" % (self.batch_size, w.shape))
+        _lib.call("dqnb_learner_update_from_replay_weighted", self._h, frame_store.handle, slots.ctypes.data,
+                  w.ctypes.data, self.stream)
 
     def sync_target(self):
         _lib.call("dqnb_learner_sync_target", self._h, self.stream)

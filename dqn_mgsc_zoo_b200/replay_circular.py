@@ -111,6 +111,22 @@ class ReservoirTransitionReplay(_uniform.ReservoirTransitionReplay):
         return self._random_state.integers(0, self._t)                # replay_circular.py:436
 
 
+class PrioritizedDistribution(_uniform.PrioritizedDistribution):
+    """replay_circular.py:893-1116: the Generator twin (`integers` for the uniform positions)."""
+
+    def _draw_positions(self, size):
+        return self._random_state.integers(self.size, size=size)      # replay_circular.py:1017
+
+
+class PrioritizedTransitionReplay(_uniform.PrioritizedTransitionReplay):
+    """replay_circular.py:1315-1430."""
+    _DISTRIBUTION = PrioritizedDistribution
+
+
+SumTree = _uniform.SumTree
+importance_sampling_weights = _uniform.importance_sampling_weights
+
+
 class _DeviceLogits:
     """float32 logits[capacity] in device memory; absolute indices."""
 

@@ -112,7 +112,10 @@ typedef struct dqnb_learner_config {
                                all-reduce and for the MGSC weighted gradient */
   int32_t row_weighted;     /* 1: every row's clipped cotangent is multiplied by DQNB_ROW_WEIGHT[row] (initially
                                1) - with loss_mean_over = 1 the gradient is sum_i w_i grad(loss_i), the
-                               vmapped weighted_grads of dqn_mgsc_batched/agent.py:171-176 as ONE batched pass */
+                               vmapped weighted_grads of dqn_mgsc_batched/agent.py:171-176 as ONE batched pass.
+                               2: importance-sampling weights of prioritized replay (prioritized/agent.py:85-115):
+                               loss = mean(w_i * 0.5 td_i^2), so the weight multiplies the cotangent BEFORE
+                               rlax.clip_gradient clips it: dq = -clip(w_i td_i / B) */
 } dqnb_learner_config;
 
 /* state arrays addressable by read/write */
@@ -179,6 +182,10 @@ int dqnb_learner_update_host(dqnb_learner* h, const uint8_t* s_tm1_host, const i
  * given replay slots straight into the learner's batch buffers, then the step. */
 int dqnb_learner_update_from_replay(dqnb_learner* h, dqnb_replay* replay, const int64_t* slots_host,
                                     uintptr_t stream);
+/* the same with per-row weights for this batch (host float32 [batch]; learners created with row_weighted != 0):
+ * the importance-sampling weights of `_learn` in prioritized/agent.py:215-236. */
+int dqnb_learner_update_from_replay_weighted(dqnb_learner* h, dqnb_replay* replay, const int64_t* slots_host,
+                                             const float* weights_host, uintptr_t stream);
 /* target_params = online_params (dqn/agent.py:155-156). */
 int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream);
 /* Q-values of n <= batch_size host observations under the online (0) or target (1) params;
@@ -271,6 +278,29 @@ int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream);
 /* whole-array copies for get_state / set_state / `_logits` pokes; n must equal capacity. */
 int dqnb_logits_read(dqnb_logits* h, float* host, int64_t n);
 int dqnb_logits_write(dqnb_logits* h, const float* host, int64_t n);
+
+/* ---------------------------------------------------------------------------------------------
+ * Prioritized replay sum tree in device memory (replay.py:379-559 SumTree; used by PrioritizedDistribution
+ * :562-784).  storage[2 * first_leaf] float64, node i = storage[2i] + storage[2i+1], root at 1, leaves from
+ * first_leaf (a power of two, the reference's `capacity`): the reference's layout and the reference's float64
+ * arithmetic, so nodes and query results are bit-identical.  Which leaf an id owns, sizes and the NumPy random
+ * stream stay with the caller.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct dqnb_sumtree dqnb_sumtree;
+int dqnb_sumtree_create(int64_t first_leaf, int device, dqnb_sumtree** out);
+int dqnb_sumtree_destroy(dqnb_sumtree* h);
+/* SumTree.set (replay.py:402-414): leaves[indices] = values (duplicates: last wins), ancestors re-summed.
+ * Values must be finite and >= 0.  Asynchronous. */
+int dqnb_sumtree_set(dqnb_sumtree* h, const int64_t* indices, const double* values, int64_t n, uintptr_t stream);
+/* SumTree.query (replay.py:424-440): for each target the smallest leaf with target < inclusive cumulative sum.
+ * scale_by_root = 1: the inputs are uniforms in [0,1) and target = uniform * root is formed on the device
+ * (PrioritizedDistribution.sample, replay.py:697-699).  *root receives storage[1] (nullable).  Fails with the
+ * reference's message when a target is outside [0, root).  Synchronous. */
+int dqnb_sumtree_query(dqnb_sumtree* h, const double* targets_or_uniforms, int64_t n, int scale_by_root,
+                       int64_t* indices, double* root, uintptr_t stream);
+/* whole-storage copies (n = 2 * first_leaf): get_state / set_state / resize / set_all. */
+int dqnb_sumtree_read(dqnb_sumtree* h, double* storage_host, int64_t n);
+int dqnb_sumtree_write(dqnb_sumtree* h, const double* storage_host, int64_t n);
 
 /* Test hook (not part of the drop-in surface): C[M,N] = A*B^T through the tcgen05 tile GEMM on
  * fp32 device matrices (operands rounded to bf16); *_mn_major selects [K,M]/[K,N] storage. */

@@ -318,3 +318,119 @@ class PairAccumulator:
                                   timestep.discount, timestep.observation))
         self.prev, self.prev_action = timestep, action
         return out
+
+
+# ---- prioritized replay (replay.py:336-784, 1046-1160), restated in array form -------------------------
+def is_weights(probs, uniform_prob, exponent, normalize):
+    """(uniform_prob / p) ** exponent, optionally scaled so the largest weight is 1 (replay.py:344-376)."""
+    w = (uniform_prob / probs) ** exponent
+    return w / w.max() if normalize else w
+
+
+class PrefixTree:
+    """Complete binary tree of float64 partial sums over `width` leaves (width = next power of two of the
+    capacity): node k = node 2k + node 2k+1, root at 1, leaves from `width` (replay.py:386-396 layout).  The
+    additions happen in tree order, which is what makes query results reproducible bit for bit."""
+
+    def __init__(self, capacity):
+        self.width = 1
+        while self.width < capacity:
+            self.width *= 2
+        self.node = np.zeros(2 * self.width, dtype=np.float64)
+
+    @property
+    def total(self):
+        return self.node[1]
+
+    def assign(self, leaves, values):
+        for leaf, v in zip(leaves, values):          # in order: a later duplicate overrides an earlier one
+            k = self.width + int(leaf)
+            self.node[k] = v
+            k //= 2
+            while k >= 1:
+                self.node[k] = self.node[2 * k] + self.node[2 * k + 1]
+                k //= 2
+
+    def locate(self, target):
+        """Smallest leaf whose inclusive running sum exceeds `target` (replay.py:536-559)."""
+        if not 0.0 <= target < self.total:
+            raise ValueError("Require 0 <= target < total sum.")
+        k = 1
+        while k < self.width:
+            left = self.node[2 * k]
+            if target < left:
+                k = 2 * k
+            else:
+                target -= left
+                k = 2 * k + 1
+        return k - self.width
+
+
+class PrioritizedReplay:
+    """FIFO items + proportional prioritisation (replay.py:562-784 + 1046-1160).  Leaf allocation mirrors the
+    reference: free leaves are a stack initialised 0..capacity-1 and popped from the END, a removed id's leaf is
+    pushed back; the `active` list (uniform part of the mixture) uses swap-with-last removal."""
+
+    def __init__(self, capacity, structure, priority_exponent, importance_sampling_exponent,
+                 uniform_sample_probability, normalize_weights, random_state):
+        self.capacity, self.structure, self.rs = capacity, structure, random_state
+        self.alpha, self.beta_fn = priority_exponent, importance_sampling_exponent
+        self.usp, self.normalize = uniform_sample_probability, normalize_weights
+        self.tree = PrefixTree(capacity)
+        self.free = list(range(capacity))
+        self.active, self.where = [], {}          # active leaves; leaf -> position in `active`
+        self.leaf_of, self.id_of = {}, {}
+        self.items = collections.OrderedDict()
+        self.t = 0
+
+    @property
+    def size(self):
+        return len(self.items)
+
+    def _pow(self, p):
+        p = np.asarray(p)
+        return np.where(p == 0.0, 0.0, p ** self.alpha)
+
+    def add(self, item, priority):
+        if len(self.items) == self.capacity:
+            old, _ = self.items.popitem(last=False)
+            leaf = self.leaf_of.pop(old)
+            del self.id_of[leaf]
+            pos = self.where.pop(leaf)
+            tail = self.active.pop()
+            if tail != leaf:
+                self.active[pos] = tail
+                self.where[tail] = pos
+            self.free.append(leaf)
+            self.tree.assign([leaf], [0.0])
+        leaf = self.free.pop()
+        self.where[leaf] = len(self.active)
+        self.active.append(leaf)
+        self.leaf_of[self.t], self.id_of[leaf] = leaf, self.t
+        self.tree.assign([leaf], self._pow([priority]))
+        self.items[self.t] = item
+        self.t += 1
+
+    def sample_ids(self, n):
+        """-> (ids, importance weights); RandomState consumption as replay.py:681-717."""
+        draw = self.rs.integers if isinstance(self.rs, np.random.Generator) else self.rs.randint   # replay_circular.py:1017
+        uniform_leaves = np.array([self.active[j] for j in draw(self.size, size=n)])
+        total = self.tree.total
+        if total == 0.0:
+            picked = uniform_leaves
+        else:
+            picked = np.array([self.tree.locate(x) for x in self.rs.uniform(size=n) * total])
+        leaves = np.where(self.rs.uniform(size=n) < self.usp, uniform_leaves, picked)
+        u = np.asarray(1.0 / self.size)
+        pri = self.tree.node[self.tree.width + leaves]
+        p = np.full_like(pri, u) if total == 0.0 else pri / total
+        probs = (1.0 - self.usp) * p + self.usp * u
+        ids = np.array([self.id_of[int(l)] for l in leaves], dtype=np.int64)
+        return ids, is_weights(probs, 1.0 / self.size, self.beta_fn(self.t), self.normalize)
+
+    def sample(self, n):
+        ids, w = self.sample_ids(n)
+        return _stack_fields(self.structure, [self.items[int(i)] for i in ids]), ids, w
+
+    def update_priorities(self, ids, priorities):
+        self.tree.assign([self.leaf_of[int(i)] for i in ids], self._pow(np.asarray(priorities)))

@@ -20,12 +20,14 @@ Adam = collections.namedtuple("Adam", "lr b1 b2 eps")
 META_ADAM = Adam(lr=0.00025, b1=0.9, b2=0.999, eps=1e-8)             # optax.adam defaults
 
 
-def td_and_dq(q_tm1, a, r, disc, q_target_t, q_sel_t=None, grad_bound=1.0 / 32, mean_over=None):
+def td_and_dq(q_tm1, a, r, disc, q_target_t, q_sel_t=None, grad_bound=1.0 / 32, mean_over=None, weights=None):
     """td errors, loss and d loss / d q_tm1.
 
     q_learning: y = r + disc*max_a q_target_t;  double: y = r + disc*q_target_t[argmax q_sel_t]
     td = y - q_tm1[a]; loss = mean(0.5 td^2); clip_gradient clips the *cotangent*
     td/B to +-grad_bound (dqn/agent.py:94-106).  mean_over overrides B (MGSC batch-of-1).
+    weights: importance-sampling weights of prioritized replay (prioritized/agent.py:85-115):
+    loss = mean(w * 0.5 td^2), so the cotangent reaching clip_gradient is w*td/B.
     """
     B = q_tm1.shape[0]
     rows = np.arange(B)
@@ -33,10 +35,11 @@ def td_and_dq(q_tm1, a, r, disc, q_target_t, q_sel_t=None, grad_bound=1.0 / 32, 
     y = r + disc * q_target_t[rows, sel]
     td = y - q_tm1[rows, a]
     denom = B if mean_over is None else mean_over
-    cot = np.clip(td / denom, -grad_bound, grad_bound)
+    w = 1.0 if weights is None else np.asarray(weights, dtype=q_tm1.dtype)
+    cot = np.clip(td * w / denom, -grad_bound, grad_bound)
     dq = np.zeros_like(q_tm1)
     dq[rows, a] = -cot
-    loss = np.sum(0.5 * td * td) / denom
+    loss = np.sum(0.5 * td * td * w) / denom
     return td, loss, dq
 
 
@@ -58,7 +61,7 @@ def adam_step(x, g, m, v, count, h=META_ADAM):
     return x + (-h.lr) * (mh / (np.sqrt(vh) + h.eps)), m2, v2, c
 
 
-def loss_and_grads(online, target, batch, double_q=False, grad_bound=1.0 / 32, mean_over=None):
+def loss_and_grads(online, target, batch, double_q=False, grad_bound=1.0 / 32, mean_over=None, weights=None):
     """jax.grad(loss_fn) (dqn/agent.py:112-114).  batch = (s_tm1,a,r,disc,s_t)."""
     s_tm1, a, r, disc, s_t = batch
     dt = online["fc1.w"].dtype
@@ -66,17 +69,17 @@ def loss_and_grads(online, target, batch, double_q=False, grad_bound=1.0 / 32, m
     q_tm1, cache = net.forward(online, s_tm1, keep=True)
     q_tgt = net.forward(target, s_t)
     q_sel = net.forward(online, s_t) if double_q else None
-    td, loss, dq = td_and_dq(q_tm1, np.asarray(a), r, disc, q_tgt, q_sel, grad_bound, mean_over)
+    td, loss, dq = td_and_dq(q_tm1, np.asarray(a), r, disc, q_tgt, q_sel, grad_bound, mean_over, weights)
     grads = net.backward(online, cache, dq)
     return {"q_tm1": q_tm1, "q_target_t": q_tgt, "q_sel_t": q_sel, "td": td, "loss": loss,
             "dq": dq, "grads": grads, "cache": cache}
 
 
-def update(online, target, mu, nu, batch, double_q=False, grad_bound=1.0 / 32, h=DQN_RMSPROP):
+def update(online, target, mu, nu, batch, double_q=False, grad_bound=1.0 / 32, h=DQN_RMSPROP, weights=None):
     """`update` of dqn/agent.py:109-117 on flat opt-state vectors mu, nu."""
     A = online["fc2.w"].shape[1]
     shared = online["fc2.b"].shape == (1,)
-    out = loss_and_grads(online, target, batch, double_q, grad_bound)
+    out = loss_and_grads(online, target, batch, double_q, grad_bound, weights=weights)
     g = net.flatten(out["grads"])
     p2, mu2, nu2 = rmsprop_step(net.flatten(online), g, mu, nu, h)
     out.update(params=net.unflatten(p2, A, shared), mu=mu2, nu=nu2, flat_grad=g)

@@ -20,10 +20,14 @@ from tests import replay_scenarios as sc  # noqa: E402
 
 def reference_factory(kind):
     r, rc = ref_shim.load("replay"), ref_shim.load("replay_circular")
-    cls = {"fifo": r.TransitionReplay, "reservoir": r.ReservoirTransitionReplay,
+    cls = {"per": None, "gen_per": None, "fifo": r.TransitionReplay, "reservoir": r.ReservoirTransitionReplay,
            "gen_fifo": rc.TransitionReplay, "gen_reservoir": rc.ReservoirTransitionReplay,
            "mgsc_fifo": rc.MGSCFiFoTransitionReplay,
            "mgsc_reservoir": rc.MGSCReservoirTransitionReplay}[kind]
+    if kind in ("per", "gen_per"):
+        cls = (r if kind == "per" else rc).PrioritizedTransitionReplay
+        return lambda capacity, structure, alpha, beta, usp, normalize, rng: cls(
+            capacity, structure, alpha, beta, usp, normalize, rng)
     return lambda capacity, structure, rng: cls(capacity, structure, rng)
 
 

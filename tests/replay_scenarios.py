@@ -52,6 +52,32 @@ def pairs_mgsc(make, seed, capacity, n_add, every, batch, meta):
             "meta_logits": np.stack(meta_logits), "next_draw": rng.integers(1 << 30)}
 
 
+def pairs_prioritized(make, seed, capacity, n_add, every, batch, alpha=0.6, usp=0.1, normalize=True,
+                      generator=False, zero_until=0):
+    """Prioritized replay: adds with priorities (the first `zero_until` all zero: the uniform fall-back branch of
+    sample, which consumes one uniform draw less), samples, priority updates from a td-like signal."""
+    rs = np.random.default_rng(seed) if generator else np.random.RandomState(seed)
+    beta = lambda t: min(1.0, 0.4 + 0.6 * t / float(n_add))
+    rep = make(capacity, Pair(None, None), alpha, beta, usp, normalize, rs)
+    ids_log, w_log, a_log = [], [], []
+    max_pri = 1.0
+    for i in range(n_add):
+        rep.add(Pair(i, 2 * i + 1), 0.0 if i < zero_until else max_pri)
+        if i % every == every - 1 and rep.size >= batch:
+            tr, ids, w = rep.sample(batch)
+            assert np.array_equal(tr.b, 2 * tr.a + 1)
+            ids_log.append(np.asarray(ids, dtype=np.int64))
+            w_log.append(np.asarray(w, dtype=np.float64))
+            a_log.append(np.asarray(tr.a, dtype=np.int64))
+            pri = np.abs(np.sin(np.asarray(tr.a) * 0.37 + i).astype(np.float32)) * np.float32(2.0)   # |td| as float32
+            if i % (3 * every) == every - 1:
+                pri[0] = 0.0                       # an exact zero priority: 0 ** alpha stays 0
+            max_pri = float(max(max_pri, pri.max()))
+            rep.update_priorities(ids, pri)
+    return {"ids": np.stack(ids_log), "weights": np.stack(w_log), "a": np.stack(a_log),
+            "next_draw": rs.integers(1 << 30) if generator else rs.randint(1 << 30)}
+
+
 def frames_uniform(make, accumulator, structure, seed, capacity, n_add, sample_every, batch, num_actions=6,
                    hw=(84, 84), short_every=5, max_len=23):
     """Atari-shaped transitions (short episodes => many early-episode stacks)."""
@@ -78,6 +104,9 @@ SCENARIOS = {
     "reservoir_pairs": dict(kind="reservoir", fn="pairs_uniform", args=dict(seed=11, capacity=50, n_add=600, sample_every=4, batch=8)),
     "gen_fifo_pairs": dict(kind="gen_fifo", fn="pairs_uniform", args=dict(seed=19, capacity=23, n_add=150, sample_every=3, batch=8, generator=True)),
     "gen_reservoir_pairs": dict(kind="gen_reservoir", fn="pairs_uniform", args=dict(seed=23, capacity=40, n_add=500, sample_every=4, batch=8, generator=True)),
+    "per_pairs": dict(kind="per", fn="pairs_prioritized", args=dict(seed=29, capacity=37, n_add=260, every=3, batch=8)),
+    "per_pairs_zero_start": dict(kind="per", fn="pairs_prioritized", args=dict(seed=31, capacity=16, n_add=90, every=2, batch=6, usp=0.25, normalize=False, zero_until=30)),
+    "gen_per_pairs": dict(kind="gen_per", fn="pairs_prioritized", args=dict(seed=37, capacity=50, n_add=300, every=4, batch=8, generator=True)),
     "mgsc_fifo_pairs": dict(kind="mgsc_fifo", fn="pairs_mgsc", args=dict(seed=3, capacity=24, n_add=90, every=2, batch=6, meta=5)),
     "mgsc_reservoir_pairs": dict(kind="mgsc_reservoir", fn="pairs_mgsc", args=dict(seed=5, capacity=24, n_add=140, every=2, batch=6, meta=5)),
     "fifo_frames": dict(kind="fifo", fn="frames_uniform", args=dict(seed=13, capacity=64, n_add=260, sample_every=10, batch=16)),

@@ -25,15 +25,16 @@ def rel(x, ref):
     return np.abs(x - ref).max() / (np.abs(ref).max() + 1e-30)
 
 
-def make_agent(cls, replay, seed=7, eps=1.0, reservoir=False):
-    spec = networks.double_dqn_atari_network(A) if cls is agent_lib.DoubleDqn else networks.dqn_atari_network(A)
+def make_agent(cls, replay, seed=7, eps=1.0, reservoir=False, precision="fp32"):
+    # fp32 (SIMT) is the parity mode of these lock-step tests; the agents themselves default to tf32
+    spec = networks.double_dqn_atari_network(A) if cls._DOUBLE_Q else networks.dqn_atari_network(A)
     return cls(
         preprocessor=synthetic.StackingPreprocessor(num_action_repeats=2),
         sample_network_input=np.zeros((84, 84, 4), np.uint8), network=spec,
         optimizer=networks.rmsprop(learning_rate=0.00025, decay=0.95, eps=0.01 / 32 ** 2, centered=True),
         transition_accumulator=rp.TransitionAccumulator(), replay=replay, batch_size=B,
         exploration_epsilon=lambda t: eps, min_replay_capacity_fraction=0.25, learn_period=4,
-        target_network_update_period=24, grad_error_bound=1.0 / 32, rng_key=seed)
+        target_network_update_period=24, grad_error_bound=1.0 / 32, rng_key=seed, precision=precision)
 
 
 class OracleAgent:
@@ -187,3 +188,116 @@ def test_epsilon_greedy_actor_uses_online_params():
     st = actor.get_state()
     assert set(st) == {'rng_key', 'network_params'}
     actor.set_state(pickle.loads(pickle.dumps(st)))
+
+
+
+def test_agents_default_to_the_tensor_core_learner():
+    replay = rp.TransitionReplay(CAP, rp.Transition(None, None, None, None, None), np.random.RandomState(0))
+    ag = agent_lib.DoubleDqn(
+        preprocessor=synthetic.StackingPreprocessor(num_action_repeats=2),
+        sample_network_input=np.zeros((84, 84, 4), np.uint8), network=networks.double_dqn_atari_network(A),
+        optimizer=networks.rmsprop(learning_rate=0.00025, decay=0.95, eps=0.01 / 32 ** 2, centered=True),
+        transition_accumulator=rp.TransitionAccumulator(), replay=replay, batch_size=B,
+        exploration_epsilon=lambda t: 1.0, min_replay_capacity_fraction=0.25, learn_period=4,
+        target_network_update_period=24, grad_error_bound=1.0 / 32, rng_key=3)
+    assert ag.precision == "tf32"
+
+
+class OraclePrioritizedAgent:
+    """prioritized/agent.py:133-236 on the CPU oracle; actions come from the CUDA agent's tape."""
+
+    def __init__(self, online, replay):
+        self.pre = synthetic.StackingPreprocessor(num_action_repeats=2)
+        self.acc = ro.PairAccumulator()
+        self.replay = replay
+        self.online = {k: v.astype(np.float64) for k, v in online.items()}
+        self.target = {k: v.copy() for k, v in self.online.items()}
+        P = net.flatten(self.online).size
+        self.mu, self.nu = np.zeros(P), np.zeros(P)
+        self.frame_t, self.max_seen, self.log = -1, 1.0, []
+
+    def reset(self):
+        self.acc.reset()
+        self.pre.reset()
+
+    def step(self, timestep, action, device_td=None):
+        self.frame_t += 1
+        ts = self.pre(timestep)
+        if ts is not None:
+            for tr in self.acc.step(ts, action):
+                self.replay.add(tr, self.max_seen)
+        if self.replay.size < 0.25 * CAP:
+            return
+        if self.frame_t % 4 == 0:
+            batch, ids, w = self.replay.sample(B)
+            out = upd.update(self.online, self.target, self.mu, self.nu,
+                             (batch.s_tm1, batch.a_tm1, batch.r_t, batch.discount_t, batch.s_t), True, weights=w)
+            self.log.append((ids, w, out["td"], out["loss"], net.flatten(self.online), self.mu, self.nu, batch))
+            self.online, self.mu, self.nu = out["params"], out["mu"], out["nu"]
+            # priorities: |td| as float32, exactly what the device hands back (teacher-forced with the device's
+            # own td so that both replays keep sampling the same ids; the td values themselves are compared)
+            pri = np.abs(np.asarray(device_td if device_td is not None else out["td"], dtype=np.float32))
+            self.max_seen = np.max([self.max_seen, pri.max()])
+            self.replay.update_priorities(ids, pri)
+        if self.frame_t % 24 == 0:
+            self.target = {k: v.copy() for k, v in self.online.items()}
+
+
+def test_prioritized_agent_tracks_oracle():
+    """PrioritizedDqn in lock-step with an oracle agent over the oracle prioritized replay: sampled ids
+    bit-exact, importance weights rel 1e-6 (float64 on both sides: exact in practice), td errors and the
+    importance-weighted loss at the fp32 tolerance; priorities are teacher-forced with the device's |td|."""
+    beta = lambda t: min(1.0, 0.4 + 0.002 * t)
+    structure = rp.Transition(None, None, None, None, None)
+    ours = rp.PrioritizedTransitionReplay(CAP, structure, 0.6, beta, 0.1, True, np.random.RandomState(5))
+    ref = ro.PrioritizedReplay(CAP, ro.Transition(None, None, None, None, None), 0.6, beta, 0.1, True,
+                               np.random.RandomState(5))
+    ag = make_agent(agent_lib.PrioritizedDqn, ours)
+    ora = OraclePrioritizedAgent(ag.learner.get_params(lrn.ONLINE), ref)
+    seen = []
+    real_sample, real_update = ours.sample_slots_ids_weights, ours.update_priorities
+
+    def spy_sample(n):
+        slots, ids, w = real_sample(n)
+        state = (ag.learner.read(lrn.ONLINE), ag.learner.read(lrn.MU), ag.learner.read(lrn.NU),
+                 ag.learner.read(lrn.TARGET))
+        seen.append({"ids": np.array(ids), "w": np.array(w), "batch": ours.frame_store.gather_host(slots),
+                     "state": state})
+        return slots, ids, w
+
+    def spy_update(ids, pri):
+        seen[-1]["pri"] = np.array(pri)
+        seen[-1]["loss"] = ag.learner.loss()
+        real_update(ids, pri)
+    ours.sample_slots_ids_weights, ours.update_priorities = spy_sample, spy_update
+
+    env = synthetic.SyntheticEnvironment(np.random.default_rng(13), A, min_len=3, max_len=40)
+    frames = 0
+    for _, timestep, _, action in parts.run_loop(ag, env, max_steps_per_episode=30, yield_before_reset=True):
+        if timestep is None:
+            ora.reset()
+            continue
+        n_before = len(ora.log)
+        # the device learnt during ag.step (already done inside run_loop); hand its |td| to the oracle replay
+        ora.step(timestep, ag._action, device_td=seen[len(ora.log)]["pri"] if len(seen) > len(ora.log) else None)
+        assert len(ora.log) - n_before in (0, 1)
+        frames += 1
+        if frames >= 240:
+            break
+    assert len(seen) == len(ora.log) >= 25
+    for k, (got, want) in enumerate(zip(seen, ora.log)):
+        ids, w, td, loss, theta, mu, nu, batch = want
+        assert np.array_equal(got["ids"], ids), k
+        assert rel(got["w"], w) < 1e-6, k
+        assert np.array_equal(got["batch"][0], batch.s_tm1) and np.array_equal(got["batch"][4], batch.s_t)
+        # one-step parity from the device's own state (teacher-forced like test_chained_updates_teacher_forced)
+        on = net.unflatten(got["state"][0].astype(np.float64), A, True)
+        tgt = net.unflatten(got["state"][3].astype(np.float64), A, True)
+        out = upd.update(on, tgt, got["state"][1].astype(np.float64), got["state"][2].astype(np.float64),
+                         (batch.s_tm1, batch.a_tm1, batch.r_t, batch.discount_t, batch.s_t), True, weights=got["w"])
+        assert rel(got["pri"], np.abs(out["td"])) < 1e-5, k
+        assert abs(got["loss"] - out["loss"]) < 1e-5 * max(1.0, abs(out["loss"])), k
+    assert ag.max_seen_priority >= 1.0 and 0.4 <= ag.importance_sampling_exponent <= 1.0
+    assert ours.check_valid() == (True, '')
+    state = ag.get_state()
+    assert state['max_seen_priority'] == ag.max_seen_priority and 'distribution' in state['replay']

@@ -16,11 +16,13 @@ pytestmark = pytest.mark.gpu
 TOL = {"fp32": 1e-5, "tf32": 1e-3}
 # tf32 bounds that are NOT 1e-3, with their derivation:
 #  * raw (unconditioned) gradients: a forward perturbation of 5e-4 flips the ReLU mask of units whose
-#    pre-activation is within that of zero; each flip changes a gradient entry by O(|dy| * |x|), which at batch 32
-#    measures up to 1.5e-2 of max|g| - a property of the function (discontinuous), bounded here at 5e-2;
+#    pre-activation is within that of zero.  With three forced-clip rows carrying most of the cotangent, ONE flipped
+#    unit of such a row moves a bias gradient by ~1/sqrt(active units) of max|g|: measured 2e-2 - 5.3e-2 at batch 32.
+#    A property of the (discontinuous) function, bounded at 1e-1 - and pinned to its cause by mask_flip_report():
+#    fewer than 0.2 % of the units differ and every one of them has an oracle pre-activation within 2e-3 of zero;
 #  * the parameter step g * rsqrt(nu - mu^2 + eps): where nu ~ mu^2 the rsqrt amplifies a relative gradient
 #    error e by up to (1 + g^2/(nu - mu^2 + eps)) ~ 2 at the test's state: 2e-3.
-TF32_RAW_GRAD = 5e-2
+TF32_RAW_GRAD = 1e-1
 TF32_PARAM_STEP = 2e-3
 
 
@@ -35,6 +37,19 @@ def conditioned_grads(L, online, batch, B, A):
     backward kernels without the discontinuities a near-zero pre-activation introduces."""
     cache = cond.device_cache(L.read, batch[0], B)
     return cond.grads(online, cache, L.read(lrn.TD).astype(np.float64), batch[1], B)
+
+
+def mask_flip_report(L, online, cache, B):
+    """Per conv layer: (fraction of units whose ReLU mask differs between the device and the float64 oracle,
+    largest |oracle pre-activation| among them relative to max|activation|)."""
+    out = {}
+    for name, tap in (("conv1", 113), ("conv2", 112), ("conv3", 111)):
+        w, b = online[name + ".w"].astype(np.float64), online[name + ".b"].astype(np.float64)
+        pre = (cache[name + ".cols"] @ w.reshape(-1, w.shape[3]) + b).ravel()
+        dev = L.read(tap).astype(np.float64)
+        flipped = (dev > 0) != (pre > 0)
+        out[name] = (float(flipped.mean()), float(np.abs(pre[flipped]).max() / np.abs(pre).max()) if flipped.any() else 0.0)
+    return out
 
 
 def setup(seed, B, A, shared, double_q, precision="fp32"):
@@ -204,6 +219,10 @@ def test_single_update_tf32_matches_oracle(B, A, shared, double_q):
     errs["mu"], errs["nu"] = rel(L.read(lrn.MU), mu2), rel(L.read(lrn.NU), nu2)
     errs["param_step"] = rel(L.read(lrn.ONLINE).astype(np.float64) - net.flatten(online), p2 - net.flatten(online))
     print("tf32 B%d A%d:" % (B, A), {k: "%.1e" % v for k, v in errs.items()})
+    flips = mask_flip_report(L, online, want["cache"], B)
+    print("tf32 B%d A%d mask flips (fraction, |pre|/max):" % (B, A), flips)
+    for name, (frac, mag) in flips.items():
+        assert frac < 2e-3 and mag < 2e-3, (name, frac, mag)
     for k, v in errs.items():
         lim = 1e-5 if k in ("mu", "nu") else TF32_PARAM_STEP if k == "param_step" else \
             TF32_RAW_GRAD if k.startswith("rawgrad.") else tol

@@ -54,6 +54,23 @@ def test_grads_match_torch_autograd(double_q, shared, A):
         assert np.abs(out["grads"][k] - g[k]).max() / scale < 1e-10, k
 
 
+def test_importance_weighted_grads_match_torch_autograd():
+    # prioritized/agent.py:85-115: loss = mean(w * l2_loss(clip_gradient(td))): the weight reaches the clip
+    rng, online, target, batch = _setup(6, 8, 6, True)
+    s_tm1, a, r, d, s_t = batch
+    r = np.array([40.0, -40.0, 0.3, 0.0, 1.0, -1.0, 0.5, 0.2], dtype=np.float32)      # rows 0/1 clip for w ~ 1
+    w = np.array([1.0, 0.2, 0.7, 1.0, 0.05, 0.9, 0.4, 1.0])
+    out = upd.loss_and_grads(online, target, (s_tm1, a, r, d, s_t), True, weights=w)
+    loss, q, g = torch_ref.grads(online, target, (s_tm1, a, r, d, s_t), True, weights=w)
+    assert abs(out["loss"] - loss) < 1e-12 * max(1, abs(loss))
+    for k in g:
+        scale = np.abs(g[k]).max() + 1e-30
+        assert np.abs(out["grads"][k] - g[k]).max() / scale < 1e-10, k
+    dq = out["dq"][np.arange(8), a]
+    assert dq[0] == -1.0 / 32                      # w = 1: |w td / B| > 1/32 -> clipped
+    assert abs(dq[1]) < 1.0 / 32 or dq[1] == 1.0 / 32
+
+
 def test_clip_is_on_cotangent():
     # with big rewards |td|/B exceeds 1/32 -> dq saturates at +-1/32 (dqn/agent.py:101-103)
     _, online, target, batch = _setup(3, 4, 6, False)

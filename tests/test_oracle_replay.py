@@ -18,6 +18,9 @@ GOLDEN = np.load(os.path.join(os.path.dirname(__file__), "golden", "replay_golde
 
 
 def oracle_factory(kind):
+    if kind in ("per", "gen_per"):
+        return lambda capacity, structure, alpha, beta, usp, normalize, rng: ro.PrioritizedReplay(
+            capacity, structure, alpha, beta, usp, normalize, rng)
     cls = {"fifo": ro.FifoReplay, "reservoir": ro.ReservoirReplay,
            "gen_fifo": ro.FifoReplay, "gen_reservoir": ro.ReservoirReplay,
            "mgsc_fifo": ro.MgscFifoReplay, "mgsc_reservoir": ro.MgscReservoirReplay}[kind]
@@ -57,6 +60,40 @@ def test_oracle_matches_reference_fresh_seed(kind):
     b = sc.pairs_uniform(oracle_factory(kind), **args)
     for k in a:
         assert np.array_equal(a[k], b[k]), k
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not on this machine")
+@pytest.mark.parametrize("kind", ["per", "gen_per"])
+def test_oracle_prioritized_matches_reference_fresh_seed(kind):
+    from tests.golden.make_golden import reference_factory
+    args = dict(seed=4321, capacity=21, n_add=200, every=2, batch=5, alpha=0.7, usp=0.05, generator=kind == "gen_per",
+                zero_until=8)
+    a = sc.pairs_prioritized(reference_factory(kind), **args)
+    b = sc.pairs_prioritized(oracle_factory(kind), **args)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+
+
+def test_prefix_tree_known_answers():
+    # SumTreeTest (replay_test.py:820-1045): queries return the smallest index whose running sum exceeds the target
+    t = ro.PrefixTree(5)
+    t.assign(range(5), [1.0, 0.0, 2.5, 0.5, 4.0])
+    assert t.total == 8.0 and t.width == 8
+    assert [t.locate(x) for x in (0.0, 0.99, 1.0, 3.49, 3.5, 3.99, 4.0, 7.99)] == [0, 0, 2, 2, 3, 3, 4, 4]
+    with pytest.raises(ValueError):
+        t.locate(8.0)
+    with pytest.raises(ValueError):
+        t.locate(-0.1)
+    t.assign([2, 2], [0.0, 1.0])            # duplicate leaves: the later value stays
+    assert t.node[t.width + 2] == 1.0 and t.total == 6.5
+
+
+def test_importance_weights_known_answers():
+    # replay.py:344-376: weights (u/p)^beta; normalised so that the largest is 1
+    p = np.array([0.1, 0.2, 0.4])
+    assert np.allclose(ro.is_weights(p, 0.2, 1.0, False), [2.0, 1.0, 0.5])
+    assert np.allclose(ro.is_weights(p, 0.2, 0.5, True), np.sqrt([2.0, 1.0, 0.5]) / np.sqrt(2.0))
+    assert np.allclose(ro.is_weights(p, 0.2, 0.0, False), 1.0)
 
 
 @pytest.mark.skipif(not ref_shim.available(), reason="reference tree not on this machine")

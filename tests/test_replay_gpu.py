@@ -116,3 +116,104 @@ def test_commit_order_large_then_small_batches_same_slots():
             a, b = o.sample(8), p.sample(8)
             for x, y, name in zip(a, b, a._fields):
                 assert np.array_equal(x, y), (rounds, n, name)
+
+
+# ---------------------------------------------------------------- prioritized replay (N3)
+PER = [n for n, s in sc.SCENARIOS.items() if s["kind"] in ("per", "gen_per")]
+
+
+def per_factory(kind):
+    from dqn_mgsc_zoo_b200 import replay_circular as rc
+    cls = (rp if kind == "per" else rc).PrioritizedTransitionReplay
+    return lambda capacity, structure, alpha, beta, usp, normalize, rng: cls(
+        capacity, structure, alpha, beta, usp, normalize, rng)
+
+
+@pytest.mark.parametrize("name", PER)
+def test_prioritized_replay_matches_reference_golden(name):
+    """Device sum tree: sampled ids bit-exact, importance weights bit-exact (float64 on the host from bit-exact
+    probabilities), the caller's next random draw identical - against fixtures made by the unmodified reference
+    PrioritizedTransitionReplay (replay.py:1046-1160 / replay_circular.py:1315-1430)."""
+    spec = sc.SCENARIOS[name]
+    got = sc.pairs_prioritized(per_factory(spec["kind"]), **spec["args"])
+    check_against_golden(name, got)
+
+
+def test_sum_tree_matches_oracle_tree_and_reference_api():
+    """SumTreeTest (replay_test.py:820-1045): set / get / query / root / resize / set_all / state, node for node
+    against the oracle tree (same float64 additions in tree order => identical bits)."""
+    rng = np.random.default_rng(3)
+    tree = rp.SumTree()
+    assert tree.size == 0 and np.isnan(tree.root())
+    tree.resize(37)
+    assert tree.size == 37 and tree.capacity == 64 and tree.root() == 0.0
+    o = ro.PrefixTree(37)
+    for _ in range(40):
+        idx = rng.integers(0, 37, size=int(rng.integers(1, 9)))
+        val = np.where(rng.random(idx.size) < 0.2, 0.0, rng.random(idx.size) * 3.0)
+        tree.set(idx, val)
+        o.assign(idx, val)
+        assert tree.root() == o.total
+    st = tree.get_state()
+    assert st['first_leaf'] == 64 and np.array_equal(st['storage'], o.node)
+    targets = rng.random(200) * o.total
+    assert tree.query(targets) == [o.locate(t) for t in targets]
+    assert np.array_equal(tree.get(np.arange(37)), o.node[64:64 + 37])
+    assert tree.check_valid() == (True, '')
+    with pytest.raises(ValueError, match='Require 0 <= target'):
+        tree.query([o.total])
+    with pytest.raises(ValueError, match='finite and positive'):
+        tree.set([0], [-1.0])
+    with pytest.raises(IndexError):
+        tree.get([37])
+    # resize: grow within capacity, grow beyond it (values kept), shrink (tail zeroed)
+    tree.resize(50)
+    assert tree.size == 50 and tree.capacity == 64 and tree.root() == o.total
+    tree.resize(100)
+    assert tree.capacity == 128 and np.array_equal(tree.values[:37], o.node[64:64 + 37]) and tree.check_valid()[0]
+    tree.resize(10)
+    assert tree.size == 10 and tree.check_valid() == (True, '') and not tree.get_state()['storage'][tree.capacity + 10:].any()
+    tree.set_all(np.arange(1, 6, dtype=np.float64))
+    assert tree.size == 5 and tree.root() == 15.0 and tree.query([0.5, 1.0, 14.9]) == [0, 1, 4]
+    other = rp.SumTree()
+    other.set_state(tree.get_state())
+    assert other.root() == 15.0 and other.check_valid() == (True, '')
+
+
+def test_prioritized_replay_frames_match_oracle():
+    """Atari-shaped items at capacity 300 (FIFO wrap, non power-of-two), 84x84: batches bit-exact, ids exact,
+    weights exact, same RandomState consumption, state round trip."""
+    cap, n_add, batch = 300, 1200, 32
+    beta = lambda t: min(1.0, 0.4 + t * 5e-4)
+    o = ro.PrioritizedReplay(cap, ro.Transition(None, None, None, None, None), 0.6, beta, 1e-3, True,
+                             np.random.RandomState(8))
+    p = rp.PrioritizedTransitionReplay(cap, rp.Transition(None, None, None, None, None), 0.6, beta, 1e-3, True,
+                                       np.random.RandomState(8))
+    so = synthetic.transition_stream(np.random.default_rng(9), 6, ro.PairAccumulator(), short_every=7, max_len=40)
+    sp = synthetic.transition_stream(np.random.default_rng(9), 6, rp.TransitionAccumulator(), short_every=7, max_len=40)
+    rng = np.random.default_rng(1)
+    max_pri, checks = 1.0, 0
+    for i in range(n_add):
+        o.add(next(so), max_pri)
+        p.add(next(sp), max_pri)
+        if i % 23 == 22 and o.size >= batch:
+            (a, ia, wa), (b, ib, wb) = o.sample(batch), p.sample(batch)
+            assert np.array_equal(ia, ib) and np.array_equal(wa, wb), i
+            for x, y, f in zip(a, b, a._fields):
+                assert np.array_equal(x, y), (i, f)
+            pri = np.abs(rng.normal(size=batch)).astype(np.float32)
+            max_pri = float(max(max_pri, pri.max()))
+            o.update_priorities(ia, pri)
+            p.update_priorities(ib, pri)
+            checks += 1
+    assert checks >= 40 and p.size == cap and p.check_valid() == (True, '')
+    assert p._random_state.randint(1 << 30) == o.rs.randint(1 << 30)
+    q = rp.PrioritizedTransitionReplay(cap, rp.Transition(None, None, None, None, None), 0.6, beta, 1e-3, True,
+                                       np.random.RandomState(8))
+    q.set_state(p.get_state())
+    p._random_state.seed(4)
+    q._random_state.seed(4)
+    (a, ia, wa), (b, ib, wb) = p.sample(16), q.sample(16)
+    assert np.array_equal(ia, ib) and np.array_equal(wa, wb)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)

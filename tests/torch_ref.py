@@ -39,7 +39,7 @@ def forward(p, s_u8):
     return h1 @ p["fc2.w"] + p["fc2.b"]
 
 
-def loss_fn(online, target, batch, double_q=False, grad_bound=1.0 / 32):
+def loss_fn(online, target, batch, double_q=False, grad_bound=1.0 / 32, weights=None):
     s_tm1, a, r, disc, s_t = batch
     dt = online["fc1.w"].dtype
     a = torch.as_tensor(np.asarray(a), dtype=torch.long)
@@ -52,13 +52,16 @@ def loss_fn(online, target, batch, double_q=False, grad_bound=1.0 / 32):
         y = r + disc * q_tgt.gather(1, sel[:, None])[:, 0]
     td = y - q_tm1.gather(1, a[:, None])[:, 0]
     td = ClipGradient.apply(td, -grad_bound, grad_bound)
-    return (0.5 * td * td).mean(), q_tm1
+    losses = 0.5 * td * td
+    if weights is not None:     # prioritized/agent.py:103-108: jnp.mean(losses * weights)
+        losses = losses * torch.as_tensor(np.asarray(weights), dtype=dt)
+    return losses.mean(), q_tm1
 
 
-def grads(online_np, target_np, batch, double_q=False, grad_bound=1.0 / 32, dtype=torch.float64):
+def grads(online_np, target_np, batch, double_q=False, grad_bound=1.0 / 32, dtype=torch.float64, weights=None):
     online = to_torch(online_np, dtype, requires_grad=True)
     target = to_torch(target_np, dtype)
-    loss, q = loss_fn(online, target, batch, double_q, grad_bound)
+    loss, q = loss_fn(online, target, batch, double_q, grad_bound, weights)
     g = torch.autograd.grad(loss, list(online.values()))
     return float(loss), q.detach().numpy(), {k: gi.numpy() for k, gi in zip(online, g)}
 
