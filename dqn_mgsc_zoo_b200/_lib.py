@@ -31,6 +31,9 @@ SIGNATURES = {
     "dqnb_replay_gather_host": [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, STREAM],
     "dqnb_replay_set_gather_splits": [c_vp, c_int],
     "dqnb_replay_stats": [c_vp, ctypes.POINTER(c_i64)],
+    "dqnb_replay_export_size": [c_vp, ctypes.POINTER(c_i64)],
+    "dqnb_replay_export": [c_vp, c_vp, c_i64, STREAM],
+    "dqnb_replay_import": [c_vp, c_vp, c_i64, STREAM],
     "dqnb_learner_create": [c_vp, c_int, ctypes.POINTER(c_vp)],
     "dqnb_learner_destroy": [c_vp],
     "dqnb_learner_num_params": [c_vp, ctypes.POINTER(c_i64)],

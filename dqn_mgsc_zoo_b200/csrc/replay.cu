@@ -517,6 +517,117 @@ extern "C" int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]) {
   return DQNB_OK;
 }
 
+// ------------------------------------------------------------------------- checkpoint (N2)
+// One self-describing blob: header (int64 fields) + host bookkeeping + slot tables + the plane pool, the device
+// parts copied at PCIe rate in one pass each - what get_state / set_state of the replay classes carry instead
+// of one gathered 56 KB item per slot (replay.py:222-235, replay_circular.py:132-146,643-660).
+namespace {
+constexpr int64_t kBlobMagic = 0x44514E4252504C59LL;   // "DQNBRPLY"
+enum BlobField { F_MAGIC, F_VERSION, F_CAPACITY, F_H, F_W, F_S, F_STRIDE, F_POOL, F_NFREE, F_HAVE_LAST,
+                 F_OFF_SLOT_IDS, F_OFF_ACTIONS, F_OFF_REWARDS, F_OFF_DISCOUNTS, F_OFF_REFCOUNT, F_OFF_FREE,
+                 F_OFF_LAST_IDS, F_OFF_LAST_ST, F_OFF_PLANES, F_TOTAL, F_COUNTERS /* 4 */, F_FIELDS = F_COUNTERS + 4 };
+inline int64_t align64(int64_t x) { return (x + 63) / 64 * 64; }
+
+void blob_layout(const dqnb_replay* h, int64_t n_free, int64_t f[F_FIELDS]) {
+  memset(f, 0, sizeof(int64_t) * F_FIELDS);
+  f[F_MAGIC] = kBlobMagic; f[F_VERSION] = 1; f[F_CAPACITY] = h->capacity; f[F_H] = h->H; f[F_W] = h->W; f[F_S] = h->S;
+  f[F_STRIDE] = h->plane_stride; f[F_POOL] = h->pool_planes; f[F_NFREE] = n_free; f[F_HAVE_LAST] = h->have_last ? 1 : 0;
+  int64_t o = align64((int64_t)sizeof(int64_t) * F_FIELDS);
+  f[F_OFF_SLOT_IDS] = o; o = align64(o + 4 * 8 * h->capacity);
+  f[F_OFF_ACTIONS] = o; o = align64(o + 4 * h->capacity);
+  f[F_OFF_REWARDS] = o; o = align64(o + 4 * h->capacity);
+  f[F_OFF_DISCOUNTS] = o; o = align64(o + 4 * h->capacity);
+  f[F_OFF_REFCOUNT] = o; o = align64(o + 4 * h->pool_planes);
+  f[F_OFF_FREE] = o; o = align64(o + 4 * n_free);
+  f[F_OFF_LAST_IDS] = o; o = align64(o + 4 * 8);
+  f[F_OFF_LAST_ST] = o; o = align64(o + (int64_t)h->plane_bytes * h->S);
+  f[F_OFF_PLANES] = o; o += h->pool_planes * h->plane_stride;
+  f[F_TOTAL] = o;
+  f[F_COUNTERS] = h->n_puts; f[F_COUNTERS + 1] = h->n_uploaded; f[F_COUNTERS + 2] = h->n_chained; f[F_COUNTERS + 3] = h->n_growths;
+}
+}  // namespace
+
+extern "C" int dqnb_replay_export_size(dqnb_replay* h, int64_t* bytes) {
+  DQNB_REQUIRE(h && bytes, "null argument");
+  int64_t f[F_FIELDS];
+  blob_layout(h, (int64_t)(h->free_list.size() + h->pending_free.size()), f);
+  *bytes = f[F_TOTAL];
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_export(dqnb_replay* h, void* host, int64_t bytes, uintptr_t stream) {
+  DQNB_REQUIRE(h && host, "null argument");
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_TRY(flush(h, st));                       // staged puts reach the device first
+  DQNB_CUDA(cudaDeviceSynchronize());            // commits / gathers may be on the side or a caller's gather stream
+  // every released plane is reusable once the device is idle
+  h->free_list.insert(h->free_list.end(), h->pending_free.begin(), h->pending_free.end());
+  h->pending_free.clear();
+  int64_t f[F_FIELDS];
+  blob_layout(h, (int64_t)h->free_list.size(), f);
+  DQNB_REQUIRE(bytes == f[F_TOTAL], "export buffer is %lld bytes, the snapshot needs %lld", (long long)bytes,
+               (long long)f[F_TOTAL]);
+  uint8_t* out = static_cast<uint8_t*>(host);
+  memcpy(out, f, sizeof(f));
+  memcpy(out + f[F_OFF_SLOT_IDS], h->slot_ids.data(), 4 * 8 * (size_t)h->capacity);
+  DQNB_CUDA(cudaMemcpy(out + f[F_OFF_ACTIONS], h->d_actions, 4 * (size_t)h->capacity, cudaMemcpyDeviceToHost));
+  DQNB_CUDA(cudaMemcpy(out + f[F_OFF_REWARDS], h->d_rewards, 4 * (size_t)h->capacity, cudaMemcpyDeviceToHost));
+  DQNB_CUDA(cudaMemcpy(out + f[F_OFF_DISCOUNTS], h->d_discounts, 4 * (size_t)h->capacity, cudaMemcpyDeviceToHost));
+  memcpy(out + f[F_OFF_REFCOUNT], h->refcount.data(), 4 * (size_t)h->pool_planes);
+  memcpy(out + f[F_OFF_FREE], h->free_list.data(), 4 * h->free_list.size());
+  memcpy(out + f[F_OFF_LAST_IDS], h->last_ids, sizeof(h->last_ids));
+  memcpy(out + f[F_OFF_LAST_ST], h->last_st.data(), h->last_st.size());
+  DQNB_CUDA(cudaMemcpy(out + f[F_OFF_PLANES], h->d_planes, (size_t)(h->pool_planes * h->plane_stride), cudaMemcpyDeviceToHost));
+  return DQNB_OK;
+}
+
+extern "C" int dqnb_replay_import(dqnb_replay* h, const void* host, int64_t bytes, uintptr_t stream) {
+  DQNB_REQUIRE(h && host && bytes >= (int64_t)sizeof(int64_t) * F_FIELDS, "null or truncated snapshot");
+  const uint8_t* in = static_cast<const uint8_t*>(host);
+  int64_t f[F_FIELDS];
+  memcpy(f, in, sizeof(f));
+  DQNB_REQUIRE(f[F_MAGIC] == kBlobMagic && f[F_VERSION] == 1, "not a replay snapshot (magic/version)");
+  DQNB_REQUIRE(f[F_TOTAL] == bytes, "snapshot is %lld bytes, header says %lld", (long long)bytes, (long long)f[F_TOTAL]);
+  DQNB_REQUIRE(f[F_CAPACITY] == h->capacity && f[F_H] == h->H && f[F_W] == h->W && f[F_S] == h->S &&
+                   f[F_STRIDE] == h->plane_stride,
+               "snapshot geometry (capacity %lld, %lldx%lldx%lld) does not match this store (capacity %lld, %dx%dx%d)",
+               (long long)f[F_CAPACITY], (long long)f[F_H], (long long)f[F_W], (long long)f[F_S], (long long)h->capacity,
+               h->H, h->W, h->S);
+  DeviceGuard guard(h->device);
+  cudaStream_t st = as_stream(stream);
+  DQNB_CUDA(cudaDeviceSynchronize());
+  // drop whatever was staged or in flight: the snapshot replaces everything
+  for (Stage& s : h->stage) { s.n_planes = s.n_records = 0; s.in_flight = false; }
+  std::fill(h->slot_staged.begin(), h->slot_staged.end(), 0);
+  if (f[F_POOL] != h->pool_planes) {
+    uint8_t* np = nullptr;
+    cudaError_t e = cudaMalloc(&np, (size_t)(f[F_POOL] * h->plane_stride));
+    if (e != cudaSuccess) { set_error("plane pool of %lld planes: %s", (long long)f[F_POOL], cudaGetErrorString(e)); return DQNB_ENOMEM; }
+    cudaFree(h->d_planes);
+    h->d_planes = np;
+    h->pool_planes = f[F_POOL];
+  }
+  h->refcount.assign(reinterpret_cast<const int32_t*>(in + f[F_OFF_REFCOUNT]),
+                     reinterpret_cast<const int32_t*>(in + f[F_OFF_REFCOUNT]) + h->pool_planes);
+  h->free_list.assign(reinterpret_cast<const int32_t*>(in + f[F_OFF_FREE]),
+                      reinterpret_cast<const int32_t*>(in + f[F_OFF_FREE]) + f[F_NFREE]);
+  h->pending_free.clear();
+  memcpy(h->slot_ids.data(), in + f[F_OFF_SLOT_IDS], 4 * 8 * (size_t)h->capacity);
+  memcpy(h->last_ids, in + f[F_OFF_LAST_IDS], sizeof(h->last_ids));
+  memcpy(h->last_st.data(), in + f[F_OFF_LAST_ST], h->last_st.size());
+  h->have_last = f[F_HAVE_LAST] != 0;
+  h->n_puts = f[F_COUNTERS]; h->n_uploaded = f[F_COUNTERS + 1]; h->n_chained = f[F_COUNTERS + 2]; h->n_growths = f[F_COUNTERS + 3];
+  DQNB_CUDA(cudaMemcpy(h->d_slot_ids, in + f[F_OFF_SLOT_IDS], 4 * 8 * (size_t)h->capacity, cudaMemcpyHostToDevice));
+  DQNB_CUDA(cudaMemcpy(h->d_actions, in + f[F_OFF_ACTIONS], 4 * (size_t)h->capacity, cudaMemcpyHostToDevice));
+  DQNB_CUDA(cudaMemcpy(h->d_rewards, in + f[F_OFF_REWARDS], 4 * (size_t)h->capacity, cudaMemcpyHostToDevice));
+  DQNB_CUDA(cudaMemcpy(h->d_discounts, in + f[F_OFF_DISCOUNTS], 4 * (size_t)h->capacity, cudaMemcpyHostToDevice));
+  DQNB_CUDA(cudaMemcpy(h->d_planes, in + f[F_OFF_PLANES], (size_t)(h->pool_planes * h->plane_stride), cudaMemcpyHostToDevice));
+  h->have_gather = h->have_commit = false;
+  (void)st;
+  return DQNB_OK;
+}
+
 // ---- internal hooks (learner_internal.cuh)
 namespace dqnb {
 int replay_gather_into(dqnb_replay* h, const int64_t* slots_host, int64_t n, uint8_t* s_tm1, uint8_t* s_t,

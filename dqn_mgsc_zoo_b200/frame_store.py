@@ -77,6 +77,25 @@ class FrameStore:
         _lib.call("dqnb_replay_gather_dev", self._h, slots_dev_ptr, int(n), s_tm1_ptr, s_t_ptr, a_ptr, r_ptr,
                   d_ptr, self.stream if stream is None else stream)
 
+    def export_blob(self):
+        """The whole store as one uint8 array (dqnb_replay_export: tables + plane pool, one D2H pass)."""
+        n = ctypes.c_int64()
+        _lib.call("dqnb_replay_export_size", self._h, ctypes.byref(n))
+        blob = np.empty(n.value, dtype=np.uint8)
+        # the size depends on the free list, which a flush inside export may grow: retry once with the new size
+        try:
+            _lib.call("dqnb_replay_export", self._h, blob.ctypes.data, blob.size, self.stream)
+        except _lib.DqnbError:
+            _lib.call("dqnb_replay_export_size", self._h, ctypes.byref(n))
+            blob = np.empty(n.value, dtype=np.uint8)
+            _lib.call("dqnb_replay_export", self._h, blob.ctypes.data, blob.size, self.stream)
+        return blob
+
+    def import_blob(self, blob):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        _lib.call("dqnb_replay_import", self._h, blob.ctypes.data, blob.size, self.stream)
+        self._last = (None, 0)
+
     def set_gather_splits(self, splits):
         _lib.call("dqnb_replay_set_gather_splits", self._h, int(splits))
 

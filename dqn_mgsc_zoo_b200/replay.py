@@ -19,6 +19,7 @@ Items of any other shape (the reference tests use `Pair(a, b)` of Python ints) a
 the learner hot path; they are kept in a host list exactly like the reference keeps them.
 """
 import collections
+import collections.abc
 import typing
 from typing import Any, Optional
 
@@ -52,6 +53,72 @@ def _scalar_dtype(value, kind):
     if kind == 'f':
         return dt if dt.kind == 'f' else np.dtype(np.float64)
     return dt if dt.kind in 'iu' and isinstance(value, np.generic) else np.dtype(np.int64)
+
+
+class FrameSnapshot:
+    """Host copy of a whole HBM frame store (one `dqnb_replay_export` blob) + the exact host scalars, from which
+    single items are materialised on demand.  Picklable as is (NumPy arrays): a 1 M-transition replay is ~8 GB
+    of deduplicated planes instead of 1 M gathered 56 KB items."""
+
+    FIELDS = ("magic", "version", "capacity", "H", "W", "S", "stride", "pool", "nfree", "have_last", "off_slot_ids",
+              "off_actions", "off_rewards", "off_discounts", "off_refcount", "off_free", "off_last_ids",
+              "off_last_st", "off_planes", "total")
+
+    def __init__(self, blob, scalars, structure_type):
+        self.blob, self.scalars, self.structure_type = blob, scalars, structure_type
+
+    def _header(self):
+        h = np.frombuffer(self.blob, dtype=np.int64, count=len(self.FIELDS))
+        return dict(zip(self.FIELDS, (int(x) for x in h)))
+
+    def item(self, slot):
+        """The item stored in `slot`, rebuilt from the snapshot's planes (plane id -1 = the all-zero plane)."""
+        f = self._header()
+        ids = np.frombuffer(self.blob, dtype=np.int32, count=8, offset=f["off_slot_ids"] + 32 * int(slot))
+        H, W, S = f["H"], f["W"], f["S"]
+
+        def stack(plane_ids):
+            out = np.zeros((H, W, S), dtype=np.uint8)
+            for c, p in enumerate(plane_ids):
+                if p >= 0:
+                    out[:, :, c] = np.frombuffer(self.blob, dtype=np.uint8, count=H * W,
+                                                 offset=f["off_planes"] + int(p) * f["stride"]).reshape(H, W)
+            return out
+        a, r, d = (arr[int(slot)].item() for arr in self.scalars)
+        return self.structure_type(stack(ids[:S]), a, r, d, stack(ids[S:2 * S]))
+
+
+class SnapshotPairs(collections.abc.Sequence):
+    """`[(id, item), ...]` of the reference's get_state()['storage'] (replay.py:224), materialised lazily."""
+
+    def __init__(self, snapshot, ids, slots):
+        self.snapshot, self.ids, self.slots = snapshot, list(ids), list(slots)
+
+    def __len__(self):
+        return len(self.ids)
+
+    def __getitem__(self, k):
+        if isinstance(k, slice):
+            return [self[i] for i in range(*k.indices(len(self)))]
+        return self.ids[k], self.snapshot.item(self.slots[k])
+
+
+class SnapshotSlots(collections.abc.Sequence):
+    """Slot-indexed item list (`CircularBuffer._list`, replay_circular.py:132-140; reservoir storage list):
+    entry = item or None for slots that hold nothing."""
+
+    def __init__(self, snapshot, capacity, live):
+        self.snapshot, self.capacity, self.live = snapshot, capacity, live     # live: bool array per slot
+
+    def __len__(self):
+        return self.capacity
+
+    def __getitem__(self, k):
+        if isinstance(k, slice):
+            return [self[i] for i in range(*k.indices(len(self)))]
+        if k < 0:
+            k += self.capacity
+        return self.snapshot.item(k) if self.live[k] else None
 
 
 class ItemStorage:
@@ -91,6 +158,22 @@ class ItemStorage:
             a, r, d = (arr[slot].item() for arr in self.scalars)
             return type(self.structure)(s0[0], a, r, d, s1[0])
         return self.decoder(self.host_items[slot])
+
+    def snapshot(self):
+        """FrameSnapshot of the device store (None when the items live on the host)."""
+        if self.frames is None:
+            return None
+        return FrameSnapshot(self.frames.export_blob(), [a.copy() for a in self.scalars], type(self.structure))
+
+    def restore(self, snapshot):
+        """Inverse of snapshot(): one H2D pass instead of one put per item."""
+        f = snapshot._header()
+        if self.frames is None:
+            self.frames = FrameStore(self.capacity, f["H"], f["W"], f["S"], self.device, self.stream,
+                                     self.initial_planes)
+            self.host_items = None
+        self.frames.import_blob(snapshot.blob)
+        self.scalars = [a.copy() for a in snapshot.scalars]
 
     def stack(self, slots):
         """The np.stack-per-field batch the reference's sample() returns."""
@@ -222,20 +305,27 @@ class _UniformReplayBase:
         return self._storage.frames
 
     def get_state(self):
-        # Same shape as the reference (replay.py:222-229).  Frame items are read back from
-        # HBM (one gather per item): fine for tests/small buffers, ~56 KB per item at scale.
-        return {
-            'storage': [(i, self._storage.get(slot)) for i, slot in self._live.items()],
-            't': self._t,
-            'distribution': self._distribution.get_state(),
-        }
+        """Same shape as the reference (replay.py:222-229): 'storage' is a sequence of (id, item).  For frame
+        items it is a lazy view over ONE exported snapshot of the HBM store (dqnb_replay_export: tables + plane
+        pool at PCIe rate); items are materialised only if somebody indexes it.  Pickles compactly."""
+        snap = self._storage.snapshot()
+        if snap is None:
+            storage = [(i, self._storage.get(slot)) for i, slot in self._live.items()]
+        else:
+            storage = SnapshotPairs(snap, self._live.keys(), self._live.values())
+        return {'storage': storage, 't': self._t, 'distribution': self._distribution.get_state()}
 
     def set_state(self, state) -> None:
+        storage = state['storage']
         self._live = collections.OrderedDict()
-        for i, item in state['storage']:
-            slot = self._slot_for_id(i)
-            self._storage.put(slot, item)
-            self._live[i] = slot
+        if isinstance(storage, SnapshotPairs):          # our own checkpoint: one import, no per-item puts
+            self._storage.restore(storage.snapshot)
+            self._live.update(zip(storage.ids, storage.slots))
+        else:                                           # a reference-shaped list of (id, item)
+            for i, item in storage:
+                slot = self._slot_for_id(i)
+                self._storage.put(slot, item)
+                self._live[i] = slot
         self._t = state['t']
         self._distribution.set_state(state['distribution'])
 
@@ -846,18 +936,11 @@ class PrioritizedTransitionReplay:
     def frame_store(self) -> Optional[FrameStore]:
         return self._storage.frames
 
-    def get_state(self):
-        return {'storage': [(i, self._storage.get(slot)) for i, slot in self._live.items()], 't': self._t,
-                'distribution': self._distribution.get_state()}
+    get_state = _UniformReplayBase.get_state
+    set_state = _UniformReplayBase.set_state
 
-    def set_state(self, state) -> None:
-        self._live = collections.OrderedDict()
-        for i, item in state['storage']:
-            slot = i % self._capacity
-            self._storage.put(slot, item)
-            self._live[i] = slot
-        self._t = state['t']
-        self._distribution.set_state(state['distribution'])
+    def _slot_for_id(self, item_id):
+        return item_id % self._capacity
 
     def check_valid(self):
         if self._t < len(self._live):

@@ -459,8 +459,14 @@ class MGSCFiFoTransitionReplay(_MgscReplayBase):
 
     def get_state(self):
         # CircularBuffer.get_state shape (replay_circular.py:132-140): the full slot list and heads.
-        live = {(self._left_head + k) % self._capacity for k in range(self._count)}
-        items = [self._storage.get(slot) if slot in live else None for slot in range(self._capacity)]
+        # 'list' is the slot-indexed item list; for frame items a lazy view over one exported snapshot of the HBM store.
+        live = np.zeros(self._capacity, dtype=bool)
+        live[(self._left_head + np.arange(self._count)) % self._capacity] = True
+        snap = self._storage.snapshot()
+        if snap is None:
+            items = [self._storage.get(slot) if live[slot] else None for slot in range(self._capacity)]
+        else:
+            items = _uniform.SnapshotSlots(snap, self._capacity, live)
         return {'storage': {'list': items, 'capacity': self._capacity, 'size': self._count,
                             'left_head': self._left_head, 'right_head': self._right_head},
                 't': self._t, 'distribution': self._distribution.get_state()}
@@ -470,9 +476,12 @@ class MGSCFiFoTransitionReplay(_MgscReplayBase):
         if st['capacity'] != self._capacity:
             raise ValueError("snapshot capacity %d != replay capacity %d" % (st['capacity'], self._capacity))
         self._left_head, self._right_head, self._count = st['left_head'], st['right_head'], st['size']
-        for k in range(self._count):
-            slot = (self._left_head + k) % self._capacity
-            self._storage.put(slot, st['list'][slot])
+        if isinstance(st['list'], _uniform.SnapshotSlots):
+            self._storage.restore(st['list'].snapshot)
+        else:
+            for k in range(self._count):
+                slot = (self._left_head + k) % self._capacity
+                self._storage.put(slot, st['list'][slot])
         self._t = state['t']
         self._distribution.set_state(state['distribution'])
 
@@ -513,14 +522,22 @@ class MGSCReservoirTransitionReplay(_MgscReplayBase):
         return self._distribution.size
 
     def get_state(self):
-        return {'storage': [self._storage.get(k) if k < self.size else None for k in range(self._capacity)],
+        snap = self._storage.snapshot()
+        if snap is None:
+            items = [self._storage.get(k) if k < self.size else None for k in range(self._capacity)]
+        else:
+            items = _uniform.SnapshotSlots(snap, self._capacity, np.arange(self._capacity) < self.size)
+        return {'storage': items,
                 't': self._t, 'distribution': self._distribution.get_state(),
                 'random_state': self._random_state, 'capacity': self._capacity}
 
     def set_state(self, state) -> None:
-        for k, item in enumerate(state['storage']):
-            if item is not None:
-                self._storage.put(k, item)
+        if isinstance(state['storage'], _uniform.SnapshotSlots):
+            self._storage.restore(state['storage'].snapshot)
+        else:
+            for k, item in enumerate(state['storage']):
+                if item is not None:
+                    self._storage.put(k, item)
         self._t = state['t']
         self._distribution.set_state(state['distribution'])
         self._random_state = state['random_state']

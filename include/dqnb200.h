@@ -82,6 +82,18 @@ int dqnb_replay_set_gather_splits(dqnb_replay* h, int splits);
  * [4] chained puts (s_tm1 matched the previous s_t), [5] pool growths, [6] bytes of HBM held */
 int dqnb_replay_stats(dqnb_replay* h, int64_t out[8]);
 
+/* Checkpoint of the whole store (get_state / set_state of the replay classes: replay.py:222-235,
+ * replay_circular.py:132-146,643-660; the reference pickles one snappy-compressed item per slot): ONE blob -
+ * header, host bookkeeping (plane ref-counts, free list, the chaining state), slot tables and the plane pool,
+ * the device parts copied at PCIe rate.  Layout: int64 header fields [magic "DQNBRPLY", version, capacity, H, W,
+ * S, plane_stride, pool_planes, n_free, have_last, byte offsets of {slot_ids int32[capacity][8], actions
+ * int32[capacity], rewards f32, discounts f32, refcount int32[pool], free int32[n_free], last_ids int32[8],
+ * last_st u8[H*W*S], planes u8[pool][plane_stride]}, total bytes, 4 counters].  import requires a store of the
+ * same capacity and frame shape and replaces its contents.  Both synchronous. */
+int dqnb_replay_export_size(dqnb_replay* h, int64_t* bytes);
+int dqnb_replay_export(dqnb_replay* h, void* host, int64_t bytes, uintptr_t stream);
+int dqnb_replay_import(dqnb_replay* h, const void* host, int64_t bytes, uintptr_t stream);
+
 /* ------------------------------------------------------------------ learner
  * Stands in for the jitted `update` closure of Dqn / DoubleDqn (dqn/agent.py:85-119,
  * double_q/agent.py:85-121): Nature-CNN forward (networks.py:181-221,338-363) of the online

@@ -217,3 +217,57 @@ def test_prioritized_replay_frames_match_oracle():
     assert np.array_equal(ia, ib) and np.array_equal(wa, wb)
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
+
+
+# ---------------------------------------------------------------- checkpoint (N2)
+def _same_samples(p, q, seed, n=24, mgsc=False):
+    for rep in (p, q):
+        rs = rep._distribution._rng_state if mgsc else rep._random_state
+        if mgsc:
+            rs.bit_generator.state = np.random.default_rng(seed).bit_generator.state
+        else:
+            rs.seed(seed)
+    a, b = p.sample(n), q.sample(n)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+@pytest.mark.parametrize("kind", ["fifo", "reservoir", "mgsc_fifo", "mgsc_reservoir"])
+def test_snapshot_state_round_trip_resumes_identically(kind):
+    """get_state() exports the HBM store as one blob behind a lazy reference-shaped view; after a pickle round
+    trip set_state() imports it in one pass.  The restored replay samples identically, keeps accepting adds with
+    the same dedup/chaining state (ref-counts, free list, last stack) and still matches the live one afterwards."""
+    import pickle
+    from dqn_mgsc_zoo_b200 import replay_circular as rc
+    cap = 200
+    structure = rp.Transition(None, None, None, None, None)
+    mgsc = kind.startswith("mgsc")
+    cls = {"fifo": rp.TransitionReplay, "reservoir": rp.ReservoirTransitionReplay,
+           "mgsc_fifo": rc.MGSCFiFoTransitionReplay, "mgsc_reservoir": rc.MGSCReservoirTransitionReplay}[kind]
+    mk = lambda seed: cls(cap, structure, np.random.default_rng(seed) if mgsc else np.random.RandomState(seed))
+    p = mk(1)
+    stream = synthetic.transition_stream(np.random.default_rng(5), 6, rp.TransitionAccumulator(), short_every=5, max_len=30)
+    items = [next(stream) for _ in range(700)]
+    for it in items[:450]:
+        p.add(it)
+    state = pickle.loads(pickle.dumps(p.get_state(), protocol=4))
+    q = mk(2)
+    q.set_state(state)
+    assert q.size == p.size
+    if kind in ("fifo", "reservoir"):
+        # the lazy view is reference-shaped: (id, item) pairs that materialise to the stored bytes
+        i0, item0 = state['storage'][3]
+        want = next(p.get([i0]))
+        assert all(np.array_equal(x, y) for x, y in zip(item0, want))
+    if not mgsc:
+        q._random_state.set_state(p._random_state.get_state())     # reservoir decisions must continue identically
+    else:
+        q_rng = q._distribution._rng_state if kind == "mgsc_fifo" else q._random_state
+        p_rng = p._distribution._rng_state if kind == "mgsc_fifo" else p._random_state
+        q_rng.bit_generator.state = p_rng.bit_generator.state
+    _same_samples(p, q, 11, mgsc=mgsc)
+    for it in items[450:]:
+        p.add(it)
+        q.add(it)
+    _same_samples(p, q, 12, mgsc=mgsc)
+    assert p.frame_store.stats()["planes_in_use"] == q.frame_store.stats()["planes_in_use"]
