@@ -361,19 +361,32 @@ __device__ __forceinline__ void rmsprop4(float4& pv, float4& mv, float4& nv, con
 // butterfly adds the 8 lane sums (every lane performs the same commutative additions, so the
 // result is reproducible).  Elements [skip_lo, skip_hi) are updated elsewhere (fc1's fused
 // weight-gradient epilogue) and are not visited.  The rest: one thread per float4, g read as is.
-// fp16, transposed copy of the conv1 filters (arena offset 0, [K][N] -> h16[n][k]); see H16ConvFwdDoubleQ
+// fp16, transposed (K-major) copies of the convolution filters for the fp16-operand forward GEMMs: the arena
+// holds a layer's filters as [K][N] fp32 (HWIO), the GEMM wants h16[n][k].  Up to three layers (arena offset,
+// K, N, destination); whoever writes the weights keeps the copies current.  See H16ConvFwd / H16ConvFwdDoubleQ.
 struct H16Shadow {
-  __half* dst;      // null = off
-  int K, N;
+  static constexpr int kLayers = 3;
+  __half* dst[kLayers];     // null = off
+  int64_t off[kLayers];
+  int K[kLayers], N[kLayers];
   __device__ __forceinline__ void put4(int64_t i, const float4& v) const {
-    if (dst == nullptr || i >= (int64_t)K * N) return;
-    const int k = (int)i / N, n = (int)i - k * N;
-    dst[(size_t)n * K + k] = __float2half_rn(v.x);
-    dst[(size_t)(n + 1) * K + k] = __float2half_rn(v.y);
-    dst[(size_t)(n + 2) * K + k] = __float2half_rn(v.z);
-    dst[(size_t)(n + 3) * K + k] = __float2half_rn(v.w);
+#pragma unroll
+    for (int l = 0; l < kLayers; ++l) {
+      if (dst[l] == nullptr || i < off[l] || i >= off[l] + (int64_t)K[l] * N[l]) continue;
+      const int e = (int)(i - off[l]), k = e / N[l], n = e - k * N[l];
+      __half* d = dst[l] + (size_t)n * K[l] + k;
+      d[0] = __float2half_rn(v.x);
+      d[(size_t)K[l]] = __float2half_rn(v.y);
+      d[(size_t)2 * K[l]] = __float2half_rn(v.z);
+      d[(size_t)3 * K[l]] = __float2half_rn(v.w);
+    }
   }
 };
+inline H16Shadow h16_none() {
+  H16Shadow s;
+  for (int l = 0; l < H16Shadow::kLayers; ++l) { s.dst[l] = nullptr; s.off[l] = 0; s.K[l] = 0; s.N[l] = 0; }
+  return s;
+}
 template <bool APPLY>
 __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
                                       float* __restrict__ nu, float* __restrict__ g, int64_t n, GradRegions regs, int64_t split_end,

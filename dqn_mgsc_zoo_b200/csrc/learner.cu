@@ -58,7 +58,22 @@ struct dqnb_learner {
   float *online = nullptr, *target = nullptr, *mu = nullptr, *nu = nullptr, *grad = nullptr;
   float *online_r = nullptr, *target_r = nullptr;   // TF32 mode: weights rounded to tf32 (GEMM operands)
   __half* conv1_h16 = nullptr;   // TF32 mode, small batches: fp16 K-major conv1 filters [online 32 | target 32][256]
-  H16Shadow h16_online() const { return H16Shadow{conv1_h16, Conv1::KCOL, Conv1::COUT}; }
+  // TF32 mode, small batches: fp16 K-major conv2 / conv3 filters, [online: conv2 64x512 | conv3 64x576][target: same],
+  // and fp16 copies of the conv1 / conv2 outputs of every net (A operands of the fp16 conv2 / conv3 forward)
+  __half* conv23_h16 = nullptr;
+  __half *a1h[kMaxNets] = {}, *a2h[kMaxNets] = {};
+  static constexpr size_t kC2H = (size_t)Conv2::COUT * Conv2::KCOL, kC3H = (size_t)Conv3::COUT * Conv3::KCOL;
+  __half* c2h(int target) const { return conv23_h16 + (target ? kC2H + kC3H : 0); }
+  __half* c3h(int target) const { return c2h(target) + kC2H; }
+  H16Shadow h16_online() const {
+    H16Shadow s = h16_none();
+    if (conv1_h16) { s.dst[0] = conv1_h16; s.off[0] = L.w1; s.K[0] = Conv1::KCOL; s.N[0] = Conv1::COUT; }
+    if (conv23_h16) {
+      s.dst[1] = c2h(0); s.off[1] = L.w2; s.K[1] = Conv2::KCOL; s.N[1] = Conv2::COUT;
+      s.dst[2] = c3h(0); s.off[2] = L.w3; s.K[2] = Conv3::KCOL; s.N[2] = Conv3::COUT;
+    }
+    return s;
+  }
   // batch
   uint8_t *s_tm1 = nullptr, *s_t = nullptr;
   int32_t* act = nullptr;
@@ -390,12 +405,14 @@ int t32_splits(const dqnb_learner* h, const P& p, int Z, int want_ctas = 120) {
 
 template <class L, class TIn>
 int t32_conv_fwd(dqnb_learner* h, int nets, int rows, const TIn* const* x, const float* const* params,
-                 const float* const* wts, int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st) {
+                 const float* const* wts, int64_t w_off, int64_t b_off, float* const* y, cudaStream_t st,
+                 __half* const* yh = nullptr) {
   T32ConvFwd<L, TIn> p;
   p.M = rows * L::HOUT * L::WOUT; p.N = L::COUT; p.K = L::KCOL;
   for (int z = 0; z < kMaxNets; ++z) {
     int zz = std::min(z, nets - 1);
     p.x[z] = x[zz]; p.w[z] = wts[zz] + w_off; p.bias[z] = params[zz] + b_off; p.y[z] = y[zz];
+    p.yh[z] = yh ? yh[zz] : nullptr;
   }
   return run_t32(h, p, nets, t32_splits(h, p, nets), st);
 }
@@ -405,6 +422,9 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
                        const float* const* wts, cudaStream_t st) {
   const float* in2[kMaxNets]; const float* in3[kMaxNets]; const float* in4[kMaxNets];
   for (int z = 0; z < nets; ++z) { in2[z] = h->a1[z]; in3[z] = h->a2[z]; in4[z] = h->a3[z]; }
+  // conv2 / conv3 with fp16 operands (slab kernel only): every conv1 / conv2 variant below also leaves an fp16 copy
+  bool h16 = h->conv23_h16 != nullptr && !h->stream;
+  for (int z = 0; z < nets; ++z) h16 = h16 && (wts[z] == h->online_r || wts[z] == h->target_r);
   if (nets == 3 && x[1] == x[2] && wts[0] == wts[2]) {   // double-Q update: one merged conv1 GEMM
     auto fill = [&](auto& p) {
       p.Mh = rows * Conv1::HOUT * Conv1::WOUT;
@@ -412,7 +432,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       p.x[0] = x[0]; p.x[1] = x[1];
       p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
       p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
-      for (int z = 0; z < kMaxNets; ++z) p.y[z] = h->a1[z];
+      for (int z = 0; z < kMaxNets; ++z) { p.y[z] = h->a1[z]; p.yh[z] = h16 ? h->a1h[z] : nullptr; }
     };
     if (h->conv1_h16 != nullptr && wts[0] == h->online_r && wts[1] == h->target_r) {   // fp16 operands: one wave at batch 32
       H16ConvFwdDoubleQ<Conv1, uint8_t> p;
@@ -426,10 +446,28 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
     }
   } else {
-    DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st)));
+    DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st,
+                                           h16 ? h->a1h : nullptr)));
   }
-  DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
-  DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
+  if (h16) {
+    auto run_h16 = [&](auto p, __half* const* xin, __half* const* yh, float* const* y, int64_t b_off, int layer) -> int {
+      using P = decltype(p);
+      p.M = rows * P::HOUT_WOUT; p.N = P::BN; p.K = P::KWORDS;
+      for (int z = 0; z < kMaxNets; ++z) {
+        const int zz = std::min(z, nets - 1);
+        const int tgt = wts[zz] == h->target_r;
+        p.x[z] = xin[zz]; p.w16[z] = layer == 2 ? h->c2h(tgt) : h->c3h(tgt);
+        p.bias[z] = params[zz] + b_off; p.y[z] = y[zz]; p.yh[z] = yh ? yh[zz] : nullptr;
+      }
+      static const int force = getenv("DQNB_H16_SPLITS") ? atoi(getenv("DQNB_H16_SPLITS")) : 1;
+      return run_t32(h, p, nets, force > 0 ? force : t32_splits(h, p, nets), st);
+    };
+    DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, h->a2, h->L.b2, 2));
+    DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));
+  } else {
+    DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
+    DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
+  }
   T32DenseFwd p;
   p.merged = nets == 3;
   p.batch = rows;
@@ -647,7 +685,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     const int64_t skip_lo = fused ? h->L.fw1 : 0, skip_hi = fused ? h->L.fw2 : 0;
     if (h->cfg.defer_apply)   // sum the split-K partials into DQNB_GRAD, nothing else
       rmsprop_reduce_kernel<false><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
-          h->online, h->online_r, H16Shadow{nullptr, 0, 0}, h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
+          h->online, h->online_r, h16_none(), h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
           h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("grad_reduce"));
     else
       rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
@@ -762,6 +800,12 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
   if (h->tf32 && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
     DQNB_TRY(dmalloc(&h->conv1_h16, (size_t)2 * Conv1::COUT * Conv1::KCOL));
+  if (h->tf32 && !h->stream && getenv("DQNB_NO_F16_CONV23") == nullptr) {
+    DQNB_TRY(dmalloc(&h->conv23_h16, 2 * (dqnb_learner::kC2H + dqnb_learner::kC3H)));
+    for (int z = 0; z < h->nets; ++z) {
+      DQNB_TRY(dmalloc(&h->a1h[z], B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->a2h[z], B * Conv2::OUT_PER_IMG));
+    }
+  }
   DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));
   DQNB_TRY(dmalloc(&h->act, B)); DQNB_TRY(dmalloc(&h->rew, B)); DQNB_TRY(dmalloc(&h->disc, B));
@@ -855,7 +899,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   for (float* p : fl) cudaFree(p);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
   cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
-  cudaFree(h->conv1_h16);
+  cudaFree(h->conv1_h16); cudaFree(h->conv23_h16);
+  for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1h[z]); cudaFree(h->a2h[z]); }
   for (auto& s : h->side) if (s) cudaStreamDestroy(s);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->pinned_free) cudaEventDestroy(h->pinned_free);
@@ -883,6 +928,16 @@ extern "C" int dqnb_learner_num_params(dqnb_learner* h, int64_t* n) {
 }
 
 namespace {
+// fp16 K-major filter copies of one net (fp32 arena `p`) after its weights were written from outside
+void refresh_h16(dqnb_learner* h, const float* p, int target, cudaStream_t st) {
+  if (h->conv1_h16 != nullptr)
+    conv1_h16_kernel<<<(Conv1::KCOL * Conv1::COUT + 255) / 256, 256, 0, st>>>(
+        p + h->L.w1, h->conv1_h16 + (target ? Conv1::COUT * Conv1::KCOL : 0), Conv1::KCOL, Conv1::COUT);
+  if (h->conv23_h16 != nullptr) {
+    conv1_h16_kernel<<<(Conv2::KCOL * Conv2::COUT + 255) / 256, 256, 0, st>>>(p + h->L.w2, h->c2h(target), Conv2::KCOL, Conv2::COUT);
+    conv1_h16_kernel<<<(Conv3::KCOL * Conv3::COUT + 255) / 256, 256, 0, st>>>(p + h->L.w3, h->c3h(target), Conv3::KCOL, Conv3::COUT);
+  }
+}
 int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
   const int64_t P = h->L.total, BA = (int64_t)h->B * h->A;
   switch (which) {
@@ -925,9 +980,7 @@ extern "C" int dqnb_learner_write(dqnb_learner* h, int which, const float* host,
   if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
     float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
     round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
-    if (h->conv1_h16 != nullptr)
-      conv1_h16_kernel<<<(Conv1::KCOL * Conv1::COUT + 255) / 256, 256, 0, as_stream(stream)>>>(
-          p + h->L.w1, h->conv1_h16 + (which == DQNB_ONLINE ? 0 : Conv1::COUT * Conv1::KCOL), Conv1::KCOL, Conv1::COUT);
+    refresh_h16(h, p, which == DQNB_TARGET, as_stream(stream));
     DQNB_CUDA(cudaGetLastError());
   }
   DQNB_CUDA(cudaStreamSynchronize(as_stream(stream)));
@@ -953,9 +1006,7 @@ extern "C" int dqnb_learner_write_dev(dqnb_learner* h, int which, const float* d
   if (h->tf32 && (which == DQNB_ONLINE || which == DQNB_TARGET)) {
     float* shadow = which == DQNB_ONLINE ? h->online_r : h->target_r;
     round_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(p, shadow, n);
-    if (h->conv1_h16 != nullptr)
-      conv1_h16_kernel<<<(Conv1::KCOL * Conv1::COUT + 255) / 256, 256, 0, as_stream(stream)>>>(
-          p + h->L.w1, h->conv1_h16 + (which == DQNB_ONLINE ? 0 : Conv1::COUT * Conv1::KCOL), Conv1::KCOL, Conv1::COUT);
+    refresh_h16(h, p, which == DQNB_TARGET, as_stream(stream));
     DQNB_CUDA(cudaGetLastError());
   }
   return DQNB_OK;
@@ -1208,6 +1259,9 @@ extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
   if (h->conv1_h16 != nullptr)
     DQNB_CUDA(cudaMemcpyAsync(h->conv1_h16 + Conv1::COUT * Conv1::KCOL, h->conv1_h16,
                               sizeof(__half) * Conv1::COUT * Conv1::KCOL, cudaMemcpyDeviceToDevice, as_stream(stream)));
+  if (h->conv23_h16 != nullptr)
+    DQNB_CUDA(cudaMemcpyAsync(h->c2h(1), h->c2h(0), sizeof(__half) * (dqnb_learner::kC2H + dqnb_learner::kC3H),
+                              cudaMemcpyDeviceToDevice, as_stream(stream)));
   return DQNB_OK;
 }
 

@@ -26,6 +26,14 @@ __device__ __forceinline__ void t32_widen4(uint32_t dst, uint32_t w) {
   st16(dst, t32_u8_to_float(w, 0x7650), t32_u8_to_float(w, 0x7651), t32_u8_to_float(w, 0x7652),
        t32_u8_to_float(w, 0x7653));
 }
+// 4 floats -> 4 halves (round to nearest), one 8-byte store
+__device__ __forceinline__ void t32_store_half4(__half* dst, const float4& o) {
+  const __half2 lo = __floats2half2_rn(o.x, o.y), hi = __floats2half2_rn(o.z, o.w);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&lo);
+  u.y = *reinterpret_cast<const uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(dst) = u;
+}
 template <class T> struct InScale { static constexpr float value = 1.0f; };
 template <> struct InScale<uint8_t> { static constexpr float value = 1.0f / 255.0f; };
 
@@ -63,6 +71,7 @@ struct T32ConvFwd {
   const float* w[kMaxNets];
   const float* bias[kMaxNets];
   float* y[kMaxNets];
+  __half* yh[kMaxNets] = {};   // optional fp16 copy of the output (input of the next layer's fp16-operand forward)
   __device__ const uint8_t* a_row16(int z, int m) const { return reinterpret_cast<const uint8_t*>(a_row(z, m)); }
   __device__ int a_kb_off(int kb) const { return kb * (L::WIN * L::CIN); }
   using ARow = const TIn*;    // &x[b, i*s, j*s, 0] or null
@@ -91,9 +100,10 @@ struct T32ConvFwd {
   __device__ void store4(int z, int, int m, int n, float4 v) const {
     const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
     constexpr float s = InScale<TIn>::value;
-    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) =
-        tf32_rn4(make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
-                             fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f)));
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
+    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
+    if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
   }
 };
 
@@ -119,6 +129,7 @@ struct T32ConvFwdDoubleQ {
   const float* w[2];        // online, target
   const float* bias[2];
   float* y[kMaxNets];       // online(s_tm1), target(s_t), online(s_t)
+  __half* yh[kMaxNets] = {};   // optional fp16 copies (see T32ConvFwd)
   using ARow = const TIn*;
   using ACol = int;
   struct BRow { int n, which; };   // n (first of 4) inside the net's COUT columns; n = -1: out of range
@@ -154,11 +165,14 @@ struct T32ConvFwdDoubleQ {
     if (!half && which) return;
     const int nn = n - which * L::COUT;
     float* dst = half ? (which ? y[1] : y[2]) : y[0];
+    __half* dsth = half ? (which ? yh[1] : yh[2]) : yh[0];
     const float4 b = __ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + nn));
     constexpr float s = InScale<TIn>::value;
-    *reinterpret_cast<float4*>(dst + (size_t)(m - half * Mh) * L::COUT + nn) =
-        tf32_rn4(make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
-                             fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f)));
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
+    const size_t at = (size_t)(m - half * Mh) * L::COUT + nn;
+    *reinterpret_cast<float4*>(dst + at) = tf32_rn4(o);
+    if (dsth != nullptr) t32_store_half4(dsth + at, o);
   }
 };
 
@@ -182,6 +196,59 @@ struct H16ConvFwdDoubleQ : T32ConvFwdDoubleQ<L, TIn> {
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const {
     const bool ok = r >= 0 && c >= 0;
     cp16(dst, ok ? w16 + (size_t)r * L::KCOL + 2 * c : w16, ok);
+  }
+};
+// conv2 / conv3 forward with fp16 operands (slab kernel, small batches): A = the previous layer's fp16 activation
+// copy (NHWC, written by its epilogue next to the fp32 one the backward pass needs), B = the learner's fp16
+// K-major filter copy w16[n][k].  Activations are post-ReLU values of O(1) and fp16 carries tf32's 11-bit
+// significand, so the tolerance class is unchanged.  Half the operand bytes and half the MMAs: the whole K range
+// (512 / 576 halves = 8 / 9 k-blocks) fits ONE slab, so the tiles run unsplit - no cluster, no DSMEM reduce.
+// K counts 32-bit words (KCOL / 2).
+template <class L>
+struct H16ConvFwd {
+  static constexpr const char* NAME = "conv_fwd_h16";
+  static constexpr int BN = L::COUT, KB_MAX = (L::KCOL / 2 + kT32BK - 1) / kT32BK;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
+  static constexpr bool F16 = true;
+  static constexpr int HOUT_WOUT = L::HOUT * L::WOUT, KWORDS = L::KCOL / 2;
+  static_assert(L::ROWLEN % 8 == 0 && L::CIN % 8 == 0, "16-byte chunks of 8 halves must not straddle patch rows");
+  int M, N, K;              // K = KCOL / 2 words
+  const __half* x[kMaxNets];
+  const __half* w16[kMaxNets];   // [COUT][KCOL]
+  const float* bias[kMaxNets];
+  float* y[kMaxNets];
+  __half* yh[kMaxNets];     // may be null
+  using ARow = const __half*;   // &x[b, i*s, j*s, 0] or null
+  using ACol = int;             // offset (halves) of the chunk inside the patch or -1
+  using BRow = const __half*;   // w16[z] + n * KCOL or null
+  using BCol = int;             // offset (halves) inside the filter row or -1
+  __device__ ARow a_row(int z, int m) const {
+    if (m >= M) return nullptr;
+    int b = m / (L::HOUT * L::WOUT), r = m - b * (L::HOUT * L::WOUT);
+    int i = r / L::WOUT, j = r - i * L::WOUT;
+    return x[z] + ((size_t)(b * L::HIN + i * L::STRIDE) * L::WIN + j * L::STRIDE) * L::CIN;
+  }
+  __device__ ACol a_col(int, int k) const {
+    if (k >= K) return -1;
+    const int kk = 2 * k, kh = kk / L::ROWLEN;
+    return kh * (L::WIN * L::CIN) + (kk - kh * L::ROWLEN);
+  }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const {
+    const bool ok = r != nullptr && c >= 0;
+    cp16(dst, ok ? r + c : x[0], ok);
+  }
+  __device__ BRow b_row(int z, int n) const { return n < N ? w16[z] + (size_t)n * L::KCOL : nullptr; }
+  __device__ BCol b_col(int, int k) const { return k < K ? 2 * k : -1; }
+  __device__ void b_put(BRow r, BCol c, uint32_t dst) const {
+    const bool ok = r != nullptr && c >= 0;
+    cp16(dst, ok ? r + c : w16[0], ok);
+  }
+  __device__ void store4(int z, int, int m, int n, float4 v) const {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
+    const float4 o = make_float4(fmaxf(v.x + b.x, 0.f), fmaxf(v.y + b.y, 0.f), fmaxf(v.z + b.z, 0.f),
+                                 fmaxf(v.w + b.w, 0.f));
+    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
+    if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
   }
 };
 // w[k][n] fp32 (one net's conv1 filters, HWIO) -> dst[n][k] fp16
