@@ -25,6 +25,7 @@
 // grid = (tiles_m * tiles_n, splits, Z), block = 288 threads.
 #pragma once
 #include <type_traits>
+#include <utility>
 
 #include "gemm_simt.cuh"
 
@@ -239,6 +240,33 @@ __device__ __forceinline__ void t32_retire_groups(int nkb, uint64_t* full_bar) {
   }
 }
 
+// The same for ONE k-block whose index is a compile-time constant (register-staged A operands: the thread has
+// just written its chunks of k-block I with st.shared; B's group I is waited for, then both become visible).
+template <int KB, int I>
+__device__ __forceinline__ void t32_retire_one(int nkb, uint64_t* full_bar) {
+  if (I < nkb) {
+    cp_wait<KB - 1 - I>();
+    fence_proxy_async_smem();
+    mbar_arrive_warp(&full_bar[I]);
+  }
+}
+// cp.async pipeline of the generic producer path: k-block i is published kT32Lag iterations after it was issued
+// (its copies have had that long to land), so the MMA issuer works on the first k-blocks while the producers are
+// still issuing the later ones - before, every arrival came after the whole slab had been issued, which put the
+// CTA's 30-odd MMAs (~96 clocks each) behind the issue phase instead of under it.
+constexpr int kT32Lag = 3;
+template <int J = kT32Lag - 1>
+__device__ __forceinline__ void t32_drain_groups(int nkb, uint64_t* full_bar) {
+  if constexpr (J >= 0) {
+    if (nkb - 1 - J >= 0) {
+      cp_wait<J>();
+      fence_proxy_async_smem();
+      mbar_arrive_warp(&full_bar[nkb - 1 - J]);
+    }
+    t32_drain_groups<J - 1>(nkb, full_bar);
+  }
+}
+
 template <class P>
 __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   constexpr int BN = P::BN, COLS = t32_tmem_cols(BN), KB = P::KB_MAX;
@@ -316,19 +344,23 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         stage_b(i);
         cp_commit();
       }
+#pragma unroll 1
+      for (int i = nkb; i < KB; ++i) cp_commit();     // empty groups keep the wait counts static
       const uint32_t row_off = (row >> 3) * 1024 + (row & 7) * 128;
+      [&]<int... I>(std::integer_sequence<int, I...>) {
+        ([&] {
+          if (I < nkb) {
+            const uint32_t base = smem + I * A_TILE + row_off;
 #pragma unroll
-      for (int i = 0; i < KB; ++i) {
-        if (i < nkb) {
-          const uint32_t base = smem + i * A_TILE + row_off;
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            const uint32_t c = s * 4 + half * 2;   // 16-byte chunk (8 halves) inside the 128-byte row
-            t32_widen8h(base + ((c ^ (uint32_t)(row & 7)) << 4), w[i][s].x, w[i][s].y);
-            t32_widen8h(base + (((c + 1) ^ (uint32_t)(row & 7)) << 4), w[i][s].z, w[i][s].w);
+            for (int s = 0; s < 2; ++s) {
+              const uint32_t c = s * 4 + half * 2;   // 16-byte chunk (8 halves) inside the 128-byte row
+              t32_widen8h(base + ((c ^ (uint32_t)(row & 7)) << 4), w[I][s].x, w[I][s].y);
+              t32_widen8h(base + (((c + 1) ^ (uint32_t)(row & 7)) << 4), w[I][s].z, w[I][s].w);
+            }
           }
-        }
-      }
+          t32_retire_one<KB, I>(nkb, full_bar);     // k-block I is complete: the MMAs on it start now
+        }(), ...);
+      }(std::make_integer_sequence<int, KB>{});
     } else if constexpr (t32_a_row16<P>::value) {
       static_assert(!P::A_MN_MAJOR, "A_ROW16 is a K-major path");
       const int row = t >> 1, half = t & 1;
@@ -344,16 +376,20 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         stage_b(i);
         cp_commit();
       }
+#pragma unroll 1
+      for (int i = nkb; i < KB; ++i) cp_commit();     // empty groups keep the wait counts static
       const uint32_t row_off = (row >> 3) * 1024 + (row & 7) * 128;
+      [&]<int... I>(std::integer_sequence<int, I...>) {
+        ([&] {
+          if (I < nkb) {
+            const uint32_t base = smem + I * A_TILE + row_off;
+            const uint32_t wd[4] = {w[I].x, w[I].y, w[I].z, w[I].w};
 #pragma unroll
-      for (int i = 0; i < KB; ++i) {
-        if (i < nkb) {
-          const uint32_t base = smem + i * A_TILE + row_off;
-          const uint32_t wd[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) p.a_store(base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
-        }
-      }
+            for (int j = 0; j < 4; ++j) p.a_store(base + ((uint32_t)((half * 4 + j) ^ (row & 7)) << 4), wd[j]);
+          }
+          t32_retire_one<KB, I>(nkb, full_bar);
+        }(), ...);
+      }(std::make_integer_sequence<int, KB>{});
     } else if constexpr (t32_a_reg<P>::value) {
       constexpr int NW = MA::NROW * MA::NCOL;
       uint32_t word[KB * NW];
@@ -372,14 +408,18 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         stage_b(i);
         cp_commit();
       }
+#pragma unroll 1
+      for (int i = nkb; i < KB; ++i) cp_commit();     // empty groups keep the wait counts static
+      [&]<int... I>(std::integer_sequence<int, I...>) {
+        ([&] {
 #pragma unroll
-      for (int i = 0; i < KB; ++i) {
+          for (int uc = 0; uc < MA::NCOL; ++uc)
 #pragma unroll
-        for (int uc = 0; uc < MA::NCOL; ++uc)
-#pragma unroll
-          for (int ur = 0; ur < MA::NROW; ++ur)
-            if (i < nkb) p.a_store(smem + i * A_TILE + MA::offset(t, ur, uc), word[(i * MA::NCOL + uc) * MA::NROW + ur]);
-      }
+            for (int ur = 0; ur < MA::NROW; ++ur)
+              if (I < nkb) p.a_store(smem + I * A_TILE + MA::offset(t, ur, uc), word[(I * MA::NCOL + uc) * MA::NROW + ur]);
+          t32_retire_one<KB, I>(nkb, full_bar);
+        }(), ...);
+      }(std::make_integer_sequence<int, KB>{});
     } else {
 #pragma unroll 1
       for (int i = 0; i < nkb; ++i) {
@@ -393,12 +433,18 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
         }
         stage_b(i);
         cp_commit();
+        if (i >= kT32Lag) {          // publish k-block i - kT32Lag: at most the kT32Lag newest groups may still be in flight
+          cp_wait<kT32Lag>();
+          fence_proxy_async_smem();
+          mbar_arrive_warp(&full_bar[i - kT32Lag]);
+        }
       }
+      if (dbg && t == 0) sk.dbg[2] = clock64();     // all copies issued
+      t32_drain_groups<>(nkb, full_bar);
     }
-#pragma unroll 1
-    for (int i = nkb; i < KB; ++i) cp_commit();     // empty groups keep the wait counts static
-    if (dbg && t == 0) sk.dbg[2] = clock64();     // all copies issued
-    t32_retire_groups<KB>(nkb, full_bar);
+    if constexpr (t32_a_row16h<P>::value || t32_a_row16<P>::value || t32_a_reg<P>::value) {
+      if (dbg && t == 0) sk.dbg[2] = clock64();     // (register paths: issued and landed coincide)
+    }
     if (dbg && t == 0) sk.dbg[3] = clock64();     // this thread's copies landed
   } else if (t == kT32Producers) {
     // ---- MMA issuer
@@ -452,31 +498,47 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   asm volatile("griddepcontrol.launch_dependents;");
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
+    // Thread t owns one float4 column group (c4 = t mod G4) of rows t / G4 + k * RPP: the column - hence the
+    // bias / mask column the problem's store4 reads - is fixed per thread, the row advances by a constant, and
+    // the passes are fully unrolled with every shared-memory load issued before the first store4.  (A rolled
+    // loop with per-item division and store4's address arithmetic ran ~400 clocks per item at 8 warps per SM:
+    // pure instruction latency, 3 000+ clocks per tile.)
     constexpr int G4 = BN / 4;
-    const int nsum = splits;   // used by the clustered path only
-    const int R = clustered ? (kT32BM + splits - 1) / splits : kT32BM;
-    const int row_beg = clustered ? split * R : 0;
-    const int row_end = min(min(kT32BM, row_beg + R), p.M - m0);
+    constexpr int RPP = kT32Producers / G4;          // rows per pass
+    constexpr int PASSES = kT32BM / RPP;
+    const int c4 = t % G4, r0 = t / G4;
+    const int n = n0 + c4 * 4;
+    const bool col_ok = n < p.N;
+    const int rows_here = p.M - m0;                  // rows of this tile that exist
+    if (!clustered) {
+      float4 v[PASSES];
+#pragma unroll
+      for (int k = 0; k < PASSES; ++k) v[k] = ld_shared_f4(smem + ((r0 + k * RPP) * PSTRIDE + c4 * 4) * 4);
+#pragma unroll
+      for (int k = 0; k < PASSES; ++k) {
+        const int r = r0 + k * RPP;
+        if (col_ok && r < rows_here) p.store4(z, split, m0 + r, n, v[k]);
+      }
+    } else {
+      const int nsum = splits;
+      const int R = (kT32BM + splits - 1) / splits;
+      const int row_beg = split * R;
+      const int row_end = min(min(kT32BM, row_beg + R), rows_here);
 #pragma unroll 2
-    for (int item = t; item < (row_end - row_beg) * G4; item += kT32Producers) {
-      const int r = row_beg + item / G4, c4 = item % G4;
-      const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
-      float4 v;
-      if (!clustered) {
-        v = ld_shared_f4(local);
-      } else {
+      for (int r = row_beg + r0; r < row_end; r += RPP) {
+        const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
         // all partial tiles' loads in flight together (a DSMEM load is a few hundred cycles), then the
         // sum in split order
         float4 x[kT32MaxCluster];
 #pragma unroll
         for (int q = 0; q < kT32MaxCluster; ++q)
           if (q < nsum) x[q] = ld_cluster_f4(cluster_map(local, (uint32_t)q));
-        v = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int q = 0; q < kT32MaxCluster; ++q)
           if (q < nsum) { v.x += x[q].x; v.y += x[q].y; v.z += x[q].z; v.w += x[q].w; }
+        if (col_ok) p.store4(z, split, m0 + r, n, v);
       }
-      if (n0 + c4 * 4 < p.N) p.store4(z, split, m0 + r, n0 + c4 * 4, v);
     }
   }
   if (dbg && t == 0) sk.dbg[6] = clock64();       // my rows reduced and stored
