@@ -404,8 +404,23 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        for (int q = sub; q < regs.r[r].splits; q += 8) {
-          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].stride));
+        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
+        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
+        const int ns = regs.r[r].splits;
+        const size_t st = regs.r[r].stride;
+        int q = sub;
+        for (; q + 24 < ns; q += 32) {
+          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
+          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
+          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
+          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
+          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
+          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
+          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
+        }
+        for (; q < ns; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
           gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
         }
         summed = true;
@@ -478,8 +493,23 @@ __global__ void grad_reduce_range_kernel(float* __restrict__ g, GradRegions regs
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        for (int q = sub; q < regs.r[r].splits; q += 8) {
-          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * regs.r[r].stride));
+        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
+        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
+        const int ns = regs.r[r].splits;
+        const size_t st = regs.r[r].stride;
+        int q = sub;
+        for (; q + 24 < ns; q += 32) {
+          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
+          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
+          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
+          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
+          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
+          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
+          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
+        }
+        for (; q < ns; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
           gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
         }
         summed = true;
