@@ -85,7 +85,6 @@ SIGNATURES = {
     "dqnb_learner_profile": [c_vp, c_int, ctypes.c_char_p, c_sz, STREAM],
     "dqnb_learner_timeline": [c_vp, ctypes.c_char_p, c_sz, STREAM],
     "dqnb_learner_relaunch": [c_vp, c_int, STREAM],
-    "dqnb_selftest_tc_gemm": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, STREAM],
     "dqnb_selftest_tf32_gemm": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, STREAM],
 }
 

@@ -1,6 +1,6 @@
 // Generic fp32 SIMT tile GEMM with functor operand loaders (implicit im2col etc.) and a
 // deterministic split-K fix-up.  This is the fp32 / rel-1e-5 precision mode of the learner
-// (K2/K3 "SIMT twin"); the bf16 tensor-core mode lives in gemm_tc.cuh.
+// (K2/K3 "SIMT twin"); the tensor-core mode lives in gemm_tf32.cuh / gemm_tf32_stream.cuh.
 //
 // A problem type P provides:
 //   static constexpr int BM, BN;            tile (multiples of 16; 256 threads = 16x16)

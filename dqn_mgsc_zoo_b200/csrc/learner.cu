@@ -786,6 +786,8 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
                "precision %d not available in this build (DQNB_FP32 or DQNB_TF32)", cfg->precision);
   DeviceGuard guard(device);
   dqnb_learner* h = new dqnb_learner();
+  // everything below may fail half way: the handle is destroyed (destroy tolerates partial initialisation)
+  const int rc_create = [&]() -> int {
   h->cfg = *cfg;
   h->device = device;
   h->B = cfg->batch_size; h->A = cfg->num_actions; h->nets = cfg->double_q ? 3 : 2;
@@ -871,6 +873,9 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
     for (auto& e : h->set_free) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     DQNB_CUDA(cudaEventCreateWithFlags(&h->gathered, cudaEventDisableTiming));
   }
+  return DQNB_OK;
+  }();
+  if (rc_create != DQNB_OK) { dqnb_learner_destroy(h); return rc_create; }
   *out = h;
   return DQNB_OK;
 }

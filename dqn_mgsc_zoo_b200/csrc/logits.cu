@@ -239,6 +239,8 @@ extern "C" int dqnb_logits_create(int64_t capacity, int device, dqnb_logits** ou
   DQNB_REQUIRE(out && capacity >= 1 && capacity <= (int64_t)1 << 31, "bad capacity %lld", (long long)capacity);
   DeviceGuard guard(device);
   dqnb_logits* h = new dqnb_logits();
+  // everything below may fail half way: the handle is destroyed (destroy tolerates partial initialisation)
+  const int rc_create = [&]() -> int {
   h->device = device; h->capacity = capacity;
   h->nb = (int)((capacity + kBlk - 1) / kBlk);
   DQNB_CUDA(cudaMalloc(&h->l, sizeof(float) * capacity));
@@ -248,6 +250,9 @@ extern "C" int dqnb_logits_create(int64_t capacity, int device, dqnb_logits** ou
   fill_value_kernel<<<(unsigned)((capacity + 255) / 256), 256>>>(h->l, capacity, -INFINITY);
   DQNB_CUDA(cudaGetLastError());
   DQNB_CUDA(cudaDeviceSynchronize());
+  return DQNB_OK;
+  }();
+  if (rc_create != DQNB_OK) { dqnb_logits_destroy(h); return rc_create; }
   *out = h;
   return DQNB_OK;
 }

@@ -185,13 +185,13 @@ int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host,
   meta_v_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->v,
                                              h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
   DQNB_TRY(dqnb_learner_adjoint_dots(h->bat, h->v, h->dot_part, s));
-  h->count += 1;
   logits_adam_kernel<<<1, 256, 0, st>>>(h->logits, h->p, h->dot_part, h->loss_part, h->dldp, h->adam_m, h->adam_v,
-                                        h->out, h->out + M, M, h->count, h->cfg.learning_rate, h->cfg.b1,
+                                        h->out, h->out + M, M, h->count + 1, h->cfg.learning_rate, h->cfg.b1,
                                         h->cfg.b2, h->cfg.eps);
   DQNB_CUDA(cudaGetLastError());
   DQNB_CUDA(cudaMemcpyAsync(h->pinned + M, h->out, sizeof(float) * (M + 1), cudaMemcpyDeviceToHost, st));
   DQNB_CUDA(cudaStreamSynchronize(st));
+  h->count += 1;      // the Adam state advanced only if everything above ran
   memcpy(new_logits_host, h->pinned + M, sizeof(float) * M);
   if (meta_loss_host) *meta_loss_host = h->pinned[2 * M];
   return DQNB_OK;
@@ -223,6 +223,8 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
   DQNB_REQUIRE(cfg->meta_batch_size >= 1 && cfg->meta_batch_size <= kMaxMeta, "meta_batch_size %d not in 1..%d",
                cfg->meta_batch_size, kMaxMeta);
   dqnb_mgsc* h = new dqnb_mgsc();
+  // everything below may fail half way: the handle is destroyed (destroy tolerates partial initialisation)
+  const int rc_create = [&]() -> int {
   h->main = learner;
   h->cfg = *cfg;
   h->M = cfg->meta_batch_size;
@@ -231,14 +233,14 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
     set_error("MGSC uses the q_learning loss (dqn_mgsc_batched/agent.py:104-127): create the learner with double_q=0");
     rc = DQNB_EINVAL;
   }
-  if (rc != DQNB_OK) { delete h; return rc; }
+  if (rc != DQNB_OK) return rc;
   dqnb_learner_config sc = h->lcfg;
   sc.batch_size = 1; sc.loss_mean_over = 1; sc.double_q = 0; sc.defer_apply = 1;
   rc = dqnb_learner_create(&sc, h->device, &h->sub);
-  if (rc != DQNB_OK) { delete h; return rc; }
+  if (rc != DQNB_OK) return rc;
   sc.batch_size = h->M; sc.row_weighted = 1;
   rc = dqnb_learner_create(&sc, h->device, &h->bat);
-  if (rc != DQNB_OK) { dqnb_learner_destroy(h->sub); delete h; return rc; }
+  if (rc != DQNB_OK) return rc;
   DeviceGuard guard(h->device);
   DQNB_TRY(dqnb_learner_num_params(learner, &h->P));
   h->img = 84 * 84 * 4;
@@ -252,6 +254,9 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
   DQNB_TRY(dalloc(&h->adam_m, M1)); DQNB_TRY(dalloc(&h->adam_v, M1)); DQNB_TRY(dalloc(&h->out, M1 + 1));
   DQNB_CUDA(cudaMallocHost(&h->pinned, sizeof(float) * (2 * M1 + 8)));
   DQNB_CUDA(cudaMallocHost(&h->pinned_on, 2 * h->img));
+  return DQNB_OK;
+  }();
+  if (rc_create != DQNB_OK) { dqnb_mgsc_destroy(h); return rc_create; }
   *out = h;
   return DQNB_OK;
 }

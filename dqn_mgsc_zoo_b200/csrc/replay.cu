@@ -232,6 +232,8 @@ extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int s
   DQNB_REQUIRE(stack >= 1 && stack <= 4, "stack depth %d not in 1..4", stack);
   DeviceGuard guard(device);
   dqnb_replay* h = new dqnb_replay();
+  // everything below may fail half way: the handle is destroyed (destroy tolerates partial initialisation)
+  const int rc_create = [&]() -> int {
   h->device = device;
   h->capacity = capacity;
   h->H = height; h->W = width; h->S = stack;
@@ -266,6 +268,9 @@ extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int s
   h->n_growths = 0;
   DQNB_CUDA(cudaFuncSetAttribute(gather_stack4<kGatherThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  8 * 16 * 1024));
+  return DQNB_OK;
+  }();
+  if (rc_create != DQNB_OK) { dqnb_replay_destroy(h); return rc_create; }
   *out = h;
   return DQNB_OK;
 }

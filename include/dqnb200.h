@@ -105,8 +105,9 @@ int dqnb_replay_import(dqnb_replay* h, const void* host, int64_t bytes, uintptr_
  * conv2_d{w[8,8,4,32],b} conv2_d_1{w[4,4,32,64],b} conv2_d_2{w[3,3,64,64],b}
  * linear{w[3136,512],b} linear_1{w[512,A], b[A] or b[1] when shared_bias}. */
 #define DQNB_FP32 0   /* SIMT fp32 kernels; parity tolerance rel 1e-5 */
-#define DQNB_BF16 1   /* reserved (bf16 operands); not built: TF32 keeps fp32 storage and is 8x more precise */
-#define DQNB_TF32 2   /* tcgen05.mma.kind::tf32 on the fp32 arrays, fp32 accumulate in TMEM; parity tolerance rel 1e-3 */
+#define DQNB_TF32 2   /* tcgen05 tensor cores: kind::tf32 on the fp32 arrays (kind::f16 on fp16 copies of frames / post-ReLU
+                         activations / filters for the forward convolutions - same 11-bit significand), fp32 accumulate
+                         in TMEM; parity tolerance rel 1e-3.  (1 was a reserved bf16 value; never built.) */
 
 typedef struct dqnb_learner_config {
   int32_t num_actions;
@@ -314,12 +315,8 @@ int dqnb_sumtree_query(dqnb_sumtree* h, const double* targets_or_uniforms, int64
 int dqnb_sumtree_read(dqnb_sumtree* h, double* storage_host, int64_t n);
 int dqnb_sumtree_write(dqnb_sumtree* h, const double* storage_host, int64_t n);
 
-/* Test hook (not part of the drop-in surface): C[M,N] = A*B^T through the tcgen05 tile GEMM on
- * fp32 device matrices (operands rounded to bf16); *_mn_major selects [K,M]/[K,N] storage. */
-int dqnb_selftest_tc_gemm(const float* a_dev, const float* b_dev, float* c_dev, int M, int N, int K,
-                          int a_mn_major, int b_mn_major, int bn, int splits, uintptr_t stream);
-
-/* Same for the TF32 slab kernel (fp32 operands, tcgen05.mma.kind::tf32); M, N, K multiples of 4. */
+/* Test hook (not part of the drop-in surface): C[M,N] = A*B^T through the TF32 slab kernel on fp32 device matrices
+ * (tcgen05.mma.kind::tf32); *_mn_major selects [K,M]/[K,N] storage; M, N, K multiples of 4. */
 int dqnb_selftest_tf32_gemm(const float* a_dev, const float* b_dev, float* c_dev, int M, int N, int K,
                             int a_mn_major, int b_mn_major, int bn, int splits, uintptr_t stream);
 
