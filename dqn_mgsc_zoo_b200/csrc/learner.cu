@@ -459,8 +459,10 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
         p.x[z] = xin[zz]; p.w16[z] = layer == 2 ? h->c2h(tgt) : h->c3h(tgt);
         p.bias[z] = params[zz] + b_off; p.y[z] = y[zz]; p.yh[z] = yh ? yh[zz] : nullptr;
       }
-      static const int force = getenv("DQNB_H16_SPLITS") ? atoi(getenv("DQNB_H16_SPLITS")) : 1;
-      return run_t32(h, p, nets, force > 0 ? force : t32_splits(h, p, nets), st);
+      // split-K over a cluster (DQNB_H16_SPLITS2 / 3, default 1 = the whole K range in one slab)
+      static const int s2 = getenv("DQNB_H16_SPLITS2") ? atoi(getenv("DQNB_H16_SPLITS2")) : 1;
+      static const int s3 = getenv("DQNB_H16_SPLITS3") ? atoi(getenv("DQNB_H16_SPLITS3")) : 1;
+      return run_t32(h, p, nets, layer == 2 ? s2 : s3, st);
     };
     DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, h->a2, h->L.b2, 2));
     DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));

@@ -9,7 +9,14 @@
 //   sample : p = exp(l - lse) in float32, CDF in float64 (blocked prefix sums + in-order scan inside
 //            the hit block), cdf/cdf[-1] <= u  counted like searchsorted(side='right')
 // HBM/L2-bound streaming reductions; no tensor cores.
+// Running logsumexp: walking the whole ring for every add is the reference's 1.94 ms hotspot and was still three
+// passes over 4 MB here.  The device keeps (c, S) with S = sum_i exp(l_i - c) in float64, c >= every logit written
+// since the last exact pass; fill / set / popleft adjust S by the terms they add and remove (single-CTA kernels,
+// fixed summation order), so the new logit lse - log(size) costs one tiny launch.  An exact pass (the kernels
+// below) re-anchors (c, S) every kExactEvery mutations and after any whole-array write, so float64 drift stays
+// far below the float32 rounding of the logits themselves (the tests hold them to 2e-6 of the reference).
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <vector>
@@ -72,7 +79,7 @@ __global__ void sumexp_kernel(const float* __restrict__ l, int64_t n, const floa
 }
 // pass 4 (one block): lse = c + log(sum) -> stat[1]; optionally logits[fill_at] = lse - log(size)
 __global__ void lse_final_kernel(const float* __restrict__ part, int nb, float* __restrict__ stat,
-                                 float* __restrict__ l, int64_t fill_at, double log_size) {
+                                 float* __restrict__ l, int64_t fill_at, double log_size, double* __restrict__ run) {
   __shared__ float red[kThreads];
   float s = 0.f;
   for (int i = threadIdx.x; i < nb; i += kThreads) s += part[i];
@@ -82,8 +89,61 @@ __global__ void lse_final_kernel(const float* __restrict__ part, int nb, float* 
     stat[1] = lse;
     stat[2] = (s != s) ? 1.f : 0.f;   // a NaN logit (fmaxf drops it from the max, expf carries it into the sum)
     // np.float32 lse minus np.log(int) (float64), rounded when stored into the float32 array
-    if (fill_at >= 0) l[fill_at] = (float)((double)lse - log_size);
+    double c = (double)stat[0], S = (double)s;
+    if (fill_at >= 0) {
+      const float old = l[fill_at], nv = (float)((double)lse - log_size);
+      l[fill_at] = nv;
+      if (nv > stat[0]) { S *= exp(c - (double)nv); c = (double)nv; }
+      S += (double)expf(nv - (float)c) - (double)expf(old - (float)c);
+    }
+    run[0] = c; run[1] = S;      // anchor of the running logsumexp
   }
+}
+// Running-mode twins (one CTA).  run = {c, S}.
+// fill: l[at] = (float)(c + log S) - log(size), S adjusted for the slot's old and new value.
+__global__ void run_fill_kernel(float* __restrict__ l, int64_t at, double log_size, double* __restrict__ run,
+                                float* __restrict__ stat) {
+  if (threadIdx.x != 0) return;
+  double c = run[0], S = run[1];
+  const float lse = (float)(c + log(S));
+  const float old = l[at], nv = (float)((double)lse - log_size);
+  l[at] = nv;
+  if ((double)nv > c) { S *= exp(c - (double)nv); c = (double)nv; }
+  S += (double)expf(nv - (float)c) - (double)expf(old - (float)c);
+  run[0] = c; run[1] = S;
+  stat[1] = lse;
+}
+// set: l[idx[k]] = v[k] for k < n (indices distinct), S adjusted; idx == nullptr: the by-value case n == 1.
+__global__ void __launch_bounds__(kThreads) run_set_kernel(float* __restrict__ l, const int64_t* __restrict__ idx,
+                                                           const float* __restrict__ v, int n, int64_t idx0, float v0,
+                                                           double* __restrict__ run) {
+  __shared__ float redf[kThreads];
+  __shared__ double redd[kThreads];
+  __shared__ double c_s;
+  const int t = threadIdx.x;
+  float vmax = -INFINITY;
+  for (int k = t; k < n; k += kThreads) vmax = fmaxf(vmax, idx ? v[k] : v0);
+  vmax = block_max(vmax, redf);
+  if (t == 0) {
+    double c = run[0];
+    if ((double)vmax > c) { run[1] *= exp(c - (double)vmax); c = (double)vmax; run[0] = c; }
+    c_s = c;
+  }
+  __syncthreads();
+  const float c = (float)c_s;
+  double delta = 0.0;
+  for (int k = t; k < n; k += kThreads) {
+    const int64_t i = idx ? idx[k] : idx0;
+    const float nv = idx ? v[k] : v0, old = l[i];
+    l[i] = nv;
+    delta += (double)expf(nv - c) - (double)expf(old - c);
+  }
+  delta = block_sum(delta, redd);
+  if (t == 0) run[1] += delta;
+}
+// stat[1] = float32 lse from the running state (sample's softmax reference point)
+__global__ void run_lse_kernel(const double* __restrict__ run, float* __restrict__ stat) {
+  if (threadIdx.x == 0) { stat[1] = (float)(run[0] + log(run[1])); stat[2] = 0.f; }
 }
 // CDF pass: block sums of p = exp(l - lse) accumulated in float64, in index order inside a thread's
 // contiguous run so the blocked sum stays close to the sequential cumsum of the reference.
@@ -198,6 +258,9 @@ struct dqnb_logits {
   float* part = nullptr;      // [nb]
   float* stat = nullptr;      // [0] max, [1] lse
   double* dpart = nullptr;    // [nb] + [1] total
+  double* run = nullptr;      // {c, S}: running logsumexp anchor (device)
+  bool run_valid = false;     // (c, S) describe the current array
+  int run_ops = 0;            // mutations applied to (c, S) since the last exact pass
   // small pinned/device scratch for index lists
   int64_t io_cap = 0;
   int64_t* d_idx = nullptr;
@@ -207,13 +270,22 @@ struct dqnb_logits {
 };
 
 namespace {
+constexpr int kExactEvery = 64;     // running-mode mutations between two exact passes
+const bool kRunningLse = getenv("DQNB_NO_RUNNING_LSE") == nullptr;
 int lse_passes(dqnb_logits* h, int64_t fill_at, double log_size, cudaStream_t st) {
   max_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->part);
   max_final_kernel<<<1, kThreads, 0, st>>>(h->part, h->nb, h->stat);
   sumexp_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->stat, h->part);
-  lse_final_kernel<<<1, kThreads, 0, st>>>(h->part, h->nb, h->stat, h->l, fill_at, log_size);
+  lse_final_kernel<<<1, kThreads, 0, st>>>(h->part, h->nb, h->stat, h->l, fill_at, log_size, h->run);
   DQNB_CUDA(cudaGetLastError());
+  h->run_valid = kRunningLse;
+  h->run_ops = 0;
   return DQNB_OK;
+}
+// true when the next operation may use (c, S) instead of walking the array
+bool running(dqnb_logits* h) {
+  if (h->run_valid && h->run_ops >= kExactEvery) h->run_valid = false;
+  return h->run_valid;
 }
 int ensure_io(dqnb_logits* h, int64_t n) {
   if (n <= h->io_cap) return DQNB_OK;
@@ -247,6 +319,7 @@ extern "C" int dqnb_logits_create(int64_t capacity, int device, dqnb_logits** ou
   DQNB_CUDA(cudaMalloc(&h->part, sizeof(float) * h->nb));
   DQNB_CUDA(cudaMalloc(&h->stat, sizeof(float) * 4));
   DQNB_CUDA(cudaMalloc(&h->dpart, sizeof(double) * (h->nb + 1)));
+  DQNB_CUDA(cudaMalloc(&h->run, sizeof(double) * 2));
   fill_value_kernel<<<(unsigned)((capacity + 255) / 256), 256>>>(h->l, capacity, -INFINITY);
   DQNB_CUDA(cudaGetLastError());
   DQNB_CUDA(cudaDeviceSynchronize());
@@ -261,7 +334,7 @@ extern "C" int dqnb_logits_destroy(dqnb_logits* h) {
   if (!h) return DQNB_OK;
   DeviceGuard guard(h->device);
   cudaDeviceSynchronize();
-  cudaFree(h->l); cudaFree(h->part); cudaFree(h->stat); cudaFree(h->dpart);
+  cudaFree(h->l); cudaFree(h->part); cudaFree(h->stat); cudaFree(h->dpart); cudaFree(h->run);
   cudaFree(h->d_idx); cudaFree(h->d_val); cudaFree(h->d_u);
   if (h->pinned) cudaFreeHost(h->pinned);
   delete h;
@@ -276,6 +349,13 @@ extern "C" int dqnb_logits_fill(dqnb_logits* h, int64_t index, int64_t size, uin
   if (size == 0) {
     fill_value_kernel<<<1, 32, 0, st>>>(h->l + index, 1, 0.0f);
     DQNB_CUDA(cudaGetLastError());
+    h->run_valid = false;
+    return DQNB_OK;
+  }
+  if (running(h)) {
+    run_fill_kernel<<<1, 32, 0, st>>>(h->l, index, log((double)size), h->run, h->stat);
+    DQNB_CUDA(cudaGetLastError());
+    h->run_ops++;
     return DQNB_OK;
   }
   return lse_passes(h, index, log((double)size), st);
@@ -288,8 +368,15 @@ extern "C" int dqnb_logits_set(dqnb_logits* h, const int64_t* indices, const flo
   DQNB_TRY(check_indices(h, indices, n));
   DeviceGuard guard(h->device);
   cudaStream_t st = as_stream(stream);
+  for (int64_t i = 0; i < n; ++i)
+    if (values[i] != values[i] || values[i] == INFINITY) h->run_valid = false;   // NaN / +inf: only the exact pass handles them
   if (n == 1) {   // the per-add case (popleft / explicit priority): by value, nothing to wait for
-    fill_value_kernel<<<1, 32, 0, st>>>(h->l + indices[0], 1, values[0]);
+    if (running(h)) {
+      run_set_kernel<<<1, kThreads, 0, st>>>(h->l, nullptr, nullptr, 1, indices[0], values[0], h->run);
+      h->run_ops++;
+    } else {
+      fill_value_kernel<<<1, 32, 0, st>>>(h->l + indices[0], 1, values[0]);
+    }
     DQNB_CUDA(cudaGetLastError());
     return DQNB_OK;
   }
@@ -297,11 +384,28 @@ extern "C" int dqnb_logits_set(dqnb_logits* h, const int64_t* indices, const flo
   DQNB_CUDA(cudaStreamSynchronize(st));   // pinned scratch is reused call to call
   int64_t* pi = reinterpret_cast<int64_t*>(h->pinned);
   float* pv = reinterpret_cast<float*>(h->pinned + 8 * (size_t)h->io_cap);
-  memcpy(pi, indices, sizeof(int64_t) * n);
-  memcpy(pv, values, sizeof(float) * n);
-  DQNB_CUDA(cudaMemcpyAsync(h->d_idx, pi, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
-  DQNB_CUDA(cudaMemcpyAsync(h->d_val, pv, sizeof(float) * n, cudaMemcpyHostToDevice, st));
-  set_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->l, h->d_idx, h->d_val, (int)n);
+  // duplicate indices: NumPy's `l[idx] = v` keeps the last one; the running kernel needs them distinct
+  int64_t m = 0;
+  if (n <= 4096) {
+    for (int64_t i = 0; i < n; ++i) {
+      bool later = false;
+      for (int64_t j = i + 1; j < n && !later; ++j) later = indices[j] == indices[i];
+      if (!later) { pi[m] = indices[i]; pv[m] = values[i]; ++m; }
+    }
+  } else {      // big scatter (whole-array style use): plain kernel, exact pass next time
+    memcpy(pi, indices, sizeof(int64_t) * n);
+    memcpy(pv, values, sizeof(float) * n);
+    m = n;
+    h->run_valid = false;
+  }
+  DQNB_CUDA(cudaMemcpyAsync(h->d_idx, pi, sizeof(int64_t) * m, cudaMemcpyHostToDevice, st));
+  DQNB_CUDA(cudaMemcpyAsync(h->d_val, pv, sizeof(float) * m, cudaMemcpyHostToDevice, st));
+  if (running(h)) {
+    run_set_kernel<<<1, kThreads, 0, st>>>(h->l, h->d_idx, h->d_val, (int)m, 0, 0.f, h->run);
+    h->run_ops++;
+  } else {
+    set_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(h->l, h->d_idx, h->d_val, (int)m);
+  }
   DQNB_CUDA(cudaGetLastError());
   return DQNB_OK;
 }
@@ -339,7 +443,8 @@ extern "C" int dqnb_logits_sample(dqnb_logits* h, const double* uniforms, int64_
   double* pu = reinterpret_cast<double*>(h->pinned);
   memcpy(pu, uniforms, sizeof(double) * n);
   DQNB_CUDA(cudaMemcpyAsync(h->d_u, pu, sizeof(double) * n, cudaMemcpyHostToDevice, st));
-  DQNB_TRY(lse_passes(h, -1, 0.0, st));
+  if (running(h)) run_lse_kernel<<<1, 32, 0, st>>>(h->run, h->stat);
+  else DQNB_TRY(lse_passes(h, -1, 0.0, st));
   psum_kernel<<<h->nb, kThreads, 0, st>>>(h->l, h->capacity, h->stat, h->dpart);
   pscan_kernel<<<1, 32, 0, st>>>(h->dpart, h->nb, h->dpart + h->nb);
   search_kernel<<<(unsigned)((n + 1) / 2), 64, 0, st>>>(h->l, h->capacity, h->stat, h->dpart, h->nb,
@@ -367,6 +472,7 @@ extern "C" int dqnb_logits_write(dqnb_logits* h, const float* host, int64_t n) {
   DQNB_REQUIRE(h && host && n == h->capacity, "bad argument");
   DeviceGuard guard(h->device);
   DQNB_CUDA(cudaMemcpy(h->l, host, sizeof(float) * n, cudaMemcpyHostToDevice));
+  h->run_valid = false;
   return DQNB_OK;
 }
 extern "C" int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream) {

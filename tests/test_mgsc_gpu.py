@@ -274,3 +274,42 @@ def test_mgsc_agent_schedule_and_state():
     assert set(state) == {"rng_key", "frame_t", "opt_state", "online_params", "target_params", "replay",
                           "meta_opt_state"}
     assert state["meta_opt_state"][0].count == len(metas) and state["meta_opt_state"][0].mu.shape == (M,)
+
+
+def test_logit_ring_at_one_million_entries_matches_reference_semantics():
+    """The benchmarked scale: a 1 M-entry ring, 64 weighted draws and the add / popleft logit
+    chain against the oracle (= Generator.choice(p=softmax) and lse(all) - log(size), replay_circular.py:166-217).
+    The ring is loaded through whole-array state (filling it add by add costs the oracle 2 ms per add); then the
+    running logsumexp is exercised across more than one exact re-anchoring (kExactEvery = 64 mutations)."""
+    cap, live = 1_000_000, 999_000
+    rng = np.random.default_rng(123)
+    logits = np.full(cap, -np.inf, dtype=np.float32)
+    head = 4321
+    pos = (head + np.arange(live)) % cap
+    logits[pos] = rng.normal(0.0, 1.5, live).astype(np.float32)
+    o = ro.RingLogits(cap, np.random.default_rng(9))
+    o.l[:] = logits
+    o.size, o.head, o.tail = live, head, (head + live) % cap
+    p = rc.CircularLogitBuffer(cap, np.random.default_rng(9))
+    p.set_state({'capacity': cap, 'logits': logits.copy(), 'size': live, 'left_head': head,
+                 'right_head': (head + live) % cap, 'rng_state': np.random.default_rng(9)})
+    assert np.array_equal(p.sample(64), o.sample(64))
+    for step in range(150):                       # crosses two exact passes of the running logsumexp
+        if step % 3 == 2:
+            a, b = p.popleft(), o.popleft()
+            assert abs(float(a) - float(b)) == 0.0
+        else:
+            p.add()
+            o.push()
+        if step % 10 == 9:
+            k = np.array([p.size - 1, p.size - 2, 0])
+            np.testing.assert_allclose(p[k], o.get(k), rtol=0, atol=2e-6)
+        if step % 50 == 49:
+            idx = np.array([5, 17, 99, 4000])
+            vals = np.array([3.0, -2.0, 9.5, 0.25], np.float32)      # 9.5 becomes the new maximum
+            p[idx] = vals
+            o.set(idx, vals)
+            assert np.array_equal(p.sample(64), o.sample(64)), step
+    np.testing.assert_allclose(p._logits, o.l, rtol=0, atol=2e-6)
+    assert np.array_equal(p.sample(64), o.sample(64))
+    assert p._rng_state.integers(1 << 30) == o.rng.integers(1 << 30)
