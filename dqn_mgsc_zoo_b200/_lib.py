@@ -73,6 +73,7 @@ SIGNATURES = {
     "dqnb_logits_lse": [c_vp, ctypes.POINTER(c_f32), STREAM],
     "dqnb_logits_read": [c_vp, c_vp, c_i64],
     "dqnb_logits_write": [c_vp, c_vp, c_i64],
+    "dqnb_logsumexp_noalloc": [c_int, c_vp, c_i64, c_vp, STREAM],
     "dqnb_sumtree_create": [c_i64, c_int, ctypes.POINTER(c_vp)],
     "dqnb_sumtree_destroy": [c_vp],
     "dqnb_sumtree_set": [c_vp, c_vp, c_vp, c_i64, STREAM],

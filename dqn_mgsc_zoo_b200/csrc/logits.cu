@@ -486,3 +486,68 @@ extern "C" int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream) {
   *lse = stat[1];
   return DQNB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free logsumexp (no counterpart in the reference).
+// Same kernels as dqnb_logits_lse (max -> global max -> sum of exp -> lse), but on a caller-owned device array
+// and with the scratch those passes need - per-block partials [nb], the {max, lse, nan-flag} cell, the running
+// anchor - in ONE file-scope device array instead of buffers a handle allocates.  For callers that cannot call
+// cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+//   * limit: kNoAllocMaxLogits = 4 194 304 logits (4 096 blocks of 1 024) -> 16 KB of partials + a 256-byte
+//     header; every GPU that loads the library holds these 16.6 KB until the process exits;
+//   * the array is SHARED by every call and keeps the last call's contents.  Nothing in it has to start at zero:
+//     each pass overwrites exactly the cells the next pass reads (part[0..nb), stat[0..3), run[0..2)), so stale
+//     partials of a longer earlier call are never read.  Calls that overlap on the GPU (different streams, or
+//     different host threads without their own ordering) race on it: serialise them;
+//   * in host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the kernels get
+//     comes from cudaGetSymbolAddress, looked up once per device with that device current.
+namespace {
+constexpr int kNoAllocMaxBlocks = 4096;
+constexpr int64_t kNoAllocMaxLogits = (int64_t)kNoAllocMaxBlocks * kBlk;
+constexpr size_t kNoAllocHeader = 256;     // run[2] doubles at 0, stat[4] floats at 64
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHeader + sizeof(float) * kNoAllocMaxBlocks];
+
+constexpr int kNoAllocMaxDevices = 64;
+unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};     // device address of the array, per device ordinal
+
+__global__ void noalloc_publish_kernel(const float* __restrict__ stat, float* __restrict__ out) {
+  if (threadIdx.x == 0) *out = stat[1];
+}
+
+// device address of the scratch array on `device` (which must be current)
+int noalloc_scratch(int device, unsigned char** ptr) {
+  DQNB_REQUIRE(device >= 0 && device < kNoAllocMaxDevices, "device ordinal %d outside [0,%d)", device, kNoAllocMaxDevices);
+  if (g_noalloc_ptr[device] == nullptr) {
+    unsigned char* p = nullptr;
+    DQNB_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    DQNB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    g_noalloc_ptr[device] = p;
+  }
+  *ptr = g_noalloc_ptr[device];
+  return DQNB_OK;
+}
+}  // namespace
+
+extern "C" int dqnb_logsumexp_noalloc(int device, const float* logits_dev, int64_t n, float* lse_dev, uintptr_t stream) {
+  DQNB_REQUIRE(logits_dev && lse_dev, "null argument");
+  DQNB_REQUIRE(n >= 1, "n=%lld: need at least one logit", (long long)n);
+  DQNB_REQUIRE(n <= kNoAllocMaxLogits,
+               "n=%lld exceeds the allocation-free limit of %lld logits (fixed scratch of %d partials); use "
+               "dqnb_logits_create / dqnb_logits_lse for larger arrays",
+               (long long)n, (long long)kNoAllocMaxLogits, kNoAllocMaxBlocks);
+  DeviceGuard guard(device);
+  unsigned char* base = nullptr;
+  DQNB_TRY(noalloc_scratch(device, &base));
+  double* run = reinterpret_cast<double*>(base);
+  float* stat = reinterpret_cast<float*>(base + 64);
+  float* part = reinterpret_cast<float*>(base + kNoAllocHeader);
+  cudaStream_t st = as_stream(stream);
+  const int nb = (int)((n + kBlk - 1) / kBlk);
+  max_kernel<<<nb, kThreads, 0, st>>>(logits_dev, n, part);
+  max_final_kernel<<<1, kThreads, 0, st>>>(part, nb, stat);
+  sumexp_kernel<<<nb, kThreads, 0, st>>>(logits_dev, n, stat, part);
+  lse_final_kernel<<<1, kThreads, 0, st>>>(part, nb, stat, nullptr, -1, 0.0, run);
+  noalloc_publish_kernel<<<1, 32, 0, st>>>(stat, lse_dev);
+  DQNB_CUDA(cudaGetLastError());
+  return DQNB_OK;
+}

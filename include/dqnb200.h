@@ -291,6 +291,15 @@ int dqnb_logits_lse(dqnb_logits* h, float* lse, uintptr_t stream);
 /* whole-array copies for get_state / set_state / `_logits` pokes; n must equal capacity. */
 int dqnb_logits_read(dqnb_logits* h, float* host, int64_t n);
 int dqnb_logits_write(dqnb_logits* h, const float* host, int64_t n);
+/* Allocation-free logsumexp.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  *lse_dev = logsumexp(logits_dev[0..n)) in float32, computed by the same kernels as dqnb_logits_lse, with
+ * their scratch (per-block partials) in a fixed file-scope device array: the call allocates and frees nothing.
+ * Limit: n <= 4 194 304 (rejected with DQNB_EINVAL and a message beyond it); the 16.6 KB array exists on every GPU
+ * that loads the library until the process exits.  All calls share the array: calls that overlap on the GPU
+ * (different streams without ordering between them) race - serialise them.  Both pointers are device memory on
+ * `device`; asynchronous on `stream`. */
+int dqnb_logsumexp_noalloc(int device, const float* logits_dev, int64_t n, float* lse_dev, uintptr_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Prioritized replay sum tree in device memory (replay.py:379-559 SumTree; used by PrioritizedDistribution
