@@ -271,6 +271,12 @@ class MGSCDqn(Dqn):
     replay, then add, learn from a logit-weighted sample, sync.  `meta_update` (agent.py:160-220)
     runs on the device (dqnb_mgsc_meta_update: one row-weighted batched backward, two virtual RMSProp steps,
     softmax backward, Adam on the logits); neither params nor RMSProp state advance in it.
+
+    VARIANT: this is the STOP-GRADIENT meta objective of dqn_mgsc_batched (agent.py:189-191, the target
+    `stop_gradient(θ_exp + rmsprop(g'))`).  The sibling dqn_mgsc_batched_reservoir/agent.py:160-198 omits that
+    stop_gradient (a second-order objective needing Hessian-vector products through the CNN); it is NOT implemented
+    (SURVEY 8f N4).  Pairing this agent with MGSCReservoirTransitionReplay therefore gives the first-order algorithm
+    on a reservoir replay, not the reference's reservoir agent; the attribute `meta_variant == 'stop_gradient'` says so (`statistics` must hold floats for the reference's trackers).
     """
 
     def __init__(self, *args, meta_optimizer: networks.AdamSpec, meta_batch_size: int, **kwargs):
@@ -280,6 +286,7 @@ class MGSCDqn(Dqn):
                                      b1=meta_optimizer.b1, b2=meta_optimizer.b2, eps=meta_optimizer.eps)
         self._last_transitions = []
         self._statistics['meta_loss'] = np.nan
+        self.meta_variant = 'stop_gradient'      # see the class docstring (N4 is not implemented)
 
     def step(self, timestep) -> parts.Action:
         self._frame_t += 1
