@@ -40,7 +40,8 @@ def ncu_gather_traffic():
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_gather*.csv")))
     for path in reversed(files):
         try:
-            rows = [r for r in csv.DictReader(open(path)) if "gather_stack4" in r.get("kernel", "")]
+            rows = [r for r in csv.DictReader(open(path)) if "gather_stack4" in r.get("kernel", "")
+                    and float(r.get("launch__grid_size []", 0) or 0) >= 1024]      # the n = 4096 launches only
             rd = [float(r["dram__bytes_read.sum [Mbyte]"]) for r in rows]
             wr = [float(r["dram__bytes_write.sum [Mbyte]"]) for r in rows]
             if rd:
