@@ -154,3 +154,71 @@ def backward(params, cache, dq):
                               params[name + ".w"], s, need_dx=(name != "conv1"))
         g[name + ".w"], g[name + ".b"] = dw, db
     return g
+
+
+def conv_dcols(d2, w, x_shape, ho, wo, s):
+    """Input gradient of a VALID conv from the flattened cotangent d2 (rows = output positions)."""
+    k, cout = w.shape[0], w.shape[3]
+    B = x_shape[0]
+    dcols = (d2 @ w.reshape(-1, cout).T).reshape(B, ho, wo, k, k, -1)
+    dx = np.zeros(x_shape, dtype=d2.dtype)
+    for i in range(k):
+        for j in range(k):
+            dx[:, i:i + s * ho:s, j:j + s * wo:s, :] += dcols[:, :, :, i, j, :]
+    return dx
+
+
+def hvp_backward(params, direction, cache, dq, dq_dot_fn):
+    """d/d(eps) of backward(params + eps*direction, ...) at eps = 0: the Hessian-vector product of the loss whose
+    cotangent on q is `dq` (forward-over-reverse; ReLU masks are locally constant).
+
+    Tangent forward:  zdot_l = W_l * xdot_{l-1} + Wdot_l * x_{l-1} + bdot_l,  xdot_l = mask_l . zdot_l
+    dq_dot_fn(qdot) -> tangent of dq (the loss head: d clip(td/B)/d eps = 1[|td/B| < bound] * (-qdot[a]/B)).
+    Tangent backward: ddot_{l-1} = mask . (W_l^T ddot_l + Wdot_l^T d_l),
+                      (grad W_l)dot = x_{l-1}^T ddot_l + xdot_{l-1}^T d_l,   (grad b_l)dot = sum ddot_l.
+    `cache` must come from forward(params, ..., keep=True) followed by backward() (it holds dy.* per layer)."""
+    v = direction
+    g = collections.OrderedDict((k, None) for k in params)
+    strides = {name: s for name, _, s, _, _ in LAYERS}
+    x, xdot = cache["x0"], None
+    tcols, shapes_in, tin = {}, {}, {}
+    for name, k, s, _, _ in LAYERS:
+        w, wd, bd = params[name + ".w"], v[name + ".w"], v[name + ".b"]
+        cols = cache[name + ".cols"]
+        out = cache[name + ".out"]
+        z = cols @ wd.reshape(-1, wd.shape[3]) + bd
+        shapes_in[name] = x.shape
+        if xdot is not None:
+            pd = _patches(xdot, k, s)
+            tcols[name] = pd.reshape(cols.shape[0], -1)
+            z = z + tcols[name] @ w.reshape(-1, w.shape[3])
+        tin[name] = xdot
+        xdot = (z.reshape(out.shape)) * (out > 0)
+        x = out
+    h0, h1 = cache["h0"], cache["h1"]
+    h0dot = xdot.reshape(h0.shape)
+    h1dot = (h0dot @ params["fc1.w"] + h0 @ v["fc1.w"] + v["fc1.b"]) * (h1 > 0)
+    qdot = h1dot @ params["fc2.w"] + h1 @ v["fc2.w"] + v["fc2.b"]
+    dqd = dq_dot_fn(qdot)
+    g["fc2.w"] = h1dot.T @ dq + h1.T @ dqd
+    g["fc2.b"] = dqd.sum().reshape(1) if params["fc2.b"].shape == (1,) else dqd.sum(0)
+    dh1 = cache["dy.fc1"]
+    dh1d = (dqd @ params["fc2.w"].T + dq @ v["fc2.w"].T) * (h1 > 0)
+    g["fc1.w"] = h0dot.T @ dh1 + h0.T @ dh1d
+    g["fc1.b"] = dh1d.sum(0)
+    dxd = (dh1d @ params["fc1.w"].T + dh1 @ v["fc1.w"].T).reshape(cache["conv3.out"].shape)
+    for name, k, s, _, _ in reversed(LAYERS):
+        w, wd = params[name + ".w"], v[name + ".w"]
+        out = cache[name + ".out"]
+        dy = cache["dy." + name]
+        dyd = dxd * (out > 0)
+        B, ho, wo, cout = dy.shape
+        d2, d2d = dy.reshape(-1, cout), dyd.reshape(-1, cout)
+        gw = cache[name + ".cols"].T @ d2d
+        if name in tcols:
+            gw = gw + tcols[name].T @ d2
+        g[name + ".w"] = gw.reshape(w.shape)
+        g[name + ".b"] = d2d.sum(0)
+        if name != "conv1":
+            dxd = conv_dcols(d2d, w, shapes_in[name], ho, wo, s) + conv_dcols(d2, wd, shapes_in[name], ho, wo, s)
+    return g

@@ -86,14 +86,41 @@ def update(online, target, mu, nu, batch, double_q=False, grad_bound=1.0 / 32, h
     return out
 
 
+def hvp(online, target, batch, direction, double_q=False, grad_bound=1.0 / 32, mean_over=None, weights=None):
+    """H . direction, H = Jacobian of jax.grad(loss_fn) w.r.t. the online params (what differentiating THROUGH
+    jax.grad(loss_fn)(expected_online_params, ...) needs, dqn_mgsc_batched_reservoir/agent.py:183-185).
+    rlax.clip_gradient's backward `clip(g)` is itself differentiated: 1 inside the bounds, 0 outside; the target
+    (and a double-Q selector) carry no gradient.  Returns the flat vector."""
+    out = loss_and_grads(online, target, batch, double_q, grad_bound, mean_over, weights)
+    s_tm1, a, r, disc, s_t = batch
+    a = np.asarray(a)
+    B = len(a)
+    rows = np.arange(B)
+    denom = B if mean_over is None else mean_over
+    w = np.ones(B) if weights is None else np.asarray(weights, dtype=np.float64)
+    inside = np.abs(out["td"] * w / denom) < grad_bound
+
+    def dq_dot(qdot):
+        d = np.zeros_like(qdot)
+        d[rows, a] = np.where(inside, qdot[rows, a] * w / denom, 0.0)     # -(d clip(td w / B)) with td_dot = -qdot[a]
+        return d
+    A = online["fc2.w"].shape[1]
+    shared = online["fc2.b"].shape == (1,)
+    v = direction if isinstance(direction, dict) else net.unflatten(np.asarray(direction), A, shared)
+    return net.flatten(net.hvp_backward(online, v, out["cache"], out["dq"], dq_dot))
+
+
 def softmax(logits):
     c = logits.max()
     return np.exp(logits - (c + np.log(np.sum(np.exp(logits - c)))))
 
 
 def meta_update(logits, meta_batch, online, target, online_transition, mu, nu, adam_m, adam_v,
-                adam_count, grad_bound=1.0 / 32, h=DQN_RMSPROP, ha=META_ADAM):
-    """MGSC meta_update (dqn_mgsc_batched/agent.py:160-220), stop-gradient variant.
+                adam_count, grad_bound=1.0 / 32, h=DQN_RMSPROP, ha=META_ADAM, second_order=False):
+    """MGSC meta_update (dqn_mgsc_batched/agent.py:160-220), stop-gradient variant; second_order=True is the
+    dqn_mgsc_batched_reservoir/agent.py:160-198 objective (no stop_gradient on target_online_params): the loss
+    ||theta_exp - theta_tgt||^2 = ||u'||^2 with u' = rmsprop(g'(theta_exp), (mu1, nu1)) differentiated through g'
+    (a Hessian-vector product), mu1 and nu1.
 
     Materialises the M per-sample gradients exactly like the reference's vmap
     (fine at oracle sizes).  Returns new logits, new Adam state and internals.
@@ -118,10 +145,23 @@ def meta_update(logits, meta_batch, online, target, online_transition, mu, nu, a
     theta_tgt, _, _ = rmsprop_step(theta_exp, g2, mu1, nu1, h)            # :189-191 (stop-grad)
     L = np.sum((theta_exp - theta_tgt) ** 2)                              # :195
     # dL/dG through theta_exp = theta - lr*G*rsqrt(nu1 - mu1^2 + eps), mu1, nu1 functions of G.
-    e = 2.0 * (theta_exp - theta_tgt)
     s = 1.0 / np.sqrt(nu1 - mu1 * mu1 + h.eps)
     du_dG = -h.lr * s * (1.0 - (1.0 - h.decay) * G * (G - mu1) * s * s)
-    v = e * du_dG
+    if not second_order:
+        e = 2.0 * (theta_exp - theta_tgt)
+        v = e * du_dG
+    else:
+        # L = ||u'||^2, u' = -lr g' s2, s2 = rsqrt(nu2 - mu2^2 + eps), mu2 = (1-d) g' + d mu1, nu2 = (1-d) g'^2 + d nu1
+        d = h.decay
+        mu2 = (1 - d) * g2 + d * mu1
+        nu2 = (1 - d) * g2 * g2 + d * nu1
+        s2 = 1.0 / np.sqrt(nu2 - mu2 * mu2 + h.eps)
+        e = 2.0 * (theta_tgt - theta_exp)                              # 2 u'
+        du_dg = -h.lr * (s2 - (1 - d) * g2 * (g2 - mu2) * s2 ** 3)      # direct + through mu2, nu2
+        du_dmu1 = -h.lr * g2 * d * mu2 * s2 ** 3
+        du_dnu1 = 0.5 * h.lr * g2 * d * s2 ** 3
+        t = hvp(net.unflatten(theta_exp, A, shared), online, one, e * du_dg, False, grad_bound)   # cotangent on theta_exp
+        v = t * du_dG + e * du_dmu1 * (1 - d) + e * du_dnu1 * 2 * (1 - d) * G
     dL_dp = per @ v
     dL_dlogits = p * (dL_dp - np.dot(p, dL_dp))
     new_logits, m2, v2, c2 = adam_step(np.asarray(logits, dtype=p.dtype), dL_dlogits,

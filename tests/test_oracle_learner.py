@@ -130,3 +130,38 @@ def test_meta_gradient_matches_autograd():
     scale = np.abs(dlogits).max()
     assert scale > 0
     assert np.abs(out["dL_dlogits"] - dlogits).max() / scale < 1e-8
+
+
+@pytest.mark.parametrize("double_q,shared,A,B", [(False, False, 6, 1), (True, True, 4, 5)])
+def test_hvp_matches_torch_double_backward(double_q, shared, A, B):
+    rng, online, target, _ = _setup(7, 1, A, shared)
+    batch = synthetic.random_batch(rng, B, A)
+    batch[2][0] = 40.0 if B > 1 else 0.3         # one clipped row in the batched case: its Gauss-Newton term vanishes
+    direction = {k: rng.normal(size=v.shape) * (1.0 / np.sqrt(v.size)) for k, v in online.items()}
+    w = rng.random(B) if B > 1 else None
+    got = net.unflatten(upd.hvp(online, target, batch, direction, double_q, weights=w), A, shared)
+    want = torch_ref.hvp(online, target, batch, direction, double_q, weights=w)
+    for k in want:
+        scale = np.abs(want[k]).max() + 1e-30
+        assert np.abs(got[k] - want[k]).max() / scale < 1e-9, k
+
+
+def test_second_order_meta_gradient_matches_autograd():
+    # dqn_mgsc_batched_reservoir/agent.py:160-198: autograd through g'(theta_exp), mu1, nu1 (no stop_gradient)
+    rng, online, target, _ = _setup(8, 1, 6, False)
+    M = 3
+    meta_batch = synthetic.random_batch(rng, M, 6)
+    ot = tuple(x[0] for x in synthetic.random_batch(rng, 1, 6))
+    P = net.flatten(online).size
+    mu = rng.normal(size=P) * 1e-3
+    nu = mu ** 2 + rng.random(P) * 1e-4
+    logits = rng.normal(size=M)
+    out = upd.meta_update(logits, meta_batch, online, target, ot, mu, nu, np.zeros(M), np.zeros(M), 0,
+                          second_order=True)
+    L, dlogits = torch_ref.meta_grad(logits, meta_batch, online, target, ot, mu, nu, second_order=True)
+    assert abs(out["loss"] - L) < 1e-10 * max(1.0, abs(L))
+    scale = np.abs(dlogits).max()
+    assert scale > 0
+    assert np.abs(out["dL_dlogits"] - dlogits).max() / scale < 1e-7
+    first = upd.meta_update(logits, meta_batch, online, target, ot, mu, nu, np.zeros(M), np.zeros(M), 0)
+    assert np.abs(first["dL_dlogits"] - out["dL_dlogits"]).max() / scale > 1e-3      # the two objectives differ

@@ -85,8 +85,20 @@ def _rmsprop(theta, g, mu, nu, lr, decay, eps):
     return theta + (-lr) * g * torch.rsqrt(nu2 - mu2 * mu2 + eps), mu2, nu2
 
 
+def hvp(online_np, target_np, batch, direction_np, double_q=False, grad_bound=1.0 / 32, weights=None):
+    """Hessian-vector product by double backward through loss_fn (clip_gradient's backward is differentiable)."""
+    online = to_torch(online_np, torch.float64, requires_grad=True)
+    target = to_torch(target_np, torch.float64)
+    loss, _ = loss_fn(online, target, batch, double_q, grad_bound, weights)
+    g = torch.autograd.grad(loss, list(online.values()), create_graph=True)
+    d = to_torch(direction_np, torch.float64)
+    inner = sum((gi * d[k]).sum() for gi, k in zip(g, online))
+    hv = torch.autograd.grad(inner, list(online.values()))
+    return {k: x.numpy() for k, x in zip(online, hv)}
+
+
 def meta_grad(logits_np, meta_batch, online_np, target_np, online_transition, mu_np, nu_np,
-              grad_bound=1.0 / 32, lr=0.00025, decay=0.95, eps=0.01 / 32 ** 2):
+              grad_bound=1.0 / 32, lr=0.00025, decay=0.95, eps=0.01 / 32 ** 2, second_order=False):
     """d meta_loss / d logits by autograd through a literal transcription of meta_loss_fn."""
     dt = torch.float64
     online = to_torch(online_np, dt, requires_grad=True)
@@ -105,6 +117,14 @@ def meta_grad(logits_np, meta_batch, online_np, target_np, online_transition, mu
     G = torch.stack(weighted).sum(0)
     theta = _flat(online).detach()
     theta_exp, mu1, nu1 = _rmsprop(theta, G, mu, nu, lr, decay, eps)
+    if second_order:      # dqn_mgsc_batched_reservoir/agent.py:183-195: no stop_gradient anywhere
+        one = tuple(np.asarray(x)[None, ...] for x in online_transition)
+        l2, _ = loss_fn(_unflat(theta_exp, online), {k: v.detach() for k, v in online.items()}, one, False, grad_bound)
+        g2 = torch.autograd.grad(l2, theta_exp, create_graph=True)[0]
+        theta_tgt, _, _ = _rmsprop(theta_exp, g2, mu1, nu1, lr, decay, eps)
+        L = torch.sum((theta_exp - theta_tgt) ** 2)
+        (dlogits,) = torch.autograd.grad(L, logits)
+        return float(L), dlogits.numpy()
     # gradient at the expected params with the *online* params as target net (agent.py:183-185)
     exp_leaf = theta_exp.detach().clone().requires_grad_(True)
     one = tuple(np.asarray(x)[None, ...] for x in online_transition)
