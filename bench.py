@@ -633,6 +633,19 @@ def bench_mgsc(args, timed, device, rank):
     torch.cuda.synchronize()
     t_all = pc() - t_all
     us = {k: v / steps * 1e6 for k, v in acc.items()}
+    # the second-order objective of dqn_mgsc_batched_reservoir (Hessian-vector product through the CNN), same meta batch
+    meta2 = lrn.MetaLearner(L, M, second_order=True)
+    tr = rp.Transition(*src.next())
+    idx, slots, lg = replay.batch_of_ids_slots_and_logits(M)
+    for _ in range(3):
+        meta2.meta_update_from_replay(store, slots, lg, tr)
+    torch.cuda.synchronize()
+    t = pc()
+    for _ in range(50):
+        meta2.meta_update_from_replay(store, slots, lg, tr)
+    torch.cuda.synchronize()
+    us["meta-update-second-order"] = (pc() - t) / 50 * 1e6
+    meta2.close()
     out = {"capacity": cap, "meta_batch": M, "phase_us": us, "step_us": t_all / steps * 1e6,
            "steps_per_s": steps / t_all, "fill_seconds": fill,
            "reference_phase_us_v100": {"replay-add": 800, "replay-sample-meta-batch": 55600, "meta-update": 4100,

@@ -49,6 +49,7 @@ SIGNATURES = {
     "dqnb_learner_write_dev": [c_vp, c_int, c_vp, c_i64, STREAM],
     "dqnb_learner_apply_grads": [c_vp, STREAM],
     "dqnb_learner_adjoint_dots": [c_vp, c_vp, c_vp, STREAM],
+    "dqnb_learner_hvp": [c_vp, c_vp, c_vp, STREAM],
     "dqnb_dp_unique_id": [c_vp],
     "dqnb_dp_init": [c_vp, c_vp, c_int, c_int],
     "dqnb_dp_allreduce": [c_vp, STREAM],

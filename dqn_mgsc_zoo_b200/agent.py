@@ -272,21 +272,27 @@ class MGSCDqn(Dqn):
     runs on the device (dqnb_mgsc_meta_update: one row-weighted batched backward, two virtual RMSProp steps,
     softmax backward, Adam on the logits); neither params nor RMSProp state advance in it.
 
-    VARIANT: this is the STOP-GRADIENT meta objective of dqn_mgsc_batched (agent.py:189-191, the target
-    `stop_gradient(θ_exp + rmsprop(g'))`).  The sibling dqn_mgsc_batched_reservoir/agent.py:160-198 omits that
-    stop_gradient (a second-order objective needing Hessian-vector products through the CNN); it is NOT implemented
-    (SURVEY 8f N4).  Pairing this agent with MGSCReservoirTransitionReplay therefore gives the first-order algorithm
-    on a reservoir replay, not the reference's reservoir agent; the attribute `meta_variant == 'stop_gradient'` says so (`statistics` must hold floats for the reference's trackers).
+    VARIANT: `second_order=False` (default) is the STOP-GRADIENT meta objective of dqn_mgsc_batched
+    (agent.py:189-191, target `stop_gradient(theta_exp + rmsprop(g'))`).  `second_order=True` is the objective of the
+    sibling dqn_mgsc_batched_reservoir/agent.py:160-198, which omits that stop_gradient: the meta loss is
+    differentiated through the gradient at the expected parameters (a Hessian-vector product through the CNN,
+    dqnb_learner_hvp) and through the optimiser state; `MGSCReservoirDqn` below is that agent.  The attribute
+    `meta_variant` ('stop_gradient' / 'second_order') says which one runs (`statistics` must hold floats for the
+    reference's trackers).
     """
 
-    def __init__(self, *args, meta_optimizer: networks.AdamSpec, meta_batch_size: int, **kwargs):
+    _SECOND_ORDER = False
+
+    def __init__(self, *args, meta_optimizer: networks.AdamSpec, meta_batch_size: int, second_order=None, **kwargs):
         super().__init__(*args, **kwargs)
         self._meta_batch_size = meta_batch_size
+        second_order = self._SECOND_ORDER if second_order is None else bool(second_order)
         self._meta = lrn.MetaLearner(self._learner, meta_batch_size, learning_rate=meta_optimizer.learning_rate,
-                                     b1=meta_optimizer.b1, b2=meta_optimizer.b2, eps=meta_optimizer.eps)
+                                     b1=meta_optimizer.b1, b2=meta_optimizer.b2, eps=meta_optimizer.eps,
+                                     second_order=second_order)
         self._last_transitions = []
         self._statistics['meta_loss'] = np.nan
-        self.meta_variant = 'stop_gradient'      # see the class docstring (N4 is not implemented)
+        self.meta_variant = 'second_order' if second_order else 'stop_gradient'      # see the class docstring
 
     def step(self, timestep) -> parts.Action:
         self._frame_t += 1
@@ -354,3 +360,11 @@ class MGSCDqn(Dqn):
         super().set_state(state)
         adam = state['meta_opt_state'][0]
         self._meta.set_state({'count': adam.count, 'mu': adam.mu, 'nu': adam.nu})
+
+
+class MGSCReservoirDqn(MGSCDqn):
+    """The MGSCDqn of dqn_mgsc_batched_reservoir/agent.py:42-402: same agent, meta loss WITHOUT stop_gradient on the
+    target parameters (:183-195), meant for `replay_circular.MGSCReservoirTransitionReplay`
+    (dqn_mgsc_batched_reservoir/run_atari.py:211)."""
+
+    _SECOND_ORDER = True

@@ -14,10 +14,25 @@
 #include "gemm_tf32_stream.cuh"
 #include "act_kernel.cuh"
 #include "nccl_dyn.cuh"
+#include "hvp_kernels.cuh"
 
 using namespace dqnb;
 
 namespace {
+
+// The layer functors with their shape constants visible to generic lambdas (enqueue_hvp).
+template <class L, class TIn, int BM>
+struct HvpConvFwd : ConvFwd<L, TIn, BM> {
+  static constexpr int LAYER_OUT = L::HOUT * L::WOUT, LAYER_COUT = L::COUT, LAYER_KCOL = L::KCOL;
+};
+template <class L, class TIn>
+struct HvpConvWgrad : ConvWgrad<L, TIn> {
+  static constexpr int LAYER_OUT = L::HOUT * L::WOUT, LAYER_COUT = L::COUT, LAYER_KCOL = L::KCOL;
+};
+template <class L>
+struct HvpConvDgrad : ConvDgrad<L> {
+  static constexpr int LAYER_CIN = L::CIN, LAYER_COUT = L::COUT;
+};
 
 struct ArenaLayout {
   int64_t w1, b1, w2, b2, w3, b3, fw1, fb1, fw2, fb2, total;
@@ -147,6 +162,16 @@ struct dqnb_learner {
   cudaEvent_t ev[8] = {};
   int64_t updates = 0;
   int64_t launches_per_update = 0;
+  // Hessian-vector product (dqnb_learner_hvp): tangent activations / cotangents, two temporaries per direction,
+  // two gradient-shaped arenas and its own split-K scratch (the update graphs keep theirs); allocated on first use.
+  struct Hvp {
+    float *x1d = nullptr, *x2d = nullptr, *x3d = nullptr, *h1d = nullptr;      // tangent activations
+    float *dh1d = nullptr, *dy3d = nullptr, *dy2d = nullptr, *dy1d = nullptr;  // tangent cotangents
+    float *tu = nullptr, *tv = nullptr, *dqd = nullptr, *zero = nullptr;       // temporaries, dq tangent, zero bias
+    float *ga = nullptr, *gb = nullptr;                                        // gradient-shaped partial results
+    float* ws = nullptr; unsigned* counters = nullptr;
+    bool ready = false;
+  } hvp;
   // Data-parallel mode (dqnb_dp_init): the update graph itself all-reduces the gradient arena over NCCL - the
   // fc1 + fc2 part as soon as their weight gradients exist, the convolution part at the end - and then applies
   // the optimiser step, so one graph launch per rank is the whole data-parallel update.
@@ -753,6 +778,113 @@ int enqueue_adjoint(dqnb_learner* h, const float* v, float* out, cudaStream_t st
   return DQNB_OK;
 }
 
+// H . v on the batch of the last update (see hvp_kernels.cuh).  fp32 SIMT GEMMs in both precision modes, one stream.
+int enqueue_hvp(dqnb_learner* h, const float* v, float* out, cudaStream_t st) {
+  h->ws_off = h->cnt_off = 0;
+  const int B = h->B;
+  const bool live = !h->sizing;
+  dqnb_learner::Hvp& q = h->hvp;
+  const float* th = h->online;
+  const ArenaLayout& L = h->L;
+  auto add_mask = [&](const float* u, const float* w, const float* act, float* o, int64_t n) -> int {
+    if (!live) return DQNB_OK;
+    hvp_add_mask_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(u, w, act, o, n);
+    DQNB_CUDA(cudaGetLastError());
+    return DQNB_OK;
+  };
+  auto conv_lin = [&](auto p, auto xin, const float* w, const float* bias, float* y) -> int {
+    using P = decltype(p);
+    p.linear = 1;
+    p.M = B * P::LAYER_OUT; p.N = P::LAYER_COUT; p.K = P::LAYER_KCOL;
+    p.x[0] = xin; p.w[0] = w; p.bias[0] = bias; p.y[0] = y;
+    return run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st);
+  };
+  auto dense_lin = [&](const float* xin, const float* w, const float* bias, float* y) -> int {
+    DenseFwd p;
+    p.linear = 1;
+    p.M = B; p.N = kFc1Out; p.K = kFc1In;
+    p.x[0] = xin; p.w[0] = w; p.bias[0] = bias; p.y[0] = y;
+    return run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st);
+  };
+  // ---- tangent forward
+  DQNB_TRY(conv_lin(HvpConvFwd<Conv1, uint8_t, 64>{}, (const uint8_t*)h->s_tm1, v + L.w1, v + L.b1, q.tu));
+  DQNB_TRY(add_mask(q.tu, nullptr, h->a1[0], q.x1d, (int64_t)B * Conv1::OUT_PER_IMG));
+  DQNB_TRY(conv_lin(HvpConvFwd<Conv2, float, 32>{}, (const float*)q.x1d, th + L.w2, q.zero, q.tu));
+  DQNB_TRY(conv_lin(HvpConvFwd<Conv2, float, 32>{}, (const float*)h->a1[0], v + L.w2, v + L.b2, q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, h->a2[0], q.x2d, (int64_t)B * Conv2::OUT_PER_IMG));
+  DQNB_TRY(conv_lin(HvpConvFwd<Conv3, float, 32>{}, (const float*)q.x2d, th + L.w3, q.zero, q.tu));
+  DQNB_TRY(conv_lin(HvpConvFwd<Conv3, float, 32>{}, (const float*)h->a2[0], v + L.w3, v + L.b3, q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, h->a3[0], q.x3d, (int64_t)B * Conv3::OUT_PER_IMG));
+  DQNB_TRY(dense_lin(q.x3d, th + L.fw1, q.zero, q.tu));
+  DQNB_TRY(dense_lin(h->a3[0], v + L.fw1, v + L.fb1, q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, h->h1[0], q.h1d, (int64_t)B * kFc1Out));
+  // ---- fc2 / TD head
+  if (live) {
+    HvpHeadArgs g;
+    g.num_actions = h->A; g.shared_bias = h->cfg.shared_bias; g.weight_inside = h->cfg.row_weighted == 2;
+    g.grad_bound = h->cfg.grad_error_bound;
+    g.inv_mean = 1.0f / (float)(h->cfg.loss_mean_over > 0 ? h->cfg.loss_mean_over : B);
+    g.h1 = h->h1[0]; g.h1dot = q.h1d; g.w2 = th + L.fw2; g.v_w2 = v + L.fw2; g.v_b2 = v + L.fb2;
+    g.action = h->act; g.td = h->td; g.dq_taken = h->dq_taken; g.row_weight = h->row_weight;
+    g.dq_dot = q.dqd; g.dh1_dot = q.dh1d;
+    hvp_head_kernel<<<B, 128, 0, st>>>(g);
+    const int n = kFc1Out * h->A;
+    hvp_fc2_kernel<<<(n + 255) / 256, 256, 0, st>>>(B, h->A, h->cfg.shared_bias, h->h1[0], q.h1d, h->act, h->dq_taken,
+                                                    q.dqd, q.ga + L.fw2, q.ga + L.fb2);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  // ---- tangent backward
+  auto dense_wgrad = [&](const float* xin, const float* dy, float* grad) -> int {
+    DenseWgrad p;
+    p.M = kFc1In + 1; p.N = kFc1Out; p.K = B;
+    p.x = xin; p.dy = dy; p.grad = grad;
+    return run_gemm(h, p, 1, 1, st);
+  };
+  auto dense_dgrad = [&](const float* dy, const float* w, float* dx) -> int {
+    DenseDgrad p;
+    p.M = B; p.N = kFc1In; p.K = kFc1Out;
+    p.dy = dy; p.w = w; p.act = h->a3[0]; p.dx = dx;
+    return run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st);
+  };
+  auto conv_wg = [&](auto p, auto xin, const float* dy, float* grad) -> int {
+    using P = decltype(p);
+    p.M = P::LAYER_KCOL + 1; p.N = P::LAYER_COUT; p.K = B * P::LAYER_OUT;
+    p.x = xin; p.dy = dy; p.grad = grad;
+    return run_gemm(h, p, 1, pick_splits(gemm_tiles(p, 1), p.K), st);
+  };
+  auto conv_dg = [&](auto p, const float* dy, const float* w, const float* act_in, float* dx) -> int {
+    using P = decltype(p);
+    p.M = B * P::NY * P::NX; p.N = P::LAYER_CIN; p.K = P::T * P::T * P::LAYER_COUT;
+    p.dy = dy; p.w = w; p.act_in = act_in; p.dx = dx;
+    const int Z = P::S * P::S;
+    return run_gemm(h, p, Z, pick_splits(gemm_tiles(p, Z), p.K), st);
+  };
+  DQNB_TRY(dense_wgrad(h->a3[0], q.dh1d, q.ga + L.fw1));
+  DQNB_TRY(dense_wgrad(q.x3d, h->dh1, q.gb + L.fw1));
+  DQNB_TRY(dense_dgrad(q.dh1d, th + L.fw1, q.tu));
+  DQNB_TRY(dense_dgrad(h->dh1, v + L.fw1, q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, nullptr, q.dy3d, (int64_t)B * Conv3::OUT_PER_IMG));
+  DQNB_TRY(conv_wg(HvpConvWgrad<Conv3, float>{}, (const float*)h->a2[0], q.dy3d, q.ga + L.w3));
+  DQNB_TRY(conv_wg(HvpConvWgrad<Conv3, float>{}, (const float*)q.x2d, h->dy3, q.gb + L.w3));
+  DQNB_TRY(conv_dg(HvpConvDgrad<Conv3>{}, q.dy3d, th + L.w3, h->a2[0], q.tu));
+  DQNB_TRY(conv_dg(HvpConvDgrad<Conv3>{}, h->dy3, v + L.w3, h->a2[0], q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, nullptr, q.dy2d, (int64_t)B * Conv2::OUT_PER_IMG));
+  DQNB_TRY(conv_wg(HvpConvWgrad<Conv2, float>{}, (const float*)h->a1[0], q.dy2d, q.ga + L.w2));
+  DQNB_TRY(conv_wg(HvpConvWgrad<Conv2, float>{}, (const float*)q.x1d, h->dy2, q.gb + L.w2));
+  DQNB_TRY(conv_dg(HvpConvDgrad<Conv2>{}, q.dy2d, th + L.w2, h->a1[0], q.tu));
+  DQNB_TRY(conv_dg(HvpConvDgrad<Conv2>{}, h->dy2, v + L.w2, h->a1[0], q.tv));
+  DQNB_TRY(add_mask(q.tu, q.tv, nullptr, q.dy1d, (int64_t)B * Conv1::OUT_PER_IMG));
+  DQNB_TRY(conv_wg(HvpConvWgrad<Conv1, uint8_t>{}, (const uint8_t*)h->s_tm1, q.dy1d, q.ga + L.w1));
+  if (live) {
+    HvpBiasRanges r;
+    r.lo[0] = L.b1; r.hi[0] = L.w2; r.lo[1] = L.b2; r.hi[1] = L.w3; r.lo[2] = L.b3; r.hi[2] = L.fw1;
+    r.lo[3] = L.fb1; r.hi[3] = L.fw2;
+    hvp_combine_kernel<<<(unsigned)((L.total + 255) / 256), 256, 0, st>>>(q.ga, q.gb, out, L.total, r);
+    DQNB_CUDA(cudaGetLastError());
+  }
+  return DQNB_OK;
+}
+
 int build_graph(dqnb_learner* h, cudaGraphExec_t* out) {
   cudaStream_t cap;
   DQNB_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
@@ -906,6 +1038,12 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
   for (float* p : fl) cudaFree(p);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1[z]); cudaFree(h->a2[z]); cudaFree(h->a3[z]); cudaFree(h->h1[z]); cudaFree(h->q[z]); }
   cudaFree(h->s_tm1); cudaFree(h->s_t); cudaFree(h->act); cudaFree(h->counters); cudaFree(h->d_slots);
+  {
+    dqnb_learner::Hvp& q = h->hvp;
+    float* hb[] = {q.x1d, q.x2d, q.x3d, q.h1d, q.dh1d, q.dy3d, q.dy2d, q.dy1d, q.tu, q.tv, q.dqd, q.zero, q.ga, q.gb, q.ws};
+    for (float* b : hb) cudaFree(b);
+    cudaFree(q.counters);
+  }
   cudaFree(h->conv1_h16); cudaFree(h->conv23_h16);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1h[z]); cudaFree(h->a2h[z]); }
   for (auto& s : h->side) if (s) cudaStreamDestroy(s);
@@ -1109,6 +1247,39 @@ extern "C" int dqnb_dp_info(dqnb_learner* h, int* rank, int* world, int* nccl_ve
     if (nccl) nccl->GetVersion(nccl_version);
   }
   return DQNB_OK;
+}
+
+// H . v, H = Jacobian of the loss gradient w.r.t. the online parameters at the batch (and td errors, clip decisions,
+// ReLU masks) of the LAST update of this learner; v_dev / out_dev are device vectors laid out like the parameters.
+extern "C" int dqnb_learner_hvp(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream) {
+  DQNB_REQUIRE(h && v_dev && out_dev, "null argument");
+  DQNB_REQUIRE(h->updates > 0, "the Hessian-vector product is taken at the batch of the last update: run one first");
+  DeviceGuard guard(h->device);
+  dqnb_learner::Hvp& q = h->hvp;
+  float* const ws_keep = h->ws; unsigned* const cnt_keep = h->counters;
+  const int64_t launches = h->launches_per_update;
+  if (!q.ready) {
+    const size_t B = h->B, P = h->L.total;
+    const size_t big = B * Conv1::OUT_PER_IMG;
+    DQNB_TRY(dmalloc(&q.x1d, B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&q.x2d, B * Conv2::OUT_PER_IMG));
+    DQNB_TRY(dmalloc(&q.x3d, B * Conv3::OUT_PER_IMG)); DQNB_TRY(dmalloc(&q.h1d, B * kFc1Out));
+    DQNB_TRY(dmalloc(&q.dh1d, B * kFc1Out)); DQNB_TRY(dmalloc(&q.dy3d, B * Conv3::OUT_PER_IMG));
+    DQNB_TRY(dmalloc(&q.dy2d, B * Conv2::OUT_PER_IMG)); DQNB_TRY(dmalloc(&q.dy1d, B * Conv1::OUT_PER_IMG));
+    DQNB_TRY(dmalloc(&q.tu, big)); DQNB_TRY(dmalloc(&q.tv, big)); DQNB_TRY(dmalloc(&q.dqd, B));
+    DQNB_TRY(dmalloc(&q.zero, (size_t)kFc1Out)); DQNB_TRY(dmalloc(&q.ga, P)); DQNB_TRY(dmalloc(&q.gb, P));
+    h->sizing = true;
+    int rc = enqueue_hvp(h, v_dev, out_dev, nullptr);
+    h->sizing = false;
+    h->launches_per_update = launches;
+    DQNB_TRY(rc);
+    DQNB_TRY(dmalloc(&q.ws, h->ws_off)); DQNB_TRY(dmalloc(&q.counters, h->cnt_off));
+    q.ready = true;
+  }
+  h->ws = q.ws; h->counters = q.counters;
+  const int rc = enqueue_hvp(h, v_dev, out_dev, as_stream(stream));
+  h->ws = ws_keep; h->counters = cnt_keep;
+  h->launches_per_update = launches;
+  return rc;
 }
 
 extern "C" int dqnb_learner_adjoint_dots(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream) {

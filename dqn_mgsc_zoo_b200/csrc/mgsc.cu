@@ -83,6 +83,49 @@ __global__ void meta_v_kernel(const float* __restrict__ g2, const float* __restr
   if (threadIdx.x == 0) loss_part[blockIdx.x] = red[0];
 }
 
+// Second-order objective (dqn_mgsc_batched_reservoir/agent.py:160-198: no stop_gradient on target_online_params):
+//   L = |theta_exp - theta_tgt|^2 = sum u2^2,  u2 = -lr g2 s2,  s2 = rsqrt(nu2 - mu2^2 + eps),
+//   mu2 = (1-d) g2 + d mu1,  nu2 = (1-d) g2^2 + d nu1,  g2 = grad loss(theta_exp)  - all functions of G.
+// This kernel forms the cotangent on g2 (wdir = 2 u2 * du2/dg2, the direction of the Hessian-vector product) and the
+// part of dL/dG that flows through mu1 and nu1 (extra); meta_second_finish_kernel adds the part through theta_exp.
+__global__ void meta_second_kernel(const float* __restrict__ g2, const float* __restrict__ G, const float* __restrict__ mu1,
+                                   const float* __restrict__ nu1, float* __restrict__ wdir, float* __restrict__ extra,
+                                   float* __restrict__ loss_part, int64_t P, float lr, float decay, float eps) {
+  __shared__ float red[256];
+  const float om = 1.0f - decay;
+  float acc = 0.f;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < P; j += (int64_t)gridDim.x * blockDim.x) {
+    const float g = g2[j], m1 = mu1[j], n1 = nu1[j], gg = G[j];
+    const float m2 = om * g + decay * m1;
+    const float n2 = om * (g * g) + decay * n1;
+    const float s2 = rsqrtf(n2 - m2 * m2 + eps), s23 = s2 * s2 * s2;
+    const float u2 = (-lr) * (g * s2);
+    acc = fmaf(u2, u2, acc);
+    const float e = 2.0f * u2;
+    const float du_dg = (-lr) * (s2 - om * g * (g - m2) * s23);
+    const float du_dmu1 = (-lr) * g * decay * m2 * s23;
+    const float du_dnu1 = 0.5f * lr * g * decay * s23;
+    wdir[j] = e * du_dg;
+    extra[j] = e * du_dmu1 * om + e * du_dnu1 * 2.0f * om * gg;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) loss_part[blockIdx.x] = red[0];
+}
+// v = (H wdir) * d theta_exp / dG + extra
+__global__ void meta_second_finish_kernel(const float* __restrict__ t, const float* __restrict__ G,
+                                          const float* __restrict__ mu1, const float* __restrict__ nu1,
+                                          const float* __restrict__ extra, float* __restrict__ v, int64_t P, float lr,
+                                          float decay, float eps) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P) return;
+  const float om = 1.0f - decay, m1 = mu1[j], gg = G[j];
+  const float s = rsqrtf(nu1[j] - m1 * m1 + eps);
+  const float du = (-lr) * s * (1.0f - om * gg * (gg - m1) * s * s);
+  v[j] = t[j] * du + extra[j];
+}
+
 // softmax backward + optax.adam (scale_by_adam bias-corrected, eps outside the sqrt) on the logits.
 // One block; M <= kMaxMeta.
 // `wdot[i]` = <v, p_i g_i>: dL/dp_i = wdot[i] / p_i.  A p_i that underflowed leaves dL/dp_i = 0: its
@@ -136,6 +179,7 @@ struct dqnb_mgsc {
   int32_t* mb_a = nullptr;
   float *mb_r = nullptr, *mb_d = nullptr;
   float *G = nullptr, *theta_exp = nullptr, *mu1 = nullptr, *nu1 = nullptr, *v = nullptr;
+  float *wdir = nullptr, *extra = nullptr, *hv = nullptr;      // second-order objective only
   float *logits = nullptr, *p = nullptr, *dldp = nullptr, *dot_part = nullptr, *loss_part = nullptr;
   float *adam_m = nullptr, *adam_v = nullptr, *out = nullptr;   // out: [M] new logits + [1] loss
   float* pinned = nullptr;                                      // [2M + 8]
@@ -182,8 +226,18 @@ int run_meta_update(dqnb_mgsc* h, float* new_logits_host, float* meta_loss_host,
   DQNB_TRY(dqnb_learner_write_dev(h->sub, DQNB_TARGET, static_cast<const float*>(theta), P, s));
   DQNB_TRY(dqnb_learner_update(h->sub, h->mb_s0 + M * h->img, h->mb_a + M, h->mb_r + M, h->mb_d + M,
                                h->mb_s1 + M * h->img, s));
-  meta_v_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->v,
-                                             h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
+  if (h->cfg.second_order) {
+    meta_second_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->wdir,
+                                                    h->extra, h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay,
+                                                    h->lcfg.eps);
+    DQNB_CUDA(cudaGetLastError());
+    DQNB_TRY(dqnb_learner_hvp(h->sub, h->wdir, h->hv, s));     // at theta_exp, on the online transition
+    meta_second_finish_kernel<<<pb, 256, 0, st>>>(h->hv, h->G, h->mu1, h->nu1, h->extra, h->v, P,
+                                                  h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
+  } else {
+    meta_v_kernel<<<kLossBlocks, 256, 0, st>>>(static_cast<const float*>(sub_grad), h->G, h->mu1, h->nu1, h->v,
+                                               h->loss_part, P, h->lcfg.learning_rate, h->lcfg.decay, h->lcfg.eps);
+  }
   DQNB_TRY(dqnb_learner_adjoint_dots(h->bat, h->v, h->dot_part, s));
   logits_adam_kernel<<<1, 256, 0, st>>>(h->logits, h->p, h->dot_part, h->loss_part, h->dldp, h->adam_m, h->adam_v,
                                         h->out, h->out + M, M, h->count + 1, h->cfg.learning_rate, h->cfg.b1,
@@ -249,6 +303,7 @@ extern "C" int dqnb_mgsc_create(dqnb_learner* learner, const dqnb_mgsc_config* c
   DQNB_TRY(dalloc(&h->mb_a, M1)); DQNB_TRY(dalloc(&h->mb_r, M1)); DQNB_TRY(dalloc(&h->mb_d, M1));
   DQNB_TRY(dalloc(&h->G, P)); DQNB_TRY(dalloc(&h->theta_exp, P)); DQNB_TRY(dalloc(&h->mu1, P));
   DQNB_TRY(dalloc(&h->nu1, P)); DQNB_TRY(dalloc(&h->v, P));
+  if (h->cfg.second_order) { DQNB_TRY(dalloc(&h->wdir, P)); DQNB_TRY(dalloc(&h->extra, P)); DQNB_TRY(dalloc(&h->hv, P)); }
   DQNB_TRY(dalloc(&h->logits, M1)); DQNB_TRY(dalloc(&h->p, M1)); DQNB_TRY(dalloc(&h->dldp, M1));
   DQNB_TRY(dalloc(&h->dot_part, M1)); DQNB_TRY(dalloc(&h->loss_part, kLossBlocks));
   DQNB_TRY(dalloc(&h->adam_m, M1)); DQNB_TRY(dalloc(&h->adam_v, M1)); DQNB_TRY(dalloc(&h->out, M1 + 1));
@@ -268,7 +323,8 @@ extern "C" int dqnb_mgsc_destroy(dqnb_mgsc* h) {
   if (h->sub) dqnb_learner_destroy(h->sub);
   if (h->bat) dqnb_learner_destroy(h->bat);
   void* bufs[] = {h->mb_s0, h->mb_s1, h->mb_a, h->mb_r, h->mb_d, h->G, h->theta_exp, h->mu1, h->nu1, h->v,
-                  h->logits, h->p, h->dldp, h->dot_part, h->loss_part, h->adam_m, h->adam_v, h->out};
+                  h->logits, h->p, h->dldp, h->dot_part, h->loss_part, h->adam_m, h->adam_v, h->out,
+                  h->wdir, h->extra, h->hv};
   for (void* b : bufs) cudaFree(b);
   if (h->pinned) cudaFreeHost(h->pinned);
   if (h->pinned_on) cudaFreeHost(h->pinned_on);

@@ -150,6 +150,24 @@ class Learner:
         self.loss_post()
         return self.loss_take() if self._loss_outstanding > 1 else None
 
+    def hvp(self, direction):
+        """H . direction at the batch of the last update (dqnb_learner_hvp); flat float32 in, flat float32 out."""
+        v = np.ascontiguousarray(direction, dtype=np.float32).ravel()
+        if v.size != self.num_params:
+            raise ValueError("direction has %d entries, the learner %d parameters" % (v.size, self.num_params))
+        dv, do = ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.call("dqnb_dev_alloc", self.device, v.nbytes, ctypes.byref(dv))
+        _lib.call("dqnb_dev_alloc", self.device, v.nbytes, ctypes.byref(do))
+        try:
+            _lib.call("dqnb_copy_h2d", dv, v.ctypes.data, v.nbytes, self.stream)
+            _lib.call("dqnb_learner_hvp", self._h, dv, do, self.stream)
+            out = np.empty_like(v)
+            _lib.call("dqnb_copy_d2h", out.ctypes.data, do, out.nbytes, self.stream)
+        finally:
+            _lib.call("dqnb_dev_free", self.device, dv)
+            _lib.call("dqnb_dev_free", self.device, do)
+        return out
+
     def set_row_weights(self, weights):
         """Host write of DQNB_ROW_WEIGHT (synchronous): the weights the next update(s) will use."""
         w = np.ascontiguousarray(weights, dtype=np.float32)
@@ -221,7 +239,8 @@ class Learner:
 
 class MgscConfig(ctypes.Structure):
     _fields_ = [("meta_batch_size", ctypes.c_int32), ("learning_rate", ctypes.c_float),
-                ("b1", ctypes.c_float), ("b2", ctypes.c_float), ("eps", ctypes.c_float)]
+                ("b1", ctypes.c_float), ("b2", ctypes.c_float), ("eps", ctypes.c_float),
+                ("second_order", ctypes.c_int32)]
 
 
 MGSC_ADAM_M, MGSC_ADAM_V, MGSC_P, MGSC_DL_DP, MGSC_G, MGSC_V, MGSC_THETA_EXP = range(7)
@@ -234,11 +253,13 @@ class MetaLearner:
     the (meta_batch_size,) logits vector.
     """
 
-    def __init__(self, learner: Learner, meta_batch_size, learning_rate=0.00025, b1=0.9, b2=0.999, eps=1e-8):
+    def __init__(self, learner: Learner, meta_batch_size, learning_rate=0.00025, b1=0.9, b2=0.999, eps=1e-8,
+                 second_order=False):
         if learner.double_q:
             raise ValueError("MGSC uses the q_learning loss: the learner must have double_q=False")
         self.learner, self.meta_batch_size = learner, int(meta_batch_size)
-        cfg = MgscConfig(self.meta_batch_size, learning_rate, b1, b2, eps)
+        self.second_order = bool(second_order)
+        cfg = MgscConfig(self.meta_batch_size, learning_rate, b1, b2, eps, int(self.second_order))
         h = ctypes.c_void_p()
         _lib.call("dqnb_mgsc_create", learner._h, ctypes.byref(cfg), ctypes.byref(h))
         self._h = h

@@ -182,6 +182,13 @@ int dqnb_dp_info(dqnb_learner* h, int* rank, int* world, int* nccl_version);
  * one dot kernel instead of `batch` materialised per-sample gradients (the reference's
  * jax.vmap(weighted_grads), dqn_mgsc_batched/agent.py:171, holds M x 6.75 MB).  Asynchronous. */
 int dqnb_learner_adjoint_dots(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream);
+/* Hessian-vector product out_dev = H v_dev, H the Jacobian of jax.grad(loss_fn) w.r.t. the online parameters at the
+ * batch of this learner's LAST update (its td errors, clip decisions and ReLU masks are reused): what differentiating
+ * through `jax.grad(loss_fn)(expected_online_params, ...)` needs in the second-order MGSC objective
+ * (dqn_mgsc_batched_reservoir/agent.py:160-198, no stop_gradient on target_online_params).  Forward-over-reverse with
+ * the layer GEMMs (rlax.clip_gradient's backward is differentiated: 1 inside the bounds, 0 outside).  Both vectors are
+ * device memory laid out like the parameters.  Asynchronous. */
+int dqnb_learner_hvp(dqnb_learner* h, const float* v_dev, float* out_dev, uintptr_t stream);
 /* one `update` on a batch that is already in device memory (asynchronous). */
 int dqnb_learner_update(dqnb_learner* h, const uint8_t* s_tm1_dev, const int32_t* a_dev,
                         const float* r_dev, const float* disc_dev, const uint8_t* s_t_dev,
@@ -242,6 +249,9 @@ typedef struct dqnb_mgsc_config {
   int32_t meta_batch_size;   /* M */
   float learning_rate;       /* optax.adam learning_rate */
   float b1, b2, eps;         /* optax.adam defaults 0.9, 0.999, 1e-8 */
+  int32_t second_order;      /* 0: dqn_mgsc_batched (stop_gradient on target_online_params, agent.py:189-191);
+                                1: dqn_mgsc_batched_reservoir/agent.py:160-198 (no stop_gradient: the meta loss is
+                                differentiated through the gradient at the expected parameters - dqnb_learner_hvp) */
 } dqnb_mgsc_config;
 #define DQNB_MGSC_ADAM_M 0      /* [M] Adam first moment (read/write) */
 #define DQNB_MGSC_ADAM_V 1      /* [M] Adam second moment (read/write) */

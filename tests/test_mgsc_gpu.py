@@ -313,3 +313,103 @@ def test_logit_ring_at_one_million_entries_matches_reference_semantics():
     np.testing.assert_allclose(p._logits, o.l, rtol=0, atol=2e-6)
     assert np.array_equal(p.sample(64), o.sample(64))
     assert p._rng_state.integers(1 << 30) == o.rng.integers(1 << 30)
+
+
+@pytest.mark.parametrize("B,A,shared,double_q,weighted", [(1, 6, False, False, 0), (5, 4, True, True, 2),
+                                                          (32, 6, False, False, 0)])
+def test_hessian_vector_product_matches_oracle(B, A, shared, double_q, weighted):
+    """dqnb_learner_hvp (forward-over-reverse through the layer GEMMs) against the oracle R-op, which
+    tests/test_oracle_learner.py pins to torch double backward.  fp32 learner; batch 1 is the MGSC use."""
+    rng = np.random.default_rng(31 + B)
+    params = networks.init_params(rng, A, shared)
+    target = {k: (v + 0.01 * rng.standard_normal(v.shape)).astype(np.float32) for k, v in params.items()}
+    L = lrn.Learner(A, B, shared_bias=shared, double_q=double_q, precision="fp32", defer_apply=True,
+                    row_weighted=weighted)
+    L.set_params(params, lrn.ONLINE)
+    L.set_params(target, lrn.TARGET)
+    batch = synthetic.random_batch(rng, B, A)
+    if B > 1:
+        batch[2][0] = 40.0                       # a clipped row: its Gauss-Newton term must vanish
+    w = rng.random(B).astype(np.float32) if weighted else None
+    if weighted:
+        L.set_row_weights(w)
+    L.update_host(*batch)
+    f64 = lambda d: {k: v.astype(np.float64) for k, v in d.items()}
+    P = L.num_params
+    for trial in range(2):                       # two directions: the scratch of the first call is reused
+        v = (rng.standard_normal(P) / np.sqrt(P)).astype(np.float32)
+        got = L.hvp(v)
+        want = upd.hvp(f64(params), f64(target), batch, v.astype(np.float64), double_q, weights=w)
+        got_t, want_t = lrn.unflatten_params(got, A, shared), net.unflatten(want, A, shared)
+        errs = {k: rel(got_t[k], want_t[k]) for k in want_t}
+        print("hvp B%d trial %d:" % (B, trial), {k: "%.1e" % e for k, e in errs.items()})
+        for k, e in errs.items():
+            assert e < 5e-5, (k, e)
+        assert rel(got, want) < 2e-5
+    # the update's own outputs are untouched by the product
+    g = upd.loss_and_grads(f64(params), f64(target), batch, double_q,
+                           weights=None if w is None else w.astype(np.float64))["grads"]
+    assert rel(L.read(lrn.GRAD), net.flatten(g)) < 1e-5
+
+
+@pytest.mark.parametrize("A,shared,M", [(6, False, 5), (4, True, 9)])
+def test_second_order_meta_update_matches_oracle(A, shared, M):
+    """The dqn_mgsc_batched_reservoir objective (no stop_gradient, agent.py:160-198) against the oracle's
+    second_order=True path (pinned to torch autograd through the whole meta loss in tests/test_oracle_learner.py)."""
+    params, target, mu, nu, batch, online_tr, logits = _meta_case(A, shared, M, 41 + M)
+    L = lrn.Learner(A, 32, shared_bias=shared, double_q=False, precision="fp32")
+    L.set_params(params, lrn.ONLINE)
+    L.set_params(target, lrn.TARGET)
+    L.write(lrn.MU, mu)
+    L.write(lrn.NU, nu)
+    meta = lrn.MetaLearner(L, M, second_order=True)
+    f64 = lambda d: {k: v.astype(np.float64) for k, v in d.items()}
+    adam_m, adam_v, count = np.zeros(M), np.zeros(M), 0
+    cur = logits.copy()
+    for it in range(2):
+        want = upd.meta_update(cur.astype(np.float64), batch, f64(params), f64(target), online_tr,
+                               mu.astype(np.float64), nu.astype(np.float64), adam_m, adam_v, count, second_order=True)
+        got, loss = meta.meta_update(batch, cur, online_tr)
+        errs = {"G": rel(meta.read(lrn.MGSC_G), want["G"]), "v": rel(meta.read(lrn.MGSC_V), want["v"]),
+                "dL_dp": rel(meta.read(lrn.MGSC_DL_DP), want["dL_dp"]), "loss": abs(loss - want["loss"]) / want["loss"]}
+        print("meta second-order A%d M%d it%d:" % (A, M, it), {k: "%.1e" % v for k, v in errs.items()})
+        for k, v in errs.items():
+            assert v < 1e-4, (it, k, v)
+        assert np.abs(got - want["logits"]).max() < 5e-7
+        adam_m, adam_v, count = want["adam_m"], want["adam_v"], want["adam_count"]
+        cur = got
+    first = upd.meta_update(logits.astype(np.float64), batch, f64(params), f64(target), online_tr,
+                            mu.astype(np.float64), nu.astype(np.float64), np.zeros(M), np.zeros(M), 0)
+    second = upd.meta_update(logits.astype(np.float64), batch, f64(params), f64(target), online_tr,
+                             mu.astype(np.float64), nu.astype(np.float64), np.zeros(M), np.zeros(M), 0, second_order=True)
+    assert rel(first["v"], second["v"]) > 1e-2          # the two objectives really differ
+    assert np.array_equal(L.read(lrn.ONLINE), net.flatten(params))      # virtual steps only
+
+
+def test_mgsc_reservoir_agent_runs_the_second_order_objective():
+    """dqn_mgsc_batched_reservoir: MGSCReservoirDqn + MGSCReservoirTransitionReplay (run_atari.py:211), a short run."""
+    A, B, M, CAP = 6, 8, 5, 48
+    replay = rc.MGSCReservoirTransitionReplay(CAP, rp.Transition(None, None, None, None, None), np.random.default_rng(3))
+    ag = agent_lib.MGSCReservoirDqn(
+        preprocessor=synthetic.StackingPreprocessor(num_action_repeats=2),
+        sample_network_input=np.zeros((84, 84, 4), np.uint8), network=networks.dqn_atari_network(A),
+        optimizer=networks.rmsprop(learning_rate=0.00025, decay=0.95, eps=0.01 / 32 ** 2, centered=True),
+        transition_accumulator=rp.TransitionAccumulator(), replay=replay, batch_size=B,
+        exploration_epsilon=lambda t: 1.0, min_replay_capacity_fraction=0.25, learn_period=4,
+        target_network_update_period=24, grad_error_bound=1.0 / 32, rng_key=5,
+        meta_optimizer=networks.adam(0.00025), meta_batch_size=M, precision="fp32")
+    assert ag.meta_variant == 'second_order' and ag.meta_learner.second_order
+    assert agent_lib.MGSCDqn._SECOND_ORDER is False
+    env = synthetic.SyntheticEnvironment(np.random.default_rng(11), A, min_len=3, max_len=40)
+    frames = 0
+    for _, timestep, _, _ in parts.run_loop(ag, env, max_steps_per_episode=30, yield_before_reset=True):
+        if timestep is None:
+            continue
+        frames += 1
+        if frames >= 200:
+            break
+    assert replay.size == CAP and replay._t > CAP                 # reservoir replacements happened
+    assert np.isfinite(ag.statistics["meta_loss"]) and ag.statistics["meta_loss"] > 0
+    logits = replay._distribution._logits
+    assert np.isfinite(logits).all() and np.ptp(logits) > 0
+    assert ag.get_state()["meta_opt_state"][0].count >= 10
