@@ -225,6 +225,10 @@ __device__ __forceinline__ void t32_widen8h(uint32_t dst, uint32_t w0, uint32_t 
                : "memory");
 }
 template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::true_type {};
+//   static constexpr bool PRELOAD = true;  Pre preload(z, split, m, n) const;  void store4p(z, split, m, n, v, pre) const;
+// the epilogue fetches what store4 would read for ALL of a thread's rows before it stores any of them.
+template <class P, class = void> struct t32_preload : std::false_type {};
+template <class P> struct t32_preload<P, std::enable_if_t<P::PRELOAD>> : std::true_type {};
 
 // Retire this thread's commit groups oldest-first: when group I has landed, make it visible to
 // the tensor core (async proxy) and arrive on k-block I's barrier.
@@ -514,10 +518,27 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
       float4 v[PASSES];
 #pragma unroll
       for (int k = 0; k < PASSES; ++k) v[k] = ld_shared_f4(smem + ((r0 + k * RPP) * PSTRIDE + c4 * 4) * 4);
+      if constexpr (t32_preload<P>::value) {
+        // the problem's store reads global memory it also writes (fused optimiser step): the compiler cannot move
+        // pass k+1's loads above pass k's stores, so each pass would wait a full memory latency (measured 900
+        // clocks per pass) - fetch everything first
+        typename P::Pre pre[PASSES];
 #pragma unroll
-      for (int k = 0; k < PASSES; ++k) {
-        const int r = r0 + k * RPP;
-        if (col_ok && r < rows_here) p.store4(z, split, m0 + r, n, v[k]);
+        for (int k = 0; k < PASSES; ++k) {
+          const int r = r0 + k * RPP;
+          if (col_ok && r < rows_here) pre[k] = p.preload(z, split, m0 + r, n);
+        }
+#pragma unroll
+        for (int k = 0; k < PASSES; ++k) {
+          const int r = r0 + k * RPP;
+          if (col_ok && r < rows_here) p.store4p(z, split, m0 + r, n, v[k], pre[k]);
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < PASSES; ++k) {
+          const int r = r0 + k * RPP;
+          if (col_ok && r < rows_here) p.store4(z, split, m0 + r, n, v[k]);
+        }
       }
     } else {
       const int nsum = splits;

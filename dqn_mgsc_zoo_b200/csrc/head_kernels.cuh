@@ -77,14 +77,24 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
     for (int z = 0; z < kMaxNets; ++z) acc[z] = make_float4(0.f, 0.f, 0.f, 0.f);
     const size_t split_stride = (size_t)g.batch * (kFc1Out / 4);
     const float4* src = reinterpret_cast<const float4*>(g.fc1_part + (size_t)row * kFc1Out) + t;
-#pragma unroll 4
-    for (int q = 0; q < g.fc1_splits; ++q) {
+    // 8 splits x up to 3 nets = 24 float4 loads in flight per round trip (17 splits at batch 32: three rounds
+    // instead of five with a 4-deep unroll); the additions keep their split order
+    constexpr int kDepth = 8;
+    for (int q0 = 0; q0 < g.fc1_splits; q0 += kDepth) {
+      float4 x[kMaxNets][kDepth];
 #pragma unroll
       for (int z = 0; z < kMaxNets; ++z) {
-        if (z < nets) {
-          const float4 x = __ldcg(src + ((size_t)z * g.fc1_splits + q) * split_stride);
-          acc[z].x += x.x; acc[z].y += x.y; acc[z].z += x.z; acc[z].w += x.w;
-        }
+#pragma unroll
+        for (int u = 0; u < kDepth; ++u)
+          if (z < nets && q0 + u < g.fc1_splits) x[z][u] = __ldcg(src + ((size_t)z * g.fc1_splits + q0 + u) * split_stride);
+      }
+#pragma unroll
+      for (int z = 0; z < kMaxNets; ++z) {
+#pragma unroll
+        for (int u = 0; u < kDepth; ++u)
+          if (z < nets && q0 + u < g.fc1_splits) {
+            acc[z].x += x[z][u].x; acc[z].y += x[z][u].y; acc[z].z += x[z][u].z; acc[z].w += x[z][u].w;
+          }
       }
     }
 #pragma unroll

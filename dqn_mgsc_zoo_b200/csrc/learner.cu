@@ -627,10 +627,12 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     p.dy = h->dh1; p.w = h->online_r + h->L.fw1; p.act = h->a3[0]; p.dx = h->dy3;
     DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
   }
+  static const bool fc1w_early = getenv("DQNB_FC1W_EARLY") != nullptr;   // release fc1's wgrad right behind its dgrad
   if (live) DQNB_TRY(fork(h->ev[1], st, s3));
+  if (live && fc1w_early) DQNB_TRY(fork(h->ev[1], st, s2));
   DQNB_TRY((t32_conv_wgrad<Conv3, float, 8, true>(h, B, h->a2[0], h->dy3, h->L.w3, s3)));
   DQNB_TRY((t32_conv_dgrad<Conv3, 6>(h, B, h->dy3, h->online_r + h->L.w3, h->a2[0], h->dy2, st)));
-  if (live) { DQNB_TRY(fork(h->ev[2], st, s3)); DQNB_TRY(fork(h->ev[2], st, s2)); DQNB_TRY(fork(h->ev[2], st, s1)); }
+  if (live) { DQNB_TRY(fork(h->ev[2], st, s3)); if (!fc1w_early) DQNB_TRY(fork(h->ev[2], st, s2)); DQNB_TRY(fork(h->ev[2], st, s1)); }
   // fc1's weight gradient is ordered after fc1's dgrad (which reads the old weights) so that, when
   // the batch is one K block (no split-K), its epilogue can apply RMSProp to fc1 on the spot.  It
   // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
@@ -671,7 +673,11 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   int rc_c2 = t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1);
   h->boost = false;
   DQNB_TRY(rc_c2);
-  DQNB_TRY((t32_conv_dgrad<Conv2, 4>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
+  // slab mode: the whole K range (4 taps x 64 channels = 8 k-blocks) in one slab: 100 unsplit tiles, one wave, no
+  // cluster reduce (as 2-CTA clusters it was 200 CTAs over two waves: 11.5 us); DQNB_C2DGRAD_KB4 restores that
+  static const bool c2_kb4 = getenv("DQNB_C2DGRAD_KB4") != nullptr;
+  if (h->stream || c2_kb4) DQNB_TRY((t32_conv_dgrad<Conv2, 4>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
+  else DQNB_TRY((t32_conv_dgrad<Conv2, 8>(h, B, h->dy2, h->online_r + h->L.w2, h->a1[0], h->dy1, st)));
   if (live) DQNB_TRY(fork(h->ev[6], st, s1));
   h->boost = h->pdl;
   int rc_c1 = t32_conv_wgrad<Conv1, uint8_t, 4, false>(h, B, h->s_tm1, h->dy1, h->L.w1, st, s1);

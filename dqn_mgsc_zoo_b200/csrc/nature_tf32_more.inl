@@ -140,8 +140,27 @@ struct T32DenseWgrad {
       *reinterpret_cast<float4*>(gpart + (size_t)split * ((size_t)M * N) + idx) = v;
       return;
     }
-    float4 mv = *reinterpret_cast<const float4*>(fuse.mu + idx), nv = *reinterpret_cast<const float4*>(fuse.nu + idx);
-    float4 pv = *reinterpret_cast<const float4*>(fuse.p + idx);
+    store4p(0, split, m, n, v, preload(0, split, m, n));
+  }
+  // the fused optimiser step reads p / mu / nu and writes them back: loads of all rows first (gemm_tf32.cuh)
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 p, mu, nu; };
+  __device__ Pre preload(int, int, int m, int n) const {
+    Pre q;
+    if (fuse.p == nullptr) { q.p = q.mu = q.nu = make_float4(0.f, 0.f, 0.f, 0.f); return q; }
+    const size_t idx = (size_t)m * N + n;
+    q.mu = __ldcg(reinterpret_cast<const float4*>(fuse.mu + idx));
+    q.nu = __ldcg(reinterpret_cast<const float4*>(fuse.nu + idx));
+    q.p = __ldcg(reinterpret_cast<const float4*>(fuse.p + idx));
+    return q;
+  }
+  __device__ void store4p(int, int split, int m, int n, float4 v, const Pre& q) const {
+    const size_t idx = (size_t)m * N + n;
+    if (fuse.p == nullptr) {
+      *reinterpret_cast<float4*>(gpart + (size_t)split * ((size_t)M * N) + idx) = v;
+      return;
+    }
+    float4 mv = q.mu, nv = q.nu, pv = q.p;
     rmsprop4(pv, mv, nv, v, fuse.lr, fuse.decay, fuse.eps);
     *reinterpret_cast<float4*>(fuse.g + idx) = v;
     *reinterpret_cast<float4*>(fuse.mu + idx) = mv;
