@@ -1,6 +1,8 @@
 // Replay frame store: host bookkeeping (plane pool, dedup, staging) + kernel launches.
 // Replaces the item storage of the reference replays (replay.py:163-333,
 // replay_circular.py:90-146,568-664,1217-1312); see include/dqnb200.h.
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -268,6 +270,9 @@ extern "C" int dqnb_replay_create(int64_t capacity, int height, int width, int s
   h->n_growths = 0;
   DQNB_CUDA(cudaFuncSetAttribute(gather_stack4<kGatherThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  8 * 16 * 1024));
+  if ((size_t)kGatherStages * 8 * h->plane_bytes <= 200 * 1024)
+    DQNB_CUDA(cudaFuncSetAttribute(gather_stack4_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   kGatherStages * 8 * h->plane_bytes));
   return DQNB_OK;
   }();
   if (rc_create != DQNB_OK) { dqnb_replay_destroy(h); return rc_create; }
@@ -378,17 +383,28 @@ int launch_gather(dqnb_replay* h, const int32_t* slots_dev, int64_t n, uint8_t* 
   if (h->have_commit && st != h->commit_stream) DQNB_CUDA(cudaStreamWaitEvent(st, h->committed, 0));
   h->gather_stream = st;
   ReplayDeviceView v = view_of(h);
-  if (h->S == 4 && h->plane_bytes % 16 == 0) {
+  static const int pipe_min = getenv("DQNB_GATHER_PIPE_MIN") ? atoi(getenv("DQNB_GATHER_PIPE_MIN")) : (1 << 30);   // measured slower than 6 CTAs/SM of the kernel below: off
+  const size_t pipe_smem = (size_t)kGatherStages * 8 * h->plane_bytes;
+  if (h->S == 4 && h->plane_bytes % 16 == 0 && slots_dev != nullptr && n >= pipe_min && h->gather_splits == 0 &&   // (any explicit split setting selects the per-transition kernel)
+      pipe_smem <= 200 * 1024 && n <= (int64_t)kNumSMs * kGatherMaxItems) {
+    // thousands of transitions: one persistent CTA per SM, loads of the next transitions behind the stores of this one
+    gather_stack4_pipe<<<kNumSMs, kGatherPipeThreads, pipe_smem, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
+  } else if (h->S == 4 && h->plane_bytes % 16 == 0) {
     // enough CTAs to cover the 148 SMs twice for small batches; whole planes for big ones
     int splits = h->gather_splits;
+    const bool force8 = splits >= 100;          // tuning: 100 + s = s splits (0 = automatic) with 8 plane buffers per CTA
+    if (force8) splits -= 100;
     if (splits <= 0) splits = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * kNumSMs + n - 1) / n), 16);
     int chunk = ((h->plane_bytes + splits - 1) / splits + 15) / 16 * 16;
     chunk = std::min(chunk, 16 * 1024);
     splits = (h->plane_bytes + chunk - 1) / chunk;
     dim3 grid(splits, (unsigned)n);
     static const InlineSlots no_inline{};
-    gather_stack4<kGatherThreads><<<grid, kGatherThreads, 8 * (size_t)chunk, st>>>(
-        v, slots_dev, inl ? *inl : no_inline, (int)n, chunk, s_tm1, s_t, a, r, d);
+    // throughput regime: 5 plane buffers per CTA (6 CTAs per SM instead of 4); rows with more unique planes take two phases
+    static const int cap5_min = getenv("DQNB_GATHER_CAP5_MIN") ? atoi(getenv("DQNB_GATHER_CAP5_MIN")) : 256;
+    const int cap_planes = (n >= cap5_min && !force8) ? 5 : 8;
+    gather_stack4<kGatherThreads><<<grid, kGatherThreads, cap_planes * (size_t)chunk, st>>>(
+        v, slots_dev, inl ? *inl : no_inline, (int)n, chunk, cap_planes, s_tm1, s_t, a, r, d);
   } else {
     gather_generic<<<(unsigned)n, 128, 0, st>>>(v, slots_dev, (int)n, s_tm1, s_t, a, r, d);
   }

@@ -82,14 +82,53 @@ __device__ __forceinline__ uint4 interleave4(uint32_t w0, uint32_t w1, uint32_t 
 constexpr int kInlineSlots = 64;
 struct InlineSlots { int32_t v[kInlineSlots]; };
 
+// Thread 0 of a gather CTA: dedupe N plane references (registers, fully unrolled) into buffers 0.., one bulk copy per
+// unique plane completing on `bar`; buf[k] = buffer of reference k, -1 = the zero plane.
+template <int N>
+__device__ __forceinline__ void gather_issue(const int (&ids)[N], int* buf, uint8_t* smem, int chunk, int len,
+                                             const uint8_t* planes, int64_t plane_stride, int px0, uint64_t* bar) {
+  int uniq[N];
+  int nu = 0;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    int b = -1;
+    if (ids[k] >= 0) {
+#pragma unroll
+      for (int j = 0; j < N; ++j)
+        if (j < nu && uniq[j] == ids[k]) b = j;
+      if (b < 0) {
+        b = nu;
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+          if (j == nu) uniq[j] = ids[k];
+        ++nu;
+      }
+    }
+    buf[k] = b;
+  }
+  if (nu > 0) {
+    mbar_expect_tx(bar, (uint32_t)(nu * len));
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+      if (j < nu) bulk_g2s(smem + j * chunk, planes + (int64_t)uniq[j] * plane_stride + px0, (uint32_t)len, bar);
+  } else {
+    mbar_arrive(bar);
+  }
+}
+
+// `cap_planes` = plane buffers the launch gave each CTA (8, or 5 in the throughput regime: a chained transition has
+// 5 unique planes, and 5 x chunk of shared memory lets 6 CTAs share an SM instead of 4 - more loads in flight).  A row
+// with more unique planes than that (reservoir slots, episode joints) runs in two phases: the s_tm1 stack, then s_t.
 template <int kThreads>
 __global__ void __launch_bounds__(kThreads)
 gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __grid_constant__ InlineSlots inl, int n,
-              int chunk, uint8_t* __restrict__ s_tm1_out, uint8_t* __restrict__ s_t_out,
+              int chunk, int cap_planes, uint8_t* __restrict__ s_tm1_out, uint8_t* __restrict__ s_t_out,
               int32_t* __restrict__ a_out, float* __restrict__ r_out, float* __restrict__ d_out) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ int buf_of[8];   // smem buffer index per plane reference, -1 = zeros
+  __shared__ int late_ids[4]; // two-phase rows: the s_t plane references, issued after the s_tm1 stack is out
+  __shared__ int two_phase;
   const int row = blockIdx.y, split = blockIdx.x;
   const int slot = slots != nullptr ? slots[row] : inl.v[row];
   const int px0 = split * chunk;
@@ -100,28 +139,27 @@ gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __gri
     fence_mbar_init();
     const int4* idp = reinterpret_cast<const int4*>(v.slot_ids + (int64_t)slot * 8);
     int4 lo = idp[0], hi = idp[1];
-    int ids[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    int uniq[8];
-    int nu = 0;
+    const int ids[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    int nu = 8;
+    if (cap_planes < 8) {      // unique non-zero references (only when the launch is short of buffers)
+      nu = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      int b = -1;
-      if (ids[k] >= 0) {
-        for (int j = 0; j < nu; ++j)
-          if (uniq[j] == ids[k]) b = j;
-        if (b < 0) {
-          b = nu;
-          uniq[nu++] = ids[k];
-        }
+      for (int k = 0; k < 8; ++k) {
+        bool fresh = ids[k] >= 0;
+#pragma unroll
+        for (int j = 0; j < k; ++j) fresh = fresh && ids[j] != ids[k];
+        nu += fresh ? 1 : 0;
       }
-      buf_of[k] = b;
     }
-    if (nu > 0) {
-      mbar_expect_tx(&bar, (uint32_t)(nu * len));
-      for (int j = 0; j < nu; ++j)
-        bulk_g2s(smem + j * chunk, v.planes + (int64_t)uniq[j] * v.plane_stride + px0, (uint32_t)len, &bar);
+    const bool split_row = cap_planes < 8 && nu > cap_planes;
+    two_phase = split_row;
+    if (!split_row) {
+      gather_issue<8>(ids, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
     } else {
-      mbar_arrive(&bar);
+      const int first[4] = {ids[0], ids[1], ids[2], ids[3]};
+      gather_issue<4>(first, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) late_ids[k] = ids[4 + k];
     }
     if (split == 0) {
       a_out[row] = v.actions[slot];
@@ -132,19 +170,157 @@ gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __gri
   __syncthreads();
   mbar_wait(&bar, 0);
 
-  const uint32_t* w[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) w[k] = buf_of[k] >= 0 ? reinterpret_cast<const uint32_t*>(smem + buf_of[k] * chunk) : nullptr;
   const int64_t out_base = ((int64_t)row * v.plane_bytes + px0) * 4;
   uint4* o1 = reinterpret_cast<uint4*>(s_tm1_out + out_base);
   uint4* o2 = reinterpret_cast<uint4*>(s_t_out + out_base);
   const int nq = len >> 2;   // groups of 4 pixels
-  for (int q = threadIdx.x; q < nq; q += kThreads) {
-    uint32_t x[8];
+  if (!two_phase) {
+    const uint32_t* w[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) x[k] = w[k] ? w[k][q] : 0u;
-    __stcs(o1 + q, interleave4(x[0], x[1], x[2], x[3]));
-    __stcs(o2 + q, interleave4(x[4], x[5], x[6], x[7]));
+    for (int k = 0; k < 8; ++k) w[k] = buf_of[k] >= 0 ? reinterpret_cast<const uint32_t*>(smem + buf_of[k] * chunk) : nullptr;
+    for (int q = threadIdx.x; q < nq; q += kThreads) {
+      uint32_t x[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) x[k] = w[k] ? w[k][q] : 0u;
+      __stcs(o1 + q, interleave4(x[0], x[1], x[2], x[3]));
+      __stcs(o2 + q, interleave4(x[4], x[5], x[6], x[7]));
+    }
+    return;
+  }
+#pragma unroll 1
+  for (int phase = 0; phase < 2; ++phase) {
+    if (phase == 1) {
+      __syncthreads();                       // every thread has read the s_tm1 planes
+      if (threadIdx.x == 0) {
+        const int second[4] = {late_ids[0], late_ids[1], late_ids[2], late_ids[3]};
+        gather_issue<4>(second, buf_of + 4, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
+      }
+      __syncthreads();
+      mbar_wait(&bar, 1);
+    }
+    const uint32_t* w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int b = buf_of[4 * phase + k];
+      w[k] = b >= 0 ? reinterpret_cast<const uint32_t*>(smem + b * chunk) : nullptr;
+    }
+    uint4* o = phase ? o2 : o1;
+    for (int q = threadIdx.x; q < nq; q += kThreads) {
+      uint32_t x[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) x[k] = w[k] ? w[k][q] : 0u;
+      __stcs(o + q, interleave4(x[0], x[1], x[2], x[3]));
+    }
+  }
+}
+
+// Large launches (thousands of transitions: the data-parallel learner's batch, prefetch of many minibatches): the
+// one-CTA-per-transition kernel above spends most of a CTA's life in three DEPENDENT memory round trips (slot ->
+// plane ids -> planes) before its store phase, with only 4 CTAs per SM to hide them (56 KB of smem each).  Here one
+// persistent CTA per SM walks transitions row = blockIdx.x, + gridDim.x, ... through a kGatherStages-deep ring of
+// whole-transition buffers: while the CTA stores transition k, the bulk copies of k+1 are in flight and the plane
+// ids of k+2 are being fetched, so every round trip is hidden behind a store phase.
+constexpr int kGatherStages = 3;
+constexpr int kGatherConsumers = 512;                       // warps 0-15 store; warp 16 lane 0 produces
+constexpr int kGatherPipeThreads = kGatherConsumers + 32;
+constexpr int kGatherMaxItems = 1024;                       // transitions per CTA (slot list staged in smem)
+__global__ void __launch_bounds__(kGatherPipeThreads, 1)
+gather_stack4_pipe(ReplayDeviceView v, const int32_t* __restrict__ slots, int n, uint8_t* __restrict__ s_tm1_out,
+                   uint8_t* __restrict__ s_t_out, int32_t* __restrict__ a_out, float* __restrict__ r_out,
+                   float* __restrict__ d_out) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t full[kGatherStages], empty[kGatherStages];
+  __shared__ int buf_of[kGatherStages][8];
+  __shared__ int slot_s[kGatherMaxItems];
+  const int plane = v.plane_bytes;                  // multiple of 16
+  const int stage_bytes = 8 * plane;
+  const int t = threadIdx.x;
+  const int first = blockIdx.x, step = gridDim.x;
+  const int my = first < n ? (n - first + step - 1) / step : 0;     // transitions of this CTA (<= kGatherMaxItems)
+  if (t == 0) {
+    for (int s = 0; s < kGatherStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    fence_mbar_init();
+  }
+  for (int i = t; i < my; i += kGatherPipeThreads) slot_s[i] = slots[first + i * step];
+  __syncthreads();
+
+  if (t >= kGatherConsumers) {
+    // ------------------------------------------------------------------ producer (one lane)
+    if (t != kGatherConsumers) return;
+    // two register sets: everything item j+2 needs is requested while item j is being issued, so the only
+    // memory round trip the producer ever waits for was started two items earlier
+    int4 lo[2], hi[2];
+    int32_t act[2];
+    float rew[2], dis[2];
+    auto fetch = [&](int i, int set) {
+      if (i >= my) return;
+      const int slot = slot_s[i];
+      const int4* idp = reinterpret_cast<const int4*>(v.slot_ids + (int64_t)slot * 8);
+      lo[set] = __ldg(idp); hi[set] = __ldg(idp + 1);
+      act[set] = __ldg(v.actions + slot); rew[set] = __ldg(v.rewards + slot); dis[set] = __ldg(v.discounts + slot);
+    };
+    auto issue = [&](int i, int set) {
+      const int stage = i % kGatherStages;
+      if (i >= kGatherStages) mbar_wait(&empty[stage], (uint32_t)((i / kGatherStages) - 1) & 1u);
+      const int row = first + i * step;
+      const int ids[8] = {lo[set].x, lo[set].y, lo[set].z, lo[set].w, hi[set].x, hi[set].y, hi[set].z, hi[set].w};
+      int uniq[8];
+      int nu = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        int b = -1;
+        if (ids[k] >= 0) {
+          for (int q = 0; q < nu; ++q)
+            if (uniq[q] == ids[k]) b = q;
+          if (b < 0) { b = nu; uniq[nu++] = ids[k]; }
+        }
+        buf_of[stage][k] = b;
+      }
+      a_out[row] = act[set]; r_out[row] = rew[set]; d_out[row] = dis[set];
+      if (nu > 0) {
+        mbar_expect_tx(&full[stage], (uint32_t)(nu * plane));
+        for (int q = 0; q < nu; ++q)
+          bulk_g2s(smem + stage * stage_bytes + q * plane, v.planes + (int64_t)uniq[q] * v.plane_stride,
+                   (uint32_t)plane, &full[stage]);
+      } else {
+        mbar_arrive(&full[stage]);
+      }
+    };
+    fetch(0, 0);
+    fetch(1, 1);
+    for (int i = 0; i < my; i += 2) {
+      issue(i, 0);
+      fetch(i + 2, 0);
+      if (i + 1 < my) {
+        issue(i + 1, 1);
+        fetch(i + 3, 1);
+      }
+    }
+    return;
+  }
+  // -------------------------------------------------------------------- consumers
+  for (int k = 0; k < my; ++k) {
+    const int stage = k % kGatherStages;
+    const int row = first + k * step;
+    mbar_wait(&full[stage], (uint32_t)(k / kGatherStages) & 1u);
+    const uint8_t* base = smem + stage * stage_bytes;
+    const uint32_t* w[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = buf_of[stage][j] >= 0 ? reinterpret_cast<const uint32_t*>(base + buf_of[stage][j] * plane) : nullptr;
+    const int64_t out_base = (int64_t)row * plane * 4;
+    uint4* o1 = reinterpret_cast<uint4*>(s_tm1_out + out_base);
+    uint4* o2 = reinterpret_cast<uint4*>(s_t_out + out_base);
+    const int nq = plane >> 2;
+#pragma unroll 2
+    for (int q = t; q < nq; q += kGatherConsumers) {
+      uint32_t x[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] = w[j] ? w[j][q] : 0u;
+      __stcs(o1 + q, interleave4(x[0], x[1], x[2], x[3]));
+      __stcs(o2 + q, interleave4(x[4], x[5], x[6], x[7]));
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kGatherConsumers) : "memory");   // every consumer has read the stage
+    if (t == 0) mbar_arrive(&empty[stage]);
   }
 }
 

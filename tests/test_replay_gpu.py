@@ -271,3 +271,37 @@ def test_snapshot_state_round_trip_resumes_identically(kind):
         q.add(it)
     _same_samples(p, q, 12, mgsc=mgsc)
     assert p.frame_store.stats()["planes_in_use"] == q.frame_store.stats()["planes_in_use"]
+
+
+def test_pipelined_gather_equals_per_transition_gather():
+    """Large launches give every gather CTA 5 plane buffers (6 CTAs per SM) and run rows with more unique planes in
+    two phases; small ones keep 8 buffers.  Same bytes either way and for any CTA split, including early-episode
+    stacks (zero planes), reservoir slots (8 unique planes), repeated slots and odd row counts.  (DQNB_GATHER_PIPE_MIN
+    selects the persistent pipelined variant, measured slower and off by default.)"""
+    p = rp.ReservoirTransitionReplay(400, rp.Transition(None, None, None, None, None), np.random.RandomState(1))
+    stream = synthetic.transition_stream(np.random.default_rng(4), 4, rp.TransitionAccumulator(), short_every=3, max_len=9)
+    for _ in range(900):                     # reservoir replacements: slots with no temporal neighbours (8 unique planes)
+        p.add(next(stream))
+    store = p.frame_store
+    small = store.gather_host(np.arange(200))          # n < 256: 8 plane buffers per CTA, single phase
+    big = store.gather_host(np.concatenate([np.arange(200), np.arange(200)]))   # n >= 256: 5 buffers, two-phase rows
+    for x, y in zip(small, big):
+        assert np.array_equal(x, y[:200]) and np.array_equal(x, y[200:])
+    for n in (1024, 1500, 4099):
+        slots = np.random.default_rng(n).integers(0, 400, size=n)
+        store.set_gather_splits(0)
+        fast = store.gather_host(slots)
+        store.set_gather_splits(2)
+        base = store.gather_host(slots)
+        for x, y in zip(base, fast):
+            assert np.array_equal(x, y), n
+    store.set_gather_splits(0)
+    o = ro.ReservoirReplay(400, ro.Transition(None, None, None, None, None), np.random.RandomState(1))
+    so = synthetic.transition_stream(np.random.default_rng(4), 4, ro.PairAccumulator(), short_every=3, max_len=9)
+    for _ in range(900):
+        o.add(next(so))
+    ids = np.random.default_rng(7).integers(0, 400, size=2048)
+    want = o.gather(ids)
+    got = store.gather_host(ids)
+    assert np.array_equal(got[0], want.s_tm1) and np.array_equal(got[4], want.s_t)
+    assert np.array_equal(got[1], np.asarray(want.a_tm1, np.int32))
