@@ -506,6 +506,7 @@ def run_ours(args, rank, world, local_rank):
         import gc
         gc.collect()
         torch.cuda.empty_cache()
+        extras["agent_loop"] = bench_agent_loop(args, local_rank, rank)
         extras["reservoir"] = bench_reservoir(args, timed, local_rank, rank)
         extras["mgsc"] = bench_mgsc(args, timed, local_rank, rank)
         extras["dp"] = bench_dp_record(args, timed, local_rank, rank, world, dist)
@@ -537,6 +538,45 @@ def run_ours(args, rank, world, local_rank):
     emit(line)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def bench_agent_loop(args, device, rank):
+    """C1 stand-in through the reference's own seams: the DoubleDqn drop-in driven by parts.run_loop
+    (agent.step -> preprocess, act, accumulate, replay.add, _learn every 16 frames, target sync) on the synthetic
+    environment (ALE is absent and outside the optimisation target).  Host wall clock: this loop is host-paced."""
+    from dqn_mgsc_zoo_b200 import agent as agent_lib
+    from dqn_mgsc_zoo_b200 import networks, parts, synthetic
+    from dqn_mgsc_zoo_b200 import replay as rp
+    cap, frames = 50_000, 24_000
+    replay = rp.TransitionReplay(cap, rp.Transition(None, None, None, None, None), np.random.RandomState(rank),
+                                 device=device)
+    ag = agent_lib.DoubleDqn(
+        preprocessor=synthetic.StackingPreprocessor(num_action_repeats=4),
+        sample_network_input=np.zeros((84, 84, 4), np.uint8), network=networks.double_dqn_atari_network(NUM_ACTIONS),
+        optimizer=networks.rmsprop(learning_rate=0.00025, decay=0.95, eps=0.01 / 32 ** 2, centered=True),
+        transition_accumulator=rp.TransitionAccumulator(), replay=replay, batch_size=BATCH,
+        exploration_epsilon=lambda t: 0.1, min_replay_capacity_fraction=0.02, learn_period=16,
+        target_network_update_period=30_000, grad_error_bound=1.0 / 32, rng_key=1 + rank, device=device,
+        precision=args.precision)
+    env = synthetic.SyntheticEnvironment(np.random.default_rng(3 + rank), NUM_ACTIONS, min_len=50, max_len=400)
+    warm = int(0.02 * cap) * 4 + 2000
+    n, t0 = 0, None
+    for _ in parts.run_loop(ag, env, max_steps_per_episode=27_000):
+        n += 1
+        if n == warm:
+            ag.learner.synchronize()
+            t0 = time.perf_counter()
+        if n == warm + frames:
+            break
+    ag.learner.synchronize()
+    dt = time.perf_counter() - t0
+    out = {"frames_per_s": frames / dt, "learner_updates_per_s": frames / 16 / dt, "frames": frames,
+           "precision": ag.precision,
+           "what": "agent.DoubleDqn through parts.run_loop on the synthetic environment: action repeat 4, learn every "
+                   "16 frames at batch 32, epsilon 0.1, %d-transition replay; host wall clock, one rank (the "
+                   "reference's V100 runs: 1 084 train frames/s with ALE, results/dqn/seed_*.csv)" % cap}
+    ag.learner.close()
+    return out
 
 
 def bench_reservoir(args, timed, device, rank):
