@@ -229,6 +229,14 @@ template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::tr
 // the epilogue fetches what store4 would read for ALL of a thread's rows before it stores any of them.
 template <class P, class = void> struct t32_preload : std::false_type {};
 template <class P> struct t32_preload<P, std::enable_if_t<P::PRELOAD>> : std::true_type {};
+//   static constexpr bool B_TMA = true;  const void* b_tmap(int z) const;
+// B is a plain fp32 matrix described by a tiled tensor map (K-major: dims {K, N}, box {32, BN}, SWIZZLE_128B;
+// MN-major: dims {N, K}, box {32, 32}, SWIZZLE_128B_ATOM_32B - the two canonical UMMA layouts above are exactly
+// what the TMA engine writes in those modes).  The MMA issuer thread then fetches every B k-block of the CTA with
+// cp.async.bulk.tensor onto that k-block's barrier and the eight producer warps stage only A.  A null map (weights
+// that are not one of the learner's own shadows) falls back to the cp.async path at run time.
+template <class P, class = void> struct t32_b_tma : std::false_type {};
+template <class P> struct t32_b_tma<P, std::enable_if_t<P::B_TMA>> : std::true_type {};
 
 // Retire this thread's commit groups oldest-first: when group I has landed, make it visible to
 // the tensor core (async proxy) and arrive on k-block I's barrier.
@@ -294,12 +302,16 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   const int kb_beg = split * per, kb_end = min(kblocks, kb_beg + per);
   const int nkb = max(kb_end - kb_beg, 0);
 
+  const void* bmap = nullptr;
+  if constexpr (t32_b_tma<P>::value) bmap = p.b_tmap(z);
+  const bool b_tma = bmap != nullptr;   // B arrives by TMA: one more arrival (the expect_tx) per k-block
   if (t == 0) {
-    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], kT32Producers / 32);
+    for (int s = 0; s < KB; ++s) mbar_init(&full_bar[s], kT32Producers / 32 + (b_tma ? 1 : 0));
     mbar_init(&done_bar, 1);
     fence_mbar_init();
   }
   if (warp == 8) t32_alloc<COLS>(&tmem_slot);
+  if (b_tma && t == kT32Producers) tma_prefetch_map(bmap);   // the descriptor itself is never written by a kernel
   t32_fence_before();
   __syncthreads();
   t32_fence_after();
@@ -435,7 +447,7 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
 #pragma unroll
           for (int ur = 0; ur < MA::NROW; ++ur) p.a_put(arow[ur], col, tile + MA::offset(t, ur, uc));
         }
-        stage_b(i);
+        if (!b_tma) stage_b(i);
         cp_commit();
         if (i >= kT32Lag) {          // publish k-block i - kT32Lag: at most the kT32Lag newest groups may still be in flight
           cp_wait<kT32Lag>();
@@ -453,6 +465,21 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   } else if (t == kT32Producers) {
     // ---- MMA issuer
     const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
+    if constexpr (t32_b_tma<P>::value) {
+      if (b_tma) {   // every B k-block of this CTA, in k order, each onto its own barrier
+        for (int i = 0; i < nkb; ++i) {
+          const int k0 = (kb_beg + i) * kT32BK;
+          const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
+          mbar_expect_tx(&full_bar[i], B_TILE);
+          if constexpr (P::B_MN_MAJOR) {
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) tma_load_2d(tile + j * 4096, bmap, n0 + 32 * j, k0, bar);
+          } else {
+            tma_load_2d(tile, bmap, k0, n0, bar);
+          }
+        }
+      }
+    }
     for (int i = 0; i < nkb; ++i) {
       mbar_wait(&full_bar[i], 0);
       t32_fence_after();

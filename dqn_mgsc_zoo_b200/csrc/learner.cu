@@ -2,6 +2,7 @@
 // backward, centered RMSProp, target sync; captured once as a CUDA graph with parallel
 // branches.  Replaces the jitted `update` of dqn/agent.py:109-119 / double_q/agent.py:85-121
 // and the target sync of dqn/agent.py:155-156.  See include/dqnb200.h.
+#include <cuda.h>   // CUtensorMap and its enums only: the encoder is looked up through the runtime (no libcuda link)
 #include <stdlib.h>
 
 #include <algorithm>
@@ -55,6 +56,36 @@ ArenaLayout make_layout(int A, int shared_bias) {
   return L;
 }
 
+// Tensor map of a dense row-major fp32 matrix [outer][inner] for tiled TMA loads of {box_inner, box_outer} boxes.
+// cuTensorMapEncodeTiled is a pure host-side encoder; it is fetched with cudaGetDriverEntryPoint so that the
+// library keeps its single dependency on the CUDA runtime.
+int make_tmap_2d(const float* base, uint64_t inner, uint64_t outer, uint32_t box_inner, uint32_t box_outer,
+                 CUtensorMapSwizzle swizzle, CUtensorMap* out) {
+  using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      fn = nullptr;
+    }
+    return reinterpret_cast<EncodeFn>(fn);
+  }();
+  if (encode == nullptr) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DQNB_ECUDA; }
+  const cuuint64_t dims[2] = {inner, outer};
+  const cuuint64_t strides[1] = {inner * sizeof(float)};
+  const cuuint32_t box[2] = {box_inner, box_outer};
+  const cuuint32_t elem[2] = {1, 1};
+  const CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, elem,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return DQNB_ECUDA; }
+  return DQNB_OK;
+}
+
 int pick_splits(size_t ctas, int K, int want_ctas = 2 * kNumSMs) {
   int kchunks = (K + kBK - 1) / kBK;
   int s = (int)((want_ctas + ctas - 1) / ctas);
@@ -72,6 +103,12 @@ struct dqnb_learner {
   // parameter / optimiser arenas (flat fp32, oracle leaf order)
   float *online = nullptr, *target = nullptr, *mu = nullptr, *nu = nullptr, *grad = nullptr;
   float *online_r = nullptr, *target_r = nullptr;   // TF32 mode: weights rounded to tf32 (GEMM operands)
+  // TF32 slab mode: tensor maps of the fc1 weight shadows (device copies; gemm_tf32.cuh B_TMA).  [0] / [1]: online /
+  // target as the forward's MN-major B operand, [2]: online as the dgrad's K-major B operand.  Null: cp.async staging.
+  CUtensorMap* fc1_maps = nullptr;
+  const void* fc1_fwd_map(const float* wts) const {
+    return fc1_maps == nullptr ? nullptr : wts == online_r ? fc1_maps + 0 : wts == target_r ? fc1_maps + 1 : nullptr;
+  }
   __half* conv1_h16 = nullptr;   // TF32 mode, small batches: fp16 K-major conv1 filters [online 32 | target 32][256]
   // TF32 mode, small batches: fp16 K-major conv2 / conv3 filters, [online: conv2 64x512 | conv3 64x576][target: same],
   // and fp16 copies of the conv1 / conv2 outputs of every net (A operands of the fp16 conv2 / conv3 forward)
@@ -503,6 +540,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
   for (int z = 0; z < kMaxNets; ++z) {
     int zz = std::min(z, nets - 1);
     p.x[z] = in4[zz]; p.w[z] = wts[zz] + h->L.fw1;
+    p.bmap[z] = h->stream ? nullptr : h->fc1_fwd_map(wts[zz]);
   }
   p.splits = t32_splits(h, p, Z, kNumSMs);
   h->fc1_splits = p.splits;
@@ -625,6 +663,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
     T32DenseDgrad p;
     p.M = B; p.N = kFc1In; p.K = kFc1Out;
     p.dy = h->dh1; p.w = h->online_r + h->L.fw1; p.act = h->a3[0]; p.dx = h->dy3;
+    p.bmap = h->fc1_maps != nullptr && !h->stream ? h->fc1_maps + 2 : nullptr;
     DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
   }
   static const bool fc1w_early = getenv("DQNB_FC1W_EARLY") != nullptr;   // release fc1's wgrad right behind its dgrad
@@ -940,6 +979,14 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
   if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
+  if (h->tf32 && !h->stream && getenv("DQNB_NO_TMA") == nullptr) {
+    CUtensorMap maps[3];
+    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[0]));
+    DQNB_TRY(make_tmap_2d(h->target_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[1]));
+    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, kT32BK, T32DenseDgrad::BN, CU_TENSOR_MAP_SWIZZLE_128B, &maps[2]));
+    DQNB_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->fc1_maps), sizeof(maps)));
+    DQNB_CUDA(cudaMemcpy(h->fc1_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
+  }
   if (h->tf32 && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
     DQNB_TRY(dmalloc(&h->conv1_h16, (size_t)2 * Conv1::COUT * Conv1::KCOL));
   if (h->tf32 && !h->stream && getenv("DQNB_NO_F16_CONV23") == nullptr) {
@@ -1050,7 +1097,7 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
     for (float* b : hb) cudaFree(b);
     cudaFree(q.counters);
   }
-  cudaFree(h->conv1_h16); cudaFree(h->conv23_h16);
+  cudaFree(h->conv1_h16); cudaFree(h->conv23_h16); cudaFree(h->fc1_maps);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1h[z]); cudaFree(h->a2h[z]); }
   for (auto& s : h->side) if (s) cudaStreamDestroy(s);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);

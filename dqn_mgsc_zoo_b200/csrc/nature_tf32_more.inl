@@ -77,6 +77,9 @@ struct T32DenseFwd {
   const float* w[kMaxNets];
   float* part;              // [nets][splits][batch][N]
   int splits, batch, merged;
+  static constexpr bool B_TMA = true;     // gemm_tf32.cuh: W[k, n] tiles by tensor-map TMA when a map is given
+  const void* bmap[kMaxNets];             // device address of the CUtensorMap of w[z], or null
+  __device__ const void* b_tmap(int z) const { return bmap[z]; }
   using ARow = const float*;   // x + m*K or null
   using ACol = int;            // k or -1
   using BRow = T32MatKN::Row;
@@ -180,6 +183,9 @@ struct T32DenseDgrad {
   const float* w;           // [IN, OUT]
   const float* act;         // [batch, IN] forward activation feeding this layer
   float* dx;
+  static constexpr bool B_TMA = true;
+  const void* bmap;         // device address of the CUtensorMap of w viewed [IN rows, OUT contiguous], or null
+  __device__ const void* b_tmap(int) const { return bmap; }
   using ARow = const float*;
   using ACol = int;
   using BRow = const float*;
