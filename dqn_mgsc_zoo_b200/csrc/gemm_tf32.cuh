@@ -226,7 +226,9 @@ __device__ __forceinline__ void t32_widen8h(uint32_t dst, uint32_t w0, uint32_t 
 }
 template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::true_type {};
 //   static constexpr bool PRELOAD = true;  Pre preload(z, split, m, n) const;  void store4p(z, split, m, n, v, pre) const;
-// the epilogue fetches what store4 would read for ALL of a thread's rows before it stores any of them.
+// what store4 would read from global memory for each of a thread's rows is fetched by preload() while the MMAs are
+// still running and handed to store4p (store4 stays: the stream kernel and the deferred paths call it).
+struct T32NoPreload { struct Pre {}; };
 template <class P, class = void> struct t32_preload : std::false_type {};
 template <class P> struct t32_preload<P, std::enable_if_t<P::PRELOAD>> : std::true_type {};
 //   static constexpr bool B_TMA = true;  const void* b_tmap(int z) const;
@@ -495,9 +497,40 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
     t32_commit(&done_bar);
   }
 
+  // ---- the store assignment, fixed before the accumulators exist: thread t < 256 owns one float4 column group
+  // (c4 = t mod G4) of rows row_beg + t / G4 + k * RPP.  The column - hence the bias / mask column the problem's
+  // store reads - is fixed per thread, the row advances by a constant and the passes are fully unrolled.  (A rolled
+  // loop with per-item division and store4's address arithmetic ran ~400 clocks per item at 8 warps per SM.)
+  // Split-K CTAs of a tile form a cluster along grid.y (unless the problem defers the reduction): CTA `split` then
+  // owns rows [split*R, (split+1)*R) of the summed tile; otherwise the CTA owns all 128 rows of its own tile.
+  constexpr int PSTRIDE = BN + 4;   // floats; +4 keeps the float4 row writes off one bank
+  constexpr int G4 = BN / 4;
+  constexpr int RPP = kT32Producers / G4;          // rows per pass
+  constexpr int PASSES = kT32BM / RPP;
+  const bool clustered = !P::DEFER_REDUCE && splits > 1;
+  const int c4 = t % G4, r0 = t / G4;
+  const int n = n0 + c4 * 4;
+  const bool col_ok = n < p.N;
+  const int rows_here = p.M - m0;                  // rows of this tile that exist
+  const int R = clustered ? (kT32BM + splits - 1) / splits : kT32BM;
+  const int row_beg = clustered ? split * R : 0;
+  const int row_end = min(min(kT32BM, row_beg + R), rows_here);
+  // What the problem's store reads from global memory (bias, ReLU mask of the layer input, optimiser state) is
+  // fetched NOW, while the tensor core is still working: issued after the accumulators are ready, that round trip
+  // (1 000-2 000 clocks from L2) was the longest part of the store phase.
+  using PreT = typename std::conditional_t<t32_preload<P>::value, P, T32NoPreload>::Pre;
+  PreT pre[PASSES];
+  if constexpr (t32_preload<P>::value) {
+    if (warp < 8) {
+#pragma unroll
+      for (int k = 0; k < PASSES; ++k) {
+        const int r = row_beg + r0 + k * RPP;
+        if (col_ok && r < row_end) pre[k] = p.preload(z, split, m0 + r, n);
+      }
+    }
+  }
   // ---- epilogue, part 1: accumulators TMEM -> registers -> this CTA's smem tile [128][BN+4]
   // (the operand slab is dead once the MMAs are done).  Thread t < 128 owns row t (TMEM lane t).
-  constexpr int PSTRIDE = BN + 4;   // floats; +4 keeps the float4 row writes off one bank
   if (warp < 4) {
     if (nkb > 0) mbar_wait(&done_bar, 0);
     t32_fence_after();
@@ -516,11 +549,8 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
     }
   }
   if (dbg && t == 0) sk.dbg[5] = clock64();       // tile parked in smem
-  // ---- part 2: split-K CTAs of a tile form a cluster along grid.y (unless the problem defers the
-  // reduction): CTA `split` sums rows [split*R, (split+1)*R) of all partial tiles, in split order,
-  // through distributed shared memory.  Either way the tile leaves as coalesced float4 items
-  // handed to p.store4 (bias / relu / mask / partial-buffer placement live there).
-  const bool clustered = !P::DEFER_REDUCE && splits > 1;
+  // ---- part 2: the tile leaves as coalesced float4 items handed to the problem's store (bias / relu / mask /
+  // partial-buffer placement live there); clustered tiles are summed in split order through distributed smem.
   if (clustered) cluster_sync_all(); else __syncthreads();
   // Programmatic dependent launch: the MMAs are done and only the store loop is left, so let the
   // next kernel of the stream get its CTAs placed and run its prologue (barriers, TMEM) now; it
@@ -529,63 +559,38 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   asm volatile("griddepcontrol.launch_dependents;");
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
-    // Thread t owns one float4 column group (c4 = t mod G4) of rows t / G4 + k * RPP: the column - hence the
-    // bias / mask column the problem's store4 reads - is fixed per thread, the row advances by a constant, and
-    // the passes are fully unrolled with every shared-memory load issued before the first store4.  (A rolled
-    // loop with per-item division and store4's address arithmetic ran ~400 clocks per item at 8 warps per SM:
-    // pure instruction latency, 3 000+ clocks per tile.)
-    constexpr int G4 = BN / 4;
-    constexpr int RPP = kT32Producers / G4;          // rows per pass
-    constexpr int PASSES = kT32BM / RPP;
-    const int c4 = t % G4, r0 = t / G4;
-    const int n = n0 + c4 * 4;
-    const bool col_ok = n < p.N;
-    const int rows_here = p.M - m0;                  // rows of this tile that exist
+    auto emit = [&](int k, int r, const float4& v) {
+      if constexpr (t32_preload<P>::value) p.store4p(z, split, m0 + r, n, v, pre[k]);
+      else p.store4(z, split, m0 + r, n, v);
+    };
     if (!clustered) {
       float4 v[PASSES];
 #pragma unroll
       for (int k = 0; k < PASSES; ++k) v[k] = ld_shared_f4(smem + ((r0 + k * RPP) * PSTRIDE + c4 * 4) * 4);
-      if constexpr (t32_preload<P>::value) {
-        // the problem's store reads global memory it also writes (fused optimiser step): the compiler cannot move
-        // pass k+1's loads above pass k's stores, so each pass would wait a full memory latency (measured 900
-        // clocks per pass) - fetch everything first
-        typename P::Pre pre[PASSES];
 #pragma unroll
-        for (int k = 0; k < PASSES; ++k) {
-          const int r = r0 + k * RPP;
-          if (col_ok && r < rows_here) pre[k] = p.preload(z, split, m0 + r, n);
-        }
-#pragma unroll
-        for (int k = 0; k < PASSES; ++k) {
-          const int r = r0 + k * RPP;
-          if (col_ok && r < rows_here) p.store4p(z, split, m0 + r, n, v[k], pre[k]);
-        }
-      } else {
-#pragma unroll
-        for (int k = 0; k < PASSES; ++k) {
-          const int r = r0 + k * RPP;
-          if (col_ok && r < rows_here) p.store4(z, split, m0 + r, n, v[k]);
-        }
+      for (int k = 0; k < PASSES; ++k) {
+        const int r = r0 + k * RPP;
+        if (col_ok && r < row_end) emit(k, r, v[k]);
       }
     } else {
       const int nsum = splits;
-      const int R = (kT32BM + splits - 1) / splits;
-      const int row_beg = split * R;
-      const int row_end = min(min(kT32BM, row_beg + R), rows_here);
-#pragma unroll 2
-      for (int r = row_beg + r0; r < row_end; r += RPP) {
-        const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
-        // all partial tiles' loads in flight together (a DSMEM load is a few hundred cycles), then the
-        // sum in split order
-        float4 x[kT32MaxCluster];
 #pragma unroll
-        for (int q = 0; q < kT32MaxCluster; ++q)
-          if (q < nsum) x[q] = ld_cluster_f4(cluster_map(local, (uint32_t)q));
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < PASSES; ++k) {
+        const int r = row_beg + r0 + k * RPP;
+        if (r < row_end) {
+          const uint32_t local = smem + (r * PSTRIDE + c4 * 4) * 4;
+          // all partial tiles' loads in flight together (a DSMEM load is a few hundred cycles), then the
+          // sum in split order
+          float4 x[kT32MaxCluster];
 #pragma unroll
-        for (int q = 0; q < kT32MaxCluster; ++q)
-          if (q < nsum) { v.x += x[q].x; v.y += x[q].y; v.z += x[q].z; v.w += x[q].w; }
-        if (col_ok) p.store4(z, split, m0 + r, n, v);
+          for (int q = 0; q < kT32MaxCluster; ++q)
+            if (q < nsum) x[q] = ld_cluster_f4(cluster_map(local, (uint32_t)q));
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int q = 0; q < kT32MaxCluster; ++q)
+            if (q < nsum) { v.x += x[q].x; v.y += x[q].y; v.z += x[q].z; v.w += x[q].w; }
+          if (col_ok) emit(k, r, v);
+        }
       }
     }
   }

@@ -97,14 +97,19 @@ struct T32ConvFwd {
   __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
   __device__ BCol b_col(int z, int k) const { return T32MatKN::col(w[z], k, K, N); }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, w[0]); }
-  __device__ void store4(int z, int, int m, int n, float4 v) const {
-    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
+  // slab kernel: the bias is fetched while the MMAs run (gemm_tf32.cuh PRELOAD)
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 b; };
+  __device__ Pre preload(int z, int, int, int n) const { return {__ldg(reinterpret_cast<const float4*>(bias[z] + n))}; }
+  __device__ void store4p(int z, int, int m, int n, float4 v, const Pre& q) const {
     constexpr float s = InScale<TIn>::value;
+    const float4 b = q.b;
     const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
                                  fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
     *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
     if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
   }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
 };
 
 // Double-Q conv1: three nets but only two distinct inputs and two distinct weight sets.  Staging
@@ -160,13 +165,20 @@ struct T32ConvFwdDoubleQ {
     const bool ok = r.n >= 0 && c >= 0;
     cp16(dst, ok ? (r.which ? w[1] : w[0]) + (size_t)c * L::COUT + r.n : w[0], ok);
   }
-  __device__ void store4(int, int, int m, int n, float4 v) const {
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 b; };
+  __device__ Pre preload(int, int, int, int n) const {
+    const int which = n >= L::COUT;
+    return {__ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + (n - which * L::COUT)))};
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
+  __device__ void store4p(int, int, int m, int n, float4 v, const Pre& q) const {
     const int half = m >= Mh, which = n >= L::COUT;
     if (!half && which) return;
     const int nn = n - which * L::COUT;
     float* dst = half ? (which ? y[1] : y[2]) : y[0];
     __half* dsth = half ? (which ? yh[1] : yh[2]) : yh[0];
-    const float4 b = __ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + nn));
+    const float4 b = q.b;
     constexpr float s = InScale<TIn>::value;
     const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
                                  fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
@@ -243,8 +255,12 @@ struct H16ConvFwd {
     const bool ok = r != nullptr && c >= 0;
     cp16(dst, ok ? r + c : w16[0], ok);
   }
-  __device__ void store4(int z, int, int m, int n, float4 v) const {
-    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 b; };
+  __device__ Pre preload(int z, int, int, int n) const { return {__ldg(reinterpret_cast<const float4*>(bias[z] + n))}; }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
+  __device__ void store4p(int z, int, int m, int n, float4 v, const Pre& q) const {
+    const float4 b = q.b;
     const float4 o = make_float4(fmaxf(v.x + b.x, 0.f), fmaxf(v.y + b.y, 0.f), fmaxf(v.z + b.z, 0.f),
                                  fmaxf(v.w + b.w, 0.f));
     *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);

@@ -50,16 +50,24 @@ struct T32ConvDgrad {
     const bool ok = r >= 0 && c >= 0;
     cp16(dst, ok ? w + r + c : w, ok);
   }
-  __device__ void store4(int z, int, int m, int n, float4 v) const {
+  // slab kernel: the ReLU mask (the layer input) is fetched while the MMAs run (gemm_tf32.cuh PRELOAD)
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 a; int64_t idx; };   // idx < 0: the position does not exist (ragged parity class)
+  __device__ Pre preload(int z, int, int m, int n) const {
     int b = m / (NY * NX), r = m - b * (NY * NX);
     int yy = r / NX, xx = r - yy * NX;
     int y = (z / S) + S * yy, x = (z % S) + S * xx;
-    if (y >= L::HIN || x >= L::WIN) return;
-    const size_t idx = ((size_t)(b * L::HIN + y) * L::WIN + x) * L::CIN + n;
-    const float4 a = __ldg(reinterpret_cast<const float4*>(act_in + idx));
-    *reinterpret_cast<float4*>(dx + idx) =
+    if (y >= L::HIN || x >= L::WIN) return {make_float4(0.f, 0.f, 0.f, 0.f), -1};
+    const int64_t idx = ((int64_t)(b * L::HIN + y) * L::WIN + x) * L::CIN + n;
+    return {__ldg(reinterpret_cast<const float4*>(act_in + idx)), idx};
+  }
+  __device__ void store4p(int, int, int, int, float4 v, const Pre& q) const {
+    if (q.idx < 0) return;
+    const float4 a = q.a;
+    *reinterpret_cast<float4*>(dx + q.idx) =
         tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
   }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
 };
 
 // ---------------------------------------------------------------- dense layers (fc1)
@@ -145,8 +153,9 @@ struct T32DenseWgrad {
     }
     store4p(0, split, m, n, v, preload(0, split, m, n));
   }
-  // the fused optimiser step reads p / mu / nu and writes them back: loads of all rows first (gemm_tf32.cuh)
-  static constexpr bool PRELOAD = true;
+  // the fused optimiser step reads p / mu / nu and writes them back: loads of all rows first, while the MMAs run
+  // (gemm_tf32.cuh).  Only the one-k-block instantiation is ever fused; the others keep plain store4.
+  static constexpr bool PRELOAD = KB_ == 1;
   struct Pre { float4 p, mu, nu; };
   __device__ Pre preload(int, int, int m, int n) const {
     Pre q;
@@ -196,10 +205,13 @@ struct T32DenseDgrad {
   __device__ BRow b_row(int, int n) const { return n < N ? w + (size_t)n * K : nullptr; }
   __device__ BCol b_col(int, int k) const { return k < K ? k : -1; }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, w); }
-  __device__ void store4(int, int, int m, int n, float4 v) const {
-    const size_t idx = (size_t)m * N + n;
-    const float4 a = __ldg(reinterpret_cast<const float4*>(act + idx));
-    *reinterpret_cast<float4*>(dx + idx) =
+  static constexpr bool PRELOAD = true;
+  struct Pre { float4 a; };
+  __device__ Pre preload(int, int, int m, int n) const { return {__ldg(reinterpret_cast<const float4*>(act + (size_t)m * N + n))}; }
+  __device__ void store4p(int, int, int m, int n, float4 v, const Pre& q) const {
+    const float4 a = q.a;
+    *reinterpret_cast<float4*>(dx + (size_t)m * N + n) =
         tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
   }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
 };
