@@ -225,10 +225,14 @@ __device__ __forceinline__ void t32_widen8h(uint32_t dst, uint32_t w0, uint32_t 
                : "memory");
 }
 template <class P> struct t32_a_row16<P, std::enable_if_t<P::A_ROW16>> : std::true_type {};
-//   static constexpr bool PRELOAD = true;  Pre preload(z, split, m, n) const;  void store4p(z, split, m, n, v, pre) const;
-// what store4 would read from global memory for each of a thread's rows is fetched by preload() while the MMAs are
-// still running and handed to store4p (store4 stays: the stream kernel and the deferred paths call it).
-struct T32NoPreload { struct Pre {}; };
+//   static constexpr bool PRELOAD = true;
+//   Ctx  store_ctx(z, split, n) const;                      per thread: what depends on the column only (destination bases, bias)
+//   Pre  preload(const Ctx&, z, split, m, n) const;         per row: element offsets + the global loads the store needs
+//   void store4p(const Ctx&, const Pre&, float4 v) const;   the store itself: arithmetic and st.global only
+// Both are evaluated while the MMAs are still running, so that neither the round trip of those loads (1 000-2 000
+// clocks from L2) nor the address arithmetic (~60 instructions per row when left to store4) sits between the finished
+// accumulators and the stores.  store4 stays: the stream kernel and the non-PRELOAD instantiations call it.
+struct T32NoPreload { struct Pre {}; struct Ctx {}; };
 template <class P, class = void> struct t32_preload : std::false_type {};
 template <class P> struct t32_preload<P, std::enable_if_t<P::PRELOAD>> : std::true_type {};
 //   static constexpr bool B_TMA = true;  const void* b_tmap(int z) const;
@@ -518,14 +522,16 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   // What the problem's store reads from global memory (bias, ReLU mask of the layer input, optimiser state) is
   // fetched NOW, while the tensor core is still working: issued after the accumulators are ready, that round trip
   // (1 000-2 000 clocks from L2) was the longest part of the store phase.
-  using PreT = typename std::conditional_t<t32_preload<P>::value, P, T32NoPreload>::Pre;
-  PreT pre[PASSES];
+  using PreOwner = std::conditional_t<t32_preload<P>::value, P, T32NoPreload>;
+  typename PreOwner::Ctx sctx;
+  typename PreOwner::Pre pre[PASSES];
   if constexpr (t32_preload<P>::value) {
-    if (warp < 8) {
+    if (warp < 8 && col_ok) {
+      sctx = p.store_ctx(z, split, n);
 #pragma unroll
       for (int k = 0; k < PASSES; ++k) {
         const int r = row_beg + r0 + k * RPP;
-        if (col_ok && r < row_end) pre[k] = p.preload(z, split, m0 + r, n);
+        if (r < row_end) pre[k] = p.preload(sctx, z, split, m0 + r, n);
       }
     }
   }
@@ -560,7 +566,7 @@ __global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
     auto emit = [&](int k, int r, const float4& v) {
-      if constexpr (t32_preload<P>::value) p.store4p(z, split, m0 + r, n, v, pre[k]);
+      if constexpr (t32_preload<P>::value) p.store4p(sctx, pre[k], v);
       else p.store4(z, split, m0 + r, n, v);
     };
     if (!clustered) {

@@ -487,6 +487,10 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
   // conv2 / conv3 with fp16 operands (slab kernel only): every conv1 / conv2 variant below also leaves an fp16 copy
   bool h16 = h->conv23_h16 != nullptr && !h->stream;
   for (int z = 0; z < nets; ++z) h16 = h16 && (wts[z] == h->online_r || wts[z] == h->target_r);
+  // With fp16 operands downstream, the fp32 conv1 / conv2 outputs of the nets that are only evaluated (z >= 1: no
+  // backward pass reads them) are never consumed: their stores (two thirds of the layer's fp32 bytes) are skipped.
+  float* y1[kMaxNets]; float* y2[kMaxNets];
+  for (int z = 0; z < kMaxNets; ++z) { y1[z] = (h16 && z > 0) ? nullptr : h->a1[z]; y2[z] = (h16 && z > 0) ? nullptr : h->a2[z]; }
   if (nets == 3 && x[1] == x[2] && wts[0] == wts[2]) {   // double-Q update: one merged conv1 GEMM
     auto fill = [&](auto& p) {
       p.Mh = rows * Conv1::HOUT * Conv1::WOUT;
@@ -494,7 +498,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       p.x[0] = x[0]; p.x[1] = x[1];
       p.w[0] = wts[0] + h->L.w1; p.w[1] = wts[1] + h->L.w1;
       p.bias[0] = params[0] + h->L.b1; p.bias[1] = params[1] + h->L.b1;
-      for (int z = 0; z < kMaxNets; ++z) { p.y[z] = h->a1[z]; p.yh[z] = h16 ? h->a1h[z] : nullptr; }
+      for (int z = 0; z < kMaxNets; ++z) { p.y[z] = y1[z]; p.yh[z] = h16 ? h->a1h[z] : nullptr; }
     };
     if (h->conv1_h16 != nullptr && wts[0] == h->online_r && wts[1] == h->target_r) {   // fp16 operands: one wave at batch 32
       H16ConvFwdDoubleQ<Conv1, uint8_t> p;
@@ -508,7 +512,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
     }
   } else {
-    DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, h->a1, st,
+    DQNB_TRY((t32_conv_fwd<Conv1, uint8_t>(h, nets, rows, x, params, wts, h->L.w1, h->L.b1, y1, st,
                                            h16 ? h->a1h : nullptr)));
   }
   if (h16) {
@@ -526,7 +530,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       static const int s3 = getenv("DQNB_H16_SPLITS3") ? atoi(getenv("DQNB_H16_SPLITS3")) : 1;
       return run_t32(h, p, nets, layer == 2 ? s2 : s3, st);
     };
-    DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, h->a2, h->L.b2, 2));
+    DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, y2, h->L.b2, 2));
     DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));
   } else {
     DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
@@ -547,7 +551,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
   h->fc1_rows = rows;
   const size_t need = (size_t)nets * p.splits * rows * kFc1Out;
   if (h->sizing) h->fc1_part_cap = std::max(h->fc1_part_cap, need);
-  p.part = h->fc1_part;
+  p.part = getenv("DQNB_DBG_FC1_NOSTORE") ? nullptr : h->fc1_part;
   return run_t32(h, p, Z, p.splits, st);
 }
 

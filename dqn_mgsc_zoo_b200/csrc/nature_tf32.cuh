@@ -97,19 +97,26 @@ struct T32ConvFwd {
   __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
   __device__ BCol b_col(int z, int k) const { return T32MatKN::col(w[z], k, K, N); }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, w[0]); }
-  // slab kernel: the bias is fetched while the MMAs run (gemm_tf32.cuh PRELOAD)
+  // slab kernel: destinations and bias are resolved while the MMAs run (gemm_tf32.cuh PRELOAD)
   static constexpr bool PRELOAD = true;
-  struct Pre { float4 b; };
-  __device__ Pre preload(int z, int, int, int n) const { return {__ldg(reinterpret_cast<const float4*>(bias[z] + n))}; }
-  __device__ void store4p(int z, int, int m, int n, float4 v, const Pre& q) const {
-    constexpr float s = InScale<TIn>::value;
-    const float4 b = q.b;
-    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
-                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
-    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
-    if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
+  struct Ctx { float* y; __half* yh; float4 b; };   // column-offset destinations (null: not wanted) and the bias
+  struct Pre { int off; };                          // m * COUT
+  __device__ Ctx store_ctx(int z, int, int n) const {
+    return {y[z] != nullptr ? y[z] + n : nullptr, yh[z] != nullptr ? yh[z] + n : nullptr,
+            __ldg(reinterpret_cast<const float4*>(bias[z] + n))};
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
+  __device__ Pre preload(const Ctx&, int, int, int m, int) const { return {m * L::COUT}; }
+  __device__ void store4p(const Ctx& c, const Pre& q, float4 v) const {
+    constexpr float s = InScale<TIn>::value;
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, c.b.x), 0.f), fmaxf(fmaf(v.y, s, c.b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, c.b.z), 0.f), fmaxf(fmaf(v.w, s, c.b.w), 0.f));
+    if (c.y != nullptr) *reinterpret_cast<float4*>(c.y + q.off) = tf32_rn4(o);   // null: only the fp16 copy is consumed
+    if (c.yh != nullptr) t32_store_half4(c.yh + q.off, o);
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const {
+    const Ctx c = store_ctx(z, split, n);
+    store4p(c, preload(c, z, split, m, n), v);
+  }
 };
 
 // Double-Q conv1: three nets but only two distinct inputs and two distinct weight sets.  Staging
@@ -166,25 +173,36 @@ struct T32ConvFwdDoubleQ {
     cp16(dst, ok ? (r.which ? w[1] : w[0]) + (size_t)c * L::COUT + r.n : w[0], ok);
   }
   static constexpr bool PRELOAD = true;
-  struct Pre { float4 b; };
-  __device__ Pre preload(int, int, int, int n) const {
-    const int which = n >= L::COUT;
-    return {__ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + (n - which * L::COUT)))};
+  // lo: rows < Mh (s_tm1), hi: rows >= Mh (s_t); the (s_tm1, target) quadrant has no destination at all
+  struct Ctx { float *y_lo, *y_hi; __half *yh_lo, *yh_hi; float4 b; };
+  struct Pre { int off; };    // (m mod Mh) * COUT, bit 31 set for the hi half
+  __device__ Ctx store_ctx(int, int, int n) const {
+    const int which = n >= L::COUT, nn = n - which * L::COUT;
+    float* lo = which ? nullptr : y[0];
+    float* hi = which ? y[1] : y[2];
+    __half* lo_h = which ? nullptr : yh[0];
+    __half* hi_h = which ? yh[1] : yh[2];
+    return {lo != nullptr ? lo + nn : nullptr, hi != nullptr ? hi + nn : nullptr, lo_h != nullptr ? lo_h + nn : nullptr,
+            hi_h != nullptr ? hi_h + nn : nullptr, __ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + nn))};
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
-  __device__ void store4p(int, int, int m, int n, float4 v, const Pre& q) const {
-    const int half = m >= Mh, which = n >= L::COUT;
-    if (!half && which) return;
-    const int nn = n - which * L::COUT;
-    float* dst = half ? (which ? y[1] : y[2]) : y[0];
-    __half* dsth = half ? (which ? yh[1] : yh[2]) : yh[0];
-    const float4 b = q.b;
+  __device__ Pre preload(const Ctx&, int, int, int m, int) const {
+    const int half = m >= Mh;
+    return {((m - half * Mh) * L::COUT) | (half ? (int)0x80000000 : 0)};
+  }
+  __device__ void store4p(const Ctx& c, const Pre& q, float4 v) const {
+    const bool half = q.off < 0;
+    const int at = q.off & 0x7fffffff;
+    float* dst = half ? c.y_hi : c.y_lo;
+    __half* dsth = half ? c.yh_hi : c.yh_lo;
     constexpr float s = InScale<TIn>::value;
-    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
-                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
-    const size_t at = (size_t)(m - half * Mh) * L::COUT + nn;
-    *reinterpret_cast<float4*>(dst + at) = tf32_rn4(o);
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, c.b.x), 0.f), fmaxf(fmaf(v.y, s, c.b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, c.b.z), 0.f), fmaxf(fmaf(v.w, s, c.b.w), 0.f));
+    if (dst != nullptr) *reinterpret_cast<float4*>(dst + at) = tf32_rn4(o);   // null: only the fp16 copy is consumed
     if (dsth != nullptr) t32_store_half4(dsth + at, o);
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const {
+    const Ctx c = store_ctx(z, split, n);
+    store4p(c, preload(c, z, split, m, n), v);
   }
 };
 
@@ -256,15 +274,22 @@ struct H16ConvFwd {
     cp16(dst, ok ? r + c : w16[0], ok);
   }
   static constexpr bool PRELOAD = true;
-  struct Pre { float4 b; };
-  __device__ Pre preload(int z, int, int, int n) const { return {__ldg(reinterpret_cast<const float4*>(bias[z] + n))}; }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
-  __device__ void store4p(int z, int, int m, int n, float4 v, const Pre& q) const {
-    const float4 b = q.b;
-    const float4 o = make_float4(fmaxf(v.x + b.x, 0.f), fmaxf(v.y + b.y, 0.f), fmaxf(v.z + b.z, 0.f),
-                                 fmaxf(v.w + b.w, 0.f));
-    *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
-    if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
+  struct Ctx { float* y; __half* yh; float4 b; };
+  struct Pre { int off; };
+  __device__ Ctx store_ctx(int z, int, int n) const {
+    return {y[z] != nullptr ? y[z] + n : nullptr, yh[z] != nullptr ? yh[z] + n : nullptr,
+            __ldg(reinterpret_cast<const float4*>(bias[z] + n))};
+  }
+  __device__ Pre preload(const Ctx&, int, int, int m, int) const { return {m * L::COUT}; }
+  __device__ void store4p(const Ctx& c, const Pre& q, float4 v) const {
+    const float4 o = make_float4(fmaxf(v.x + c.b.x, 0.f), fmaxf(v.y + c.b.y, 0.f), fmaxf(v.z + c.b.z, 0.f),
+                                 fmaxf(v.w + c.b.w, 0.f));
+    if (c.y != nullptr) *reinterpret_cast<float4*>(c.y + q.off) = tf32_rn4(o);   // null: only the fp16 copy is consumed
+    if (c.yh != nullptr) t32_store_half4(c.yh + q.off, o);
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const {
+    const Ctx c = store_ctx(z, split, n);
+    store4p(c, preload(c, z, split, m, n), v);
   }
 };
 // w[k][n] fp32 (one net's conv1 filters, HWIO) -> dst[n][k] fp16

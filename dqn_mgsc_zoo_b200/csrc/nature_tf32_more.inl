@@ -52,22 +52,24 @@ struct T32ConvDgrad {
   }
   // slab kernel: the ReLU mask (the layer input) is fetched while the MMAs run (gemm_tf32.cuh PRELOAD)
   static constexpr bool PRELOAD = true;
-  struct Pre { float4 a; int64_t idx; };   // idx < 0: the position does not exist (ragged parity class)
-  __device__ Pre preload(int z, int, int m, int n) const {
+  struct Ctx {};
+  struct Pre { float4 a; int idx; };   // idx < 0: the position does not exist (ragged parity class)
+  __device__ Ctx store_ctx(int, int, int) const { return {}; }
+  __device__ Pre preload(const Ctx&, int z, int, int m, int n) const {
     int b = m / (NY * NX), r = m - b * (NY * NX);
     int yy = r / NX, xx = r - yy * NX;
     int y = (z / S) + S * yy, x = (z % S) + S * xx;
     if (y >= L::HIN || x >= L::WIN) return {make_float4(0.f, 0.f, 0.f, 0.f), -1};
-    const int64_t idx = ((int64_t)(b * L::HIN + y) * L::WIN + x) * L::CIN + n;
+    const int idx = ((b * L::HIN + y) * L::WIN + x) * L::CIN + n;
     return {__ldg(reinterpret_cast<const float4*>(act_in + idx)), idx};
   }
-  __device__ void store4p(int, int, int, int, float4 v, const Pre& q) const {
+  __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
     if (q.idx < 0) return;
     const float4 a = q.a;
     *reinterpret_cast<float4*>(dx + q.idx) =
         tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(Ctx{}, preload(Ctx{}, z, split, m, n), v); }
 };
 
 // ---------------------------------------------------------------- dense layers (fc1)
@@ -87,13 +89,16 @@ struct T32DenseFwd {
   int splits, batch, merged;
   static constexpr bool B_TMA = true;     // gemm_tf32.cuh: W[k, n] tiles by tensor-map TMA when a map is given
   const void* bmap[kMaxNets];             // device address of the CUtensorMap of w[z], or null
-  __device__ const void* b_tmap(int z) const { return bmap[z]; }
+  // (the per-net arrays are read through selects: a dynamically indexed kernel parameter array makes the
+  // compiler copy the whole parameter block to local memory)
+  template <class T> __device__ static T pick(const T (&a)[kMaxNets], int z) { return z == 0 ? a[0] : z == 1 ? a[1] : a[2]; }
+  __device__ const void* b_tmap(int z) const { return pick(bmap, z); }
   using ARow = const float*;   // x + m*K or null
   using ACol = int;            // k or -1
   using BRow = T32MatKN::Row;
   using BCol = T32MatKN::Col;
   __device__ ARow a_row(int z, int m) const {
-    if (!merged) return m < batch ? x[z] + (size_t)m * K : nullptr;
+    if (!merged) return m < batch ? pick(x, z) + (size_t)m * K : nullptr;
     if (z == 1) return m < batch ? x[1] + (size_t)m * K : nullptr;
     if (m < batch) return x[0] + (size_t)m * K;
     return m < 2 * batch ? x[2] + (size_t)(m - batch) * K : nullptr;
@@ -101,17 +106,28 @@ struct T32DenseFwd {
   __device__ ACol a_col(int, int k) const { return k < K ? k : -1; }
   __device__ void a_put(ARow r, ACol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, x[0]); }
   __device__ BRow b_row(int, int n) const { return T32MatKN::row(n, N); }
-  __device__ BCol b_col(int z, int k) const { return T32MatKN::col(w[z], k, K, N); }
+  __device__ BCol b_col(int z, int k) const { return T32MatKN::col(pick(w, z), k, K, N); }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, c, r, w[0]); }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const {
+  // slab kernel: the partial's element offset is worked out while the MMAs run (gemm_tf32.cuh PRELOAD)
+  static constexpr bool PRELOAD = true;
+  struct Ctx {};
+  struct Pre { int idx; };   // element offset into part, or -1: a padding row of the merged tile
+  __device__ Ctx store_ctx(int, int, int) const { return {}; }
+  __device__ Pre preload(const Ctx&, int z, int split, int m, int n) const {
     int net = z, row = m;
     if (merged) {
       if (z == 0 && m >= batch) { net = 2; row = m - batch; }
-      if (row >= batch) return;
+      if (row >= batch) return {-1};
     }
-    *reinterpret_cast<float4*>(part + (((size_t)net * splits + split) * batch + row) * N + n) = v;
+    return {(((net * splits + split) * batch + row) << 9) + n};
   }
+  __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
+    if (q.idx < 0 || part == nullptr) return;   // (null part: timing experiment DQNB_DBG_FC1_NOSTORE)
+    *reinterpret_cast<float4*>(part + q.idx) = v;
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(Ctx{}, preload(Ctx{}, z, split, m, n), v); }
 };
+static_assert(kFc1Out == 512, "T32DenseFwd::preload shifts by log2(fc1 width)");
 
 // dW[m'=k_in, n] = sum_b x[b,m'] * dy[b,n];  row m' == IN is ones -> bias gradient.
 // When the whole batch fits one CTA's K range (splits == 1, the batch-32 case) the epilogue can
@@ -151,34 +167,36 @@ struct T32DenseWgrad {
       *reinterpret_cast<float4*>(gpart + (size_t)split * ((size_t)M * N) + idx) = v;
       return;
     }
-    store4p(0, split, m, n, v, preload(0, split, m, n));
+    store4p(Ctx{}, preload(Ctx{}, 0, split, m, n), v);
   }
   // the fused optimiser step reads p / mu / nu and writes them back: loads of all rows first, while the MMAs run
   // (gemm_tf32.cuh).  Only the one-k-block instantiation is ever fused; the others keep plain store4.
   static constexpr bool PRELOAD = KB_ == 1;
-  struct Pre { float4 p, mu, nu; };
-  __device__ Pre preload(int, int, int m, int n) const {
+  struct Ctx {};
+  struct Pre { float4 p, mu, nu; int64_t idx; };   // idx: element offset into the parameter arena slices / the partial
+  __device__ Ctx store_ctx(int, int, int) const { return {}; }
+  __device__ Pre preload(const Ctx&, int, int split, int m, int n) const {
     Pre q;
-    if (fuse.p == nullptr) { q.p = q.mu = q.nu = make_float4(0.f, 0.f, 0.f, 0.f); return q; }
-    const size_t idx = (size_t)m * N + n;
+    const int64_t idx = (int64_t)m * N + n;
+    if (fuse.p == nullptr) { q.p = q.mu = q.nu = make_float4(0.f, 0.f, 0.f, 0.f); q.idx = (int64_t)split * ((int64_t)M * N) + idx; return q; }
+    q.idx = idx;
     q.mu = __ldcg(reinterpret_cast<const float4*>(fuse.mu + idx));
     q.nu = __ldcg(reinterpret_cast<const float4*>(fuse.nu + idx));
     q.p = __ldcg(reinterpret_cast<const float4*>(fuse.p + idx));
     return q;
   }
-  __device__ void store4p(int, int split, int m, int n, float4 v, const Pre& q) const {
-    const size_t idx = (size_t)m * N + n;
+  __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
     if (fuse.p == nullptr) {
-      *reinterpret_cast<float4*>(gpart + (size_t)split * ((size_t)M * N) + idx) = v;
+      *reinterpret_cast<float4*>(gpart + q.idx) = v;
       return;
     }
     float4 mv = q.mu, nv = q.nu, pv = q.p;
     rmsprop4(pv, mv, nv, v, fuse.lr, fuse.decay, fuse.eps);
-    *reinterpret_cast<float4*>(fuse.g + idx) = v;
-    *reinterpret_cast<float4*>(fuse.mu + idx) = mv;
-    *reinterpret_cast<float4*>(fuse.nu + idx) = nv;
-    *reinterpret_cast<float4*>(fuse.p + idx) = pv;
-    *reinterpret_cast<float4*>(fuse.p_r + idx) = tf32_rn4(pv);
+    *reinterpret_cast<float4*>(fuse.g + q.idx) = v;
+    *reinterpret_cast<float4*>(fuse.mu + q.idx) = mv;
+    *reinterpret_cast<float4*>(fuse.nu + q.idx) = nv;
+    *reinterpret_cast<float4*>(fuse.p + q.idx) = pv;
+    *reinterpret_cast<float4*>(fuse.p_r + q.idx) = tf32_rn4(pv);
   }
 };
 
@@ -206,12 +224,17 @@ struct T32DenseDgrad {
   __device__ BCol b_col(int, int k) const { return k < K ? k : -1; }
   __device__ void b_put(BRow r, BCol c, uint32_t dst) const { t32_put_ptr_off(dst, r, c, w); }
   static constexpr bool PRELOAD = true;
-  struct Pre { float4 a; };
-  __device__ Pre preload(int, int, int m, int n) const { return {__ldg(reinterpret_cast<const float4*>(act + (size_t)m * N + n))}; }
-  __device__ void store4p(int, int, int m, int n, float4 v, const Pre& q) const {
+  struct Ctx {};
+  struct Pre { float4 a; int idx; };
+  __device__ Ctx store_ctx(int, int, int) const { return {}; }
+  __device__ Pre preload(const Ctx&, int, int, int m, int n) const {
+    const int idx = m * N + n;
+    return {__ldg(reinterpret_cast<const float4*>(act + idx)), idx};
+  }
+  __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
     const float4 a = q.a;
-    *reinterpret_cast<float4*>(dx + (size_t)m * N + n) =
+    *reinterpret_cast<float4*>(dx + q.idx) =
         tf32_rn4(make_float4(a.x > 0.f ? v.x : 0.f, a.y > 0.f ? v.y : 0.f, a.z > 0.f ? v.z : 0.f, a.w > 0.f ? v.w : 0.f));
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(z, split, m, n, v, preload(z, split, m, n)); }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(Ctx{}, preload(Ctx{}, z, split, m, n), v); }
 };
