@@ -285,8 +285,12 @@ __device__ __forceinline__ void t32_drain_groups(int nkb, uint64_t* full_bar) {
   }
 }
 
+//   static constexpr int MIN_CTAS = n;   register budget for n resident CTAs per SM (__launch_bounds__)
+template <class P, class = void> struct t32_min_ctas : std::integral_constant<int, 1> {};
+template <class P> struct t32_min_ctas<P, std::enable_if_t<(P::MIN_CTAS > 1)>> : std::integral_constant<int, P::MIN_CTAS> {};
+
 template <class P>
-__global__ void __launch_bounds__(kT32Threads) gemm_tf32(P p, SplitK sk) {
+__global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32(P p, SplitK sk) {
   constexpr int BN = P::BN, COLS = t32_tmem_cols(BN), KB = P::KB_MAX;
   constexpr int A_TILE = t32_tile_bytes(kT32BM, P::A_MN_MAJOR), B_TILE = t32_tile_bytes(BN, P::B_MN_MAJOR);
   extern __shared__ uint8_t smem_raw[];

@@ -193,6 +193,7 @@ struct dqnb_learner {
   cudaStream_t side[3] = {};
   cudaStream_t chain = nullptr;   // stream of the dependent kernel chain in the enqueue in progress
   int prio_hi = 0;                // greatest launch priority of the device
+  int prio_boost = 0;             // priority of the long side-branch kernels (see `boost`)
   bool pdl = false;               // programmatic dependent launch between consecutive chain kernels
   bool boost = false;             // next side-branch launch gets the chain's priority
   bool stream = false;            // large batch: GEMMs go to the persistent ring kernel (gemm_tf32_stream.cuh)
@@ -453,7 +454,7 @@ int run_t32(dqnb_learner* h, const P& p, int Z, int splits, cudaStream_t st) {
   const bool on_chain = st == h->chain;
   if (h->stream) DQNB_CUDA(launch_gemm_tf32_stream(p, Z, splits, sk, st, on_chain ? h->prio_hi : 0));
   else
-    DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, (on_chain || h->boost) ? h->prio_hi : 0,
+    DQNB_CUDA(launch_gemm_tf32(p, Z, splits, sk, st, on_chain ? h->prio_hi : h->boost ? h->prio_boost : 0,
                                on_chain && !h->profiling && h->pdl));
   return mark(h, st, P::NAME);
 }
@@ -578,7 +579,7 @@ int t32_conv_wgrad(dqnb_learner* h, int rows, const TIn* x, const float* dy, int
       cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(256); cfg.stream = bias_st;
       cudaLaunchAttribute attr[1];
       attr[0].id = cudaLaunchAttributePriority;
-      attr[0].val.priority = h->boost ? h->prio_hi : 0;
+      attr[0].val.priority = h->boost ? h->prio_boost : 0;
       cfg.attrs = attr; cfg.numAttrs = 1;
       DQNB_CUDA(cudaLaunchKernelEx(&cfg, bias_colsum_kernel<L::COUT>, dy, p.K, bpart,
                                    own_bias ? (size_t)L::COUT : (size_t)P::PART,
@@ -680,6 +681,18 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   // the batch is one K block (no split-K), its epilogue can apply RMSProp to fc1 on the spot.  It
   // is bandwidth-bound (7 streams over 1.6 M parameters) and is released here, where the chain
   // kernels (conv2 dgrad, conv1 wgrad) leave room for its small CTAs beside their own on every SM.
+  // conv2's weight gradient: half slabs (88 CTAs of 97 KB) fit beside the CTAs of fc1's wgrad and conv1's wgrad, so
+  // it overlaps both; as 44 CTAs of 193 KB (DQNB_C2W_KB8) each needed an SM to itself and the kernel sat at the very
+  // end of the update (measured: span 72.3 -> 69.9 us).  DQNB_C2W_FIRST enqueues it ahead of fc1's wgrad (no gain).
+  static const bool c2w_first = getenv("DQNB_C2W_FIRST") != nullptr, c2w_kb4 = getenv("DQNB_C2W_KB8") == nullptr;
+  auto conv2_wgrad = [&]() -> int {
+    h->boost = h->pdl;   // see the fc1 wgrad below: conv2's wgrad and both bias column sums would otherwise wait for the chain
+    const int rc = c2w_kb4 ? t32_conv_wgrad<Conv2, float, 4, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1)
+                           : t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1);
+    h->boost = false;
+    return rc;
+  };
+  if (c2w_first) DQNB_TRY(conv2_wgrad());
   bool fused = false;
   if (B <= kT32BK && !h->cfg.defer_apply && !h->stream) {
     fused = true;
@@ -712,10 +725,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
                                     kNcclFloat32, kNcclSum, h->dp_comm, sd));
     DQNB_TRY(mark(h, sd, "allreduce_fc"));
   }
-  h->boost = h->pdl;   // see the fc1 wgrad above: conv2's wgrad and both bias column sums would otherwise wait for the chain
-  int rc_c2 = t32_conv_wgrad<Conv2, float, 8, false>(h, B, h->a1[0], h->dy2, h->L.w2, s3, s1);
-  h->boost = false;
-  DQNB_TRY(rc_c2);
+  if (!c2w_first) DQNB_TRY(conv2_wgrad());
   // slab mode: the whole K range (4 taps x 64 channels = 8 k-blocks) in one slab: 100 unsplit tiles, one wave, no
   // cluster reduce (as 2-CTA clusters it was 200 CTAs over two waves: 11.5 us); DQNB_C2DGRAD_KB4 restores that
   static const bool c2_kb4 = getenv("DQNB_C2DGRAD_KB4") != nullptr;
@@ -1022,6 +1032,9 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
     int least = 0, greatest = 0;
     DQNB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     h->prio_hi = greatest;
+    // (numerically lower = scheduled first)  DQNB_BOOST_PRIO = levels below the chain's priority
+    const int off = getenv("DQNB_BOOST_PRIO") ? atoi(getenv("DQNB_BOOST_PRIO")) : 0;
+    h->prio_boost = std::min(least, greatest + std::max(0, off));
     h->pdl = getenv("DQNB_NO_PDL") == nullptr;
   }
   for (auto& e : h->ev) DQNB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
