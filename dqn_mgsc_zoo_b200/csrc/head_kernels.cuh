@@ -53,130 +53,139 @@ __device__ __forceinline__ void warp_argmax(float v, int lane, float& best, int&
   }
 }
 
-// One CTA (4 warps) per batch row.  (1) h1 of every net into smem (finishing fc1 when it was
-// left as split-K partials), (2) fc2: the (net, action) dot products are dealt round-robin to
-// the warps, (3) warp 0 forms the q_learning / double_q_learning target (rlax), the td error,
-// the clipped cotangent and the per-row loss, (4) all threads write the fc2 input gradient dh1.
-constexpr int kHeadThreads = 128;
+// One CTA per batch row, one group of 128 threads (4 warps) per net.  (1) h1 of the group's net (finishing fc1 when
+// it was left as split-K partials: thread c of the group owns columns 4c..4c+3), (2) fc2: the group's (net, action)
+// dot products, (3) warp 0 forms the q_learning / double_q_learning target (rlax), the td error, the clipped
+// cotangent and the per-row loss, (4) all threads write the fc2 input gradient dh1.
+// The kernel is a chain of dependent L2 round trips, so everything that does not depend on the preceding kernel
+// (fc1 bias, fc2 weights and bias, the row's action / reward / discount / weight, the fc2 column of the taken
+// action) is fetched BEFORE griddepcontrol.wait - under programmatic dependent launch that is while fc1 is still
+// storing its partials - and all of a thread's partials are in flight at once.
+constexpr int kHeadGroup = 128;
+constexpr int kHeadThreads = kMaxNets * kHeadGroup;
 __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
-  __shared__ __align__(16) float h_s[1][kFc1Out];
+  __shared__ __align__(16) float h_s[kFc1Out];
   __shared__ float q_s[kMaxNets][kMaxActions];
+  __shared__ float red_s[kMaxNets][kHeadGroup / 32][kMaxActions];
   __shared__ float dq_s;
-  __shared__ int act_s;
   const unsigned long long tl_t0 = tl_begin(g.tl);
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int t = threadIdx.x, lane = t & 31;
+  const int z = t / kHeadGroup, c = t - z * kHeadGroup, gw = c >> 5;   // net, column group, warp inside the net's group
   const int row = blockIdx.x;
   const int A = g.num_actions, nets = g.double_q ? 3 : 2;
-  static_assert(kFc1Out == 4 * kHeadThreads, "one float4 of h1 per thread");
-  __shared__ float red_s[kHeadThreads / 32][kMaxNets][kMaxActions];
-  // (1) h1: thread t owns columns 4t..4t+3 of every net
-  float4 hv[kMaxNets];
-  if (g.fc1_part != nullptr) {
-    float4 acc[kMaxNets];
+  const bool on = z < nets;
+  static_assert(kFc1Out == 4 * kHeadGroup, "one float4 of h1 per thread of a group");
+  static_assert(kMaxNets == 3, "per-net pointers are read through selects");
+  // (a dynamically indexed kernel-parameter array would be copied to local memory)
+  auto pick = [&](auto const& a) { return z == 0 ? a[0] : z == 1 ? a[1] : a[2]; };
+  const float* w2z = pick(g.w2);
+
+  // ---- (0) operands that were final before the preceding kernel started
+  const int act = g.action[row];
+  float4 bias1 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (on && g.fc1_part != nullptr) bias1 = __ldg(reinterpret_cast<const float4*>(pick(g.b1)) + c);
+  constexpr int kGroup = 6;   // actions whose fc2 weights are fetched together (one L2 round trip per group)
+  float wv[kGroup][4];
 #pragma unroll
-    for (int z = 0; z < kMaxNets; ++z) acc[z] = make_float4(0.f, 0.f, 0.f, 0.f);
-    const size_t split_stride = (size_t)g.batch * (kFc1Out / 4);
-    const float4* src = reinterpret_cast<const float4*>(g.fc1_part + (size_t)row * kFc1Out) + t;
-    // 8 splits x up to 3 nets = 24 float4 loads in flight per round trip (17 splits at batch 32: three rounds
-    // instead of five with a 4-deep unroll); the additions keep their split order
-    constexpr int kDepth = 8;
-    for (int q0 = 0; q0 < g.fc1_splits; q0 += kDepth) {
-      float4 x[kMaxNets][kDepth];
+  for (int u = 0; u < kGroup; ++u) {
+    const bool ld = on && u < A;
 #pragma unroll
-      for (int z = 0; z < kMaxNets; ++z) {
+    for (int j = 0; j < 4; ++j) wv[u][j] = ld ? __ldg(w2z + (size_t)(4 * c + j) * A + u) : 0.f;
+  }
+  float b2v = 0.f;
+  if (t < nets * A) {
+    const int zz = t / A, a = t - zz * A;
+    b2v = (zz == 0 ? g.b2[0] : zz == 1 ? g.b2[1] : g.b2[2])[g.shared_bias ? 0 : a];
+  }
+  float rew = 0.f, disc = 0.f, wrow = 1.0f;
+  if (t < 32) {
+    rew = g.reward[row]; disc = g.discount[row];
+    if (g.row_weight) wrow = g.row_weight[row];
+  }
+  float w2a[2];   // fc2 weights of the taken action for the dh1 columns this thread writes
 #pragma unroll
-        for (int u = 0; u < kDepth; ++u)
-          if (z < nets && q0 + u < g.fc1_splits) x[z][u] = __ldcg(src + ((size_t)z * g.fc1_splits + q0 + u) * split_stride);
-      }
-#pragma unroll
-      for (int z = 0; z < kMaxNets; ++z) {
-#pragma unroll
-        for (int u = 0; u < kDepth; ++u)
-          if (z < nets && q0 + u < g.fc1_splits) {
-            acc[z].x += x[z][u].x; acc[z].y += x[z][u].y; acc[z].z += x[z][u].z; acc[z].w += x[z][u].w;
-          }
-      }
-    }
-#pragma unroll
-    for (int z = 0; z < kMaxNets; ++z) {
-      if (z < nets) {
-        const float4 bias = __ldg(reinterpret_cast<const float4*>(g.b1[z]) + t);
-        hv[z] = make_float4(fmaxf(acc[z].x + bias.x, 0.f), fmaxf(acc[z].y + bias.y, 0.f),
-                            fmaxf(acc[z].z + bias.z, 0.f), fmaxf(acc[z].w + bias.w, 0.f));
-        reinterpret_cast<float4*>(g.h1_out[z] + (size_t)row * kFc1Out)[t] = hv[z];
-      }
-    }
-  } else {
-#pragma unroll
-    for (int z = 0; z < kMaxNets; ++z)
-      if (z < nets) hv[z] = reinterpret_cast<const float4*>(g.h1[z] + (size_t)row * kFc1Out)[t];
+  for (int i = 0; i < 2; ++i) {
+    const int k = t + i * kHeadThreads;
+    w2a[i] = k < kFc1Out ? __ldg(g.w2[0] + (size_t)k * A + act) : 0.f;
   }
   if (t < kMaxNets * kMaxActions) (&q_s[0][0])[t] = -INFINITY;
-  // (2) fc2: q[z][a] = sum_k h1[z][k] w2[z][k][a].  Thread t covers k = 4t..4t+3, whose weights
-  // are 4A consecutive floats (coalesced across the CTA); warp shuffle, then 4 warp partials.
-  // Actions go in groups of kGroup: all weight loads of a group are issued first (one L2 round trip
-  // instead of one per action), then the FMAs, then kGroup * nets independent shuffle trees.
-  constexpr int kGroup = 6;
-  for (int a0 = 0; a0 < A; a0 += kGroup) {
-    float wv[kMaxNets][kGroup][4];
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  // ---- (1) h1: thread c of group z owns columns 4c..4c+3 of net z
+  float4 hv = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (on) {
+    if (g.fc1_part != nullptr) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      const size_t split_stride = (size_t)g.batch * (kFc1Out / 4);
+      const float4* src = reinterpret_cast<const float4*>(g.fc1_part + (size_t)row * kFc1Out) + c +
+                          (size_t)z * g.fc1_splits * split_stride;
+      // all partials of the thread in flight (18 splits at batch 32: one round trip); the additions keep split order
+      constexpr int kDepth = 20;
+      for (int q0 = 0; q0 < g.fc1_splits; q0 += kDepth) {
+        float4 x[kDepth];
 #pragma unroll
-    for (int z = 0; z < kMaxNets; ++z) {
+        for (int u = 0; u < kDepth; ++u)
+          if (q0 + u < g.fc1_splits) x[u] = __ldcg(src + (size_t)(q0 + u) * split_stride);
+#pragma unroll
+        for (int u = 0; u < kDepth; ++u)
+          if (q0 + u < g.fc1_splits) { acc.x += x[u].x; acc.y += x[u].y; acc.z += x[u].z; acc.w += x[u].w; }
+      }
+      hv = make_float4(fmaxf(acc.x + bias1.x, 0.f), fmaxf(acc.y + bias1.y, 0.f), fmaxf(acc.z + bias1.z, 0.f),
+                       fmaxf(acc.w + bias1.w, 0.f));
+      reinterpret_cast<float4*>(pick(g.h1_out) + (size_t)row * kFc1Out)[c] = hv;
+    } else {
+      hv = reinterpret_cast<const float4*>(pick(g.h1) + (size_t)row * kFc1Out)[c];
+    }
+  }
+  if (z == 0) reinterpret_cast<float4*>(h_s)[c] = hv;   // relu mask for dh1 below
+  // ---- (2) fc2: q[z][a] = sum_k h1[z][k] w2[z][k][a].  Thread c covers k = 4c..4c+3, whose weights are 4A
+  // consecutive floats (coalesced across the group); warp shuffle, then the group's 4 warp partials.
+  for (int a0 = 0; a0 < A; a0 += kGroup) {
+    if (a0 > 0) {   // (more than kGroup actions: the later groups were not prefetched)
 #pragma unroll
       for (int u = 0; u < kGroup; ++u) {
-        const bool on = z < nets && a0 + u < A;
-        const float* w2 = g.w2[z < nets ? z : 0] + (size_t)(4 * t) * A + (on ? a0 + u : 0);
+        const bool ld = on && a0 + u < A;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) wv[z][u][j] = on ? __ldg(w2 + j * A) : 0.f;
+        for (int j = 0; j < 4; ++j) wv[u][j] = ld ? __ldg(w2z + (size_t)(4 * c + j) * A + a0 + u) : 0.f;
       }
     }
-    float part[kMaxNets][kGroup];
+    float part[kGroup];
 #pragma unroll
-    for (int z = 0; z < kMaxNets; ++z) {
-#pragma unroll
-      for (int u = 0; u < kGroup; ++u) {
-        float s = hv[z < nets ? z : 0].x * wv[z][u][0];
-        s = fmaf(hv[z < nets ? z : 0].y, wv[z][u][1], s);
-        s = fmaf(hv[z < nets ? z : 0].z, wv[z][u][2], s);
-        s = fmaf(hv[z < nets ? z : 0].w, wv[z][u][3], s);
-        part[z][u] = s;
-      }
+    for (int u = 0; u < kGroup; ++u) {
+      float s = hv.x * wv[u][0];
+      s = fmaf(hv.y, wv[u][1], s);
+      s = fmaf(hv.z, wv[u][2], s);
+      s = fmaf(hv.w, wv[u][3], s);
+      part[u] = s;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-      for (int z = 0; z < kMaxNets; ++z) {
-#pragma unroll
-        for (int u = 0; u < kGroup; ++u) part[z][u] += __shfl_xor_sync(0xffffffffu, part[z][u], o);
-      }
+      for (int u = 0; u < kGroup; ++u) part[u] += __shfl_xor_sync(0xffffffffu, part[u], o);
     }
-    if (lane == 0) {
+    if (lane == 0 && on) {
 #pragma unroll
-      for (int z = 0; z < kMaxNets; ++z) {
-#pragma unroll
-        for (int u = 0; u < kGroup; ++u)
-          if (z < nets && a0 + u < A) red_s[warp][z][a0 + u] = part[z][u];
-      }
+      for (int u = 0; u < kGroup; ++u)
+        if (a0 + u < A) red_s[z][gw][a0 + u] = part[u];
     }
   }
-  if (t < kFc1Out / 4) reinterpret_cast<float4*>(h_s[0])[t] = hv[0];   // relu mask for dh1 below
   __syncthreads();
   if (t < nets * A) {
-    const int z = t / A, a = t - z * A;
-    float s = g.b2[z][g.shared_bias ? 0 : a];
+    const int zz = t / A, a = t - zz * A;
+    float s = b2v;
 #pragma unroll
-    for (int w = 0; w < kHeadThreads / 32; ++w) s += red_s[w][z][a];
-    q_s[z][a] = s;
-    g.q[z][(size_t)row * A + a] = s;
+    for (int w = 0; w < kHeadGroup / 32; ++w) s += red_s[zz][w][a];
+    q_s[zz][a] = s;
+    (zz == 0 ? g.q[0] : zz == 1 ? g.q[1] : g.q[2])[(size_t)row * A + a] = s;
   }
   __syncthreads();
-  if (warp == 0) {
+  // ---- (3) target, td error, clipped cotangent
+  if (t < 32) {
     float best; int sel;
     warp_argmax(q_s[g.double_q ? 2 : 1][lane], lane, best, sel);   // selector net (lanes >= A hold -inf)
     const float q_next = q_s[1][sel];                                // value from the target net
-    const int act = g.action[row];
     const float q_taken = q_s[0][act];
-    const float td = g.reward[row] + g.discount[row] * q_next - q_taken;
-    const float wrow = g.row_weight ? g.row_weight[row] : 1.0f;
+    const float td = rew + disc * q_next - q_taken;
     const float win = g.weight_inside ? wrow : 1.0f;
     float cot = fminf(fmaxf(td * g.inv_mean * win, -g.grad_bound), g.grad_bound);
     if (!g.weight_inside) cot *= wrow;
@@ -186,15 +195,18 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
       g.row_loss[row] = 0.5f * td * td * win;
       g.dq_taken[row] = dq;
       dq_s = dq;
-      act_s = act;
     }
   }
   __syncthreads();
+  // ---- (4) dh1 = relu'(h1) * dq * w2[:, act]
   const float dq = dq_s;
-  const int act = act_s;
-  for (int k = t; k < kFc1Out; k += kHeadThreads) {
-    const float d = h_s[0][k] > 0.f ? dq * g.w2[0][(size_t)k * A + act] : 0.f;
-    g.dh1[(size_t)row * kFc1Out + k] = g.round_tf32 ? tf32_rn(d) : d;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int k = t + i * kHeadThreads;
+    if (k < kFc1Out) {
+      const float d = h_s[k] > 0.f ? dq * w2a[i] : 0.f;
+      g.dh1[(size_t)row * kFc1Out + k] = g.round_tf32 ? tf32_rn(d) : d;
+    }
   }
   tl_end(g.tl, tl_t0);
 }
@@ -397,8 +409,27 @@ inline H16Shadow h16_none() {
   for (int l = 0; l < H16Shadow::kLayers; ++l) { s.dst[l] = nullptr; s.off[l] = 0; s.K[l] = 0; s.N[l] = 0; }
   return s;
 }
+// Lane `sub` of the 8 that share one float4 adds partials sub, sub + 8, ... in that order.  Eight loads are in
+// flight per round trip (conv1's weight gradient leaves ~100 partials at batch 32: 13 per lane = two round trips; a
+// rolled loop paid one L2 latency per partial).  Sixteen in flight cost the kernel its occupancy (two waves of CTAs
+// instead of one: 6.0 -> 8.1 us).  Slots past the end add +0.
+__device__ __forceinline__ void sum_partials_lane(float4& gv, const float* __restrict__ src, int ns, size_t st, int sub) {
+  constexpr int kInFlight = 8;
+  for (int q0 = sub; q0 < ns; q0 += 8 * kInFlight) {
+    float4 t[kInFlight];
+#pragma unroll
+    for (int j = 0; j < kInFlight; ++j) {
+      const int q = q0 + 8 * j;
+      t[j] = q < ns ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < kInFlight; ++j) { gv.x += t[j].x; gv.y += t[j].y; gv.z += t[j].z; gv.w += t[j].w; }
+  }
+}
+// (<= 48 registers: the ~610 blocks of a batch-32 update must be resident together, 5 per SM - a second wave costs
+// a whole block latency at the very end of the update)
 template <bool APPLY>
-__global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
+__global__ void __launch_bounds__(256, 5) rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
                                       float* __restrict__ nu, float* __restrict__ g, int64_t n, GradRegions regs, int64_t split_end,
                                       int64_t skip_lo, int64_t skip_hi, float lr, float decay, float eps,
                                       unsigned long long* tl) {
@@ -409,30 +440,18 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
     const int64_t i4 = gid >> 3, i = i4 << 2;
     const int sub = (int)(gid & 7);
     float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
+    // the optimiser state travels with the partials (one round trip instead of two)
+    float4 mv = gv, nv = gv, pv = gv;
+    if (APPLY && sub == 0) {
+      mv = __ldcg(reinterpret_cast<const float4*>(mu) + i4); nv = __ldcg(reinterpret_cast<const float4*>(nu) + i4);
+      pv = __ldcg(reinterpret_cast<const float4*>(p) + i4);
+    }
     bool summed = false;
 #pragma unroll
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
-        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
-        const int ns = regs.r[r].splits;
-        const size_t st = regs.r[r].stride;
-        int q = sub;
-        for (; q + 24 < ns; q += 32) {
-          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
-          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
-          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
-          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
-          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
-          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
-          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
-          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
-        }
-        for (; q < ns; q += 8) {
-          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
-          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
-        }
+        sum_partials_lane(gv, src, regs.r[r].splits, regs.r[r].stride, sub);
         summed = true;
       }
     }
@@ -447,8 +466,6 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
       if (summed) reinterpret_cast<float4*>(g)[i4] = gv;
       else gv = reinterpret_cast<const float4*>(g)[i4];
       if (APPLY) {
-        float4 mv = reinterpret_cast<float4*>(mu)[i4], nv = reinterpret_cast<float4*>(nu)[i4];
-        float4 pv = reinterpret_cast<float4*>(p)[i4];
         rmsprop4(pv, mv, nv, gv, lr, decay, eps);
         reinterpret_cast<float4*>(mu)[i4] = mv;
         reinterpret_cast<float4*>(nu)[i4] = nv;
@@ -503,25 +520,7 @@ __global__ void grad_reduce_range_kernel(float* __restrict__ g, GradRegions regs
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
-        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
-        const int ns = regs.r[r].splits;
-        const size_t st = regs.r[r].stride;
-        int q = sub;
-        for (; q + 24 < ns; q += 32) {
-          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
-          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
-          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
-          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
-          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
-          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
-          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
-          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
-        }
-        for (; q < ns; q += 8) {
-          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
-          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
-        }
+        sum_partials_lane(gv, src, regs.r[r].splits, regs.r[r].stride, sub);
         summed = true;
       }
     }

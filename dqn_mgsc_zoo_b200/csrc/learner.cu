@@ -641,8 +641,20 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
   h->launches_per_update++;
   if (live) {
     g.tl = h->next_tl("head_td");
-    head_td_kernel<<<B, kHeadThreads, 0, st>>>(g);
-    DQNB_CUDA(cudaGetLastError());
+    // a link of the dependent chain: chain priority, and (programmatic dependent launch) placed while fc1 still
+    // stores its partials - the kernel prefetches its own operands ahead of its griddepcontrol.wait
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(B); cfg.blockDim = dim3(kHeadThreads); cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    unsigned na = 0;
+    attr[na].id = cudaLaunchAttributePriority;
+    attr[na++].val.priority = h->prio_hi;
+    if (h->pdl && !h->profiling && getenv("DQNB_NO_HEAD_PDL") == nullptr) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na++].val.programmaticStreamSerializationAllowed = 1;
+    }
+    cfg.attrs = attr; cfg.numAttrs = na;
+    DQNB_CUDA(cudaLaunchKernelEx(&cfg, head_td_kernel, g));
     DQNB_TRY(mark(h, st, "head_td"));
   }
   if (live) DQNB_TRY(fork(h->ev[0], st, s1));
