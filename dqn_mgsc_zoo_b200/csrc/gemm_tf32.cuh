@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
       }
 #pragma unroll 1
       for (int i = 0; i < nkb; ++i) {
-        stage_b(i);
+        if (!b_tma) stage_b(i);
         cp_commit();
       }
 #pragma unroll 1
@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
       }
 #pragma unroll 1
       for (int i = 0; i < nkb; ++i) {
-        stage_b(i);
+        if (!b_tma) stage_b(i);
         cp_commit();
       }
 #pragma unroll 1
@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
       }
 #pragma unroll 1
       for (int i = 0; i < nkb; ++i) {
-        stage_b(i);
+        if (!b_tma) stage_b(i);
         cp_commit();
       }
 #pragma unroll 1
@@ -478,7 +478,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
     if constexpr (t32_b_tma<P>::value) {
       if (b_tma) {   // every B k-block of this CTA, in k order, each onto its own barrier
         for (int i = 0; i < nkb; ++i) {
-          const int k0 = (kb_beg + i) * kT32BK;
+          const int k0 = (kb_beg + i) * (t32_f16<P>::value ? 2 * kT32BK : kT32BK);   // in elements of the map's type
           const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
           mbar_expect_tx(&full_bar[i], B_TILE);
           if constexpr (P::B_MN_MAJOR) {

@@ -56,11 +56,13 @@ ArenaLayout make_layout(int A, int shared_bias) {
   return L;
 }
 
-// Tensor map of a dense row-major fp32 matrix [outer][inner] for tiled TMA loads of {box_inner, box_outer} boxes.
+// Tensor map of a dense row-major fp32 / fp16 matrix [outer][inner] for tiled TMA loads of {box_inner, box_outer} boxes.
 // cuTensorMapEncodeTiled is a pure host-side encoder; it is fetched with cudaGetDriverEntryPoint so that the
 // library keeps its single dependency on the CUDA runtime.
-int make_tmap_2d(const float* base, uint64_t inner, uint64_t outer, uint32_t box_inner, uint32_t box_outer,
+template <class T>
+int make_tmap_2d(const T* base, uint64_t inner, uint64_t outer, uint32_t box_inner, uint32_t box_outer,
                  CUtensorMapSwizzle swizzle, CUtensorMap* out) {
+  static_assert(sizeof(T) == 4 || sizeof(T) == 2, "fp32 or fp16 operands");
   using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -76,10 +78,11 @@ int make_tmap_2d(const float* base, uint64_t inner, uint64_t outer, uint32_t box
   }();
   if (encode == nullptr) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DQNB_ECUDA; }
   const cuuint64_t dims[2] = {inner, outer};
-  const cuuint64_t strides[1] = {inner * sizeof(float)};
+  const cuuint64_t strides[1] = {inner * sizeof(T)};
   const cuuint32_t box[2] = {box_inner, box_outer};
   const cuuint32_t elem[2] = {1, 1};
-  const CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, elem,
+  const CUresult r = encode(out, sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                            const_cast<T*>(base), dims, strides, box, elem,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return DQNB_ECUDA; }
@@ -105,10 +108,14 @@ struct dqnb_learner {
   float *online_r = nullptr, *target_r = nullptr;   // TF32 mode: weights rounded to tf32 (GEMM operands)
   // TF32 slab mode: tensor maps of the fc1 weight shadows (device copies; gemm_tf32.cuh B_TMA).  [0] / [1]: online /
   // target as the forward's MN-major B operand, [2]: online as the dgrad's K-major B operand.  Null: cp.async staging.
+  // [3]: both nets' fp16 conv1 filters (64 rows of 256 halves), [4] / [5]: online / target fp16 conv2 filters,
+  // [6] / [7]: online / target fp16 conv3 filters - K-major B operands of the fp16 forward GEMMs.
   CUtensorMap* fc1_maps = nullptr;
   const void* fc1_fwd_map(const float* wts) const {
     return fc1_maps == nullptr ? nullptr : wts == online_r ? fc1_maps + 0 : wts == target_r ? fc1_maps + 1 : nullptr;
   }
+  const void* h16_map(int slot) const { return fc1_maps == nullptr || !h16_maps ? nullptr : fc1_maps + slot; }
+  bool h16_maps = false;
   __half* conv1_h16 = nullptr;   // TF32 mode, small batches: fp16 K-major conv1 filters [online 32 | target 32][256]
   // TF32 mode, small batches: fp16 K-major conv2 / conv3 filters, [online: conv2 64x512 | conv3 64x576][target: same],
   // and fp16 copies of the conv1 / conv2 outputs of every net (A operands of the fp16 conv2 / conv3 forward)
@@ -506,6 +513,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       fill(p);
       p.K = Conv1::KCOL / 2;   // 32-bit words
       p.w16 = h->conv1_h16;
+      p.bmap = h->h16_map(3);
       DQNB_TRY(run_t32(h, p, 1, t32_splits(h, p, 1), st));
     } else {
       T32ConvFwdDoubleQ<Conv1, uint8_t> p;
@@ -524,6 +532,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
         const int zz = std::min(z, nets - 1);
         const int tgt = wts[zz] == h->target_r;
         p.x[z] = xin[zz]; p.w16[z] = layer == 2 ? h->c2h(tgt) : h->c3h(tgt);
+        p.bmap[z] = h->h16_map((layer == 2 ? 4 : 6) + tgt);
         p.bias[z] = params[zz] + b_off; p.y[z] = y[zz]; p.yh[z] = yh ? yh[zz] : nullptr;
       }
       // split-K over a cluster (DQNB_H16_SPLITS2 / 3, default 1 = the whole K range in one slab)
@@ -1005,14 +1014,6 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
   const size_t B = h->B, P = h->L.total;
   DQNB_TRY(dmalloc(&h->online, P)); DQNB_TRY(dmalloc(&h->target, P)); DQNB_TRY(dmalloc(&h->mu, P));
   if (h->tf32) { DQNB_TRY(dmalloc(&h->online_r, P)); DQNB_TRY(dmalloc(&h->target_r, P)); }
-  if (h->tf32 && !h->stream && getenv("DQNB_NO_TMA") == nullptr) {
-    CUtensorMap maps[3];
-    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[0]));
-    DQNB_TRY(make_tmap_2d(h->target_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[1]));
-    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, kT32BK, T32DenseDgrad::BN, CU_TENSOR_MAP_SWIZZLE_128B, &maps[2]));
-    DQNB_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->fc1_maps), sizeof(maps)));
-    DQNB_CUDA(cudaMemcpy(h->fc1_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
-  }
   if (h->tf32 && cfg->double_q && getenv("DQNB_NO_F16_CONV1") == nullptr)
     DQNB_TRY(dmalloc(&h->conv1_h16, (size_t)2 * Conv1::COUT * Conv1::KCOL));
   if (h->tf32 && !h->stream && getenv("DQNB_NO_F16_CONV23") == nullptr) {
@@ -1020,6 +1021,23 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
     for (int z = 0; z < h->nets; ++z) {
       DQNB_TRY(dmalloc(&h->a1h[z], B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->a2h[z], B * Conv2::OUT_PER_IMG));
     }
+  }
+  if (h->tf32 && !h->stream && getenv("DQNB_NO_TMA") == nullptr) {
+    CUtensorMap maps[8] = {};
+    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[0]));
+    DQNB_TRY(make_tmap_2d(h->target_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[1]));
+    DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, kT32BK, T32DenseDgrad::BN, CU_TENSOR_MAP_SWIZZLE_128B, &maps[2]));
+    h->h16_maps = getenv("DQNB_NO_TMA_H16") == nullptr;
+    if (h->h16_maps && h->conv1_h16 != nullptr)
+      DQNB_TRY(make_tmap_2d(h->conv1_h16, Conv1::KCOL, 2 * Conv1::COUT, 64, 2 * Conv1::COUT, CU_TENSOR_MAP_SWIZZLE_128B, &maps[3]));
+    if (h->h16_maps && h->conv23_h16 != nullptr) {
+      for (int tgt = 0; tgt < 2; ++tgt) {
+        DQNB_TRY(make_tmap_2d(h->c2h(tgt), Conv2::KCOL, Conv2::COUT, 64, Conv2::COUT, CU_TENSOR_MAP_SWIZZLE_128B, &maps[4 + tgt]));
+        DQNB_TRY(make_tmap_2d(h->c3h(tgt), Conv3::KCOL, Conv3::COUT, 64, Conv3::COUT, CU_TENSOR_MAP_SWIZZLE_128B, &maps[6 + tgt]));
+      }
+    }
+    DQNB_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->fc1_maps), sizeof(maps)));
+    DQNB_CUDA(cudaMemcpy(h->fc1_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
   }
   DQNB_TRY(dmalloc(&h->nu, P)); DQNB_TRY(dmalloc(&h->grad, P));
   DQNB_TRY(dmalloc(&h->s_tm1, B * Conv1::IN_PER_IMG)); DQNB_TRY(dmalloc(&h->s_t, B * Conv1::IN_PER_IMG));

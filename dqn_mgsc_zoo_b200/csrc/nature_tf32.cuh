@@ -219,6 +219,9 @@ struct H16ConvFwdDoubleQ : T32ConvFwdDoubleQ<L, TIn> {
   static constexpr bool F16 = true, A_ROW16H = true, A_ROW16 = false, A_REG = true;
   static constexpr int B_RESIDENT_KB = L::KCOL / 64;   // stream kernel: k-blocks of 64 halves
   const __half* w16;        // [2 * COUT][KCOL]
+  static constexpr bool B_TMA = true;   // gemm_tf32.cuh: the filters by tensor-map TMA when a map is given
+  const void* bmap = nullptr;           // device address of the CUtensorMap of w16, or null
+  __device__ const void* b_tmap(int) const { return bmap; }
   using BRow = int;         // n or -1
   using BCol = int;         // word index k (2 halves each; first of 4) or -1
   __device__ BRow b_row(int, int n) const { return n < this->N ? n : -1; }
@@ -248,6 +251,9 @@ struct H16ConvFwd {
   const float* bias[kMaxNets];
   float* y[kMaxNets];
   __half* yh[kMaxNets];     // may be null
+  static constexpr bool B_TMA = true;   // gemm_tf32.cuh: the filters by tensor-map TMA when a map is given
+  const void* bmap[kMaxNets] = {};      // device addresses of the CUtensorMaps of w16[z], or null
+  __device__ const void* b_tmap(int z) const { return z == 0 ? bmap[0] : z == 1 ? bmap[1] : bmap[2]; }
   using ARow = const __half*;   // &x[b, i*s, j*s, 0] or null
   using ACol = int;             // offset (halves) of the chunk inside the patch or -1
   using BRow = const __half*;   // w16[z] + n * KCOL or null
