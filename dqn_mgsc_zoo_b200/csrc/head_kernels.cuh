@@ -61,9 +61,12 @@ __device__ __forceinline__ void warp_argmax(float v, int lane, float& best, int&
 // (fc1 bias, fc2 weights and bias, the row's action / reward / discount / weight, the fc2 column of the taken
 // action) is fetched BEFORE griddepcontrol.wait - under programmatic dependent launch that is while fc1 is still
 // storing its partials - and all of a thread's partials are in flight at once.
+// kDepth = split-K partials a thread keeps in flight: 20 for the small-batch slab path (17-18 splits, one CTA per SM
+// is all a batch of 32 rows needs), 4 for large batches (1-3 splits; two CTAs per SM, the grid is thousands of rows).
 constexpr int kHeadGroup = 128;
 constexpr int kHeadThreads = kMaxNets * kHeadGroup;
-__global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
+template <int kDepth>
+__global__ void __launch_bounds__(kHeadThreads, kDepth > 8 ? 1 : 2) head_td_kernel(HeadArgs g) {
   __shared__ __align__(16) float h_s[kFc1Out];
   __shared__ float q_s[kMaxNets][kMaxActions];
   __shared__ float red_s[kMaxNets][kHeadGroup / 32][kMaxActions];
@@ -120,7 +123,6 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
       const float4* src = reinterpret_cast<const float4*>(g.fc1_part + (size_t)row * kFc1Out) + c +
                           (size_t)z * g.fc1_splits * split_stride;
       // all partials of the thread in flight (18 splits at batch 32: one round trip); the additions keep split order
-      constexpr int kDepth = 20;
       for (int q0 = 0; q0 < g.fc1_splits; q0 += kDepth) {
         float4 x[kDepth];
 #pragma unroll
@@ -210,6 +212,7 @@ __global__ void __launch_bounds__(kHeadThreads) head_td_kernel(HeadArgs g) {
   }
   tl_end(g.tl, tl_t0);
 }
+inline auto head_td_for(int batch) { return batch <= 64 ? head_td_kernel<20> : head_td_kernel<4>; }
 
 // fc2 parameter gradients + scalar loss.  thread (k,a): gW2[k,a] = sum_b h1[b,k] * dq[b,a];
 // block 0 also writes the bias gradient and loss (fixed summation order => reproducible).
@@ -409,27 +412,8 @@ inline H16Shadow h16_none() {
   for (int l = 0; l < H16Shadow::kLayers; ++l) { s.dst[l] = nullptr; s.off[l] = 0; s.K[l] = 0; s.N[l] = 0; }
   return s;
 }
-// Lane `sub` of the 8 that share one float4 adds partials sub, sub + 8, ... in that order.  Eight loads are in
-// flight per round trip (conv1's weight gradient leaves ~100 partials at batch 32: 13 per lane = two round trips; a
-// rolled loop paid one L2 latency per partial).  Sixteen in flight cost the kernel its occupancy (two waves of CTAs
-// instead of one: 6.0 -> 8.1 us).  Slots past the end add +0.
-__device__ __forceinline__ void sum_partials_lane(float4& gv, const float* __restrict__ src, int ns, size_t st, int sub) {
-  constexpr int kInFlight = 8;
-  for (int q0 = sub; q0 < ns; q0 += 8 * kInFlight) {
-    float4 t[kInFlight];
-#pragma unroll
-    for (int j = 0; j < kInFlight; ++j) {
-      const int q = q0 + 8 * j;
-      t[j] = q < ns ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int j = 0; j < kInFlight; ++j) { gv.x += t[j].x; gv.y += t[j].y; gv.z += t[j].z; gv.w += t[j].w; }
-  }
-}
-// (<= 48 registers: the ~610 blocks of a batch-32 update must be resident together, 5 per SM - a second wave costs
-// a whole block latency at the very end of the update)
 template <bool APPLY>
-__global__ void __launch_bounds__(256, 5) rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
+__global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__ p_r, H16Shadow h16, float* __restrict__ mu,
                                       float* __restrict__ nu, float* __restrict__ g, int64_t n, GradRegions regs, int64_t split_end,
                                       int64_t skip_lo, int64_t skip_hi, float lr, float decay, float eps,
                                       unsigned long long* tl) {
@@ -440,18 +424,30 @@ __global__ void __launch_bounds__(256, 5) rmsprop_reduce_kernel(float* __restric
     const int64_t i4 = gid >> 3, i = i4 << 2;
     const int sub = (int)(gid & 7);
     float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
-    // the optimiser state travels with the partials (one round trip instead of two)
-    float4 mv = gv, nv = gv, pv = gv;
-    if (APPLY && sub == 0) {
-      mv = __ldcg(reinterpret_cast<const float4*>(mu) + i4); nv = __ldcg(reinterpret_cast<const float4*>(nu) + i4);
-      pv = __ldcg(reinterpret_cast<const float4*>(p) + i4);
-    }
     bool summed = false;
 #pragma unroll
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        sum_partials_lane(gv, src, regs.r[r].splits, regs.r[r].stride, sub);
+        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
+        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
+        const int ns = regs.r[r].splits;
+        const size_t st = regs.r[r].stride;
+        int q = sub;
+        for (; q + 24 < ns; q += 32) {
+          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
+          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
+          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
+          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
+          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
+          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
+          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
+        }
+        for (; q < ns; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
+        }
         summed = true;
       }
     }
@@ -466,6 +462,8 @@ __global__ void __launch_bounds__(256, 5) rmsprop_reduce_kernel(float* __restric
       if (summed) reinterpret_cast<float4*>(g)[i4] = gv;
       else gv = reinterpret_cast<const float4*>(g)[i4];
       if (APPLY) {
+        float4 mv = reinterpret_cast<float4*>(mu)[i4], nv = reinterpret_cast<float4*>(nu)[i4];
+        float4 pv = reinterpret_cast<float4*>(p)[i4];
         rmsprop4(pv, mv, nv, gv, lr, decay, eps);
         reinterpret_cast<float4*>(mu)[i4] = mv;
         reinterpret_cast<float4*>(nu)[i4] = nv;
@@ -520,7 +518,25 @@ __global__ void grad_reduce_range_kernel(float* __restrict__ g, GradRegions regs
     for (int r = 0; r < kMaxGradRegions; ++r) {
       if (r < regs.n && i >= regs.r[r].off && i < regs.r[r].off + regs.r[r].count) {
         const float* src = regs.r[r].part + (i - regs.r[r].off);
-        sum_partials_lane(gv, src, regs.r[r].splits, regs.r[r].stride, sub);
+        // four partials in flight per round trip (conv1's weight gradient leaves ~100 of them: 13 per lane, which
+        // a rolled loop fetched one L2 latency after the other); the additions keep their q order
+        const int ns = regs.r[r].splits;
+        const size_t st = regs.r[r].stride;
+        int q = sub;
+        for (; q + 24 < ns; q += 32) {
+          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 8) * st));
+          const float4 t2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 16) * st));
+          const float4 t3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(q + 24) * st));
+          gv.x += t0.x; gv.y += t0.y; gv.z += t0.z; gv.w += t0.w;
+          gv.x += t1.x; gv.y += t1.y; gv.z += t1.z; gv.w += t1.w;
+          gv.x += t2.x; gv.y += t2.y; gv.z += t2.z; gv.w += t2.w;
+          gv.x += t3.x; gv.y += t3.y; gv.z += t3.z; gv.w += t3.w;
+        }
+        for (; q < ns; q += 8) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)q * st));
+          gv.x += t.x; gv.y += t.y; gv.z += t.z; gv.w += t.w;
+        }
         summed = true;
       }
     }

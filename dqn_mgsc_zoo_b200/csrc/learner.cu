@@ -383,7 +383,7 @@ int enqueue_update(dqnb_learner* h, cudaStream_t st) {
   h->launches_per_update++;
   if (live) {
     g.tl = h->next_tl("head_td");
-    head_td_kernel<<<B, kHeadThreads, 0, st>>>(g);
+    head_td_for(B)<<<B, kHeadThreads, 0, st>>>(g);
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, st, "head_td"));
   }
@@ -663,7 +663,7 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
       attr[na++].val.programmaticStreamSerializationAllowed = 1;
     }
     cfg.attrs = attr; cfg.numAttrs = na;
-    DQNB_CUDA(cudaLaunchKernelEx(&cfg, head_td_kernel, g));
+    DQNB_CUDA(cudaLaunchKernelEx(&cfg, head_td_for(B), g));
     DQNB_TRY(mark(h, st, "head_td"));
   }
   if (live) DQNB_TRY(fork(h->ev[0], st, s1));
@@ -1562,7 +1562,7 @@ int enqueue_q_forward(dqnb_learner* h, int which_params, int n, cudaStream_t st)
     g.fc1_part = h->fc1_part; g.fc1_splits = h->fc1_splits;
   }
   g.td = h->td; g.dh1 = h->dh1;
-  head_td_kernel<<<n, kHeadThreads, 0, st>>>(g);
+  head_td_for(n)<<<n, kHeadThreads, 0, st>>>(g);
   DQNB_CUDA(cudaGetLastError());
   return DQNB_OK;
 }

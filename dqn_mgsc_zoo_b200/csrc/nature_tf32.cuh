@@ -113,9 +113,14 @@ struct T32ConvFwd {
     if (c.y != nullptr) *reinterpret_cast<float4*>(c.y + q.off) = tf32_rn4(o);   // null: only the fp16 copy is consumed
     if (c.yh != nullptr) t32_store_half4(c.yh + q.off, o);
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const {
-    const Ctx c = store_ctx(z, split, n);
-    store4p(c, preload(c, z, split, m, n), v);
+  // (stream kernel: one call per float4 of a thread's row - kept free of the context bookkeeping above)
+  __device__ void store4(int z, int, int m, int n, float4 v) const {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias[z] + n));
+    constexpr float s = InScale<TIn>::value;
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
+    if (y[z] != nullptr) *reinterpret_cast<float4*>(y[z] + (size_t)m * N + n) = tf32_rn4(o);
+    if (yh[z] != nullptr) t32_store_half4(yh[z] + (size_t)m * N + n, o);
   }
 };
 
@@ -200,9 +205,20 @@ struct T32ConvFwdDoubleQ {
     if (dst != nullptr) *reinterpret_cast<float4*>(dst + at) = tf32_rn4(o);   // null: only the fp16 copy is consumed
     if (dsth != nullptr) t32_store_half4(dsth + at, o);
   }
-  __device__ void store4(int z, int split, int m, int n, float4 v) const {
-    const Ctx c = store_ctx(z, split, n);
-    store4p(c, preload(c, z, split, m, n), v);
+  // (stream kernel: one call per float4 of a thread's row - kept free of the context bookkeeping above)
+  __device__ void store4(int, int, int m, int n, float4 v) const {
+    const int half = m >= Mh, which = n >= L::COUT;
+    if (!half && which) return;
+    const int nn = n - which * L::COUT;
+    float* dst = half ? (which ? y[1] : y[2]) : y[0];
+    __half* dsth = half ? (which ? yh[1] : yh[2]) : yh[0];
+    const float4 b = __ldg(reinterpret_cast<const float4*>((which ? bias[1] : bias[0]) + nn));
+    constexpr float s = InScale<TIn>::value;
+    const float4 o = make_float4(fmaxf(fmaf(v.x, s, b.x), 0.f), fmaxf(fmaf(v.y, s, b.y), 0.f),
+                                 fmaxf(fmaf(v.z, s, b.z), 0.f), fmaxf(fmaf(v.w, s, b.w), 0.f));
+    const size_t at = (size_t)(m - half * Mh) * L::COUT + nn;
+    if (dst != nullptr) *reinterpret_cast<float4*>(dst + at) = tf32_rn4(o);
+    if (dsth != nullptr) t32_store_half4(dsth + at, o);
   }
 };
 
