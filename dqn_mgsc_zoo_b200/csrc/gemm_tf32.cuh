@@ -285,6 +285,12 @@ __device__ __forceinline__ void t32_drain_groups(int nkb, uint64_t* full_bar) {
   }
 }
 
+//   static constexpr bool EARLY_TRIGGER = true;   griddepcontrol.launch_dependents at the START of the kernel
+// (forward chain, where no side-branch kernel competes for the idle SMs): the next kernel's CTAs are placed on
+// whatever SMs this grid leaves free, set up their barriers / TMEM and pull their weight operands by TMA while this
+// kernel still computes; they block at their own griddepcontrol.wait until this grid has completed.
+template <class P, class = void> struct t32_early_trigger : std::false_type {};
+template <class P> struct t32_early_trigger<P, std::enable_if_t<P::EARLY_TRIGGER>> : std::true_type {};
 //   static constexpr int MIN_CTAS = n;   register budget for n resident CTAs per SM (__launch_bounds__)
 template <class P, class = void> struct t32_min_ctas : std::integral_constant<int, 1> {};
 template <class P> struct t32_min_ctas<P, std::enable_if_t<(P::MIN_CTAS > 1)>> : std::integral_constant<int, P::MIN_CTAS> {};
@@ -326,9 +332,29 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
   __syncthreads();
   t32_fence_after();
   const uint32_t tmem = tmem_slot;
-  // everything above touched only this CTA's shared memory / TMEM; from here on the kernel reads
-  // what its predecessors wrote
+  // B by tensor-map TMA = the learner's own weight shadows, final before the update's graph started (the fused fc1
+  // optimiser step that rewrites them is ordered behind every reader by events): every B k-block of this CTA is
+  // requested NOW, ahead of griddepcontrol.wait - under programmatic dependent launch that is while the preceding
+  // kernel is still storing, so a third to a half of the CTA's operand bytes arrive before its inputs even exist.
+  if constexpr (t32_b_tma<P>::value) {
+    if (b_tma && t == kT32Producers) {
+      for (int i = 0; i < nkb; ++i) {
+        const int k0 = (kb_beg + i) * (t32_f16<P>::value ? 2 * kT32BK : kT32BK);   // in elements of the map's type
+        const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
+        mbar_expect_tx(&full_bar[i], B_TILE);
+        if constexpr (P::B_MN_MAJOR) {
+#pragma unroll
+          for (int j = 0; j < BN / 32; ++j) tma_load_2d(tile + j * 4096, bmap, n0 + 32 * j, k0, bar);
+        } else {
+          tma_load_2d(tile, bmap, k0, n0, bar);
+        }
+      }
+    }
+  }
+  // everything above touched only this CTA's shared memory / TMEM and constant weights; from here on the kernel
+  // reads what its predecessors wrote
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if constexpr (t32_early_trigger<P>::value) asm volatile("griddepcontrol.launch_dependents;");
   if (dbg && t == 0) sk.dbg[1] = clock64();     // setup done
 
   if (warp < 8) {
@@ -475,21 +501,6 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
   } else if (t == kT32Producers) {
     // ---- MMA issuer
     const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
-    if constexpr (t32_b_tma<P>::value) {
-      if (b_tma) {   // every B k-block of this CTA, in k order, each onto its own barrier
-        for (int i = 0; i < nkb; ++i) {
-          const int k0 = (kb_beg + i) * (t32_f16<P>::value ? 2 * kT32BK : kT32BK);   // in elements of the map's type
-          const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
-          mbar_expect_tx(&full_bar[i], B_TILE);
-          if constexpr (P::B_MN_MAJOR) {
-#pragma unroll
-            for (int j = 0; j < BN / 32; ++j) tma_load_2d(tile + j * 4096, bmap, n0 + 32 * j, k0, bar);
-          } else {
-            tma_load_2d(tile, bmap, k0, n0, bar);
-          }
-        }
-      }
-    }
     for (int i = 0; i < nkb; ++i) {
       mbar_wait(&full_bar[i], 0);
       t32_fence_after();
@@ -566,7 +577,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
   // next kernel of the stream get its CTAs placed and run its prologue (barriers, TMEM) now; it
   // blocks at its griddepcontrol.wait until this grid has completed.  Triggering earlier parks idle
   // CTAs on SMs the side-branch kernels need.  (No-ops for launches without the attribute.)
-  asm volatile("griddepcontrol.launch_dependents;");
+  if constexpr (!t32_early_trigger<P>::value) asm volatile("griddepcontrol.launch_dependents;");
   if (dbg && t == 0) sk.dbg[7] = clock64();
   if (warp < 8) {
     auto emit = [&](int k, int r, const float4& v) {

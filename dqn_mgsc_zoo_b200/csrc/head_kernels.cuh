@@ -113,6 +113,8 @@ __global__ void __launch_bounds__(kHeadThreads, kDepth > 8 ? 1 : 2) head_td_kern
   }
   if (t < kMaxNets * kMaxActions) (&q_s[0][0])[t] = -INFINITY;
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  // the 32 rows of a small batch leave 116 SMs idle: let fc1's dgrad set up there and pull its weights meanwhile
+  asm volatile("griddepcontrol.launch_dependents;");
 
   // ---- (1) h1: thread c of group z owns columns 4c..4c+3 of net z
   float4 hv = make_float4(0.f, 0.f, 0.f, 0.f);

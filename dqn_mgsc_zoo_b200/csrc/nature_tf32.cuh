@@ -259,6 +259,7 @@ struct H16ConvFwd {
   static constexpr int BN = L::COUT, KB_MAX = (L::KCOL / 2 + kT32BK - 1) / kT32BK;
   static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = false, DEFER_REDUCE = false;
   static constexpr bool F16 = true;
+  static constexpr bool EARLY_TRIGGER = true;   // conv2 -> conv3 -> fc1: 63 / 39 CTAs leave most SMs to the successor
   static constexpr int HOUT_WOUT = L::HOUT * L::WOUT, KWORDS = L::KCOL / 2;
   static_assert(L::ROWLEN % 8 == 0 && L::CIN % 8 == 0, "16-byte chunks of 8 halves must not straddle patch rows");
   int M, N, K;              // K = KCOL / 2 words
