@@ -173,6 +173,14 @@ __device__ __forceinline__ void tl_end(unsigned long long* tl, unsigned long lon
   atomicMax(tl + 1, now);
   if (began) atomicMax(tl + 3, now - began);
 }
+// One lane of a converged warp (elect.sync): ptxas keeps what the elected lane computes from warp-uniform inputs in
+// uniform registers; a `threadIdx.x == k` test makes it move every tcgen05 / TMA operand through a
+// R2UR.BROADCAST + BRA.U.ANY waterfall loop (measured: 18 instructions per tcgen05.mma).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

@@ -16,6 +16,7 @@
 #include "act_kernel.cuh"
 #include "nccl_dyn.cuh"
 #include "hvp_kernels.cuh"
+#include "conv23_fused.cuh"
 
 using namespace dqnb;
 
@@ -540,8 +541,29 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       static const int s3 = getenv("DQNB_H16_SPLITS3") ? atoi(getenv("DQNB_H16_SPLITS3")) : 1;
       return run_t32(h, p, nets, layer == 2 ? s2 : s3, st);
     };
-    DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, y2, h->L.b2, 2));
-    DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));
+    static const bool no_fused = getenv("DQNB_NO_FUSED_C23") != nullptr;
+    if (!no_fused && h->h16_map(4) != nullptr) {
+      // conv2 + conv3 in one kernel, one CTA per (image, net) (conv23_fused.cuh)
+      Conv23Args g = {};
+      for (int z = 0; z < kMaxNets; ++z) {
+        const int zz = std::min(z, nets - 1);
+        const int tgt = wts[zz] == h->target_r;
+        g.a1h[z] = h->a1h[zz]; g.map2[z] = h->h16_map(4 + tgt); g.map3[z] = h->h16_map(6 + tgt);
+        g.bias2[z] = params[zz] + h->L.b2; g.bias3[z] = params[zz] + h->L.b3;
+        g.a2[z] = y2[zz]; g.a3[z] = h->a3[zz];
+      }
+      h->launches_per_update++;
+      if (!h->sizing) {
+        g.tl = h->next_tl("conv23_fwd");
+        g.dbg = (h->profiling && h->dbg_clocks) ? h->dbg_clocks + 8 * h->prof_n : nullptr;
+        const bool on_chain = st == h->chain;
+        DQNB_CUDA(launch_conv23_fwd(g, rows, nets, st, on_chain ? h->prio_hi : 0, on_chain && !h->profiling && h->pdl));
+        DQNB_TRY(mark(h, st, "conv23_fwd"));
+      }
+    } else {
+      DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, y2, h->L.b2, 2));
+      DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));
+    }
   } else {
     DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
     DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
