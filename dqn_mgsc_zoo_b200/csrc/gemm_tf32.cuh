@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
     fence_mbar_init();
   }
   if (warp == 8) t32_alloc<COLS>(&tmem_slot);
-  if (b_tma && t == kT32Producers) tma_prefetch_map(bmap);   // the descriptor itself is never written by a kernel
+  if (b_tma && warp == 8 && elect_one()) tma_prefetch_map(bmap);   // the descriptor itself is never written by a kernel
   t32_fence_before();
   __syncthreads();
   t32_fence_after();
@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
   // requested NOW, ahead of griddepcontrol.wait - under programmatic dependent launch that is while the preceding
   // kernel is still storing, so a third to a half of the CTA's operand bytes arrive before its inputs even exist.
   if constexpr (t32_b_tma<P>::value) {
-    if (b_tma && t == kT32Producers) {
+    if (b_tma && warp == 8 && elect_one()) {
       for (int i = 0; i < nkb; ++i) {
         const int k0 = (kb_beg + i) * (t32_f16<P>::value ? 2 * kT32BK : kT32BK);   // in elements of the map's type
         const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
@@ -498,22 +498,32 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
       if (dbg && t == 0) sk.dbg[2] = clock64();     // (register paths: issued and landed coincide)
     }
     if (dbg && t == 0) sk.dbg[3] = clock64();     // this thread's copies landed
-  } else if (t == kT32Producers) {
-    // ---- MMA issuer
+  } else if (warp == 8) {
+    // ---- MMA issuer: the whole warp walks the barriers and one ELECTED lane issues - with descriptors formed as a
+    // warp-uniform base plus a compile-time offset ptxas keeps them in uniform registers (a `threadIdx.x == 256`
+    // test made it move every operand through a R2UR.BROADCAST waterfall: 18 instructions per tcgen05.mma)
+    const bool leader = elect_one();
     const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
-    for (int i = 0; i < nkb; ++i) {
-      mbar_wait(&full_bar[i], 0);
-      t32_fence_after();
-      const uint32_t a_addr = smem + i * A_TILE, b_addr = smem + KB * A_TILE + i * B_TILE;
+    const uint64_t a_d0 = P::A_MN_MAJOR ? t32_desc(smem, 4096, 512, 1) : t32_desc(smem, 16, 1024);
+    const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(smem + KB * A_TILE, 4096, 512, 1) : t32_desc(smem + KB * A_TILE, 16, 1024);
+    constexpr uint32_t A_KS = (P::A_MN_MAJOR ? 1024 : 32) >> 4, B_KS = (P::B_MN_MAJOR ? 1024 : 32) >> 4;
 #pragma unroll
-      for (int ks = 0; ks < kT32BK / 8; ++ks) {
-        uint64_t ad = P::A_MN_MAJOR ? t32_desc(a_addr + ks * 1024, 4096, 512, 1) : t32_desc(a_addr + ks * 32, 16, 1024);
-        uint64_t bd = P::B_MN_MAJOR ? t32_desc(b_addr + ks * 1024, 4096, 512, 1) : t32_desc(b_addr + ks * 32, 16, 1024);
-        if constexpr (t32_f16<P>::value) t32_mma_f16(tmem, ad, bd, idesc, i > 0 || ks > 0);
-        else t32_mma(tmem, ad, bd, idesc, i > 0 || ks > 0);
+    for (int i = 0; i < KB; ++i) {
+      if (i < nkb) {
+        mbar_wait(&full_bar[i], 0);
+        t32_fence_after();
+        if (leader) {
+#pragma unroll
+          for (int ks = 0; ks < kT32BK / 8; ++ks) {
+            const uint64_t ad = a_d0 + (uint32_t)((i * A_TILE) >> 4) + ks * A_KS;
+            const uint64_t bd = b_d0 + (uint32_t)((i * B_TILE) >> 4) + ks * B_KS;
+            if constexpr (t32_f16<P>::value) t32_mma_f16(tmem, ad, bd, idesc, i > 0 || ks > 0);
+            else t32_mma(tmem, ad, bd, idesc, i > 0 || ks > 0);
+          }
+        }
       }
     }
-    t32_commit(&done_bar);
+    if (leader) t32_commit(&done_bar);
   }
 
   // ---- the store assignment, fixed before the accumulators exist: thread t < 256 owns one float4 column group
