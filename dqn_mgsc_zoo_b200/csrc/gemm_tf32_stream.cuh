@@ -439,12 +439,15 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
       }
     }
     flush();   // the last D stages
-  } else if (t == kT32SMmaWarp * 32) {
+  } else if (warp == kT32SMmaWarp) {
     // ------------------------------------------------------------------ MMA issuer
-    // One thread issues everything the tensor core does, so this loop is the serial spine of the CTA and
+    // The whole warp walks the barriers and one ELECTED lane issues everything the tensor core does (elect.sync keeps
+    // the descriptors in uniform registers; a threadIdx test put a R2UR waterfall loop - ~10 instructions and ~96
+    // clocks - around every tcgen05.mma).  This loop is the serial spine of the CTA and
     // is kept to a handful of instructions per k-block: descriptors are a constant high word plus a low
     // word that is advanced by adds (smem address >> 4 lives in bits 0-13, and the CTA's window is
     // < 256 KB, so no carry leaves the field); ring slot and phase are counters, not divisions.
+    const bool leader = elect_one();
     const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     const uint64_t a_d0 = P::A_MN_MAJOR ? t32_desc(smem + RING, 4096, 512, 1) : t32_desc(smem + RING, 16, 1024);
     const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(RKB > 0 ? smem : smem + RING + t32s_kps<P>() * A_TILE, 4096, 512, 1)
@@ -478,10 +481,11 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
         mbar_wait_a(full_bar + 8 * s, ph);
         t32_fence_after();
         t32s_trace(sk.dbg, 2, (n * nkb + i) / t32s_kps<P>());   // series 2: stage seen full by the MMA thread (uniform nkb only)
+        if (leader) {
 #pragma unroll
         for (int sub = 0; sub < t32s_kps<P>(); ++sub) {
           const uint32_t a_lo = (uint32_t)a_d0 + s * (STAGE >> 4) + sub * (A_TILE >> 4);
-          const uint32_t b_lo = RKB > 0 ? b_lo_res : (uint32_t)b_d0 + s * (STAGE >> 4) + sub * (B_TILE >> 4);
+          const uint32_t b_lo = RKB > 0 ? b_lo_res + sub * (B_TILE >> 4) : (uint32_t)b_d0 + s * (STAGE >> 4) + sub * (B_TILE >> 4);
 #pragma unroll
           for (int ks = 0; ks < kT32BK / 8; ++ks) {
             if constexpr (t32_f16<P>::value)
@@ -491,12 +495,13 @@ __global__ void __launch_bounds__(kT32SThreads, 1) gemm_tf32_stream(P p, SplitK 
               t32_mma(d_tmem, ((uint64_t)a_hi << 32) | (a_lo + ks * A_KS), ((uint64_t)b_hi << 32) | (b_lo + ks * B_KS), idesc,
                       i > 0 || sub > 0 || ks > 0);
           }
-          b_lo_res += B_TILE >> 4;
         }
         t32_commit_a(empty_bar + 8 * s);   // slot free once these MMAs have read it
+        }
+        b_lo_res += t32s_kps<P>() * (B_TILE >> 4);
         if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
       }
-      t32_commit_a(acc_full + 8 * a);
+      if (leader) t32_commit_a(acc_full + 8 * a);
       t32s_trace(sk.dbg, 3, n);   // series 3: tile n fully issued
     }
   } else if (warp >= kT32SEpiWarp && warp < kT32SEpiWarp + 4) {

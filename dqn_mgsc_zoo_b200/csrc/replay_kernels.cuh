@@ -82,11 +82,14 @@ __device__ __forceinline__ uint4 interleave4(uint32_t w0, uint32_t w1, uint32_t 
 constexpr int kInlineSlots = 64;
 struct InlineSlots { int32_t v[kInlineSlots]; };
 
-// Thread 0 of a gather CTA: dedupe N plane references (registers, fully unrolled) into buffers 0.., one bulk copy per
-// unique plane completing on `bar`; buf[k] = buffer of reference k, -1 = the zero plane.
+// Warp 0 of a gather CTA (every lane computes the same, warp-uniform values; `leader` = the elect.sync lane, which
+// alone touches shared memory and issues - a `threadIdx.x == 0` test made ptxas wrap every bulk copy in a
+// R2UR.BROADCAST waterfall loop): dedupe N plane references (registers, fully unrolled) into buffers 0.., one bulk
+// copy per unique plane completing on `bar`; buf[k] = buffer of reference k, -1 = the zero plane.
 template <int N>
 __device__ __forceinline__ void gather_issue(const int (&ids)[N], int* buf, uint8_t* smem, int chunk, int len,
-                                             const uint8_t* planes, int64_t plane_stride, int px0, uint64_t* bar) {
+                                             const uint8_t* planes, int64_t plane_stride, int px0, uint64_t* bar,
+                                             bool leader) {
   int uniq[N];
   int nu = 0;
 #pragma unroll
@@ -104,15 +107,17 @@ __device__ __forceinline__ void gather_issue(const int (&ids)[N], int* buf, uint
         ++nu;
       }
     }
-    buf[k] = b;
+    if (leader) buf[k] = b;
   }
-  if (nu > 0) {
-    mbar_expect_tx(bar, (uint32_t)(nu * len));
+  if (leader) {
+    if (nu > 0) {
+      mbar_expect_tx(bar, (uint32_t)(nu * len));
 #pragma unroll
-    for (int j = 0; j < N; ++j)
-      if (j < nu) bulk_g2s(smem + j * chunk, planes + (int64_t)uniq[j] * plane_stride + px0, (uint32_t)len, bar);
-  } else {
-    mbar_arrive(bar);
+      for (int j = 0; j < N; ++j)
+        if (j < nu) bulk_g2s(smem + j * chunk, planes + (int64_t)uniq[j] * plane_stride + px0, (uint32_t)len, bar);
+    } else {
+      mbar_arrive(bar);
+    }
   }
 }
 
@@ -134,9 +139,13 @@ gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __gri
   const int px0 = split * chunk;
   const int len = min(chunk, v.plane_bytes - px0);   // multiple of 16 by construction
 
-  if (threadIdx.x == 0) {
-    mbar_init(&bar, 1);
-    fence_mbar_init();
+  if (threadIdx.x < 32) {
+    const bool leader = elect_one();
+    if (leader) {
+      mbar_init(&bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
     const int4* idp = reinterpret_cast<const int4*>(v.slot_ids + (int64_t)slot * 8);
     int4 lo = idp[0], hi = idp[1];
     const int ids[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
@@ -152,16 +161,18 @@ gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __gri
       }
     }
     const bool split_row = cap_planes < 8 && nu > cap_planes;
-    two_phase = split_row;
+    if (leader) two_phase = split_row;
     if (!split_row) {
-      gather_issue<8>(ids, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
+      gather_issue<8>(ids, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar, leader);
     } else {
       const int first[4] = {ids[0], ids[1], ids[2], ids[3]};
-      gather_issue<4>(first, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
+      gather_issue<4>(first, buf_of, smem, chunk, len, v.planes, v.plane_stride, px0, &bar, leader);
+      if (leader) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) late_ids[k] = ids[4 + k];
+        for (int k = 0; k < 4; ++k) late_ids[k] = ids[4 + k];
+      }
     }
-    if (split == 0) {
+    if (split == 0 && leader) {
       a_out[row] = v.actions[slot];
       r_out[row] = v.rewards[slot];
       d_out[row] = v.discounts[slot];
@@ -191,9 +202,9 @@ gather_stack4(ReplayDeviceView v, const int32_t* __restrict__ slots, const __gri
   for (int phase = 0; phase < 2; ++phase) {
     if (phase == 1) {
       __syncthreads();                       // every thread has read the s_tm1 planes
-      if (threadIdx.x == 0) {
+      if (threadIdx.x < 32) {
         const int second[4] = {late_ids[0], late_ids[1], late_ids[2], late_ids[3]};
-        gather_issue<4>(second, buf_of + 4, smem, chunk, len, v.planes, v.plane_stride, px0, &bar);
+        gather_issue<4>(second, buf_of + 4, smem, chunk, len, v.planes, v.plane_stride, px0, &bar, elect_one());
       }
       __syncthreads();
       mbar_wait(&bar, 1);
