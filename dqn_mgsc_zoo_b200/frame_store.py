@@ -10,6 +10,18 @@ def _ptr(arr):
     return arr.ctypes.data
 
 
+_addressof, _from_buffer = ctypes.addressof, ctypes.c_char.from_buffer
+
+
+def _fast_ptr(arr):
+    """Address of a C-contiguous array's data through the buffer protocol: ~1 us instead of the ~2 us of
+    `arr.ctypes.data` (which builds a ctypes helper object); read-only arrays take the slow road."""
+    try:
+        return _addressof(_from_buffer(arr))
+    except TypeError:
+        return arr.ctypes.data
+
+
 class FrameStore:
     """uint8 frame planes + per-slot (action, reward, discount) resident in HBM."""
 
@@ -45,8 +57,8 @@ class FrameStore:
         # `arr.ctypes.data` costs ~1-2 us; the accumulator hands over the previous s_t object as the
         # next s_tm1 (replay.py:1184-1190), so its address is remembered (the array is kept alive here).
         last = self._last
-        p0 = last[1] if last[0] is s_tm1 else s_tm1.ctypes.data
-        p1 = s_t.ctypes.data
+        p0 = last[1] if last[0] is s_tm1 else _fast_ptr(s_tm1)
+        p1 = _fast_ptr(s_t)
         self._last = (s_t, p1)
         _lib.check(self._put(self._h, int(slot), p0, p1, int(action), float(reward), float(discount), self.stream))
 

@@ -147,8 +147,10 @@ class ItemStorage:
         if self.frames is not None:
             s0, a, r, d, s1 = item
             self.frames.put(slot, s0, s1, a, r, d)
-            for arr, val in zip(self.scalars, (a, r, d)):
-                arr[slot] = val
+            sc = self.scalars
+            sc[0][slot] = a
+            sc[1][slot] = r
+            sc[2][slot] = d
         else:
             self.host_items[slot] = self.encoder(item)
 
@@ -347,15 +349,40 @@ class TransitionReplay(_UniformReplayBase):
     """Uniform replay with FIFO eviction (replay.py:163-243); ring slot = id mod capacity."""
 
     def add(self, item) -> None:
-        if self.size == self._capacity:
-            oldest_id, _ = self._live.popitem(last=False)
-            self._distribution.remove([oldest_id])
+        live, dist = self._live, self._distribution
         item_id = self._t
-        self._distribution.add([item_id])
+        if type(dist) is UniformDistribution:
+            # the stock distribution: remove([oldest]) + add([new]) of replay.py:87-160 written out for ONE id (same
+            # state afterwards; the list wrappers, loops and property calls were a third of an add's host time)
+            ids, index = dist._ids, dist._id_to_index
+            if len(live) == self._capacity:
+                oldest_id, _ = live.popitem(last=False)
+                if oldest_id not in index:
+                    raise IndexError('Cannot remove ID %d, it does not exist.' % oldest_id)
+                pos = index.pop(oldest_id)
+                tail = ids.pop()
+                if tail != oldest_id:
+                    ids[pos] = tail
+                    dist._ids_np[pos] = tail
+                    index[tail] = pos
+            if item_id in index:
+                raise IndexError('Cannot add ID %d, it already exists.' % item_id)
+            n = len(ids)
+            index[item_id] = n
+            if n < dist._ids_np.shape[0]:
+                dist._ids_np[n] = item_id
+            else:
+                dist._mirror(n, item_id)
+            ids.append(item_id)
+        else:
+            if len(live) == self._capacity:
+                oldest_id, _ = live.popitem(last=False)
+                dist.remove([oldest_id])
+            dist.add([item_id])
         slot = item_id % self._capacity
         self._storage.put(slot, item)
-        self._live[item_id] = slot
-        self._t += 1
+        live[item_id] = slot
+        self._t = item_id + 1
 
 
 class ReservoirTransitionReplay(_UniformReplayBase):
