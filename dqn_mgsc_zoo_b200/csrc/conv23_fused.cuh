@@ -34,6 +34,7 @@ struct Conv23Args {
   const float* bias3[kMaxNets];
   float* a2[kMaxNets];            // [batch, 9, 9, 64] fp32 or null
   float* a3[kMaxNets];            // [batch, 7, 7, 64] fp32
+  __half* a3h[kMaxNets];          // optional fp16 copy of a3 (A operand of the fp16 fc1 forward), or null
   unsigned long long* tl;         // optional timeline slot
   long long* dbg;                 // optional: CTA (0, 0) stamps clock64() at its phase boundaries (profiling)
 };
@@ -251,12 +252,15 @@ __global__ void __launch_bounds__(kC23Threads, 1) conv23_fwd_kernel(Conv23Args g
       float v[32];
       c23_ld32(lane_addr + 64, v);
       if (row < 49) {
+        __half* oh = c23_pick(g.a3h, z);
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           const float4 bb = *reinterpret_cast<const float4*>(bias_s + 64 + half * 32 + i);
-          const float4 o = tf32_rn4(make_float4(fmaxf(v[i] + bb.x, 0.f), fmaxf(v[i + 1] + bb.y, 0.f),
-                                                fmaxf(v[i + 2] + bb.z, 0.f), fmaxf(v[i + 3] + bb.w, 0.f)));
+          const float4 r = make_float4(fmaxf(v[i] + bb.x, 0.f), fmaxf(v[i + 1] + bb.y, 0.f), fmaxf(v[i + 2] + bb.z, 0.f),
+                                       fmaxf(v[i + 3] + bb.w, 0.f));
+          const float4 o = tf32_rn4(r);
           st16(OUT + row * 256 + (((half * 8 + (i >> 2)) ^ (row & 7)) << 4), o.x, o.y, o.z, o.w);
+          if (oh != nullptr) t32_store_half4(oh + ((size_t)img * 49 + row) * 64 + half * 32 + i, r);
         }
       }
     }

@@ -77,8 +77,8 @@ __device__ __forceinline__ void t32_mma(uint32_t tmem_d, uint64_t adesc, uint64_
 }
 // kind::f16 twin (fp16 operands, fp32 accumulate): K = 16 per instruction, i.e. the same 32 bytes of a
 // K-major SWIZZLE_128B row as kind::tf32's K = 8, so descriptors and their k-step are shared.
-__device__ __forceinline__ uint32_t t32_idesc_f16(int n) {
-  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kT32BM >> 4) << 24);   // D = f32, A = B = F16, K-major
+__device__ __forceinline__ uint32_t t32_idesc_f16(int n, bool b_mn = false) {
+  return (1u << 4) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kT32BM >> 4) << 24);   // D = f32, A = B = F16
 }
 __device__ __forceinline__ void t32_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool acc) {
   asm volatile(
@@ -342,7 +342,10 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
         const int k0 = (kb_beg + i) * (t32_f16<P>::value ? 2 * kT32BK : kT32BK);   // in elements of the map's type
         const uint32_t tile = smem + KB * A_TILE + i * B_TILE, bar = smem_u32(&full_bar[i]);
         mbar_expect_tx(&full_bar[i], B_TILE);
-        if constexpr (P::B_MN_MAJOR) {
+        if constexpr (P::B_MN_MAJOR && t32_f16<P>::value) {   // 16-bit MN-major: atoms of 64 n x 64 k
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) tma_load_2d(tile + j * 8192, bmap, n0 + 64 * j, k0, bar);
+        } else if constexpr (P::B_MN_MAJOR) {
 #pragma unroll
           for (int j = 0; j < BN / 32; ++j) tma_load_2d(tile + j * 4096, bmap, n0 + 32 * j, k0, bar);
         } else {
@@ -503,10 +506,14 @@ __global__ void __launch_bounds__(kT32Threads, t32_min_ctas<P>::value) gemm_tf32
     // warp-uniform base plus a compile-time offset ptxas keeps them in uniform registers (a `threadIdx.x == 256`
     // test made it move every operand through a R2UR.BROADCAST waterfall: 18 instructions per tcgen05.mma)
     const bool leader = elect_one();
-    const uint32_t idesc = t32_f16<P>::value ? t32_idesc_f16(BN) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
+    constexpr bool F16 = t32_f16<P>::value;
+    static_assert(!(F16 && P::A_MN_MAJOR), "fp16 A operands are K-major");
+    const uint32_t idesc = F16 ? t32_idesc_f16(BN, P::B_MN_MAJOR) : t32_idesc(BN, P::A_MN_MAJOR, P::B_MN_MAJOR);
     const uint64_t a_d0 = P::A_MN_MAJOR ? t32_desc(smem, 4096, 512, 1) : t32_desc(smem, 16, 1024);
-    const uint64_t b_d0 = P::B_MN_MAJOR ? t32_desc(smem + KB * A_TILE, 4096, 512, 1) : t32_desc(smem + KB * A_TILE, 16, 1024);
-    constexpr uint32_t A_KS = (P::A_MN_MAJOR ? 1024 : 32) >> 4, B_KS = (P::B_MN_MAJOR ? 1024 : 32) >> 4;
+    // MN-major B: fp32 in SWIZZLE_128B_BASE32B atoms of 32 n x 4 k, fp16 in SWIZZLE_128B atoms of 64 n x 8 k
+    const uint64_t b_d0 = !P::B_MN_MAJOR ? t32_desc(smem + KB * A_TILE, 16, 1024)
+                          : F16 ? t32_desc(smem + KB * A_TILE, 8192, 1024, 2) : t32_desc(smem + KB * A_TILE, 4096, 512, 1);
+    constexpr uint32_t A_KS = (P::A_MN_MAJOR ? 1024 : 32) >> 4, B_KS = (!P::B_MN_MAJOR ? 32 : F16 ? 2048 : 1024) >> 4;
 #pragma unroll
     for (int i = 0; i < KB; ++i) {
       if (i < nkb) {

@@ -396,7 +396,18 @@ struct H16Shadow {
   __half* dst[kLayers];     // null = off
   int64_t off[kLayers];
   int K[kLayers], N[kLayers];
+  // one more range kept as a plain (same-layout) fp16 copy: fc1's weights [3136][512], the MN-major B operand of the
+  // fp16 fc1 forward and never transposed
+  __half* plain_dst;        // null = off
+  int64_t plain_off, plain_count;
   __device__ __forceinline__ void put4(int64_t i, const float4& v) const {
+    if (plain_dst != nullptr && i >= plain_off && i < plain_off + plain_count) {
+      const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+      uint2 u;
+      u.x = *reinterpret_cast<const uint32_t*>(&lo);
+      u.y = *reinterpret_cast<const uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(plain_dst + (i - plain_off)) = u;
+    }
 #pragma unroll
     for (int l = 0; l < kLayers; ++l) {
       if (dst[l] == nullptr || i < off[l] || i >= off[l] + (int64_t)K[l] * N[l]) continue;
@@ -412,6 +423,7 @@ struct H16Shadow {
 inline H16Shadow h16_none() {
   H16Shadow s;
   for (int l = 0; l < H16Shadow::kLayers; ++l) { s.dst[l] = nullptr; s.off[l] = 0; s.K[l] = 0; s.N[l] = 0; }
+  s.plain_dst = nullptr; s.plain_off = s.plain_count = 0;
   return s;
 }
 template <bool APPLY>

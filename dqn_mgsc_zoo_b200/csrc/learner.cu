@@ -110,7 +110,8 @@ struct dqnb_learner {
   // TF32 slab mode: tensor maps of the fc1 weight shadows (device copies; gemm_tf32.cuh B_TMA).  [0] / [1]: online /
   // target as the forward's MN-major B operand, [2]: online as the dgrad's K-major B operand.  Null: cp.async staging.
   // [3]: both nets' fp16 conv1 filters (64 rows of 256 halves), [4] / [5]: online / target fp16 conv2 filters,
-  // [6] / [7]: online / target fp16 conv3 filters - K-major B operands of the fp16 forward GEMMs.
+  // [6] / [7]: online / target fp16 conv3 filters - K-major B operands of the fp16 forward GEMMs;
+  // [8] / [9]: online / target fp16 fc1 weights [3136][512] as the MN-major B operand of the fp16 fc1 forward.
   CUtensorMap* fc1_maps = nullptr;
   const void* fc1_fwd_map(const float* wts) const {
     return fc1_maps == nullptr ? nullptr : wts == online_r ? fc1_maps + 0 : wts == target_r ? fc1_maps + 1 : nullptr;
@@ -122,6 +123,11 @@ struct dqnb_learner {
   // and fp16 copies of the conv1 / conv2 outputs of every net (A operands of the fp16 conv2 / conv3 forward)
   __half* conv23_h16 = nullptr;
   __half *a1h[kMaxNets] = {}, *a2h[kMaxNets] = {};
+  // fp16 fc1 forward (slab mode): plain fp16 copies of fc1's weights [online | target][3136][512] and of conv3's output
+  __half* fc1_h16 = nullptr;
+  __half* a3h[kMaxNets] = {};
+  static constexpr size_t kFc1H = (size_t)kFc1In * kFc1Out;
+  __half* fc1h(int target) const { return fc1_h16 + (target ? kFc1H : 0); }
   static constexpr size_t kC2H = (size_t)Conv2::COUT * Conv2::KCOL, kC3H = (size_t)Conv3::COUT * Conv3::KCOL;
   __half* c2h(int target) const { return conv23_h16 + (target ? kC2H + kC3H : 0); }
   __half* c3h(int target) const { return c2h(target) + kC2H; }
@@ -132,6 +138,7 @@ struct dqnb_learner {
       s.dst[1] = c2h(0); s.off[1] = L.w2; s.K[1] = Conv2::KCOL; s.N[1] = Conv2::COUT;
       s.dst[2] = c3h(0); s.off[2] = L.w3; s.K[2] = Conv3::KCOL; s.N[2] = Conv3::COUT;
     }
+    if (fc1_h16) { s.plain_dst = fc1h(0); s.plain_off = L.fw1; s.plain_count = (int64_t)kFc1H; }
     return s;
   }
   // batch
@@ -550,7 +557,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
         const int tgt = wts[zz] == h->target_r;
         g.a1h[z] = h->a1h[zz]; g.map2[z] = h->h16_map(4 + tgt); g.map3[z] = h->h16_map(6 + tgt);
         g.bias2[z] = params[zz] + h->L.b2; g.bias3[z] = params[zz] + h->L.b3;
-        g.a2[z] = y2[zz]; g.a3[z] = h->a3[zz];
+        g.a2[z] = y2[zz]; g.a3[z] = h->a3[zz]; g.a3h[z] = h->a3h[zz];
       }
       h->launches_per_update++;
       if (!h->sizing) {
@@ -562,11 +569,29 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
       }
     } else {
       DQNB_TRY(run_h16(H16ConvFwd<Conv2>{}, h->a1h, h->a2h, y2, h->L.b2, 2));
-      DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, nullptr, h->a3, h->L.b3, 3));
+      DQNB_TRY(run_h16(H16ConvFwd<Conv3>{}, h->a2h, h->fc1_h16 != nullptr ? h->a3h : nullptr, h->a3, h->L.b3, 3));
     }
   } else {
     DQNB_TRY((t32_conv_fwd<Conv2, float>(h, nets, rows, in2, params, wts, h->L.w2, h->L.b2, h->a2, st)));
     DQNB_TRY((t32_conv_fwd<Conv3, float>(h, nets, rows, in3, params, wts, h->L.w3, h->L.b3, h->a3, st)));
+  }
+  if (h16 && h->fc1_h16 != nullptr && h->h16_map(8) != nullptr) {   // fp16 operands, weights by TMA only
+    H16DenseFwd p;
+    p.merged = nets == 3;
+    p.batch = rows;
+    p.M = p.merged ? 2 * rows : rows; p.N = kFc1Out; p.K = kFc1In / 2;
+    const int Z = p.merged ? 2 : nets;
+    for (int z = 0; z < kMaxNets; ++z) {
+      const int zz = std::min(z, nets - 1);
+      p.x[z] = h->a3h[zz]; p.bmap[z] = h->h16_map(8 + (wts[zz] == h->target_r));
+    }
+    p.splits = t32_splits(h, p, Z, kNumSMs);
+    h->fc1_splits = p.splits;
+    h->fc1_rows = rows;
+    const size_t need = (size_t)nets * p.splits * rows * kFc1Out;
+    if (h->sizing) h->fc1_part_cap = std::max(h->fc1_part_cap, need);
+    p.part = h->fc1_part;
+    return run_t32(h, p, Z, p.splits, st);
   }
   T32DenseFwd p;
   p.merged = nets == 3;
@@ -644,6 +669,7 @@ int t32_dense_wgrad(dqnb_learner* h, int rows, bool fuse, cudaStream_t st) {
     const int64_t o = h->L.fw1;
     p.fuse = FusedRmsProp{h->online + o, h->online_r + o, h->mu + o, h->nu + o, h->grad + o,
                           h->cfg.learning_rate, h->cfg.decay, h->cfg.eps};
+    p.fuse.p_h = h->fc1_h16;   // (online copy; null when the fp16 fc1 forward is off)
   } else {
     p.gpart = h->take_part(h->L.fw1, (int64_t)p.M * p.N, splits);
   }
@@ -1044,8 +1070,13 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
       DQNB_TRY(dmalloc(&h->a1h[z], B * Conv1::OUT_PER_IMG)); DQNB_TRY(dmalloc(&h->a2h[z], B * Conv2::OUT_PER_IMG));
     }
   }
+  if (h->tf32 && !h->stream && h->conv23_h16 != nullptr && getenv("DQNB_NO_TMA") == nullptr &&
+      getenv("DQNB_NO_TMA_H16") == nullptr && getenv("DQNB_NO_F16_FC1") == nullptr) {
+    DQNB_TRY(dmalloc(&h->fc1_h16, 2 * dqnb_learner::kFc1H));
+    for (int z = 0; z < h->nets; ++z) DQNB_TRY(dmalloc(&h->a3h[z], B * Conv3::OUT_PER_IMG));
+  }
   if (h->tf32 && !h->stream && getenv("DQNB_NO_TMA") == nullptr) {
-    CUtensorMap maps[8] = {};
+    CUtensorMap maps[10] = {};
     DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[0]));
     DQNB_TRY(make_tmap_2d(h->target_r + h->L.fw1, kFc1Out, kFc1In, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, &maps[1]));
     DQNB_TRY(make_tmap_2d(h->online_r + h->L.fw1, kFc1Out, kFc1In, kT32BK, T32DenseDgrad::BN, CU_TENSOR_MAP_SWIZZLE_128B, &maps[2]));
@@ -1058,6 +1089,9 @@ extern "C" int dqnb_learner_create(const dqnb_learner_config* cfg, int device, d
         DQNB_TRY(make_tmap_2d(h->c3h(tgt), Conv3::KCOL, Conv3::COUT, 64, Conv3::COUT, CU_TENSOR_MAP_SWIZZLE_128B, &maps[6 + tgt]));
       }
     }
+    if (h->fc1_h16 != nullptr)
+      for (int tgt = 0; tgt < 2; ++tgt)
+        DQNB_TRY(make_tmap_2d(h->fc1h(tgt), kFc1Out, kFc1In, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B, &maps[8 + tgt]));
     DQNB_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->fc1_maps), sizeof(maps)));
     DQNB_CUDA(cudaMemcpy(h->fc1_maps, maps, sizeof(maps), cudaMemcpyHostToDevice));
   }
@@ -1166,7 +1200,8 @@ extern "C" int dqnb_learner_destroy(dqnb_learner* h) {
     for (float* b : hb) cudaFree(b);
     cudaFree(q.counters);
   }
-  cudaFree(h->conv1_h16); cudaFree(h->conv23_h16); cudaFree(h->fc1_maps);
+  cudaFree(h->conv1_h16); cudaFree(h->conv23_h16); cudaFree(h->fc1_maps); cudaFree(h->fc1_h16);
+  for (int z = 0; z < kMaxNets; ++z) cudaFree(h->a3h[z]);
   for (int z = 0; z < kMaxNets; ++z) { cudaFree(h->a1h[z]); cudaFree(h->a2h[z]); }
   for (auto& s : h->side) if (s) cudaStreamDestroy(s);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -1203,6 +1238,10 @@ void refresh_h16(dqnb_learner* h, const float* p, int target, cudaStream_t st) {
   if (h->conv23_h16 != nullptr) {
     conv1_h16_kernel<<<(Conv2::KCOL * Conv2::COUT + 255) / 256, 256, 0, st>>>(p + h->L.w2, h->c2h(target), Conv2::KCOL, Conv2::COUT);
     conv1_h16_kernel<<<(Conv3::KCOL * Conv3::COUT + 255) / 256, 256, 0, st>>>(p + h->L.w3, h->c3h(target), Conv3::KCOL, Conv3::COUT);
+  }
+  if (h->fc1_h16 != nullptr) {
+    const int64_t n = (int64_t)dqnb_learner::kFc1H;
+    half_copy_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, st>>>(p + h->L.fw1, h->fc1h(target), n);
   }
 }
 int locate(dqnb_learner* h, int which, float** p, int64_t* n) {
@@ -1562,6 +1601,9 @@ extern "C" int dqnb_learner_sync_target(dqnb_learner* h, uintptr_t stream) {
   if (h->conv23_h16 != nullptr)
     DQNB_CUDA(cudaMemcpyAsync(h->c2h(1), h->c2h(0), sizeof(__half) * (dqnb_learner::kC2H + dqnb_learner::kC3H),
                               cudaMemcpyDeviceToDevice, as_stream(stream)));
+  if (h->fc1_h16 != nullptr)
+    DQNB_CUDA(cudaMemcpyAsync(h->fc1h(1), h->fc1h(0), sizeof(__half) * dqnb_learner::kFc1H, cudaMemcpyDeviceToDevice,
+                              as_stream(stream)));
   return DQNB_OK;
 }
 

@@ -321,6 +321,12 @@ __global__ void conv1_h16_kernel(const float* __restrict__ w, __half* __restrict
   if (i < K * N) dst[(size_t)(i % N) * K + i / N] = __float2half_rn(w[i]);
 }
 
+// src fp32 -> dst fp16, same layout (n a multiple of 4)
+__global__ void half_copy_kernel(const float* __restrict__ src, __half* __restrict__ dst, int64_t n) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i < n) t32_store_half4(dst + i, __ldg(reinterpret_cast<const float4*>(src + i)));
+}
+
 // ---------------------------------------------------------------- conv weight gradient
 // dW[m'=(kh,kw,c), n] = scale * sum_{k'=(b,i,j)} x[...] * dy[k', n]; row m' == KCOL is all ones
 // and yields the bias gradient, which sits right behind the weights in the arena.  Where KCOL is

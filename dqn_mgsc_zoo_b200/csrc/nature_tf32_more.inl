@@ -129,6 +129,63 @@ struct T32DenseFwd {
 };
 static_assert(kFc1Out == 512, "T32DenseFwd::preload shifts by log2(fc1 width)");
 
+// The same GEMM with fp16 operands (slab kernel, small batches): A = the fp16 copy of conv3's output that its epilogue
+// writes next to the fp32 one, B = a plain fp16 copy of fc1's weights [k][n] (kept current by whoever writes the
+// weights) as the MN-major operand: TMA boxes of 64 n x 64 k in SWIZZLE_128B are exactly UMMA's canonical MN-major
+// tile of 16-bit elements (LBO = 8 KB between the two 64-column atoms, SBO = 1 KB between groups of 8 k-rows).  Half
+// the weight bytes, half the MMAs, and 10 split-K partials instead of 18 for the head to sum.  Weights only by TMA:
+// the problem is used only when the tensor maps exist.  K counts 32-bit words (3136 / 2).
+struct H16DenseFwd {
+  static constexpr const char* NAME = "fc1_fwd_h16";
+  static constexpr int BN = 128, KB_MAX = 6;
+  static constexpr bool A_MN_MAJOR = false, B_MN_MAJOR = true, DEFER_REDUCE = true;
+  static constexpr bool F16 = true, B_TMA = true;
+  static constexpr bool EARLY_TRIGGER = true;   // 80 CTAs: the TD head sets up and prefetches on the idle SMs
+  int M, N, K;              // M = rows per GEMM (2 * batch when merged), K = 1568 words
+  const __half* x[kMaxNets];
+  const void* bmap[kMaxNets];
+  float* part;              // [nets][splits][batch][N]
+  int splits, batch, merged;
+  template <class T> __device__ static T pick(const T (&a)[kMaxNets], int z) { return z == 0 ? a[0] : z == 1 ? a[1] : a[2]; }
+  __device__ const void* b_tmap(int z) const { return pick(bmap, z); }
+  using ARow = const __half*;  // x + m * 3136 or null
+  using ACol = int;            // offset in halves or -1
+  using BRow = int;
+  using BCol = int;
+  __device__ ARow a_row(int z, int m) const {
+    if (!merged) return m < batch ? pick(x, z) + (size_t)m * kFc1In : nullptr;
+    if (z == 1) return m < batch ? x[1] + (size_t)m * kFc1In : nullptr;
+    if (m < batch) return x[0] + (size_t)m * kFc1In;
+    return m < 2 * batch ? x[2] + (size_t)(m - batch) * kFc1In : nullptr;
+  }
+  __device__ ACol a_col(int, int k) const { return k < K ? 2 * k : -1; }
+  __device__ void a_put(ARow r, ACol c, uint32_t dst) const {
+    const bool ok = r != nullptr && c >= 0;
+    cp16(dst, ok ? r + c : x[0], ok);
+  }
+  // (never staged with cp.async: B_TMA without a map is rejected on the host)
+  __device__ BRow b_row(int, int) const { return 0; }
+  __device__ BCol b_col(int, int) const { return 0; }
+  __device__ void b_put(BRow, BCol, uint32_t) const {}
+  static constexpr bool PRELOAD = true;
+  struct Ctx {};
+  struct Pre { int idx; };   // element offset into part, or -1: a padding row of the merged tile
+  __device__ Ctx store_ctx(int, int, int) const { return {}; }
+  __device__ Pre preload(const Ctx&, int z, int split, int m, int n) const {
+    int net = z, row = m;
+    if (merged) {
+      if (z == 0 && m >= batch) { net = 2; row = m - batch; }
+      if (row >= batch) return {-1};
+    }
+    return {(((net * splits + split) * batch + row) << 9) + n};
+  }
+  __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
+    if (q.idx < 0) return;
+    *reinterpret_cast<float4*>(part + q.idx) = v;
+  }
+  __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(Ctx{}, preload(Ctx{}, z, split, m, n), v); }
+};
+
 // dW[m'=k_in, n] = sum_b x[b,m'] * dy[b,n];  row m' == IN is ones -> bias gradient.
 // When the whole batch fits one CTA's K range (splits == 1, the batch-32 case) the epilogue can
 // apply centered RMSProp to fc1 (95 % of all parameters) on the spot: `fuse` points at the arena
@@ -137,6 +194,7 @@ static_assert(kFc1Out == 512, "T32DenseFwd::preload shifts by log2(fc1 width)");
 struct FusedRmsProp {
   float *p, *p_r, *mu, *nu, *g;   // null p: not fused; p_r: tf32-rounded shadow of p
   float lr, decay, eps;
+  __half* p_h = nullptr;          // optional fp16 copy of p (same layout): B operand of the fp16 fc1 forward
 };
 template <int KB_, int BN_>
 struct T32DenseWgrad {
@@ -197,6 +255,8 @@ struct T32DenseWgrad {
     *reinterpret_cast<float4*>(fuse.nu + q.idx) = nv;
     *reinterpret_cast<float4*>(fuse.p + q.idx) = pv;
     *reinterpret_cast<float4*>(fuse.p_r + q.idx) = tf32_rn4(pv);
+    // (the bias row m = IN updates fc1.b, which follows fc1.w in the arena but has no place in the fp16 copy)
+    if (fuse.p_h != nullptr && q.idx < (int64_t)(M - 1) * N) t32_store_half4(fuse.p_h + q.idx, pv);
   }
 };
 
