@@ -432,6 +432,9 @@ __global__ void rmsprop_reduce_kernel(float* __restrict__ p, float* __restrict__
                                       int64_t skip_lo, int64_t skip_hi, float lr, float decay, float eps,
                                       unsigned long long* tl) {
   tl_begin(tl);
+  // (launched as a programmatic dependent of the last weight-gradient kernel of the chain: placed while that one
+  // still stores, released when it has completed; a no-op for ordinary launches)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nA = (split_end >> 2) * 8;
   if (gid < nA) {

@@ -842,10 +842,22 @@ int enqueue_update_tf32(dqnb_learner* h, cudaStream_t st) {
       rmsprop_reduce_kernel<false><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
           h->online, h->online_r, h16_none(), h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
           h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("grad_reduce"));
-    else
-      rmsprop_reduce_kernel<true><<<rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi), 256, 0, st>>>(
-          h->online, h->online_r, h->h16_online(), h->mu, h->nu, h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi,
-          h->cfg.learning_rate, h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce"));
+    else {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(rmsprop_reduce_blocks(h->L.total, split_end, skip_lo, skip_hi)); cfg.blockDim = dim3(256); cfg.stream = st;
+      cudaLaunchAttribute attr[2];
+      unsigned na = 0;
+      attr[na].id = cudaLaunchAttributePriority;
+      attr[na++].val.priority = h->prio_hi;
+      if (h->pdl && !h->profiling && getenv("DQNB_NO_RMSPROP_PDL") == nullptr) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na++].val.programmaticStreamSerializationAllowed = 1;
+      }
+      cfg.attrs = attr; cfg.numAttrs = na;
+      DQNB_CUDA(cudaLaunchKernelEx(&cfg, rmsprop_reduce_kernel<true>, h->online, h->online_r, h->h16_online(), h->mu, h->nu,
+                                   h->grad, h->L.total, h->regions, split_end, skip_lo, skip_hi, h->cfg.learning_rate,
+                                   h->cfg.decay, h->cfg.eps, h->next_tl("rmsprop_reduce")));
+    }
     DQNB_CUDA(cudaGetLastError());
     DQNB_TRY(mark(h, st, "rmsprop_reduce"));
   }

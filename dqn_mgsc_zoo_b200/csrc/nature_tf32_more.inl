@@ -231,12 +231,12 @@ struct T32DenseWgrad {
   // (gemm_tf32.cuh).  Only the one-k-block instantiation is ever fused; the others keep plain store4.
   static constexpr bool PRELOAD = KB_ == 1;
   struct Ctx {};
-  struct Pre { float4 p, mu, nu; int64_t idx; };   // idx: element offset into the parameter arena slices / the partial
+  struct Pre { float4 p, mu, nu; int idx; };   // idx: element offset into the parameter arena slices / the partial
   __device__ Ctx store_ctx(int, int, int) const { return {}; }
   __device__ Pre preload(const Ctx&, int, int split, int m, int n) const {
     Pre q;
-    const int64_t idx = (int64_t)m * N + n;
-    if (fuse.p == nullptr) { q.p = q.mu = q.nu = make_float4(0.f, 0.f, 0.f, 0.f); q.idx = (int64_t)split * ((int64_t)M * N) + idx; return q; }
+    const int idx = m * N + n;
+    if (fuse.p == nullptr) { q.p = q.mu = q.nu = make_float4(0.f, 0.f, 0.f, 0.f); q.idx = split * (M * N) + idx; return q; }
     q.idx = idx;
     q.mu = __ldcg(reinterpret_cast<const float4*>(fuse.mu + idx));
     q.nu = __ldcg(reinterpret_cast<const float4*>(fuse.nu + idx));
@@ -256,7 +256,7 @@ struct T32DenseWgrad {
     *reinterpret_cast<float4*>(fuse.p + q.idx) = pv;
     *reinterpret_cast<float4*>(fuse.p_r + q.idx) = tf32_rn4(pv);
     // (the bias row m = IN updates fc1.b, which follows fc1.w in the arena but has no place in the fp16 copy)
-    if (fuse.p_h != nullptr && q.idx < (int64_t)(M - 1) * N) t32_store_half4(fuse.p_h + q.idx, pv);
+    if (fuse.p_h != nullptr && q.idx < (M - 1) * N) t32_store_half4(fuse.p_h + q.idx, pv);
   }
 };
 
