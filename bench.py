@@ -408,8 +408,12 @@ def run_ours(args, rank, world, local_rank):
     e2e_windows = max(1, min(windows, 12000 // max(1, args.steps)))
     e2e_total = args.steps * e2e_windows
     sync_steps = min(args.steps, 300)
-    pending = collections.deque(src.next() for _ in range(ADDS_PER_LEARN * (e2e_total + sync_steps + 10)))
-    for _ in range(5):
+    # the e2e leg is paced by the HOST (Python replay bookkeeping + driver calls ~60 us per step against a ~64 us
+    # device step): its warm-up is longer than --warmup so that the interpreter, the CPU caches over the 1 M-entry
+    # id tables and the host cores' clocks are in steady state before the timed windows (untimed, stated in the line)
+    e2e_warm = max(300, args.warmup)
+    pending = collections.deque(src.next() for _ in range(ADDS_PER_LEARN * (e2e_total + sync_steps + e2e_warm + 10)))
+    for _ in range(e2e_warm):
         e2e_step()
     up0 = store.stats()["planes_uploaded"]
     ms_e2e = timed(e2e_step, args.steps, e2e_windows)     # the closing barrier waits for the last step's update
@@ -422,6 +426,7 @@ def run_ours(args, rank, world, local_rank):
     ms_sync = timed(e2e_step_sync, sync_steps)
     e2e = {"value": world * args.steps / (ms_e2e * 1e-3), "unit": "updates/s",
            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "steps": args.steps, "windows": win_e2e,
+           "warmup_steps": e2e_warm,
            "what": "per step: 4 replay.add(host transition) [H2D of the new frames via pinned staging] + "
                    "sample_slots + update_from_replay + D2H of the step's loss; the loss copy is queued "
                    "behind the update and consumed one step later, so host work overlaps the device",

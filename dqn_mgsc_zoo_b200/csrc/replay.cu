@@ -47,6 +47,7 @@ struct dqnb_replay {
   std::vector<int32_t> refcount, free_list, pending_free, slot_ids;
   std::vector<uint8_t> slot_staged;      // slot already has a record in the open batch
   std::vector<uint8_t> last_st;
+  std::vector<uint8_t> newest;   // scratch: channel 3 of the stack being put, as a plane
   int32_t last_ids[8];
   bool have_last = false;
   // gather index ring + host-return buffers
@@ -159,7 +160,9 @@ inline void release_plane(dqnb_replay* h, int32_t p) {
 }
 
 // Copies channel c of an HWC stack into a staged plane; returns the new plane id.
-int stage_plane(dqnb_replay* h, const uint8_t* stack, int c, cudaStream_t st, int32_t* out_id) {
+// `extracted`: channel c of `stack` already pulled out as a plane (match_copy_extract), or null.
+int stage_plane(dqnb_replay* h, const uint8_t* stack, int c, cudaStream_t st, int32_t* out_id,
+                const uint8_t* extracted = nullptr) {
   if (h->stage[h->cur].n_planes == kStagePlanes) DQNB_TRY(flush(h, st));
   if (h->free_list.empty()) {
     DQNB_TRY(flush(h, st));   // recycles pending_free
@@ -171,7 +174,9 @@ int stage_plane(dqnb_replay* h, const uint8_t* stack, int c, cudaStream_t st, in
   Stage& s = h->stage[h->cur];
   uint8_t* dst = h->planes_of(s) + (size_t)s.n_planes * h->plane_stride;
   const int n = h->plane_bytes, S = h->S;
-  if (S == 4) {
+  if (extracted != nullptr) {
+    memcpy(dst, extracted, (size_t)n);
+  } else if (S == 4) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(stack);
     const int sh = 8 * c;
     for (int i = 0; i < n; ++i) dst[i] = (uint8_t)(src[i] >> sh);
@@ -220,6 +225,30 @@ void match_channels(const uint8_t* cur, const uint8_t* prev, int npx, int S, int
       for (int i = 0; i < npx && eq; ++i) eq = cur[(size_t)i * S + c] == prev[(size_t)i * S + d];
       if (eq) match[c] = d;
     }
+  }
+}
+
+// match_channels(cur, prev) for 4-deep stacks in ONE pass that also leaves a copy of `cur` in `copy` (the next put's
+// chain check) and the newest channel (3: the frame a chained observation adds) as a plane in `newest`: a put used
+// to walk the 28 KB stack four times (compare, match, extract, copy), which was half of its host time.
+void match_copy_extract(const uint8_t* cur, const uint8_t* prev, int npx, uint8_t* copy, uint8_t* newest, int* match) {
+  const uint32_t* a = reinterpret_cast<const uint32_t*>(cur);
+  const uint32_t* b = reinterpret_cast<const uint32_t*>(prev);
+  uint32_t* c = reinterpret_cast<uint32_t*>(copy);
+  uint32_t any = 0, dshift = 0, dsame = 0;
+  for (int i = 0; i < npx; ++i) {
+    const uint32_t x = a[i], y = b[i];
+    any |= x;
+    dshift |= (x & 0x00FFFFFFu) ^ (y >> 8);
+    dsame |= x ^ y;
+    c[i] = x;
+    newest[i] = (uint8_t)(x >> 24);
+  }
+  for (int ch = 0; ch < 4; ++ch) {
+    if (((any >> (8 * ch)) & 0xFF) == 0) match[ch] = -1;
+    else if (ch < 3 && ((dshift >> (8 * ch)) & 0xFF) == 0) match[ch] = ch + 1;
+    else if (((dsame >> (8 * ch)) & 0xFF) == 0) match[ch] = ch;
+    else match[ch] = -2;
   }
 }
 
@@ -328,27 +357,35 @@ extern "C" int dqnb_replay_put(dqnb_replay* h, int64_t slot, const uint8_t* s_tm
       if (m[c] != -1) DQNB_TRY(stage_plane(h, s_tm1, c, st, &ids[c]));
   }
   int m[4];
-  match_channels(s_t, s_tm1, h->plane_bytes, S, m);
+  const bool one_pass = S == 4;   // (last_st may be overwritten now: the chain check above is done)
+  const bool had_last = h->have_last;
+  if (one_pass) {
+    h->have_last = false;         // until last_ids match the new contents again (an error return below leaves it off)
+    if (h->newest.size() < (size_t)h->plane_bytes) h->newest.resize((size_t)h->plane_bytes);
+    match_copy_extract(s_t, s_tm1, h->plane_bytes, h->last_st.data(), h->newest.data(), m);
+  } else {
+    match_channels(s_t, s_tm1, h->plane_bytes, S, m);
+  }
   for (int c = 0; c < S; ++c) {
     if (m[c] == -1) continue;
     if (m[c] >= 0 && ids[m[c]] >= 0) {
       ids[S + c] = ids[m[c]];
       h->refcount[ids[S + c]]++;
     } else {
-      DQNB_TRY(stage_plane(h, s_t, c, st, &ids[S + c]));
+      DQNB_TRY(stage_plane(h, s_t, c, st, &ids[S + c], one_pass && c == 3 ? h->newest.data() : nullptr));
     }
   }
   // release what the slot held, then what `last` held; take refs for the new `last`.
   int32_t* old = &h->slot_ids[(size_t)slot * 8];
   for (int k = 0; k < 8; ++k) release_plane(h, old[k]);
   for (int k = 0; k < 8; ++k) old[k] = ids[k];
-  if (h->have_last)
+  if (had_last)
     for (int c = 0; c < S; ++c) release_plane(h, h->last_ids[c]);
   for (int c = 0; c < S; ++c) {
     h->last_ids[c] = ids[S + c];
     if (ids[S + c] >= 0) h->refcount[ids[S + c]]++;
   }
-  memcpy(h->last_st.data(), s_t, stack_bytes);
+  if (!one_pass) memcpy(h->last_st.data(), s_t, stack_bytes);
   h->have_last = true;
 
   Stage& s = h->stage[h->cur];

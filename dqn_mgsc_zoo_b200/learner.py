@@ -62,6 +62,12 @@ class Learner:
         _lib.call("dqnb_learner_num_params", self._h, ctypes.byref(n))
         self.num_params = n.value
         self._update_from_replay = _lib.load().dqnb_learner_update_from_replay
+        # per-step calls: bound once, their out-parameter allocated once (a fresh c_float + byref + name lookup per
+        # call were a third of loss_lagged's host time)
+        self._loss_post_fn = _lib.load().dqnb_learner_loss_post
+        self._loss_take_fn = _lib.load().dqnb_learner_loss_take
+        self._loss_out = ctypes.c_float()
+        self._loss_out_ref = ctypes.byref(self._loss_out)
 
     def close(self):
         if self._h is not None:
@@ -134,15 +140,14 @@ class Learner:
 
     def loss_post(self):
         """Queues a read-back of the latest update's loss behind it (does not wait)."""
-        _lib.call("dqnb_learner_loss_post", self._h, self.stream)
+        _lib.check(self._loss_post_fn(self._h, self.stream))
         self._loss_outstanding += 1
 
     def loss_take(self):
         """Waits for the oldest queued loss read-back and returns it."""
-        out = ctypes.c_float()
-        _lib.call("dqnb_learner_loss_take", self._h, ctypes.byref(out))
+        _lib.check(self._loss_take_fn(self._h, self._loss_out_ref))
         self._loss_outstanding -= 1
-        return float(out.value)
+        return self._loss_out.value
 
     def loss_lagged(self):
         """loss_post() for this update, then the previous update's loss (None the first time):
