@@ -608,7 +608,7 @@ int forward_torso_tf32(dqnb_learner* h, int nets, int rows, const uint8_t* const
   h->fc1_rows = rows;
   const size_t need = (size_t)nets * p.splits * rows * kFc1Out;
   if (h->sizing) h->fc1_part_cap = std::max(h->fc1_part_cap, need);
-  p.part = getenv("DQNB_DBG_FC1_NOSTORE") ? nullptr : h->fc1_part;
+  p.part = h->fc1_part;
   return run_t32(h, p, Z, p.splits, st);
 }
 

@@ -122,7 +122,7 @@ struct T32DenseFwd {
     return {(((net * splits + split) * batch + row) << 9) + n};
   }
   __device__ void store4p(const Ctx&, const Pre& q, float4 v) const {
-    if (q.idx < 0 || part == nullptr) return;   // (null part: timing experiment DQNB_DBG_FC1_NOSTORE)
+    if (q.idx < 0) return;
     *reinterpret_cast<float4*>(part + q.idx) = v;
   }
   __device__ void store4(int z, int split, int m, int n, float4 v) const { store4p(Ctx{}, preload(Ctx{}, z, split, m, n), v); }
