@@ -127,3 +127,26 @@ def check(status):
 
 def call(name, *args):
     check(getattr(load(), name)(*args))
+
+
+def fastcall():
+    """The optional CPython helper for the per-step calls (csrc_host/fastcall.c), or None when it is not built.
+    It calls the same C-ABI entry points as the ctypes wrappers; only the per-call Python overhead differs."""
+    global _FASTCALL
+    try:
+        return _FASTCALL
+    except NameError:
+        pass
+    try:
+        from dqn_mgsc_zoo_b200 import _fastcall as mod
+    except ImportError:
+        mod = None
+    if os.environ.get("DQNB_NO_FASTCALL"):
+        mod = None
+    _FASTCALL = mod
+    return mod
+
+
+def fn_address(name):
+    """Address of an exported C-ABI function, for the helper."""
+    return ctypes.cast(getattr(load(), name), ctypes.c_void_p).value

@@ -37,5 +37,26 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def fastcall_path():
+    import sysconfig
+    return os.path.join(HERE, "_fastcall" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_fastcall(force=False):
+    """The optional CPython helper for the per-step calls (csrc_host/fastcall.c): plain gcc, no CUDA."""
+    import sysconfig
+    src, out = os.path.join(HERE, "csrc_host", "fastcall.c"), fastcall_path()
+    if not force and os.path.isfile(out) and os.path.getmtime(out) >= os.path.getmtime(src):
+        return out
+    cmd = [os.environ.get("CC", "gcc"), "-O2", "-shared", "-fPIC", "-Wall", "-I", sysconfig.get_paths()["include"],
+           "-o", out, src]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("gcc failed building the _fastcall helper")
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_fastcall(force="--force" in sys.argv))

@@ -33,6 +33,9 @@ class FrameStore:
         self._h = h
         self._put = _lib.load().dqnb_replay_put
         self._last = (None, 0)
+        fc = _lib.fastcall()
+        self._fc_put = fc.put if fc is not None else None
+        self._fc_args = (_lib.fn_address("dqnb_replay_put"), h.value)
 
     @property
     def handle(self):
@@ -42,6 +45,7 @@ class FrameStore:
         if self._h is not None:
             _lib.call("dqnb_replay_destroy", self._h)
             self._h = None
+            self._fc_put = None
 
     def __del__(self):
         try:
@@ -50,6 +54,15 @@ class FrameStore:
             pass
 
     def put(self, slot, s_tm1, s_t, action, reward, discount):
+        fc = self._fc_put
+        if fc is not None:   # buffer-protocol fast path: same C entry point, ~3 us less Python per call
+            fn, h = self._fc_args
+            hh, ww, ss = self.shape
+            rc = fc(fn, h, slot, s_tm1, s_t, action, reward, discount, self.stream, hh, ww, ss)
+            if rc == 0:
+                return
+            if rc != -1000:
+                _lib.check(rc)
         s_tm1 = np.ascontiguousarray(s_tm1, dtype=np.uint8)
         s_t = np.ascontiguousarray(s_t, dtype=np.uint8)
         if s_tm1.shape != self.shape or s_t.shape != self.shape:

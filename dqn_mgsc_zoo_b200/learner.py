@@ -64,6 +64,12 @@ class Learner:
         self._update_from_replay = _lib.load().dqnb_learner_update_from_replay
         # per-step calls: bound once, their out-parameter allocated once (a fresh c_float + byref + name lookup per
         # call were a third of loss_lagged's host time)
+        fc = _lib.fastcall()
+        self._fc = fc
+        if fc is not None:
+            self._fc_update = (_lib.fn_address("dqnb_learner_update_from_replay"), self._h.value)
+            self._fc_loss = (_lib.fn_address("dqnb_learner_loss_post"), _lib.fn_address("dqnb_learner_loss_take"),
+                             self._h.value)
         self._loss_post_fn = _lib.load().dqnb_learner_loss_post
         self._loss_take_fn = _lib.load().dqnb_learner_loss_take
         self._loss_out = ctypes.c_float()
@@ -73,6 +79,7 @@ class Learner:
         if self._h is not None:
             _lib.call("dqnb_learner_destroy", self._h)
             self._h = None
+            self._fc = None
 
     def __del__(self):
         try:
@@ -152,6 +159,15 @@ class Learner:
     def loss_lagged(self):
         """loss_post() for this update, then the previous update's loss (None the first time):
         per-step statistics without ever idling the device."""
+        if self._fc is not None:
+            post, take, h = self._fc_loss
+            want = self._loss_outstanding >= 1
+            rc, loss = self._fc.loss_lagged(post, take, h, self.stream, want)
+            if rc != 0:
+                _lib.check(rc)
+            if not want:
+                self._loss_outstanding += 1
+            return loss
         self.loss_post()
         return self.loss_take() if self._loss_outstanding > 1 else None
 
@@ -197,6 +213,13 @@ class Learner:
 
     def update_from_replay(self, frame_store, slots, weights=None):
         """`weights`: per-row weights of this batch (row_weighted learners; prioritized replay's importance weights)."""
+        if weights is None and self._fc is not None:
+            fn, h = self._fc_update
+            rc = self._fc.update(fn, h, frame_store.handle.value, slots, self.stream, self.batch_size)
+            if rc == 0:
+                return
+            if rc != -1000:
+                _lib.check(rc)
         slots = np.ascontiguousarray(slots, dtype=np.int64)
         if slots.size != self.batch_size:
             raise ValueError("need %d slots, got %d" % (self.batch_size, slots.size))
