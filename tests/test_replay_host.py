@@ -282,3 +282,30 @@ def test_n_step_accumulator_matches_reference_semantics():
     assert tail[-1].r_t == 5.0 and tail[-1].discount_t == 0.0
     with pytest.raises(ValueError, match="Expected FIRST"):
         replay_lib.NStepTransitionAccumulator(2).step(TS(1, 0.0, 1.0, 0), 0).__next__()
+
+
+def test_inlined_single_id_bookkeeping_equals_the_distribution_methods():
+    """TransitionReplay.add writes remove([oldest]) + add([new]) out for the stock UniformDistribution; any other
+    distribution type (here: a trivial subclass) goes through the methods.  Both must leave identical state and
+    draw identical samples, through the fill, the first wrap and many wraps."""
+    class Routed(replay_lib.UniformDistribution):
+        pass
+
+    class RoutedReplay(replay_lib.TransitionReplay):
+        _DISTRIBUTION = Routed
+
+    capacity = 37
+    fast = replay_lib.TransitionReplay(capacity, Pair(a=None, b=None), np.random.RandomState(11))
+    slow = RoutedReplay(capacity, Pair(a=None, b=None), np.random.RandomState(11))
+    assert type(fast._distribution) is replay_lib.UniformDistribution and type(slow._distribution) is Routed
+    for i in range(5 * capacity + 3):
+        fast.add(Pair(a=i, b=2 * i))
+        slow.add(Pair(a=i, b=2 * i))
+        if i % 7 == 0:
+            df, ds = fast._distribution, slow._distribution
+            assert df._ids == ds._ids and df._id_to_index == ds._id_to_index
+            assert np.array_equal(df._ids_np[:df.size], ds._ids_np[:ds.size])
+            assert list(fast.ids()) == list(slow.ids()) and fast._t == slow._t
+            if i > 3:
+                assert np.array_equal(fast.sample_slots(5), slow.sample_slots(5))
+    assert fast.check_valid()[0] and slow.check_valid()[0]
